@@ -1,0 +1,245 @@
+// context.cu -- process context, error reporting, HBM column store primitives of libaqgpu.
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+namespace aq {
+
+static Context g_ctx;
+static thread_local char g_err[1024] = "";
+static std::mutex g_init_mu;
+
+Context& ctx() { return g_ctx; }
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int fail(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return -1;
+}
+
+int DevBuf::alloc(size_t n) {
+    release();
+    if (n == 0) n = 16;
+    cudaError_t e = cudaMallocAsync(&p, n, ctx().stream);
+    if (e != cudaSuccess) {
+        p = nullptr;
+        return fail("cudaMallocAsync(%zu bytes): %s", n, cudaGetErrorString(e));
+    }
+    bytes = n;
+    return 0;
+}
+
+int DevBuf::alloc_zero(size_t n) {
+    AQ_TRY(alloc(n));
+    AQ_CUDA(cudaMemsetAsync(p, 0, bytes, ctx().stream));
+    return 0;
+}
+
+void DevBuf::release() {
+    if (p) cudaFreeAsync(p, ctx().stream);
+    p = nullptr;
+    bytes = 0;
+}
+
+bool is_device_ptr(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+int InCol::bind(const void* p, size_t bytes) {
+    if (!p) return fail("null input column");
+    if (is_device_ptr(p)) { d = p; return 0; }
+    AQ_TRY(tmp.alloc(bytes));
+    AQ_CUDA(cudaMemcpyAsync(tmp.p, p, bytes, cudaMemcpyHostToDevice, ctx().stream));
+    d = tmp.p;
+    return 0;
+}
+
+int OutCol::bind(void* p, size_t n) {
+    if (!p) return fail("null output column");
+    bytes = n;
+    if (is_device_ptr(p)) { d = p; host = nullptr; return 0; }
+    AQ_TRY(tmp.alloc(n));
+    d = tmp.p;
+    host = p;
+    return 0;
+}
+
+int OutCol::finish(size_t used) {
+    if (!host || used == 0) return 0;
+    if (used > bytes) used = bytes;
+    AQ_CUDA(cudaMemcpyAsync(host, d, used, cudaMemcpyDeviceToHost, ctx().stream));
+    return 0;
+}
+
+} // namespace aq
+
+using namespace aq;
+
+extern "C" {
+
+int aqgpu_abi_version(void) { return AQGPU_ABI_VERSION; }
+
+const char* aqgpu_last_error(void) { return g_err; }
+
+int aqgpu_init(int device) {
+    std::lock_guard<std::mutex> lk(g_init_mu);
+    Context& c = g_ctx;
+    if (c.ready && (device < 0 || device == c.device)) return 0;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail("libaqgpu needs a CUDA device (sm_100a); none is visible (%s). There is no CPU fallback.",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    }
+    if (device < 0) {
+        if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+    }
+    if (device >= n) return fail("device %d out of range (%d visible)", device, n);
+    AQ_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    AQ_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail("libaqgpu is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+    c.device = device;
+    c.sm_count = prop.multiProcessorCount;
+    c.smem_optin = prop.sharedMemPerBlockOptin;
+    if (!c.own_stream) AQ_CUDA(cudaStreamCreateWithFlags(&c.own_stream, cudaStreamNonBlocking));
+    c.stream = c.own_stream;
+    if (!c.ev0) AQ_CUDA(cudaEventCreate(&c.ev0));
+    if (!c.ev1) AQ_CUDA(cudaEventCreate(&c.ev1));
+    cudaMemPool_t pool;
+    AQ_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t thr = UINT64_MAX;
+    AQ_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    if (!c.d_flags) AQ_CUDA(cudaMalloc(&c.d_flags, 64 * sizeof(uint32_t)));
+    if (!c.h_flags) AQ_CUDA(cudaHostAlloc(&c.h_flags, 64 * sizeof(uint32_t), cudaHostAllocDefault));
+    c.ready = true;
+    return 0;
+}
+
+int aqgpu_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_init_mu);
+    Context& c = g_ctx;
+    if (!c.ready) return 0;
+    cudaStreamSynchronize(c.stream);
+    if (c.d_flags) cudaFree(c.d_flags);
+    if (c.h_flags) cudaFreeHost(c.h_flags);
+    if (c.ev0) cudaEventDestroy(c.ev0);
+    if (c.ev1) cudaEventDestroy(c.ev1);
+    if (c.own_stream) cudaStreamDestroy(c.own_stream);
+    c.d_flags = nullptr; c.h_flags = nullptr; c.ev0 = c.ev1 = nullptr;
+    c.own_stream = c.stream = nullptr;
+    c.ready = false;
+    return 0;
+}
+
+int aqgpu_set_stream(void* s) {
+    AQ_REQUIRE_INIT();
+    g_ctx.stream = s ? static_cast<cudaStream_t>(s) : g_ctx.own_stream;
+    return 0;
+}
+
+int aqgpu_sync(void) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    return 0;
+}
+
+uint64_t aqgpu_launch_count(void) { return g_ctx.launches.load(); }
+
+int aqgpu_timer_begin(void) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaEventRecord(g_ctx.ev0, g_ctx.stream));
+    return 0;
+}
+
+int aqgpu_timer_end(float* ms) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaEventRecord(g_ctx.ev1, g_ctx.stream));
+    AQ_CUDA(cudaEventSynchronize(g_ctx.ev1));
+    AQ_CUDA(cudaEventElapsedTime(ms, g_ctx.ev0, g_ctx.ev1));
+    return 0;
+}
+
+int aqgpu_col_alloc(size_t bytes, void** dptr) {
+    AQ_REQUIRE_INIT();
+    if (!dptr) return fail("null dptr");
+    AQ_CUDA(cudaMalloc(dptr, bytes ? bytes : 16));
+    return 0;
+}
+
+int aqgpu_col_free(void* dptr) {
+    if (dptr) AQ_CUDA(cudaFree(dptr));
+    return 0;
+}
+
+int aqgpu_col_upload(void* dptr, const void* host, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaMemcpyAsync(dptr, host, bytes, cudaMemcpyHostToDevice, g_ctx.stream));
+    AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    return 0;
+}
+
+int aqgpu_col_download(void* host, const void* dptr, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaMemcpyAsync(host, dptr, bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
+    AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    return 0;
+}
+
+int aqgpu_host_alloc(size_t bytes, void** hptr) {
+    AQ_REQUIRE_INIT();
+    if (!hptr) return fail("null hptr");
+    AQ_CUDA(cudaHostAlloc(hptr, bytes ? bytes : 16, cudaHostAllocDefault));
+    return 0;
+}
+
+int aqgpu_host_free(void* hptr) {
+    if (hptr) AQ_CUDA(cudaFreeHost(hptr));
+    return 0;
+}
+
+size_t aqgpu_dtype_size(int dtype) { return dtype_size(dtype); }
+
+int aqgpu_reduce_out_type(int op, int vtype) {
+    if (op == AQ_COUNT) return AQ_UINT32;
+    if (!is_val_type(vtype)) return -2;
+    switch (op) {
+    case AQ_SUM: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;     // types.h:205-210
+    case AQ_AVG: case AQ_VAR: case AQ_STDDEV: case AQ_CORR: return AQ_DOUBLE;
+    case AQ_MIN: case AQ_MAX: case AQ_FIRST: case AQ_LAST: return vtype;
+    default: return -2;
+    }
+}
+
+int aqgpu_scan_out_type(int op, int vtype) {
+    if (!is_val_type(vtype)) return -2;
+    switch (op) {
+    case AQ_SUMS: case AQ_SUMW: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;
+    case AQ_AVGS: case AQ_AVGW: return AQ_DOUBLE;                       // GetFPType<GetLongType<T>>
+    case AQ_RATIOW: return (vtype == AQ_INT32 || vtype == AQ_FLOAT) ? AQ_FLOAT : AQ_DOUBLE;  // types.h:199-204
+    case AQ_MINS: case AQ_MAXS: case AQ_MINW: case AQ_MAXW:
+    case AQ_DELTAS: case AQ_PREV: case AQ_NEXT: return vtype;
+    default: return -2;
+    }
+}
+
+} // extern "C"

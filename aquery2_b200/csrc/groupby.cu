@@ -1,0 +1,613 @@
+// groupby.cu -- hash group-by with fused scalar aggregation: planning, global-table path, ranking, emit.
+//
+// Replaces AQHashTable::hashtable_push (reference server/hasher.h:176-179), the observable order of
+// ht_postproc (hasher.h:181-198), the gather col[vecs[g]] (server/table.h:184-189) and the scalar
+// aggregates of server/aggregations.h in one pass over the key and value columns.
+//
+// Table: open addressing, linear probing, array-of-structs slots of `sw` 64-bit words (one 32-byte
+// sector for up to 3 accumulators): word 0 = (tag << 32 | min row id), words 1.. = accumulators.
+//   * tag = the single 32-bit key, or the bit-packed (k - lo) fields when per-column bounds are
+//     known (the reference's PerfectHashTable packing, hasher.h:226-243): membership is decided by
+//     word 0 alone;
+//   * otherwise tag = high hash bits and a tag match is verified against the key columns at the
+//     slot's representative row (any row of the group works: word 0 only ever moves to smaller
+//     rows of the same group, via atomicMin).
+// The low half therefore ends as the group's FIRST-APPEARANCE row.  Group ids are the rank of that
+// row among all first rows -- a prefix-popcount over an nrows-bit bitmap, no sort of the groups --
+// which is exactly the insertion index m_values gives (server/unordered_dense.h:1142-1146).
+#include "groupby.cuh"
+#include <cstring>
+
+namespace aq {
+
+// ------------------------------------------------------------------------------------------------
+// host-side planning
+// ------------------------------------------------------------------------------------------------
+int KeyCols::bind(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows) {
+    if (!keys || !key_types || nkeys < 1 || nkeys > MAX_KEY_COLS) return fail("need 1..%d key columns", MAX_KEY_COLS);
+    n = nkeys;
+    for (int k = 0; k < nkeys; ++k) {
+        type[k] = key_types[k];
+        if (type[k] != AQ_INT32 && type[k] != AQ_UINT32 && type[k] != AQ_INT64)
+            return fail("unsupported key dtype %d (int32, uint32, int64 keys only)", type[k]);
+        AQ_TRY(col[k].bind(keys[k], dtype_size(type[k]) * nrows));
+    }
+    return 0;
+}
+
+int KeyCols::make_spec(const int64_t* key_min, const int64_t* key_max, KeySpec& ks) const {
+    memset(&ks, 0, sizeof(ks));
+    int w = 0;
+    int vec_ok = 1;
+    bool all32 = true;
+    for (int k = 0; k < n; ++k) {
+        const uint32_t* p = static_cast<const uint32_t*>(col[k].d);
+        if (type[k] == AQ_INT32 || type[k] == AQ_UINT32) {
+            if (w + 1 > MAX_KEY_WORDS) return fail("key tuple wider than %d words", MAX_KEY_WORDS);
+            ks.base[w] = p; ks.stride[w] = 1; ++w;
+            if (reinterpret_cast<uintptr_t>(p) & 15) vec_ok = 0;
+        } else {
+            if (w + 2 > MAX_KEY_WORDS) return fail("key tuple wider than %d words", MAX_KEY_WORDS);
+            ks.base[w] = p; ks.stride[w] = 2; ++w;
+            ks.base[w] = p + 1; ks.stride[w] = 2; ++w;
+            all32 = false;
+        }
+    }
+    ks.nwords = w;
+    ks.vec_ok = vec_ok;
+    ks.exact = (w == 1) ? 1 : 0;
+    if (key_min && key_max && all32 && ks.exact == 0) {
+        // PerfectHashTable-style packing (hasher.h:226-243): sum of field widths must fit 32 bits
+        int bits = 0;
+        bool ok = true;
+        for (int k = 0; k < n && ok; ++k) {
+            const int64_t lo = key_min[k], hi = key_max[k];
+            if (hi < lo || hi - lo > 0xffffffffLL) { ok = false; break; }
+            const uint64_t range = uint64_t(hi - lo);
+            int b = 0;
+            while (b < 32 && (range >> b) != 0) ++b;
+            ks.pack_lo[k] = (uint32_t)lo;            // modular: (uint32)k - (uint32)lo == k - lo
+            ks.pack_range[k] = (uint32_t)range;
+            ks.pack_shift[k] = (uint32_t)bits;
+            bits += b;
+            if (bits > 32) ok = false;
+        }
+        if (ok) { ks.exact = 2; ks.pack_bits = bits; }
+    }
+    return 0;
+}
+
+AggPlan::AggPlan() {
+    memset(&prog, 0, sizeof(prog));
+    memset(&emit, 0, sizeof(emit));
+}
+
+int AggPlan::add_acc(int kind, int xform, int vtype, const void* v, const void* v2) {
+    for (int i = 0; i < n_acc; ++i) {           // share identical accumulators (e.g. COUNT)
+        const AccOp& o = prog.op[i];
+        if (o.kind == kind && o.xform == xform && o.vtype == vtype && o.v == v && o.v2 == v2) return i;
+    }
+    if (n_acc >= MAX_ACC) return -1;
+    AccOp& o = prog.op[n_acc];
+    o.kind = kind; o.xform = xform; o.vtype = vtype; o.v = v; o.v2 = v2;
+    o.vec_ok = ((reinterpret_cast<uintptr_t>(v) & 15) == 0) && ((reinterpret_cast<uintptr_t>(v2) & 15) == 0);
+    prog.n = ++n_acc;
+    return n_acc - 1;
+}
+
+int AggPlan::find(int kind) const {
+    for (int i = 0; i < n_acc; ++i) if (prog.op[i].kind == kind) return i;
+    return -1;
+}
+
+int AggPlan::plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* dout) {
+    if (emit.n >= MAX_AGGS) return fail("more than %d aggregates in one call", MAX_AGGS);
+    EmitAgg& e = emit.agg[emit.n];
+    memset(&e, 0, sizeof(e));
+    e.op = a.op; e.vtype = a.vtype; e.v = dv; e.out = dout;
+    e.cnt = e.maxrow = -1;
+    for (int i = 0; i < 5; ++i) e.a[i] = -1;
+    const int def = aqgpu_reduce_out_type(a.op, a.vtype);
+    if (def < 0) return fail("unsupported aggregate op %d on dtype %d", a.op, a.vtype);
+    e.out_type = a.out_type ? a.out_type : def;
+    if (e.out_type != def && !(def == AQ_INT128 && e.out_type == AQ_INT64) &&
+        !(a.op == AQ_COUNT && e.out_type == AQ_INT64))
+        return fail("aggregate op %d on dtype %d cannot produce dtype %d", a.op, a.vtype, e.out_type);
+    const bool isint = is_int_type(a.vtype);
+    const int add = isint ? ACC_ADD_I64 : ACC_ADD_F64;
+    bool ok = true;
+    switch (a.op) {
+    case AQ_SUM: ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
+    case AQ_AVG: ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0 && (e.cnt = add_count()) >= 0; break;
+    case AQ_MIN: ok = (e.a[0] = add_acc(ACC_MIN_I64, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
+    case AQ_MAX: ok = (e.a[0] = add_acc(ACC_MAX_I64, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
+    case AQ_COUNT: ok = (e.cnt = add_count()) >= 0; break;
+    case AQ_FIRST: case AQ_LAST: {
+        // DESC row lists (reference): first = largest row id, last = first-appearance row.
+        const bool need_max = (a.op == AQ_FIRST) == (emit.row_order == AQ_ROWS_DESC);
+        if (need_max) ok = (e.maxrow = add_maxrow()) >= 0;
+        break; }
+    case AQ_VAR: case AQ_STDDEV:
+        ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0 &&
+             (e.a[1] = add_acc(add, X_SQUARE, a.vtype, dv, nullptr)) >= 0 && (e.cnt = add_count()) >= 0;
+        break;
+    case AQ_CORR:
+        if (!isint) return fail("corr: integer inputs only (the reference truncates fp inputs to __int128, aggregations.h:387-389)");
+        if (!dv2) return fail("corr needs a second column");
+        ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0 &&
+             (e.a[1] = add_acc(add, X_IDENT, a.vtype, dv2, nullptr)) >= 0 &&
+             (e.a[2] = add_acc(add, X_PRODUCT, a.vtype, dv, dv2)) >= 0 &&
+             (e.a[3] = add_acc(add, X_SQUARE, a.vtype, dv, nullptr)) >= 0 &&
+             (e.a[4] = add_acc(add, X_SQUARE, a.vtype, dv2, nullptr)) >= 0 && (e.cnt = add_count()) >= 0;
+        break;
+    default: return fail("unknown aggregate op %d", a.op);
+    }
+    if (!ok) return fail("too many accumulators (max %d per call)", MAX_ACC);
+    ++emit.n;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// device code
+// ------------------------------------------------------------------------------------------------
+struct InitPattern { unsigned long long w[16]; };
+
+// slot word 0 = SLOT_EMPTY, accumulator words = their identities
+__global__ void k_init_table(unsigned long long* __restrict__ tab, size_t nwords, uint32_t sw, const InitPattern pat) {
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nwords; i += size_t(gridDim.x) * blockDim.x)
+        tab[i] = pat.w[i & (sw - 1)];
+}
+
+// value column -> 4 (int64 image | double image) values
+__device__ __forceinline__ void load4_val(const void* v, int vtype, uint32_t row0, int cnt, bool vec,
+                                          long long iv[4], double dv[4], float fv[4]) {
+    if (vtype == AQ_INT32 || vtype == AQ_FLOAT) {
+        uint32_t u[4];
+        load4_b32(v, row0, cnt, vec, u);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (vtype == AQ_INT32) { iv[r] = (long long)(int)u[r]; }
+            else { fv[r] = __uint_as_float(u[r]); dv[r] = (double)fv[r]; }
+        }
+    } else {
+        unsigned long long u[4];
+        load4_b64(v, row0, cnt, vec, u);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (vtype == AQ_INT64) iv[r] = (long long)u[r];
+            else dv[r] = __longlong_as_double((long long)u[r]);
+        }
+    }
+}
+
+// x[r] for one accumulator: integer image in xi (int columns), double image in xd (fp columns)
+__device__ __forceinline__ void acc_inputs(const AccOp& o, uint32_t row0, int cnt, long long xi[4], double xd[4]) {
+    long long iv[4] = {0, 0, 0, 0}; double dv[4] = {0, 0, 0, 0}; float fv[4] = {0, 0, 0, 0};
+    load4_val(o.v, o.vtype, row0, cnt, o.vec_ok, iv, dv, fv);
+    if (o.xform == X_IDENT) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { xi[r] = iv[r]; xd[r] = dv[r]; }
+        return;
+    }
+    long long iw[4] = {0, 0, 0, 0}; double dw[4] = {0, 0, 0, 0}; float fw[4] = {0, 0, 0, 0};
+    if (o.xform == X_PRODUCT) {
+        load4_val(o.v2, o.vtype, row0, cnt, o.vec_ok, iw, dw, fw);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { iw[r] = iv[r]; dw[r] = dv[r]; fw[r] = fv[r]; }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        xi[r] = iv[r] * iw[r];
+        // the reference multiplies in the column's own type before widening (aggregations.h:339-345)
+        xd[r] = o.vtype == AQ_FLOAT ? (double)__fmul_rn(fv[r], fw[r]) : __dmul_rn(dv[r], dw[r]);
+    }
+}
+
+__device__ __forceinline__ void acc_apply(const AccProg& p, int a, const uint32_t slot[4], uint32_t row0, int cnt) {
+    const AccOp& o = p.op[a];
+    if (o.kind == ACC_COUNT) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) if (r < cnt) atomicAdd(slot_word(p, slot[r]) + 1 + a, 1ull);
+        return;
+    }
+    if (o.kind == ACC_MAXROW) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) if (r < cnt) atomicMax(slot_word(p, slot[r]) + 1 + a, (unsigned long long)(row0 + r));
+        return;
+    }
+    long long xi[4]; double xd[4];
+    acc_inputs(o, row0, cnt, xi, xd);
+    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        if (r >= cnt) continue;
+        unsigned long long* c = slot_word(p, slot[r]) + 1 + a;
+        switch (o.kind) {
+        case ACC_ADD_I64: atomicAdd(c, (unsigned long long)xi[r]); break;
+        case ACC_ADD_F64: atomicAdd(reinterpret_cast<double*>(c), isint ? (double)xi[r] : xd[r]); break;
+        case ACC_MIN_I64: atomicMin(reinterpret_cast<long long*>(c), isint ? xi[r] : f64_to_ordered(xd[r])); break;
+        case ACC_MAX_I64: atomicMax(reinterpret_cast<long long*>(c), isint ? xi[r] : f64_to_ordered(xd[r])); break;
+        default: break;
+        }
+    }
+}
+
+// One thread = 4 consecutive rows per iteration: 128-bit coalesced loads of every column.
+template <bool EXACT>
+__global__ void __launch_bounds__(256)
+k_probe_agg(const KeySpec ks, const uint32_t nrows, const uint32_t mask, const uint32_t max_probe,
+            const AccProg prog, uint32_t* __restrict__ row_slot, uint32_t* __restrict__ flags) {
+    const uint32_t nquad = (nrows + 3u) >> 2;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nquad; q += gridDim.x * blockDim.x) {
+        if (*reinterpret_cast<volatile uint32_t*>(flags + FLAG_ABORT)) return;   // another CTA gave up
+        const uint32_t row0 = q << 2;
+        const int cnt = min(4u, nrows - row0);
+        uint32_t tag[4], hsh[4], slot[4];
+        if (!key_tags4(ks, row0, cnt, tag, hsh)) { atomicExch(flags + FLAG_ABORT, 3u); return; }
+        bool bad = false;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            slot[r] = 0;
+            if (r < cnt) {
+                slot[r] = probe_insert<EXACT>(ks, prog.tab, prog.sw, mask, max_probe, hsh[r], tag[r], row0 + r);
+                bad |= slot[r] == NOSLOT;
+            }
+        }
+        if (bad) { atomicCAS(flags + FLAG_ABORT, 0u, 1u); return; }
+        if (row_slot) {
+            if (cnt == 4) *reinterpret_cast<uint4*>(row_slot + row0) = make_uint4(slot[0], slot[1], slot[2], slot[3]);
+            else for (int r = 0; r < cnt; ++r) row_slot[row0 + r] = slot[r];
+        }
+        for (int a = 0; a < prog.n; ++a) acc_apply(prog, a, slot, row0, cnt);
+    }
+}
+
+// first-appearance rows -> bitmap
+__global__ void k_mark(const unsigned long long* __restrict__ tab, uint32_t cap, uint32_t sw, uint32_t* __restrict__ bitmap) {
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < cap; s += gridDim.x * blockDim.x) {
+        const unsigned long long w = tab[size_t(s) * sw];
+        if (w != SLOT_EMPTY) {
+            const uint32_t fr = (uint32_t)w;
+            atomicOr(bitmap + (fr >> 5), 1u << (fr & 31));
+        }
+    }
+}
+
+// prefix-popcount over the bitmap, 3 kernels: block sums, scan of block sums, per-word prefixes.
+constexpr int RANK_THREADS = 256;
+constexpr int RANK_WORDS = RANK_THREADS * 4;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_sums[RANK_THREADS / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t s = lane < RANK_THREADS / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < RANK_THREADS / 32; d <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, s, d);
+            if (lane >= d) s += y;
+        }
+        if (lane < RANK_THREADS / 32) warp_sums[lane] = s;
+    }
+    __syncthreads();
+    const uint32_t base = wid ? warp_sums[wid - 1] : 0;
+    if (total) *total = warp_sums[RANK_THREADS / 32 - 1];
+    __syncthreads();
+    return base + x - v;
+}
+
+__global__ void __launch_bounds__(RANK_THREADS)
+k_rank_blocksum(const uint32_t* __restrict__ bitmap, uint32_t nwords, uint32_t* __restrict__ blocksum) {
+    const uint32_t w0 = blockIdx.x * RANK_WORDS + threadIdx.x * 4;
+    uint32_t c = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (w0 + i < nwords) c += __popc(bitmap[w0 + i]);
+    uint32_t total;
+    block_exclusive_scan(c, &total);
+    if (threadIdx.x == 0) blocksum[blockIdx.x] = total;
+}
+
+// single block; exclusive scan in place, total number of groups -> flags[FLAG_NGROUPS]
+__global__ void __launch_bounds__(RANK_THREADS)
+k_rank_scan_blocks(uint32_t* __restrict__ blocksum, uint32_t nblocks, uint32_t* __restrict__ flags) {
+    uint32_t carry = 0;
+    for (uint32_t b0 = 0; b0 < nblocks; b0 += RANK_THREADS) {
+        const uint32_t i = b0 + threadIdx.x;
+        const uint32_t v = i < nblocks ? blocksum[i] : 0;
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan(v, &total);
+        if (i < nblocks) blocksum[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) flags[FLAG_NGROUPS] = carry;
+}
+
+__global__ void __launch_bounds__(RANK_THREADS)
+k_rank_wordprefix(const uint32_t* __restrict__ bitmap, uint32_t nwords, const uint32_t* __restrict__ blocksum,
+                  uint32_t* __restrict__ wordprefix) {
+    const uint32_t w0 = blockIdx.x * RANK_WORDS + threadIdx.x * 4;
+    uint32_t c[4];
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { c[i] = (w0 + i < nwords) ? __popc(bitmap[w0 + i]) : 0; s += c[i]; }
+    uint32_t ex = block_exclusive_scan(s, nullptr) + blocksum[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (w0 + i < nwords) wordprefix[w0 + i] = ex;
+        ex += c[i];
+    }
+}
+
+struct alignas(16) I128 { unsigned long long lo; long long hi; };
+
+__device__ __forceinline__ double i128_to_f64(__int128 x) { return (double)x; }
+
+__device__ void emit_one(const EmitAgg& e, const unsigned long long* __restrict__ sl, uint32_t gid,
+                         uint32_t first_row, int row_order) {
+    auto cell = [&](int a) -> unsigned long long { return sl[1 + a]; };
+    const bool isint = (e.vtype == AQ_INT32 || e.vtype == AQ_INT64);
+    const uint32_t n = e.cnt >= 0 ? (uint32_t)cell(e.cnt) : 0u;
+    switch (e.op) {
+    case AQ_SUM:
+        if (isint) {
+            const long long s = (long long)cell(e.a[0]);
+            if (e.out_type == AQ_INT128) { I128 v; v.lo = (unsigned long long)s; v.hi = s >> 63; static_cast<I128*>(e.out)[gid] = v; }
+            else static_cast<long long*>(e.out)[gid] = s;
+        } else {
+            static_cast<double*>(e.out)[gid] = __longlong_as_double((long long)cell(e.a[0]));
+        }
+        break;
+    case AQ_AVG: {     // aggregations.h:30: sum / static_cast<double>(size)
+        const double s = isint ? (double)(long long)cell(e.a[0]) : __longlong_as_double((long long)cell(e.a[0]));
+        static_cast<double*>(e.out)[gid] = s / (double)n;
+        break; }
+    case AQ_MIN: case AQ_MAX: {
+        const long long k = (long long)cell(e.a[0]);
+        if (e.vtype == AQ_INT32) static_cast<int*>(e.out)[gid] = (int)k;
+        else if (e.vtype == AQ_INT64) static_cast<long long*>(e.out)[gid] = k;
+        else {
+            double d = ordered_to_f64(k);
+            if (e.vtype == AQ_FLOAT) {
+                float f = (float)d;
+                // aggregations.h:73: max starts at numeric_limits<T>::min() = smallest positive normal
+                if (e.op == AQ_MAX && !(f > 1.17549435e-38f)) f = 1.17549435e-38f;
+                static_cast<float*>(e.out)[gid] = f;
+            } else {
+                if (e.op == AQ_MAX && !(d > 2.2250738585072014e-308)) d = 2.2250738585072014e-308;
+                static_cast<double*>(e.out)[gid] = d;
+            }
+        }
+        break; }
+    case AQ_COUNT:
+        if (e.out_type == AQ_INT64) static_cast<long long*>(e.out)[gid] = (long long)n;
+        else static_cast<uint32_t*>(e.out)[gid] = n;
+        break;
+    case AQ_FIRST: case AQ_LAST: {
+        const bool want_max = (e.op == AQ_FIRST) == (row_order == AQ_ROWS_DESC);
+        const uint32_t r = want_max ? (uint32_t)cell(e.maxrow) : first_row;
+        if (e.vtype == AQ_INT32 || e.vtype == AQ_FLOAT) static_cast<uint32_t*>(e.out)[gid] = static_cast<const uint32_t*>(e.v)[r];
+        else static_cast<unsigned long long*>(e.out)[gid] = static_cast<const unsigned long long*>(e.v)[r];
+        break; }
+    case AQ_VAR: case AQ_STDDEV: {   // aggregations.h:332-348: (ssq - s*s/(len+1)) / (len+1)
+        const double np1 = (double)(n + 1u);
+        double r;
+        if (isint) {
+            const long long s = (long long)cell(e.a[0]), ssq = (long long)cell(e.a[1]);
+            r = ((double)ssq - i128_to_f64((__int128)s * (__int128)s) / np1) / np1;
+        } else {
+            const double s = __longlong_as_double((long long)cell(e.a[0])), ssq = __longlong_as_double((long long)cell(e.a[1]));
+            r = (ssq - s * s / np1) / np1;
+        }
+        static_cast<double*>(e.out)[gid] = e.op == AQ_STDDEV ? sqrt(r) : r;
+        break; }
+    case AQ_CORR: {                  // aggregations.h:400-406
+        const long long sx = (long long)cell(e.a[0]), sy = (long long)cell(e.a[1]), sxy = (long long)cell(e.a[2]),
+                        sx2 = (long long)cell(e.a[3]), sy2 = (long long)cell(e.a[4]);
+        const __int128 len = (__int128)n;
+        const double num = i128_to_f64(len * sxy) - i128_to_f64((__int128)sx * sy);
+        const double dx = i128_to_f64(len * sx2) - i128_to_f64((__int128)sx * sx);
+        const double dy = i128_to_f64(len * sy2) - i128_to_f64((__int128)sy * sy);
+        static_cast<double*>(e.out)[gid] = num / sqrt(dx * dy);
+        break; }
+    default: break;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_emit(const unsigned long long* __restrict__ tab, const uint32_t cap, const uint32_t sw,
+       const uint32_t* __restrict__ bitmap, const uint32_t* __restrict__ wordprefix, const KeyOut ko,
+       uint32_t* __restrict__ first_row_out, uint32_t* __restrict__ counts_out, uint32_t* __restrict__ last_row_out,
+       uint32_t* __restrict__ slot_gid, const EmitProg ep, const int cnt_acc, const int maxrow_acc,
+       const uint32_t max_groups, const uint32_t* __restrict__ flags) {
+    if (flags[FLAG_ABORT] != 0 || flags[FLAG_NGROUPS] > max_groups) return;   // host reports the error
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < cap; s += gridDim.x * blockDim.x) {
+        const unsigned long long* sl = tab + size_t(s) * sw;
+        const unsigned long long w = sl[0];
+        if (w == SLOT_EMPTY) continue;
+        const uint32_t fr = (uint32_t)w;
+        const uint32_t gid = wordprefix[fr >> 5] + __popc(bitmap[fr >> 5] & ((1u << (fr & 31)) - 1u));
+        if (slot_gid) slot_gid[s] = gid;
+        if (first_row_out) first_row_out[gid] = fr;
+        if (counts_out) counts_out[gid] = (uint32_t)sl[1 + cnt_acc];
+        if (last_row_out) last_row_out[gid] = (uint32_t)sl[1 + maxrow_acc];
+        for (int k = 0; k < ko.n; ++k) {
+            if (!ko.dst[k]) continue;
+            if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[gid] = static_cast<const uint32_t*>(ko.src[k])[fr];
+            else static_cast<unsigned long long*>(ko.dst[k])[gid] = static_cast<const unsigned long long*>(ko.src[k])[fr];
+        }
+        for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], sl, gid, fr, ep.row_order);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host pipeline
+// ------------------------------------------------------------------------------------------------
+static uint32_t pow2_ceil(uint64_t x) {
+    uint64_t p = 1024;
+    while (p < x && p < (1ull << 31)) p <<= 1;
+    return (uint32_t)p;
+}
+
+static unsigned long long acc_identity(int kind) {
+    switch (kind) {
+    case ACC_MIN_I64: return 0x7fffffffffffffffULL;
+    case ACC_MAX_I64: return 0x8000000000000000ULL;
+    default: return 0ull;
+    }
+}
+
+int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& plan,
+                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups) {
+    Context& c = ctx();
+    const uint32_t max_cap = pow2_ceil(2ull * (nrows ? nrows : 1));
+    uint32_t cap = groups_hint ? pow2_ceil(2ull * groups_hint) : (1u << 16);
+    if (cap > max_cap) cap = max_cap;
+    uint32_t sw = 1;
+    while (sw < uint32_t(1 + plan.n_acc)) sw <<= 1;
+    hr.sw = sw;
+    const uint32_t nwords_bm = (nrows + 31) / 32 + 1;
+    const uint32_t rank_blocks = (nwords_bm + RANK_WORDS - 1) / RANK_WORDS;
+    DevBuf blocksum;
+    AQ_TRY(hr.bitmap.alloc(size_t(nwords_bm) * 4));
+    AQ_TRY(hr.wordprefix.alloc(size_t(nwords_bm) * 4));
+    AQ_TRY(blocksum.alloc(size_t(rank_blocks) * 4));
+    InitPattern pat;
+    for (int i = 0; i < 16; ++i) pat.w[i] = 0;
+    pat.w[0] = SLOT_EMPTY;
+    for (int a = 0; a < plan.n_acc; ++a) pat.w[1 + a] = acc_identity(plan.prog.op[a].kind);
+    bool allow_smem = d_row_slot == nullptr;
+
+    for (int attempt = 0; attempt < 16; ++attempt) {
+        hr.cap = cap;
+        const uint32_t max_probe = cap == max_cap ? cap : 256u;
+        const size_t tab_words = size_t(cap) * sw;
+        AQ_TRY(hr.tab.alloc(tab_words * 8));
+        plan.prog.tab = hr.tab.as<unsigned long long>();
+        plan.prog.sw = sw;
+        AQ_LAUNCH(k_init_table, grid_for(tab_words, 256, 4), 256, 0, plan.prog.tab, tab_words, sw, pat);
+        AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
+        AQ_CUDA(cudaMemsetAsync(hr.bitmap.p, 0, size_t(nwords_bm) * 4, c.stream));
+
+        bool used_smem = false;
+        if (allow_smem && nrows) AQ_TRY(launch_smem_probe(ks, nrows, cap, max_probe, plan.prog, groups_hint, &used_smem));
+        if (!used_smem && nrows) {
+            const int grid = grid_for((nrows + 3) / 4, 256, 1, 16);
+            if (ks.exact) AQ_LAUNCH(k_probe_agg<true>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
+            else AQ_LAUNCH(k_probe_agg<false>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
+        }
+        AQ_LAUNCH(k_mark, grid_for(cap, 256, 4), 256, 0, plan.prog.tab, cap, sw, hr.bitmap.as<uint32_t>());
+        AQ_LAUNCH(k_rank_blocksum, rank_blocks, RANK_THREADS, 0, hr.bitmap.as<uint32_t>(), nwords_bm, blocksum.as<uint32_t>());
+        AQ_LAUNCH(k_rank_scan_blocks, 1, RANK_THREADS, 0, blocksum.as<uint32_t>(), rank_blocks, c.d_flags);
+        AQ_LAUNCH(k_rank_wordprefix, rank_blocks, RANK_THREADS, 0, hr.bitmap.as<uint32_t>(), nwords_bm,
+                  blocksum.as<uint32_t>(), hr.wordprefix.as<uint32_t>());
+        AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+        AQ_CUDA(cudaStreamSynchronize(c.stream));
+        const uint32_t st = c.h_flags[FLAG_ABORT];
+        if (st == 0) { *ngroups = c.h_flags[FLAG_NGROUPS]; return 0; }
+        if (st == 2 || st == 4) { allow_smem = false; continue; }   // CTA-local overflow / inexact fp: global path
+        if (st == 3) {                                              // a key outside the caller's bounds
+            if (ks.exact != 2) return fail("internal: bounds flag without packed keys");
+            ks.exact = 0; ks.pack_bits = 0;
+            continue;
+        }
+        if (cap == max_cap) return fail("hash table overflow at maximum capacity (%u slots)", cap);
+        const uint64_t next = uint64_t(cap) * 16;                   // grow and retry
+        cap = next > max_cap ? max_cap : (uint32_t)next;
+    }
+    return fail("hash build did not converge");
+}
+
+int emit_groups(const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row, uint32_t* d_counts,
+                uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups) {
+    const int cnt_acc = plan.find(ACC_COUNT), maxrow_acc = plan.find(ACC_MAXROW);
+    if (d_counts && cnt_acc < 0) return fail("internal: counts requested without a COUNT accumulator");
+    if (d_last_row && maxrow_acc < 0) return fail("internal: last rows requested without a MAXROW accumulator");
+    AQ_LAUNCH(k_emit, grid_for(hr.cap, 256, 2), 256, 0, hr.tab.as<unsigned long long>(), hr.cap, hr.sw,
+              hr.bitmap.as<uint32_t>(), hr.wordprefix.as<uint32_t>(), ko, d_first_row, d_counts, d_last_row,
+              d_slot_gid, plan.emit, cnt_acc, maxrow_acc, max_groups, ctx().d_flags);
+    return 0;
+}
+
+} // namespace aq
+
+using namespace aq;
+
+extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                                 const int64_t* key_min, const int64_t* key_max,
+                                 int row_order, uint32_t groups_hint,
+                                 const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
+                                 void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups) {
+    AQ_REQUIRE_INIT();
+    if (n_aggs < 0 || n_aggs > MAX_AGGS || (n_aggs && !aggs)) return fail("need 0..%d aggregates", MAX_AGGS);
+    if (!ngroups) return fail("ngroups must not be null");
+    if (row_order != AQ_ROWS_DESC && row_order != AQ_ROWS_ASC) return fail("bad row_order %d", row_order);
+    *ngroups = 0;
+    KeyCols kc;
+    if (nrows == 0) {
+        if (!keys || !key_types || nkeys < 1 || nkeys > MAX_KEY_COLS) return fail("need 1..%d key columns", MAX_KEY_COLS);
+        return 0;
+    }
+    AQ_TRY(kc.bind(keys, key_types, nkeys, nrows));
+    if (max_groups == 0) max_groups = nrows;
+    KeySpec ks;
+    AQ_TRY(kc.make_spec(key_min, key_max, ks));
+
+    AggPlan plan;
+    plan.emit.row_order = row_order;
+    std::vector<InCol> vin(n_aggs), vin2(n_aggs);
+    std::vector<OutCol> vout(n_aggs);
+    for (int a = 0; a < n_aggs; ++a) {
+        const aqgpu_agg_t& g = aggs[a];
+        const void* dv = nullptr; const void* dv2 = nullptr;
+        if (g.op != AQ_COUNT) {
+            if (!is_val_type(g.vtype)) return fail("aggregate %d: unsupported value dtype %d", a, g.vtype);
+            AQ_TRY(vin[a].bind(g.v, dtype_size(g.vtype) * nrows));
+            dv = vin[a].d;
+            if (g.v2) { AQ_TRY(vin2[a].bind(g.v2, dtype_size(g.vtype) * nrows)); dv2 = vin2[a].d; }
+        }
+        const int ot = g.out_type ? g.out_type : aqgpu_reduce_out_type(g.op, g.vtype);
+        if (ot < 0 || dtype_size(ot) == 0) return fail("aggregate %d: bad output dtype", a);
+        AQ_TRY(vout[a].bind(g.out, dtype_size(ot) * max_groups));
+        AQ_TRY(plan.plan(g, dv, dv2, vout[a].d));
+    }
+
+    HashResult hr;
+    uint32_t ng = 0;
+    AQ_TRY(hash_aggregate(ks, nrows, groups_hint, plan, nullptr, hr, &ng));
+    if (ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
+
+    KeyOut ko;
+    memset(&ko, 0, sizeof(ko));
+    ko.n = nkeys;
+    std::vector<OutCol> kout(nkeys);
+    for (int k = 0; k < nkeys; ++k) {
+        ko.src[k] = kc.col[k].d;
+        ko.size[k] = (int)dtype_size(key_types[k]);
+        if (out_keys && out_keys[k]) {
+            AQ_TRY(kout[k].bind(out_keys[k], size_t(ko.size[k]) * max_groups));
+            ko.dst[k] = kout[k].d;
+        }
+    }
+    OutCol fr;
+    uint32_t* d_fr = nullptr;
+    if (out_first_row) { AQ_TRY(fr.bind(out_first_row, size_t(4) * max_groups)); d_fr = static_cast<uint32_t*>(fr.d); }
+
+    AQ_TRY(emit_groups(hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
+    bool any_host = false;
+    for (int a = 0; a < n_aggs; ++a) { AQ_TRY(vout[a].finish(dtype_size(plan.emit.agg[a].out_type) * ng)); any_host |= vout[a].host != nullptr; }
+    for (int k = 0; k < nkeys; ++k) if (ko.dst[k]) { AQ_TRY(kout[k].finish(size_t(ko.size[k]) * ng)); any_host |= kout[k].host != nullptr; }
+    if (out_first_row) { AQ_TRY(fr.finish(size_t(4) * ng)); any_host |= fr.host != nullptr; }
+    *ngroups = ng;
+    // host outputs are complete on return; device outputs are stream-ordered
+    if (any_host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}

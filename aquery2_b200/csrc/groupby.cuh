@@ -1,0 +1,243 @@
+// groupby.cuh -- internal structures of the group-by engine (groupby.cu, groupby_smem.cu, groups.cu).
+#pragma once
+#include "common.cuh"
+
+namespace aq {
+
+constexpr int MAX_KEY_COLS = 12;
+constexpr int MAX_KEY_WORDS = 12;     // 32-bit words per key tuple (an int64 column is 2 words)
+constexpr int MAX_ACC = 15;           // accumulator cells per group (slot = 1 + cells, <= 16 words)
+constexpr int MAX_AGGS = 16;
+constexpr unsigned long long SLOT_EMPTY = 0xffffffffffffffffULL;
+constexpr uint32_t NOSLOT = 0xffffffffu;
+
+// flags[] protocol between kernels and host (ctx().d_flags)
+enum : int {
+    FLAG_ABORT = 0,     // 0 ok, 1 table too full (grow), 2 CTA-local table overflow (use global path),
+                        // 3 key outside the supplied bounds (drop the bounds), 4 fp fixed-point inexact
+    FLAG_NGROUPS = 1
+};
+
+// Key tuple as a list of 32-bit words: word w of row i is base[w][i * stride[w]].
+struct KeySpec {
+    const uint32_t* base[MAX_KEY_WORDS];
+    uint32_t stride[MAX_KEY_WORDS];
+    int nwords;
+    int vec_ok;          // every stride-1 column is 16-byte aligned: 128-bit loads allowed
+    // exact 32-bit image of the key tuple ("tag"): 0 = none (tag = hash bits, verified against the
+    // key columns), 1 = the single 32-bit key itself, 2 = bit-packed (k - lo) fields, the scheme of
+    // the reference's PerfectHashTable (server/hasher.h:226-243) from per-column bounds.
+    int exact;
+    uint32_t pack_lo[MAX_KEY_WORDS];
+    uint32_t pack_range[MAX_KEY_WORDS];   // hi - lo
+    uint32_t pack_shift[MAX_KEY_WORDS];
+    int pack_bits;
+};
+
+// One 64-bit accumulator cell per group and AccOp.
+enum AccKind : int {
+    ACC_COUNT = 0,     // += 1
+    ACC_ADD_I64 = 1,   // += (int64) x
+    ACC_ADD_F64 = 2,   // += (double) x
+    ACC_MIN_I64 = 3,   // min of the int64 image (ints: value, fp: order-preserving bits of the double)
+    ACC_MAX_I64 = 4,
+    ACC_MAXROW = 5     // max row id of the group
+};
+enum AccXform : int {
+    X_IDENT = 0,       // x = v[i]
+    X_SQUARE = 1,      // x = v[i] * v[i]   (fp: product rounded in the column's own type, as
+                       //                    aggregations.h:339-345 computes arr[i]*arr[i] in T)
+    X_PRODUCT = 2      // x = v[i] * v2[i]
+};
+struct AccOp {
+    int kind;
+    int xform;
+    int vtype;
+    int vec_ok;        // v (and v2) 16-byte aligned
+    const void* v;
+    const void* v2;
+};
+// Global table: cap slots of `sw` 64-bit words; word 0 = (tag << 32 | min row) or SLOT_EMPTY,
+// word 1 + a = accumulator a.  sw is a power of two so that a slot never straddles a 32 B sector
+// boundary more than necessary (sw = 4 -> exactly one sector).
+struct AccProg {
+    AccOp op[MAX_ACC];
+    int n;
+    unsigned long long* tab;
+    uint32_t sw;
+};
+__host__ __device__ __forceinline__ unsigned long long* slot_word(const AccProg& p, uint32_t slot) {
+    return p.tab + size_t(slot) * p.sw;
+}
+
+// How one requested aggregate is produced from accumulator cells at emit time.
+struct EmitAgg {
+    int op;            // aqgpu_reduce_op
+    int vtype;
+    int out_type;
+    int a[5];          // accumulator indices (meaning depends on op)
+    int cnt;           // index of the COUNT accumulator or -1
+    int maxrow;        // index of the MAXROW accumulator or -1
+    const void* v;     // value column for FIRST / LAST gathers
+    void* out;
+};
+struct EmitProg {
+    EmitAgg agg[MAX_AGGS];
+    int n;
+    int row_order;
+};
+
+struct KeyOut {
+    const void* src[MAX_KEY_COLS];
+    void* dst[MAX_KEY_COLS];
+    int size[MAX_KEY_COLS];    // 4 or 8
+    int n;
+};
+
+// Host-side description of the key columns after pointer binding.
+struct KeyCols {
+    int n = 0;
+    int type[MAX_KEY_COLS];
+    InCol col[MAX_KEY_COLS];
+    int bind(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows);
+    int make_spec(const int64_t* key_min, const int64_t* key_max, KeySpec& ks) const;
+};
+
+struct AggPlan {
+    AccProg prog;
+    EmitProg emit;
+    int n_acc = 0;
+    AggPlan();
+    int add_acc(int kind, int xform, int vtype, const void* v, const void* v2);
+    int add_count() { return add_acc(ACC_COUNT, X_IDENT, 0, nullptr, nullptr); }
+    int add_maxrow() { return add_acc(ACC_MAXROW, X_IDENT, 0, nullptr, nullptr); }
+    int find(int kind) const;
+    int plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* dout);
+};
+
+// Result of the hash phase, consumed by emit / handle construction.
+struct HashResult {
+    uint32_t cap = 0;
+    uint32_t sw = 0;
+    DevBuf tab;                   // cap x sw u64
+    DevBuf bitmap;                // nrows bits: first-appearance rows
+    DevBuf wordprefix;            // per bitmap word: number of groups before it
+};
+
+// Hash build + fused accumulation + ranking of the groups by first row.  Synchronises once to
+// return *ngroups.  d_row_slot (optional, nrows) receives every row's table slot.
+int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& plan,
+                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups);
+
+// Writes keys / first rows / aggregates in first-appearance order (gid = rank of the first row).
+int emit_groups(const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row, uint32_t* d_counts,
+                uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups);
+
+// smem-privatised scan (groupby_smem.cu).  *used = false if the request does not qualify.
+int launch_smem_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t max_probe,
+                      const AccProg& prog, uint32_t groups_hint, bool* used);
+
+#ifdef __CUDACC__
+// ---- device helpers shared by the probe kernels ------------------------------------------------
+__device__ __forceinline__ void load4_b32(const void* base, uint32_t row0, int cnt, bool vec, uint32_t out[4]) {
+    const uint32_t* p = static_cast<const uint32_t*>(base) + row0;
+    if (vec && cnt == 4) {
+        int4 t = ld_stream_v4(p);
+        out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) out[r] = r < cnt ? ld_stream_u32(p + r) : 0u;
+    }
+}
+__device__ __forceinline__ void load4_b64(const void* base, uint32_t row0, int cnt, bool vec, unsigned long long out[4]) {
+    const unsigned long long* p = static_cast<const unsigned long long*>(base) + row0;
+    if (vec && cnt == 4) {
+        int4 t0 = ld_stream_v4(p), t1 = ld_stream_v4(p + 2);
+        out[0] = (unsigned long long)(uint32_t)t0.x | ((unsigned long long)(uint32_t)t0.y << 32);
+        out[1] = (unsigned long long)(uint32_t)t0.z | ((unsigned long long)(uint32_t)t0.w << 32);
+        out[2] = (unsigned long long)(uint32_t)t1.x | ((unsigned long long)(uint32_t)t1.y << 32);
+        out[3] = (unsigned long long)(uint32_t)t1.z | ((unsigned long long)(uint32_t)t1.w << 32);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) out[r] = r < cnt ? __ldg(p + r) : 0ull;
+    }
+}
+
+__device__ __forceinline__ bool keys_equal(const KeySpec& ks, uint32_t a, uint32_t b) {
+    for (int w = 0; w < ks.nwords; ++w) {
+        const uint32_t* p = ks.base[w];
+        if (__ldg(p + size_t(a) * ks.stride[w]) != __ldg(p + size_t(b) * ks.stride[w])) return false;
+    }
+    return true;
+}
+
+// Loads the key words of 4 consecutive rows; produces the 32-bit tag and the slot hash of each.
+// Returns false if a key lies outside the supplied bounds (packed mode).
+__device__ __forceinline__ bool key_tags4(const KeySpec& ks, uint32_t row0, int cnt, uint32_t tag[4], uint32_t hsh[4]) {
+    bool ok = true;
+    if (ks.exact) {
+        uint32_t t[4] = {0, 0, 0, 0};
+        for (int w = 0; w < ks.nwords; ++w) {
+            uint32_t kw[4];
+            load4_b32(ks.base[w], row0, cnt, ks.vec_ok, kw);
+            if (ks.exact == 1) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) t[r] = kw[r];
+            } else {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const uint32_t d = kw[r] - ks.pack_lo[w];
+                    ok &= (r >= cnt) || (d <= ks.pack_range[w]);
+                    t[r] |= d << ks.pack_shift[w];
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { tag[r] = t[r]; hsh[r] = mix32(t[r]); }
+    } else {
+        uint64_t h[4] = {0x9e3779b97f4a7c15ULL, 0x9e3779b97f4a7c15ULL, 0x9e3779b97f4a7c15ULL, 0x9e3779b97f4a7c15ULL};
+        for (int w = 0; w < ks.nwords; ++w) {
+            uint32_t kw[4];
+            if (ks.stride[w] == 1) {
+                load4_b32(ks.base[w], row0, cnt, ks.vec_ok, kw);
+            } else {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) kw[r] = r < cnt ? __ldg(ks.base[w] + size_t(row0 + r) * ks.stride[w]) : 0u;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) h[r] = mix64(h[r] ^ kw[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { tag[r] = (uint32_t)(h[r] >> 32); hsh[r] = (uint32_t)h[r]; }
+    }
+    return ok;
+}
+
+// find-or-insert in the global table; keeps the smallest row id in the low half of word 0.
+template <bool EXACT>
+__device__ __forceinline__ uint32_t probe_insert(const KeySpec& ks, unsigned long long* tab, uint32_t sw,
+                                                 uint32_t mask, uint32_t max_probe, uint32_t h, uint32_t tag,
+                                                 uint32_t row) {
+    const unsigned long long mine = ((unsigned long long)tag << 32) | row;
+    uint32_t slot = h & mask;
+    for (uint32_t step = 0; step <= max_probe; ++step) {
+        unsigned long long* w0 = tab + size_t(slot) * sw;
+        unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(w0);
+        if (cur == SLOT_EMPTY) {
+            const unsigned long long old = atomicCAS(w0, SLOT_EMPTY, mine);
+            if (old == SLOT_EMPTY) return slot;
+            cur = old;
+        }
+        if ((uint32_t)(cur >> 32) == tag) {
+            if (EXACT || keys_equal(ks, row, (uint32_t)cur)) {
+                if (row < (uint32_t)cur) atomicMin(w0, mine);
+                return slot;
+            }
+        }
+        slot = (slot + 1) & mask;
+    }
+    return NOSLOT;
+}
+#endif
+
+} // namespace aq

@@ -1,0 +1,387 @@
+// groups.cu -- the group handle: HashTableComponents {size, keys, values, offsets} of the reference
+// (server/hasher.h:201-207) kept in HBM, plus the per-group reduce / scan / order_by entry points.
+#include "groupby.cuh"
+#include "sort.cuh"
+#include "scan.cuh"
+#include <cstring>
+#include <mutex>
+
+using namespace aq;
+
+struct aqgpu_groups {
+    uint32_t nrows = 0, ngroups = 0;
+    int row_order = AQ_ROWS_DESC;
+    int nkeys = 0;
+    int key_type[MAX_KEY_COLS];
+    DevBuf keys[MAX_KEY_COLS];      // ngroups cells each, first-appearance order
+    DevBuf first_row, last_row;     // ngroups
+    DevBuf counts;                  // ngroups + 1 (last = 0)
+    DevBuf gid;                     // nrows: "reversemap"
+    DevBuf offsets;                 // ngroups + 1: "ht_base" after ht_postproc + terminal
+    DevBuf perm;                    // nrows: "mapbase"
+    DevBuf segstart;                // nrows: first CSR position of the owning group
+    bool has_offsets = false, has_perm = false, has_segstart = false;
+};
+
+namespace aq {
+
+__global__ void k_map_gid(const uint32_t* __restrict__ row_slot, const uint32_t* __restrict__ slot_gid,
+                          uint32_t n, uint32_t* __restrict__ gid) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        gid[i] = slot_gid[row_slot[i]];
+}
+
+static int ensure_offsets(aqgpu_groups* g) {
+    if (g->has_offsets) return 0;
+    AQ_TRY(g->offsets.alloc(size_t(g->ngroups + 1) * 4));
+    AQ_TRY(exclusive_scan_u32(g->counts.as<uint32_t>(), g->offsets.as<uint32_t>(), size_t(g->ngroups) + 1, nullptr));
+    g->has_offsets = true;
+    return 0;
+}
+
+// ht_postproc (hasher.h:181-198): rows grouped by gid; descending row ids inside a group in the
+// reference order, ascending in AQ_ROWS_ASC.  Stable LSD radix sort of the (reversed) row list.
+static int ensure_perm(aqgpu_groups* g) {
+    if (g->has_perm) return 0;
+    AQ_TRY(ensure_offsets(g));
+    AQ_TRY(g->perm.alloc(size_t(g->nrows) * 4));
+    SortJob job;
+    job.n = g->nrows;
+    job.rows_in = nullptr;
+    job.reverse = g->row_order == AQ_ROWS_DESC;
+    job.col = g->gid.as<uint32_t>();
+    int bits = 0;
+    while (bits < 32 && (uint64_t(1) << bits) < uint64_t(g->ngroups)) ++bits;
+    job.key_bits = bits;
+    job.rows_out = g->perm.as<uint32_t>();
+    AQ_TRY(sort_rows_by_key(job));
+    g->has_perm = true;
+    return 0;
+}
+
+static int ensure_segstart(aqgpu_groups* g) {
+    if (g->has_segstart) return 0;
+    AQ_TRY(ensure_offsets(g));
+    AQ_TRY(g->segstart.alloc(size_t(g->nrows) * 4));
+    AQ_TRY(compute_segment_starts(g->offsets.as<uint32_t>(), g->ngroups, g->nrows, g->segstart.as<uint32_t>()));
+    g->has_segstart = true;
+    return 0;
+}
+
+static int copy_out(void* dst, const void* d_src, size_t bytes) {
+    if (!dst) return fail("null output pointer");
+    if (bytes == 0) return 0;
+    const bool dev = is_device_ptr(dst);
+    AQ_CUDA(cudaMemcpyAsync(dst, d_src, bytes, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx().stream));
+    if (!dev) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+// ---- min / max of an integer column --------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(256)
+k_minmax(const T* __restrict__ v, uint32_t n, long long* __restrict__ out /* [min, max] */) {
+    long long lo = 0x7fffffffffffffffLL, hi = (long long)0x8000000000000000ULL;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const long long x = (long long)v[i];
+        lo = x < lo ? x : lo; hi = x > hi ? x : hi;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const long long l2 = __shfl_down_sync(0xffffffffu, lo, d), h2 = __shfl_down_sync(0xffffffffu, hi, d);
+        lo = l2 < lo ? l2 : lo; hi = h2 > hi ? h2 : hi;
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(out, lo); atomicMax(out + 1, hi); }
+}
+
+// ---- element-wise helpers -------------------------------------------------------------------------
+template <class T>
+__global__ void k_vec_sub(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ o, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) o[i] = a[i] - b[i];
+}
+__global__ void k_avg_finalize(int sum_type, const void* __restrict__ sum, const uint32_t* __restrict__ cnt,
+                               double* __restrict__ o, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        double s;
+        if (sum_type == AQ_DOUBLE) s = static_cast<const double*>(sum)[i];
+        else if (sum_type == AQ_INT64) s = (double)static_cast<const long long*>(sum)[i];
+        else s = (double)(static_cast<const __int128*>(sum)[i]);
+        o[i] = s / (double)cnt[i];
+    }
+}
+__global__ void k_vec_pow(const double* __restrict__ x, double p, double* __restrict__ o, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) o[i] = pow(x[i], p);
+}
+
+} // namespace aq
+
+extern "C" {
+
+int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                        const int64_t* key_min, const int64_t* key_max,
+                        int row_order, uint32_t groups_hint, aqgpu_groups_t** out) {
+    AQ_REQUIRE_INIT();
+    if (!out) return fail("null handle pointer");
+    *out = nullptr;
+    if (row_order != AQ_ROWS_DESC && row_order != AQ_ROWS_ASC) return fail("bad row_order %d", row_order);
+    if (!keys || !key_types || nkeys < 1 || nkeys > MAX_KEY_COLS) return fail("need 1..%d key columns", MAX_KEY_COLS);
+    aqgpu_groups* g = new aqgpu_groups();
+    g->nrows = nrows; g->row_order = row_order; g->nkeys = nkeys;
+    for (int k = 0; k < nkeys; ++k) g->key_type[k] = key_types[k];
+    struct Guard { aqgpu_groups* g; ~Guard() { delete g; } } guard{g};
+    if (nrows == 0) {
+        AQ_TRY(g->counts.alloc_zero(4));
+        guard.g = nullptr; *out = g;
+        return 0;
+    }
+    KeyCols kc;
+    AQ_TRY(kc.bind(keys, key_types, nkeys, nrows));
+    KeySpec ks;
+    AQ_TRY(kc.make_spec(key_min, key_max, ks));
+    AggPlan plan;
+    plan.emit.row_order = row_order;
+    if (plan.add_count() < 0 || plan.add_maxrow() < 0) return fail("internal: accumulator allocation");
+    DevBuf row_slot;
+    AQ_TRY(row_slot.alloc(size_t(nrows) * 4));
+    HashResult hr;
+    uint32_t ng = 0;
+    AQ_TRY(hash_aggregate(ks, nrows, groups_hint, plan, row_slot.as<uint32_t>(), hr, &ng));
+    g->ngroups = ng;
+
+    KeyOut ko;
+    memset(&ko, 0, sizeof(ko));
+    ko.n = nkeys;
+    for (int k = 0; k < nkeys; ++k) {
+        ko.size[k] = (int)dtype_size(key_types[k]);
+        AQ_TRY(g->keys[k].alloc(size_t(ng) * ko.size[k]));
+        ko.src[k] = kc.col[k].d;
+        ko.dst[k] = g->keys[k].p;
+    }
+    AQ_TRY(g->first_row.alloc(size_t(ng) * 4));
+    AQ_TRY(g->last_row.alloc(size_t(ng) * 4));
+    AQ_TRY(g->counts.alloc_zero(size_t(ng + 1) * 4));
+    DevBuf slot_gid;
+    AQ_TRY(slot_gid.alloc(size_t(hr.cap) * 4));
+    AQ_TRY(emit_groups(hr, ko, g->first_row.as<uint32_t>(), g->counts.as<uint32_t>(), g->last_row.as<uint32_t>(),
+                       slot_gid.as<uint32_t>(), plan, ng));
+    AQ_TRY(g->gid.alloc(size_t(nrows) * 4));
+    AQ_LAUNCH(k_map_gid, grid_for(nrows, 256, 1, 32), 256, 0, row_slot.as<uint32_t>(), slot_gid.as<uint32_t>(), nrows,
+              g->gid.as<uint32_t>());
+    AQ_CUDA(cudaStreamSynchronize(ctx().stream));    // staged key columns (host inputs) are released on return
+    guard.g = nullptr;
+    *out = g;
+    return 0;
+}
+
+int aqgpu_groups_free(aqgpu_groups_t* g) {
+    delete g;
+    return 0;
+}
+
+int aqgpu_groups_size(aqgpu_groups_t* g, uint32_t* ngroups) {
+    if (!g || !ngroups) return fail("null argument");
+    *ngroups = g->ngroups;
+    return 0;
+}
+
+int aqgpu_groups_keys(aqgpu_groups_t* g, int k, void* out_keys) {
+    if (!g || k < 0 || k >= g->nkeys) return fail("bad key column index %d", k);
+    return copy_out(out_keys, g->keys[k].p, size_t(g->ngroups) * dtype_size(g->key_type[k]));
+}
+
+int aqgpu_groups_first_row(aqgpu_groups_t* g, uint32_t* out) {
+    if (!g) return fail("null handle");
+    return copy_out(out, g->first_row.p, size_t(g->ngroups) * 4);
+}
+
+int aqgpu_groups_gid(aqgpu_groups_t* g, uint32_t* out_gid) {
+    if (!g) return fail("null handle");
+    return copy_out(out_gid, g->gid.p, size_t(g->nrows) * 4);
+}
+
+int aqgpu_groups_csr(aqgpu_groups_t* g, uint32_t* out_offsets, uint32_t* out_perm) {
+    if (!g) return fail("null handle");
+    if (g->nrows == 0) {
+        if (out_offsets) { uint32_t z = 0; if (is_device_ptr(out_offsets)) AQ_CUDA(cudaMemsetAsync(out_offsets, 0, 4, ctx().stream)); else *out_offsets = z; }
+        return 0;
+    }
+    if (out_offsets) { AQ_TRY(ensure_offsets(g)); AQ_TRY(copy_out(out_offsets, g->offsets.p, size_t(g->ngroups + 1) * 4)); }
+    if (out_perm) { AQ_TRY(ensure_perm(g)); AQ_TRY(copy_out(out_perm, g->perm.p, size_t(g->nrows) * 4)); }
+    return 0;
+}
+
+int aqgpu_groups_device_views(aqgpu_groups_t* g, const uint32_t** d_gid, const uint32_t** d_offsets,
+                              const uint32_t** d_perm) {
+    if (!g) return fail("null handle");
+    if (g->nrows) {
+        if (d_offsets) AQ_TRY(ensure_offsets(g));
+        if (d_perm) AQ_TRY(ensure_perm(g));
+    }
+    if (d_gid) *d_gid = g->gid.as<uint32_t>();
+    if (d_offsets) *d_offsets = g->offsets.as<uint32_t>();
+    if (d_perm) *d_perm = g->perm.as<uint32_t>();
+    return 0;
+}
+
+// Scalar aggregate per group == group-by on the dense gid column: ids were handed out in
+// first-appearance order, so the fused engine returns the cells already in gid order.
+int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, const void* v2,
+                       int out_type, void* out) {
+    AQ_REQUIRE_INIT();
+    if (!g) return fail("null handle");
+    if (g->nrows == 0) return 0;
+    const void* keys[1] = { g->gid.p };
+    const int kt[1] = { AQ_UINT32 };
+    aqgpu_agg_t a;
+    a.op = op; a.vtype = vtype; a.v = v; a.v2 = v2; a.out_type = out_type; a.out = out;
+    uint32_t ng = 0;
+    AQ_TRY(aqgpu_groupby_agg(keys, kt, 1, g->nrows, nullptr, nullptr, g->row_order, g->ngroups, &a, 1, g->ngroups,
+                             nullptr, nullptr, &ng));
+    if (ng != g->ngroups) return fail("internal: reduce saw %u groups, handle has %u", ng, g->ngroups);
+    return 0;
+}
+
+int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const void* v, int out_type, void* out) {
+    AQ_REQUIRE_INIT();
+    if (!g) return fail("null handle");
+    if (g->nrows == 0) return 0;
+    if (!is_val_type(vtype)) return fail("unsupported value dtype %d", vtype);
+    const int def = aqgpu_scan_out_type(op, vtype);
+    if (def < 0) return fail("unknown scan op %d", op);
+    if (out_type == 0 && def != 0) out_type = def;
+    if (out_type != def && !(def == AQ_INT128 && out_type == AQ_INT64))
+        return fail("scan op %d on dtype %d cannot produce dtype %d", op, vtype, out_type);
+    AQ_TRY(ensure_perm(g));
+    AQ_TRY(ensure_segstart(g));
+    InCol in;
+    AQ_TRY(in.bind(v, dtype_size(vtype) * g->nrows));
+    OutCol oc;
+    AQ_TRY(oc.bind(out, dtype_size(out_type) * g->nrows));
+    AQ_TRY(group_scan_device(op, w, vtype, in.d, g->nrows, g->ngroups, g->gid.as<uint32_t>(), g->offsets.as<uint32_t>(),
+                             g->perm.as<uint32_t>(), g->segstart.as<uint32_t>(), out_type, oc.d));
+    AQ_TRY(oc.finish(dtype_size(out_type) * g->nrows));
+    if (oc.host || in.tmp.p) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+// TableInfo::order_by per group (table.h:447-461, common/groupby.py:54-59) as one segmented sort:
+// stable LSD passes over the order columns (last column first), then over gid.
+int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int* col_types,
+                          const int* desc, int ncols) {
+    AQ_REQUIRE_INIT();
+    if (!g || !cols || !col_types || ncols < 1) return fail("bad order_by arguments");
+    if (g->nrows == 0) return 0;
+    AQ_TRY(ensure_perm(g));
+    const uint32_t n = g->nrows;
+    DevBuf a, b;
+    AQ_TRY(a.alloc(size_t(n) * 4));
+    AQ_TRY(b.alloc(size_t(n) * 4));
+    const uint32_t* cur = g->perm.as<uint32_t>();
+    uint32_t* bufs[2] = { a.as<uint32_t>(), b.as<uint32_t>() };
+    int which = 0;
+    std::vector<InCol> in(ncols);
+    for (int c = ncols - 1; c >= 0; --c) {
+        const int t = col_types[c];
+        const bool d = desc && desc[c];
+        AQ_TRY(in[c].bind(cols[c], dtype_size(t) * n));
+        SortJob job;
+        job.n = n; job.key_bits = 32;
+        if (t == AQ_INT32 || t == AQ_UINT32 || t == AQ_FLOAT) {
+            job.rows_in = cur; job.col = static_cast<const uint32_t*>(in[c].d); job.col_stride = 1;
+            job.float_flip = t == AQ_FLOAT;
+            const uint32_t asc_mask = t == AQ_INT32 ? 0x80000000u : 0u;
+            job.xor_mask = d ? ~asc_mask : asc_mask;
+            job.rows_out = bufs[which];
+            AQ_TRY(sort_rows_by_key(job));
+            cur = bufs[which]; which ^= 1;
+        } else if (t == AQ_INT64) {
+            for (int half = 0; half < 2; ++half) {           // low word (unsigned) then high word (signed)
+                job.rows_in = cur; job.col = static_cast<const uint32_t*>(in[c].d) + half; job.col_stride = 2;
+                const uint32_t asc_mask = half ? 0x80000000u : 0u;
+                job.xor_mask = d ? ~asc_mask : asc_mask;
+                job.rows_out = bufs[which];
+                AQ_TRY(sort_rows_by_key(job));
+                cur = bufs[which]; which ^= 1;
+            }
+        } else {
+            return fail("order_by: unsupported column dtype %d (int32, uint32, float, int64)", t);
+        }
+    }
+    SortJob job;                                              // regroup
+    job.n = n; job.rows_in = cur; job.col = g->gid.as<uint32_t>();
+    int bits = 0;
+    while (bits < 32 && (uint64_t(1) << bits) < uint64_t(g->ngroups)) ++bits;
+    job.key_bits = bits;
+    job.rows_out = g->perm.as<uint32_t>();
+    if (bits == 0) AQ_CUDA(cudaMemcpyAsync(g->perm.p, cur, size_t(n) * 4, cudaMemcpyDeviceToDevice, ctx().stream));
+    else AQ_TRY(sort_rows_by_key(job));
+    AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+int aqgpu_col_minmax(int dtype, const void* col, uint32_t nrows, int64_t* out_min, int64_t* out_max) {
+    AQ_REQUIRE_INIT();
+    if (!out_min || !out_max) return fail("null output");
+    if (nrows == 0) { *out_min = 0; *out_max = -1; return 0; }
+    const size_t sz = dtype_size(dtype);
+    if (dtype != AQ_INT32 && dtype != AQ_UINT32 && dtype != AQ_INT64) return fail("minmax: integer columns only");
+    InCol in;
+    AQ_TRY(in.bind(col, sz * nrows));
+    DevBuf mm;
+    AQ_TRY(mm.alloc(16));
+    const long long init[2] = { 0x7fffffffffffffffLL, (long long)0x8000000000000000ULL };
+    AQ_CUDA(cudaMemcpyAsync(mm.p, init, 16, cudaMemcpyHostToDevice, ctx().stream));
+    const int grid = grid_for(nrows, 256, 8, 8);
+    if (dtype == AQ_INT32) AQ_LAUNCH(k_minmax<int>, grid, 256, 0, static_cast<const int*>(in.d), nrows, mm.as<long long>());
+    else if (dtype == AQ_UINT32) AQ_LAUNCH(k_minmax<uint32_t>, grid, 256, 0, static_cast<const uint32_t*>(in.d), nrows, mm.as<long long>());
+    else AQ_LAUNCH(k_minmax<long long>, grid, 256, 0, static_cast<const long long*>(in.d), nrows, mm.as<long long>());
+    long long res[2];
+    AQ_CUDA(cudaMemcpyAsync(res, mm.p, 16, cudaMemcpyDeviceToHost, ctx().stream));
+    AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    *out_min = res[0]; *out_max = res[1];
+    return 0;
+}
+
+int aqgpu_vec_sub(int dtype, const void* a, const void* b, void* out, uint32_t n) {
+    AQ_REQUIRE_INIT();
+    if (n == 0) return 0;
+    const size_t sz = dtype_size(dtype);
+    if (!is_val_type(dtype)) return fail("vec_sub: unsupported dtype %d", dtype);
+    InCol ia, ib; OutCol oc;
+    AQ_TRY(ia.bind(a, sz * n)); AQ_TRY(ib.bind(b, sz * n)); AQ_TRY(oc.bind(out, sz * n));
+    const int grid = grid_for(n, 256, 1, 16);
+    switch (dtype) {
+    case AQ_INT32: AQ_LAUNCH(k_vec_sub<int>, grid, 256, 0, (const int*)ia.d, (const int*)ib.d, (int*)oc.d, n); break;
+    case AQ_INT64: AQ_LAUNCH(k_vec_sub<long long>, grid, 256, 0, (const long long*)ia.d, (const long long*)ib.d, (long long*)oc.d, n); break;
+    case AQ_FLOAT: AQ_LAUNCH(k_vec_sub<float>, grid, 256, 0, (const float*)ia.d, (const float*)ib.d, (float*)oc.d, n); break;
+    default: AQ_LAUNCH(k_vec_sub<double>, grid, 256, 0, (const double*)ia.d, (const double*)ib.d, (double*)oc.d, n); break;
+    }
+    AQ_TRY(oc.finish(sz * n));
+    if (oc.host || ia.tmp.p || ib.tmp.p) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+int aqgpu_avg_finalize(int sum_type, const void* sum, const uint32_t* count, double* out, uint32_t n) {
+    AQ_REQUIRE_INIT();
+    if (n == 0) return 0;
+    if (sum_type != AQ_DOUBLE && sum_type != AQ_INT64 && sum_type != AQ_INT128) return fail("avg_finalize: bad sum dtype %d", sum_type);
+    InCol is, ic; OutCol oc;
+    AQ_TRY(is.bind(sum, dtype_size(sum_type) * n)); AQ_TRY(ic.bind(count, size_t(4) * n)); AQ_TRY(oc.bind(out, size_t(8) * n));
+    AQ_LAUNCH(k_avg_finalize, grid_for(n, 256, 1, 16), 256, 0, sum_type, is.d, (const uint32_t*)ic.d, (double*)oc.d, n);
+    AQ_TRY(oc.finish(size_t(8) * n));
+    if (oc.host || is.tmp.p || ic.tmp.p) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+int aqgpu_vec_pow(const double* x, double p, double* out, uint32_t n) {
+    AQ_REQUIRE_INIT();
+    if (n == 0) return 0;
+    InCol ix; OutCol oc;
+    AQ_TRY(ix.bind(x, size_t(8) * n)); AQ_TRY(oc.bind(out, size_t(8) * n));
+    AQ_LAUNCH(k_vec_pow, grid_for(n, 256, 1, 16), 256, 0, (const double*)ix.d, p, (double*)oc.d, n);
+    AQ_TRY(oc.finish(size_t(8) * n));
+    if (oc.host || ix.tmp.p) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,203 @@
+/*
+ * aqgpu.h -- C ABI of libaqgpu: AQuery++'s post-processor hot path (hash group-by over column
+ * batches + per-group scalar / running / windowed aggregation) on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  The reference runs this path inside its generated dll.so by
+ * instantiating header templates (server/hasher.h, server/table.h, server/aggregations.h); there is
+ * no FFI in the reference for it, so every entry point below cites the reference template / loop it
+ * replaces (paths relative to the reference tree).  The C++ drop-in headers under
+ * aquery2_b200/host/server/ keep the reference's names (ColRef, vector_type, TableInfo,
+ * HashTableFactory, sum/avg/...) and forward here; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ / torch types cross this boundary;
+ *   - every function returns 0 on success, non-zero on error (server/monetdb_conn.cpp:393-396 uses
+ *     the int result as a boolean); aqgpu_last_error() gives the message; nothing throws;
+ *   - column pointers may be DEVICE pointers (HBM-resident column store, the normal case) or HOST
+ *     pointers (pageable or pinned): host inputs are staged to HBM and host outputs copied back by
+ *     the call itself, on the library stream;
+ *   - row counts and row ids are uint32_t as in the reference (server/vector_type.hpp:66,
+ *     server/hasher.h:149-198); byte counts are size_t;
+ *   - dtype codes are the reference's types::Type_t values (server/aquery_types.h:1-5);
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef AQGPU_H
+#define AQGPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AQGPU_ABI_VERSION 1
+
+/* ---- dtypes: types::Type_t (server/aquery_types.h:1-5) ------------------------------------- */
+enum aqgpu_dtype {
+    AQ_INT32 = 0, AQ_FLOAT = 1, AQ_DOUBLE = 3, AQ_INT64 = 5, AQ_INT128 = 6, AQ_UINT32 = 11
+};
+
+/* ---- per-group scalar aggregates (server/aggregations.h) ------------------------------------
+ * Result cell types follow the reference (server/types.h:199-210):
+ *   SUM(int32|int64) -> AQ_INT128 (or AQ_INT64 on request), SUM(float|double) -> AQ_DOUBLE,
+ *   AVG/VAR/STDDEV/CORR -> AQ_DOUBLE, MIN/MAX/FIRST/LAST -> the input type, COUNT -> AQ_UINT32.  */
+enum aqgpu_reduce_op {
+    AQ_SUM = 0,     /* aggregations.h:19-27  */
+    AQ_AVG = 1,     /* aggregations.h:28-32  sum / double(size) */
+    AQ_MIN = 2,     /* aggregations.h:79-86  */
+    AQ_MAX = 3,     /* aggregations.h:71-78  identity numeric_limits<T>::min(): fp quirk kept */
+    AQ_COUNT = 4,   /* engine/ast.py:763     count(*) == vecs[g].size */
+    AQ_FIRST = 5,   /* aggregations.h:493-497 first element of the group's row list */
+    AQ_LAST = 6,    /* aggregations.h:487-491 */
+    AQ_VAR = 7,     /* aggregations.h:332-348 (divides by len+1, kept) */
+    AQ_STDDEV = 8,  /* aggregations.h:413-415 */
+    AQ_CORR = 9     /* aggregations.h:383-407 integer inputs only */
+};
+
+/* ---- per-group vector-valued aggregates, CSR output (engine/ast.py:696-718) ------------------ */
+enum aqgpu_scan_op {
+    AQ_SUMS = 0,    /* aggregations.h:203-210 */
+    AQ_AVGS = 1,    /* aggregations.h:219-228 */
+    AQ_MINS = 2,    /* aggregations.h:89-98   */
+    AQ_MAXS = 3,    /* aggregations.h:108-117 */
+    AQ_SUMW = 4,    /* aggregations.h:238-249 SQL sums(w, x) */
+    AQ_AVGW = 5,    /* aggregations.h:258-272 SQL avgs(w, x) */
+    AQ_MINW = 6,    /* aggregations.h:127-138 SQL mins(w, x) */
+    AQ_MAXW = 7,    /* aggregations.h:148-159 SQL maxs(w, x) */
+    AQ_DELTAS = 8,  /* aggregations.h:439-446 */
+    AQ_PREV = 9,    /* aggregations.h:455-462 */
+    AQ_NEXT = 10,   /* aggregations.h:471-478 (aggnext) */
+    AQ_RATIOW = 11  /* aggregations.h:169-184 ratios(x) == ratiow(1, x) */
+};
+
+/* Order of the rows inside a group's row list. */
+enum aqgpu_row_order {
+    AQ_ROWS_DESC = 0,  /* reference AQHashTable::ht_postproc (server/hasher.h:193-196): descending */
+    AQ_ROWS_ASC = 1    /* PerfectHashTable / legacy emplace_back(i) (hasher.h:292-295,
+                          common/groupby.py:42-46): ascending */
+};
+
+/* ---- context -------------------------------------------------------------------------------- */
+int aqgpu_abi_version(void);
+/* Binds the calling process to CUDA device `device`, creates the library stream and memory pool. */
+int aqgpu_init(int device);
+int aqgpu_shutdown(void);
+const char* aqgpu_last_error(void);
+/* Use `cuda_stream` (a cudaStream_t) for all subsequent work; NULL restores the library stream. */
+int aqgpu_set_stream(void* cuda_stream);
+int aqgpu_sync(void);
+/* Number of kernels this library has launched since aqgpu_init (bench.py's gpu_launches). */
+uint64_t aqgpu_launch_count(void);
+/* CUDA-event timing on the library stream: begin/end return elapsed milliseconds in *ms. */
+int aqgpu_timer_begin(void);
+int aqgpu_timer_end(float* ms);
+
+/* ---- HBM column store (replaces the malloc'ed / MonetDB-owned buffers ColRef points into:
+ *      server/table.h:96-103 ColRef(size, void*), server/monetdb_conn.cpp:203-224 getCol) -------- */
+int aqgpu_col_alloc(size_t bytes, void** dptr);
+int aqgpu_col_free(void* dptr);
+int aqgpu_col_upload(void* dptr, const void* host, size_t bytes);
+int aqgpu_col_download(void* host, const void* dptr, size_t bytes);
+int aqgpu_host_alloc(size_t bytes, void** hptr);      /* pinned host memory for staging */
+int aqgpu_host_free(void* hptr);
+
+/* ---- fused group-by + scalar aggregation -----------------------------------------------------
+ * Replaces, in one pass over the columns and without materialising row lists:
+ *   AQHashTable::hashtable_push per row     server/hasher.h:176-179
+ *   AQHashTable::ht_postproc                server/hasher.h:181-198   (only its observable order)
+ *   gather col[vecs[g]]                     server/table.h:184-189
+ *   agg(...) per group                      server/aggregations.h, loop at engine/ast.py:720-790
+ * Groups come out in FIRST-APPEARANCE order of their key tuple, as m_values does
+ * (server/unordered_dense.h:1142-1146).                                                        */
+typedef struct aqgpu_agg {
+    int op;            /* aqgpu_reduce_op */
+    int vtype;         /* dtype of v (and v2); ignored for AQ_COUNT */
+    const void* v;     /* value column, nrows elements (device or host) */
+    const void* v2;    /* second column of AQ_CORR, else NULL */
+    int out_type;      /* requested cell type; 0-initialised structs get the reference default via
+                          aqgpu_reduce_out_type(); AQ_INT64 is accepted for integer SUM */
+    void* out;         /* result column, room for max_groups cells (device or host) */
+} aqgpu_agg_t;
+
+int aqgpu_reduce_out_type(int op, int vtype);
+int aqgpu_scan_out_type(int op, int vtype);
+size_t aqgpu_dtype_size(int dtype);
+
+/*   keys[k]        key column k: nrows elements of key_types[k] (AQ_INT32, AQ_UINT32, AQ_INT64)
+ *   key_min/max    optional per-column inclusive bounds of the key values (both NULL = unknown): the
+ *                  column statistics the reference keeps in ColRef::stats (server/table.h:60-91) and
+ *                  HashTableFactory::get consults (server/hasher.h:335-343).  With bounds whose
+ *                  bit-widths sum to <= 32 the tuple is bit-packed like PerfectHashTable does
+ *                  (hasher.h:226-243); a key outside its bounds is detected and the call silently
+ *                  re-runs without them.  Output order is first-appearance either way.
+ *   row_order      aqgpu_row_order: decides what FIRST/LAST mean (reference: AQ_ROWS_DESC)
+ *   groups_hint    expected number of groups (table sizing); 0 = unknown (adaptive growth)
+ *   max_groups     capacity, in cells, of out_keys[k], out_first_row and aggs[a].out
+ *   out_keys[k]    key column k of the result, first-appearance order (may be NULL)
+ *   out_first_row  row id of each group's first appearance (may be NULL)
+ *   ngroups        host out
+ * Fails with a "capacity" error if the number of groups exceeds max_groups.                      */
+int aqgpu_groupby_agg(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                      const int64_t* key_min, const int64_t* key_max,
+                      int row_order, uint32_t groups_hint,
+                      const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
+                      void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups);
+
+/* ---- group handle: ids, row lists, per-group vectors ----------------------------------------
+ * aqgpu_groupby_build replaces HashTableFactory<...>::get(cols...) / AQHashTable (server/hasher.h:
+ * 146-199, 324-357): the handle is the HashTableComponents {size, keys, values, offsets}
+ * (server/hasher.h:201-207) kept in HBM.                                                         */
+typedef struct aqgpu_groups aqgpu_groups_t;
+
+int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                        const int64_t* key_min, const int64_t* key_max,
+                        int row_order, uint32_t groups_hint, aqgpu_groups_t** out);
+/* Inclusive [min, max] of an integer column (AQ_INT32, AQ_UINT32, AQ_INT64): ColRef::populate_stats
+ * (server/table.h:76-91).  One streaming pass; callers cache the result with the column. */
+int aqgpu_col_minmax(int dtype, const void* col, uint32_t nrows, int64_t* out_min, int64_t* out_max);
+int aqgpu_groups_free(aqgpu_groups_t* g);
+int aqgpu_groups_size(aqgpu_groups_t* g, uint32_t* ngroups);                 /* .size           */
+int aqgpu_groups_keys(aqgpu_groups_t* g, int k, void* out_keys);             /* .keys, column k */
+int aqgpu_groups_first_row(aqgpu_groups_t* g, uint32_t* out);
+int aqgpu_groups_gid(aqgpu_groups_t* g, uint32_t* out_gid);                  /* reversemap      */
+/* offsets[ngroups+1] (.offsets / ht_base + terminal) and perm[nrows] (mapbase, the storage all
+ * .values[g] views alias); either may be NULL. */
+int aqgpu_groups_csr(aqgpu_groups_t* g, uint32_t* out_offsets, uint32_t* out_perm);
+/* Device-resident views for callers that keep working on the GPU (NULL until first needed). */
+int aqgpu_groups_device_views(aqgpu_groups_t* g, const uint32_t** d_gid, const uint32_t** d_offsets,
+                              const uint32_t** d_perm);
+
+/* out[g] = op(v[rows of g])  -- server/aggregations.h scalar aggregates over col[vecs[g]]. */
+int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, const void* v2,
+                       int out_type, void* out);
+/* out[offsets[g] + j] = op(w, v[rows of g])[j]  -- running / windowed / neighbour aggregates in
+ * the CSR layout of engine/ast.py:696-718.  out has nrows cells of out_type. */
+int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const void* v,
+                     int out_type, void* out);
+/* ASSUMING-ordered evaluation for unsorted input (common/groupby.py:54-59 ->
+ * TableInfo::order_by, server/table.h:447-461): re-orders every group's row list by the given
+ * columns (desc[c] != 0 = descending), ties by the current order.  Integer / float keys. */
+int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int* col_types,
+                          const int* desc, int ncols);
+
+/* ---- element-wise helpers used by generated code around the aggregates ----------------------- */
+/* out[i] = a[i] - b[i] (same dtype); q7 max(v1) - min(v2) (server/table.h:820-973 vector arith). */
+int aqgpu_vec_sub(int dtype, const void* a, const void* b, void* out, uint32_t n);
+/* out[i] = sum[i] / double(count[i]): AVG finalisation after a multi-GPU merge. sum is AQ_INT64,
+ * AQ_INT128 or AQ_DOUBLE. */
+int aqgpu_avg_finalize(int sum_type, const void* sum, const uint32_t* count, double* out, uint32_t n);
+/* out[i] = pow(x[i], p) in fp64 (q9 pow(corr, 2); aggregations.h:409-411). */
+int aqgpu_vec_pow(const double* x, double p, double* out, uint32_t n);
+
+/* ---- synthetic column generators (bench / tests; same streams as aquery2_b200/synth.py) ------ */
+/* kind: 0 = 1+U[0,k) int32, 1 = U[0,k) int32, 2 = U[0,k)/1e6 as float32 (k = 1e8 gives
+ * round(U(0,100),6)), 3 = row+1 int32, 4 = trade price in [50,500] (key1 = symbol stream, key2 =
+ * per-symbol base key, k = number of symbols), 5 = aux_k + U[0,k) int32.
+ * Rows are GLOBAL ids [row_lo, row_lo+n); key0 = stream key of the column (synth.stream_key). */
+int aqgpu_synth_column(int kind, uint64_t key0, uint64_t key1, uint64_t key2, uint32_t k, uint32_t aux_k,
+                       uint64_t row_lo, uint32_t n, void* d_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AQGPU_H */

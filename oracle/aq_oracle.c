@@ -1,0 +1,317 @@
+/*
+ * aq_oracle.c -- plain-C restatement of AQuery++'s post-processor hot path (CPU oracle, "port").
+ *
+ * TEST INFRASTRUCTURE ONLY (see oracle/aqo.h): loaded by tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py, never by the product library.
+ *
+ * Parity status: PINNED.  tests/test_oracle_vs_ref.py checks every function below against
+ * oracle/_ref/libaqref.so (the reference's own headers compiled from /root/reference, see
+ * ref_harness.cpp) on seeded inputs, and tests/test_oracle_golden.py checks it against the fixtures
+ * under tests/golden/ that oracle/gen_golden.py generated with that reference build.  The reference's
+ * own tests hold no expected outputs for this path, so the reference build is
+ * the only possible anchor.
+ *
+ * Every function cites the reference lines it restates (paths relative to /root/reference).
+ */
+#define _POSIX_C_SOURCE 200809L
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <float.h>
+#include <limits.h>
+#include <time.h>
+#include "aqo.h"
+
+typedef __int128 i128;
+
+const char* aqo_kind(void) { return "port"; }
+
+/* ------------------------------------------------------------------------------------------------
+ * Group build.  server/hasher.h:176-179 (AQHashTable::hashtable_push) on top of
+ * server/unordered_dense.h:1117-1147: a key tuple not seen before is appended to m_values and its
+ * index (= number of distinct tuples seen so far) is the group id; reversemap[i] = gid;
+ * ++ht_base[gid].  The probing scheme (robin hood, wyhash) does not influence any output, so a plain
+ * linear-probing table keyed on a representative row is used here.
+ * ---------------------------------------------------------------------------------------------- */
+static inline uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ULL;
+    x ^= x >> 27; x *= 0x94d049bb133111ebULL;
+    return x ^ (x >> 31);
+}
+
+static inline uint64_t key_at(const void* col, int type, uint32_t i) {
+    return type == AQO_INT64 ? (uint64_t)((const int64_t*)col)[i]
+                             : (uint64_t)(int64_t)((const int32_t*)col)[i];
+}
+
+int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                uint32_t* ngroups, uint32_t* gid_out, uint32_t* offsets, uint32_t* perm) {
+    if (nkeys < 1 || nkeys > 16) return -2;
+    for (int k = 0; k < nkeys; ++k)
+        if (key_types[k] != AQO_INT32 && key_types[k] != AQO_INT64) return -2;
+    if (nrows == 0) { *ngroups = 0; if (offsets) offsets[0] = 0; return 0; }
+
+    uint64_t cap = 16;
+    while (cap < (uint64_t)nrows * 2) cap <<= 1;
+    const uint64_t mask = cap - 1;
+    uint32_t* slot_gid = (uint32_t*)malloc(cap * sizeof(uint32_t));     /* 0xffffffff = empty */
+    uint32_t* rep_row = (uint32_t*)malloc((size_t)nrows * sizeof(uint32_t)); /* gid -> first row */
+    uint32_t* gid = gid_out ? gid_out : (uint32_t*)malloc((size_t)nrows * sizeof(uint32_t));
+    uint32_t* count = (uint32_t*)calloc((size_t)nrows + 1, sizeof(uint32_t));  /* hasher.h:157 ht_base */
+    if (!slot_gid || !rep_row || !gid || !count) return -1;
+    memset(slot_gid, 0xff, cap * sizeof(uint32_t));
+
+    uint32_t ng = 0;
+    for (uint32_t i = 0; i < nrows; ++i) {
+        uint64_t h = 0x9e3779b97f4a7c15ULL;
+        for (int k = 0; k < nkeys; ++k) h = mix64(h ^ key_at(keys[k], key_types[k], i));
+        uint64_t s = h & mask;
+        uint32_t g;
+        for (;;) {
+            g = slot_gid[s];
+            if (g == 0xffffffffu) {                 /* unseen tuple: next dense id (unordered_dense.h:1142-1146) */
+                g = ng++;
+                slot_gid[s] = g;
+                rep_row[g] = i;
+                break;
+            }
+            const uint32_t r = rep_row[g];
+            int eq = 1;
+            for (int k = 0; k < nkeys && eq; ++k)
+                eq = key_at(keys[k], key_types[k], i) == key_at(keys[k], key_types[k], r);
+            if (eq) break;
+            s = (s + 1) & mask;
+        }
+        gid[i] = g;                                 /* hasher.h:177 */
+        ++count[g];                                 /* hasher.h:178 */
+    }
+    *ngroups = ng;
+
+    /* ht_postproc, server/hasher.h:181-198: inclusive prefix sum of the counts, then
+     * mapbase[--ht_base[gid]] = i for ascending i, i.e. every group's row list ends up in
+     * DESCENDING row order and ht_base[g] ends as the start offset of group g. */
+    if (offsets || perm) {
+        for (uint32_t g = 1; g < ng; ++g) count[g] += count[g - 1];            /* hasher.h:188-191 */
+        if (perm) {
+            for (uint32_t i = 0; i < nrows; ++i) perm[--count[gid[i]]] = i;    /* hasher.h:193-196 */
+        } else {                                   /* caller wants offsets only: inclusive -> exclusive */
+            for (uint32_t g = ng; g-- > 1;) count[g] = count[g - 1];
+            count[0] = 0;
+        }
+        if (offsets) {
+            for (uint32_t g = 0; g < ng; ++g) offsets[g] = count[g];
+            offsets[ng] = nrows;
+        }
+    }
+    free(slot_gid); free(rep_row); free(count);
+    if (!gid_out) free(gid);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Result types.  server/types.h:199-210: GetLongType (signed int -> __int128, fp -> double),
+ * GetFPType (4-byte -> float, else double); avg is always double (aggregations.h:30).
+ * ---------------------------------------------------------------------------------------------- */
+static int is_int(int t) { return t == AQO_INT32 || t == AQO_INT64; }
+static int is_val(int t) { return is_int(t) || t == AQO_FLOAT || t == AQO_DOUBLE; }
+
+int aqo_reduce_out_type(int op, int vtype) {
+    if (!is_val(vtype)) return -2;
+    switch (op) {
+    case AQO_SUM: return is_int(vtype) ? AQO_INT128 : AQO_DOUBLE;
+    case AQO_AVG: case AQO_VAR: case AQO_STDDEV: case AQO_CORR: return AQO_DOUBLE;
+    case AQO_MIN: case AQO_MAX: case AQO_FIRST: case AQO_LAST: return vtype;
+    case AQO_COUNT: return AQO_UINT32;
+    default: return -2;
+    }
+}
+int aqo_scan_out_type(int op, int vtype) {
+    if (!is_val(vtype)) return -2;
+    switch (op) {
+    case AQO_SUMS: case AQO_SUMW: return is_int(vtype) ? AQO_INT128 : AQO_DOUBLE;
+    case AQO_AVGS: case AQO_AVGW: return AQO_DOUBLE;
+    case AQO_RATIOW: return (vtype == AQO_INT32 || vtype == AQO_FLOAT) ? AQO_FLOAT : AQO_DOUBLE;
+    case AQO_MINS: case AQO_MAXS: case AQO_MINW: case AQO_MAXW:
+    case AQO_DELTAS: case AQO_PREV: case AQO_NEXT: return vtype;
+    default: return -2;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Per-type kernels.  GEN(T, L, FP, TMIN, TMAX, SFX):
+ *   T = element type, L = GetLongType<T>, FP = GetFPType<T> (ratios), TMIN = numeric_limits<T>::min()
+ *   (for floating point that is the smallest POSITIVE normal -- the reference's max/maxs start there,
+ *   aggregations.h:73,111, so all-negative fp input yields 2.2e-308/1.2e-38; kept on purpose).
+ * `a` below is the gathered vector col[vecs[g]] (server/table.h:184-189): a[j] = v[rows[j]].
+ * ---------------------------------------------------------------------------------------------- */
+#define GEN(T, L, FP, TMIN, TMAX, SFX)                                                              \
+/* aggregations.h:19-27 */                                                                          \
+static L sum_##SFX(const T* v, const uint32_t* r, uint32_t n) {                                     \
+    L s = 0; for (uint32_t j = 0; j < n; ++j) s += v[r[j]]; return s; }                             \
+/* aggregations.h:28-32 */                                                                          \
+static double avg_##SFX(const T* v, const uint32_t* r, uint32_t n) {                                \
+    return sum_##SFX(v, r, n) / (double)n; }                                                        \
+/* aggregations.h:71-78 */                                                                          \
+static T max_##SFX(const T* v, const uint32_t* r, uint32_t n) {                                     \
+    T m = TMIN; for (uint32_t j = 0; j < n; ++j) m = m > v[r[j]] ? m : v[r[j]]; return m; }         \
+/* aggregations.h:79-86 */                                                                          \
+static T min_##SFX(const T* v, const uint32_t* r, uint32_t n) {                                     \
+    T m = TMAX; for (uint32_t j = 0; j < n; ++j) m = m < v[r[j]] ? m : v[r[j]]; return m; }         \
+/* aggregations.h:332-348 (divides by len+1; kept) */                                               \
+static double var_##SFX(const T* v, const uint32_t* r, uint32_t n) {                                \
+    L s = 0, ssq = 0;                                                                               \
+    if (n) { s = v[r[0]]; ssq = v[r[0]] * v[r[0]]; }                                                \
+    for (uint32_t j = 1; j < n; ++j) { s += v[r[j]]; ssq += v[r[j]] * v[r[j]]; }                    \
+    return (ssq - s * s / (double)(n + 1)) / (double)(n + 1); }                                     \
+/* aggregations.h:383-407.  `types::Coercion<...>` is used there without ::type, so InnerType is a  \
+ * struct, GetLongType of it is __int128 and ALL five sums are __int128 for every input type: fp     \
+ * inputs are truncated at each `+=` (usual arithmetic conversions, then back to __int128). */      \
+static double corr_##SFX(const T* x, const T* y, const uint32_t* r, uint32_t n) {                   \
+    i128 sx = 0, sy = 0, sxy = 0, sx2 = 0, sy2 = 0;                                                 \
+    for (uint32_t j = 0; j < n; ++j) {                                                              \
+        const T a = x[r[j]], b = y[r[j]];                                                           \
+        sx += a; sx2 += a * a; sy += b; sxy += a * b; sy2 += b * b; }                               \
+    return (n * sxy - (double)(sx * sy)) /                                                          \
+           sqrt((n * sx2 - (double)(sx * sx)) * (n * sy2 - (double)(sy * sy))); }                   \
+static int reduce_##SFX(int op, const T* v, const T* v2, uint32_t ng, const uint32_t* off,          \
+                        const uint32_t* perm, void* out) {                                          \
+    for (uint32_t g = 0; g < ng; ++g) {                                                             \
+        const uint32_t* r = perm + off[g]; const uint32_t n = off[g + 1] - off[g];                  \
+        switch (op) {                                                                               \
+        case AQO_SUM: ((L*)out)[g] = sum_##SFX(v, r, n); break;                                     \
+        case AQO_AVG: ((double*)out)[g] = avg_##SFX(v, r, n); break;                                \
+        case AQO_MIN: ((T*)out)[g] = min_##SFX(v, r, n); break;                                     \
+        case AQO_MAX: ((T*)out)[g] = max_##SFX(v, r, n); break;                                     \
+        case AQO_FIRST: ((T*)out)[g] = n ? v[r[0]] : 0; break;        /* aggregations.h:493-497 */  \
+        case AQO_LAST: ((T*)out)[g] = n ? v[r[n - 1]] : 0; break;     /* aggregations.h:487-491 */  \
+        case AQO_VAR: ((double*)out)[g] = var_##SFX(v, r, n); break;                                \
+        case AQO_STDDEV: ((double*)out)[g] = sqrt(var_##SFX(v, r, n)); break; /* :413-415 */        \
+        case AQO_CORR: ((double*)out)[g] = corr_##SFX(v, v2, r, n); break;                          \
+        default: return -2; } }                                                                     \
+    return 0; }                                                                                     \
+/* sliding min/max keep a monotonic deque of (value, index), aggregations.h:127-167; the window is   \
+ * the last w elements because the front is dropped when its index equals i - w. */                 \
+static void minmaxw_##SFX(int is_max, uint32_t w, const T* v, const uint32_t* r, uint32_t n, T* ret, \
+                          T* dq_v, uint32_t* dq_i) {                                                \
+    uint32_t head = 0, tail = 0;                                                                    \
+    for (uint32_t i = 0; i < n; ++i) {                                                              \
+        const T x = v[r[i]];                                                                        \
+        if (tail > head && dq_i[head] == i - w) ++head;                                             \
+        if (is_max) while (tail > head && dq_v[tail - 1] < x) --tail;                               \
+        else        while (tail > head && dq_v[tail - 1] > x) --tail;                               \
+        dq_v[tail] = x; dq_i[tail] = i; ++tail;                                                     \
+        ret[i] = dq_v[head]; } }                                                                    \
+static int scan_##SFX(int op, uint32_t w0, const T* v, uint32_t ng, const uint32_t* off,            \
+                      const uint32_t* perm, void* out) {                                            \
+    uint32_t maxn = 0;                                                                              \
+    for (uint32_t g = 0; g < ng; ++g) if (off[g + 1] - off[g] > maxn) maxn = off[g + 1] - off[g];   \
+    T* dq_v = NULL; uint32_t* dq_i = NULL;                                                          \
+    if (op == AQO_MINW || op == AQO_MAXW) {                                                         \
+        dq_v = (T*)malloc(sizeof(T) * (maxn + 1)); dq_i = (uint32_t*)malloc(4 * ((size_t)maxn + 1)); } \
+    for (uint32_t g = 0; g < ng; ++g) {                                                             \
+        const uint32_t* r = perm + off[g]; const uint32_t n = off[g + 1] - off[g];                  \
+        const size_t o = off[g]; uint32_t w = w0;                                                   \
+        switch (op) {                                                                               \
+        case AQO_SUMS: { L* ret = (L*)out + o;                       /* aggregations.h:203-210 */   \
+            if (n) ret[0] = v[r[0]];                                                                \
+            for (uint32_t i = 1; i < n; ++i) ret[i] = ret[i - 1] + v[r[i]]; } break;                \
+        case AQO_AVGS: { double* ret = (double*)out + o; L s = 0;    /* aggregations.h:219-228 */   \
+            if (n) { s = v[r[0]]; ret[0] = v[r[0]]; }                                               \
+            for (uint32_t i = 1; i < n; ++i) ret[i] = (s += v[r[i]]) / (double)(i + 1); } break;    \
+        case AQO_MINS: { T* ret = (T*)out + o; T m = TMAX;           /* aggregations.h:89-98 */     \
+            for (uint32_t i = 0; i < n; ++i) { if (v[r[i]] < m) m = v[r[i]]; ret[i] = m; } } break; \
+        case AQO_MAXS: { T* ret = (T*)out + o; T m = TMIN;           /* aggregations.h:108-117 */   \
+            for (uint32_t i = 0; i < n; ++i) { if (v[r[i]] > m) m = v[r[i]]; ret[i] = m; } } break; \
+        case AQO_SUMW: { L* ret = (L*)out + o;                       /* aggregations.h:238-249 */   \
+            w = w > n ? n : w;                                                                      \
+            if (n) ret[0] = v[r[0]];                                                                \
+            for (uint32_t i = 1; i < w; ++i) ret[i] = ret[i - 1] + v[r[i]];                         \
+            for (uint32_t i = w; i < n; ++i) ret[i] = ret[i - 1] + v[r[i]] - v[r[i - w]]; } break;  \
+        case AQO_AVGW: { double* ret = (double*)out + o; L s = 0;    /* aggregations.h:258-272 */   \
+            w = w > n ? n : w;                                                                      \
+            if (n) { s = v[r[0]]; ret[0] = v[r[0]]; }                                               \
+            for (uint32_t i = 1; i < w; ++i) ret[i] = (s += v[r[i]]) / (double)(i + 1);             \
+            for (uint32_t i = w; i < n; ++i)                                                        \
+                ret[i] = ret[i - 1] + (v[r[i]] - v[r[i - w]]) / (double)w; } break;                 \
+        case AQO_MINW: minmaxw_##SFX(0, w, v, r, n, (T*)out + o, dq_v, dq_i); break;                \
+        case AQO_MAXW: minmaxw_##SFX(1, w, v, r, n, (T*)out + o, dq_v, dq_i); break;                \
+        case AQO_DELTAS: { T* ret = (T*)out + o;                     /* aggregations.h:439-446 */   \
+            if (n) ret[0] = 0;                                                                      \
+            for (uint32_t i = 1; i < n; ++i) ret[i] = v[r[i]] - v[r[i - 1]]; } break;               \
+        case AQO_PREV: { T* ret = (T*)out + o;                       /* aggregations.h:455-462 */   \
+            if (n) ret[0] = v[r[0]];                                                                \
+            for (uint32_t i = 1; i < n; ++i) ret[i] = v[r[i - 1]]; } break;                         \
+        case AQO_NEXT: { T* ret = (T*)out + o;                       /* aggregations.h:471-478 */   \
+            for (uint32_t i = 1; i < n; ++i) ret[i - 1] = v[r[i]];                                  \
+            if (n) ret[n - 1] = v[r[n - 1]]; } break;                                               \
+        case AQO_RATIOW: { FP* ret = (FP*)out + o;                   /* aggregations.h:169-184 */   \
+            uint32_t len = n; if (n <= w) len = 1;                                                  \
+            w = w > len ? len : w;                                                                  \
+            if (n) ret[0] = 0;                                                                      \
+            for (uint32_t i = 0; i < w && i < n; ++i) ret[i] = v[r[i]] / (FP)v[r[0]];               \
+            for (uint32_t i = w; i < n; ++i) ret[i] = v[r[i]] / (FP)v[r[i - w]]; } break;           \
+        default: free(dq_v); free(dq_i); return -2; } }                                             \
+    free(dq_v); free(dq_i);                                                                         \
+    return 0; }
+
+GEN(int32_t, i128, float, INT32_MIN, INT32_MAX, i32)
+GEN(int64_t, i128, double, INT64_MIN, INT64_MAX, i64)
+GEN(float, double, float, FLT_MIN, FLT_MAX, f32)
+GEN(double, double, double, DBL_MIN, DBL_MAX, f64)
+
+int aqo_reduce(int op, int vtype, const void* v, const void* v2,
+               uint32_t ngroups, const uint32_t* offsets, const uint32_t* perm, void* out) {
+    if (op == AQO_COUNT) {                     /* engine/ast.py:763: count(*) is emitted as val.size */
+        for (uint32_t g = 0; g < ngroups; ++g) ((uint32_t*)out)[g] = offsets[g + 1] - offsets[g];
+        return 0;
+    }
+    switch (vtype) {
+    case AQO_INT32: return reduce_i32(op, (const int32_t*)v, (const int32_t*)v2, ngroups, offsets, perm, out);
+    case AQO_INT64: return reduce_i64(op, (const int64_t*)v, (const int64_t*)v2, ngroups, offsets, perm, out);
+    case AQO_FLOAT: return reduce_f32(op, (const float*)v, (const float*)v2, ngroups, offsets, perm, out);
+    case AQO_DOUBLE: return reduce_f64(op, (const double*)v, (const double*)v2, ngroups, offsets, perm, out);
+    default: return -2;
+    }
+}
+
+int aqo_scan(int op, uint32_t w, int vtype, const void* v,
+             uint32_t ngroups, const uint32_t* offsets, const uint32_t* perm, void* out) {
+    if ((op == AQO_SUMW || op == AQO_AVGW || op == AQO_MINW || op == AQO_MAXW || op == AQO_RATIOW) && w == 0)
+        return -2;                             /* the reference indexes ret[-1] for w == 0 */
+    switch (vtype) {
+    case AQO_INT32: return scan_i32(op, w, (const int32_t*)v, ngroups, offsets, perm, out);
+    case AQO_INT64: return scan_i64(op, w, (const int64_t*)v, ngroups, offsets, perm, out);
+    case AQO_FLOAT: return scan_f32(op, w, (const float*)v, ngroups, offsets, perm, out);
+    case AQO_DOUBLE: return scan_f64(op, w, (const double*)v, ngroups, offsets, perm, out);
+    default: return -2;
+    }
+}
+
+/* The reference's `postproc_time` bracket (server/server.cpp:303-305): hash build + row lists +
+ * per-group aggregation, single thread, as the generated code runs them. */
+int64_t aqo_time_groupby_reduce(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                                int n_aggs, const int* ops, const int* vtypes,
+                                const void* const* vals, const void* const* vals2,
+                                void* const* outs, uint32_t* ngroups) {
+    uint32_t* gid = (uint32_t*)malloc(sizeof(uint32_t) * ((size_t)nrows * 3 + 2));
+    if (!gid) return -1;
+    uint32_t* perm = gid + nrows;
+    uint32_t* offsets = perm + nrows;
+    void** tmp = (void**)calloc(n_aggs ? n_aggs : 1, sizeof(void*));
+    for (int a = 0; a < n_aggs; ++a)
+        if (!outs || !outs[a]) tmp[a] = malloc((size_t)(nrows ? nrows : 1) * 16);
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    uint32_t ng = 0;
+    int rc = aqo_groupby(keys, key_types, nkeys, nrows, &ng, gid, offsets, perm);
+    for (int a = 0; rc == 0 && a < n_aggs; ++a)
+        rc = aqo_reduce(ops[a], vtypes[a], vals[a], vals2 ? vals2[a] : NULL, ng, offsets, perm,
+                        tmp[a] ? tmp[a] : outs[a]);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    for (int a = 0; a < n_aggs; ++a) free(tmp[a]);
+    free(tmp); free(gid);
+    if (ngroups) *ngroups = ng;
+    if (rc) return rc;
+    return (int64_t)(t1.tv_sec - t0.tv_sec) * 1000000000LL + (t1.tv_nsec - t0.tv_nsec);
+}

@@ -1,0 +1,177 @@
+"""ctypes binding of the CPU oracles declared in oracle/aqo.h.
+
+TEST INFRASTRUCTURE ONLY.  Import this from tests/, from __graft_entry__.smoke() and from the
+cpu_baseline / ``--impl reference`` legs of bench.py -- never from aquery2_b200/ (the product has no
+CPU path and fails loudly when its CUDA library is missing).
+
+Two libraries export the same symbols:
+  * ``oracle/_ref/libaqref.so``  -- kind "reference": the reference's own C++ headers
+    (server/hasher.h, server/table.h, server/aggregations.h) compiled by oracle/Makefile;
+  * ``oracle/libaqoracle.so``    -- kind "port": the plain-C restatement aq_oracle.c.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_LIB = os.path.join(HERE, "_ref", "libaqref.so")
+PORT_LIB = os.path.join(HERE, "libaqoracle.so")
+
+# dtype codes = reference types::Type_t (server/aquery_types.h:1-5)
+INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
+# aqo_reduce_op
+SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR = range(10)
+# aqo_scan_op
+SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
+
+REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
+                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR}
+SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
+              "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
+              "ratiow": RATIOW}
+
+_NP2CODE = {np.dtype(np.int32): INT32, np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE,
+            np.dtype(np.int64): INT64, np.dtype(np.uint32): UINT32}
+_CODE2NP = {INT32: np.int32, FLOAT: np.float32, DOUBLE: np.float64, INT64: np.int64,
+            UINT32: np.uint32}
+
+
+def build(which: str = "all") -> None:
+    """Run oracle/Makefile (``port``, ``ref`` or ``all``).  Building the checker is not using it."""
+    subprocess.run(["make", "-s", "-C", HERE, which], check=True)
+
+
+def i128_to_int64(cells: np.ndarray) -> np.ndarray:
+    """(n,2) int64 [lo, hi] little-endian __int128 cells -> int64, asserting they fit."""
+    cells = cells.reshape(-1, 2)
+    lo, hi = cells[:, 0], cells[:, 1]
+    if not np.array_equal(hi, lo >> 63):
+        raise OverflowError("__int128 result does not fit in int64")
+    return lo.copy()
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Oracle:
+    def __init__(self, path: str):
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.path = path
+        L = self.lib = ctypes.CDLL(path)
+        L.aqo_kind.restype = ctypes.c_char_p
+        L.aqo_groupby.restype = ctypes.c_int
+        L.aqo_reduce.restype = ctypes.c_int
+        L.aqo_scan.restype = ctypes.c_int
+        L.aqo_reduce_out_type.restype = ctypes.c_int
+        L.aqo_scan_out_type.restype = ctypes.c_int
+        L.aqo_time_groupby_reduce.restype = ctypes.c_int64
+        self.kind = L.aqo_kind().decode()
+
+    # -- A1 + A2 -----------------------------------------------------------------------------
+    def groupby(self, keys):
+        keys = [np.ascontiguousarray(k) for k in keys]
+        n = len(keys[0])
+        kp = (ctypes.c_void_p * len(keys))(*[k.ctypes.data for k in keys])
+        kt = (ctypes.c_int * len(keys))(*[_NP2CODE[k.dtype] for k in keys])
+        ng = ctypes.c_uint32(0)
+        gid = np.empty(n, np.uint32)
+        offsets = np.empty(n + 1, np.uint32)
+        perm = np.empty(n, np.uint32)
+        rc = self.lib.aqo_groupby(kp, kt, len(keys), ctypes.c_uint32(n), ctypes.byref(ng),
+                                  _ptr(gid), _ptr(offsets), _ptr(perm))
+        if rc != 0:
+            raise RuntimeError(f"aqo_groupby rc={rc}")
+        return ng.value, gid, offsets[: ng.value + 1].copy(), perm
+
+    # -- A5 / A9 -----------------------------------------------------------------------------
+    def reduce(self, op, v, offsets, perm, v2=None, raw128=False):
+        if isinstance(op, str):
+            op = REDUCE_NAMES[op]
+        ng = len(offsets) - 1
+        if op == COUNT:
+            vt = INT32
+        else:
+            v = np.ascontiguousarray(v)
+            vt = _NP2CODE[v.dtype]
+        ot = self.lib.aqo_reduce_out_type(op, vt)
+        if ot < 0:
+            raise RuntimeError(f"unsupported reduce op={op} vtype={vt}")
+        out = np.zeros((ng, 2), np.int64) if ot == INT128 else np.zeros(ng, _CODE2NP[ot])
+        if v2 is not None:
+            v2 = np.ascontiguousarray(v2)
+        rc = self.lib.aqo_reduce(op, vt, _ptr(v) if op != COUNT else None, _ptr(v2),
+                                 ctypes.c_uint32(ng), _ptr(offsets), _ptr(perm), _ptr(out))
+        if rc != 0:
+            raise RuntimeError(f"aqo_reduce rc={rc}")
+        if ot == INT128 and not raw128:
+            return i128_to_int64(out)
+        return out
+
+    # -- A6 / A7 / A8 ------------------------------------------------------------------------
+    def scan(self, op, v, offsets, perm, w=0, raw128=False):
+        if isinstance(op, str):
+            op = SCAN_NAMES[op]
+        v = np.ascontiguousarray(v)
+        vt = _NP2CODE[v.dtype]
+        ng = len(offsets) - 1
+        n = int(offsets[-1]) if ng >= 0 and len(offsets) else 0
+        ot = self.lib.aqo_scan_out_type(op, vt)
+        if ot < 0:
+            raise RuntimeError(f"unsupported scan op={op} vtype={vt}")
+        out = np.zeros((n, 2), np.int64) if ot == INT128 else np.zeros(n, _CODE2NP[ot])
+        rc = self.lib.aqo_scan(op, ctypes.c_uint32(w), vt, _ptr(v), ctypes.c_uint32(ng),
+                               _ptr(offsets), _ptr(perm), _ptr(out))
+        if rc != 0:
+            raise RuntimeError(f"aqo_scan rc={rc}")
+        if ot == INT128 and not raw128:
+            return i128_to_int64(out)
+        return out
+
+    # -- the postproc_time bracket -----------------------------------------------------------
+    def time_groupby_reduce(self, keys, aggs):
+        """aggs: list of (op, v[, v2]).  Returns (seconds, ngroups)."""
+        keys = [np.ascontiguousarray(k) for k in keys]
+        n = len(keys[0])
+        kp = (ctypes.c_void_p * len(keys))(*[k.ctypes.data for k in keys])
+        kt = (ctypes.c_int * len(keys))(*[_NP2CODE[k.dtype] for k in keys])
+        na = len(aggs)
+        ops = (ctypes.c_int * max(na, 1))()
+        vts = (ctypes.c_int * max(na, 1))()
+        vals = (ctypes.c_void_p * max(na, 1))()
+        vals2 = (ctypes.c_void_p * max(na, 1))()
+        keep = []
+        for a, agg in enumerate(aggs):
+            op = REDUCE_NAMES[agg[0]] if isinstance(agg[0], str) else agg[0]
+            ops[a] = op
+            if op == COUNT:
+                vts[a] = INT32
+                continue
+            v = np.ascontiguousarray(agg[1]); keep.append(v)
+            vts[a] = _NP2CODE[v.dtype]
+            vals[a] = v.ctypes.data
+            if len(agg) > 2 and agg[2] is not None:
+                v2 = np.ascontiguousarray(agg[2]); keep.append(v2)
+                vals2[a] = v2.ctypes.data
+        ng = ctypes.c_uint32(0)
+        ns = self.lib.aqo_time_groupby_reduce(kp, kt, len(keys), ctypes.c_uint32(n), na, ops, vts,
+                                              vals, vals2, None, ctypes.byref(ng))
+        if ns < 0:
+            raise RuntimeError(f"aqo_time_groupby_reduce rc={ns}")
+        return ns * 1e-9, ng.value
+
+
+def load_port(build_if_missing: bool = True) -> Oracle:
+    if not os.path.exists(PORT_LIB) and build_if_missing:
+        build("port")
+    return Oracle(PORT_LIB)
+
+
+def load_ref() -> Oracle | None:
+    """The reference-built oracle, or None when it has not been built (no /root/reference)."""
+    return Oracle(REF_LIB) if os.path.exists(REF_LIB) else None

@@ -1,0 +1,389 @@
+"""ctypes binding of libaqgpu.so (include/aqgpu.h) -- plumbing for tests, bench.py and smoke().
+
+The product is the C-ABI library plus the C++ drop-in headers under aquery2_b200/host/; this module
+only marshals numpy arrays / device columns into the plain-pointer calls.  There is NO CPU fallback:
+importing works anywhere, but every compute call fails loudly when the library or a CUDA device is
+missing.  Nothing here imports or calls oracle/.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libaqgpu.so")
+
+# dtype codes = reference types::Type_t (server/aquery_types.h:1-5)
+INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
+SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND = range(11)
+SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
+ROWS_DESC, ROWS_ASC = 0, 1
+
+REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
+                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR, "second": SECOND}
+SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
+              "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
+              "ratiow": RATIOW}
+
+NP2CODE = {np.dtype(np.int32): INT32, np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE,
+           np.dtype(np.int64): INT64, np.dtype(np.uint32): UINT32}
+CODE2NP = {INT32: np.dtype(np.int32), FLOAT: np.dtype(np.float32), DOUBLE: np.dtype(np.float64),
+           INT64: np.dtype(np.int64), UINT32: np.dtype(np.uint32)}
+CODE_SIZE = {INT32: 4, FLOAT: 4, DOUBLE: 8, INT64: 8, INT128: 16, UINT32: 4}
+
+EXPORTS = [
+    "aqgpu_abi_version", "aqgpu_init", "aqgpu_shutdown", "aqgpu_last_error", "aqgpu_set_stream",
+    "aqgpu_sync", "aqgpu_launch_count", "aqgpu_timer_begin", "aqgpu_timer_end",
+    "aqgpu_profile_enable", "aqgpu_profile_tag", "aqgpu_profile_report",
+    "aqgpu_col_alloc", "aqgpu_col_free", "aqgpu_col_upload", "aqgpu_col_download",
+    "aqgpu_host_alloc", "aqgpu_host_free",
+    "aqgpu_reduce_out_type", "aqgpu_scan_out_type", "aqgpu_dtype_size",
+    "aqgpu_groupby_agg", "aqgpu_groupby_build", "aqgpu_col_minmax", "aqgpu_groups_free",
+    "aqgpu_groups_size", "aqgpu_groups_keys", "aqgpu_groups_first_row", "aqgpu_groups_gid",
+    "aqgpu_groups_csr", "aqgpu_groups_device_views", "aqgpu_group_reduce", "aqgpu_group_scan",
+    "aqgpu_groups_order_by", "aqgpu_vec_sub", "aqgpu_avg_finalize", "aqgpu_vec_pow",
+    "aqgpu_synth_column",
+]
+
+
+class AqgpuError(RuntimeError):
+    pass
+
+
+class AggSpec(ctypes.Structure):
+    """struct aqgpu_agg (include/aqgpu.h)."""
+    _fields_ = [("op", ctypes.c_int), ("vtype", ctypes.c_int), ("v", ctypes.c_void_p),
+                ("v2", ctypes.c_void_p), ("out_type", ctypes.c_int), ("out", ctypes.c_void_p)]
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """The loaded C-ABI library.  Raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise AqgpuError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(or make -C aquery2_b200/csrc). libaqgpu has no CPU fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        L.aqgpu_last_error.restype = ctypes.c_char_p
+        L.aqgpu_launch_count.restype = ctypes.c_uint64
+        L.aqgpu_dtype_size.restype = ctypes.c_size_t
+        for name in EXPORTS:
+            getattr(L, name)              # AttributeError here = header/library mismatch
+        _lib = L
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise AqgpuError(lib().aqgpu_last_error().decode(errors="replace"))
+
+
+def init(device: int = -1) -> None:
+    check(lib().aqgpu_init(device))
+
+
+def sync() -> None:
+    check(lib().aqgpu_sync())
+
+
+def launch_count() -> int:
+    return int(lib().aqgpu_launch_count())
+
+
+def set_stream(cuda_stream_handle: int | None) -> None:
+    check(lib().aqgpu_set_stream(ctypes.c_void_p(cuda_stream_handle or 0)))
+
+
+def timer_begin() -> None:
+    check(lib().aqgpu_timer_begin())
+
+
+def timer_end() -> float:
+    ms = ctypes.c_float(0)
+    check(lib().aqgpu_timer_end(ctypes.byref(ms)))
+    return float(ms.value)
+
+
+def profile_enable(on: bool) -> None:
+    check(lib().aqgpu_profile_enable(int(on)))
+
+
+def profile_tag(tag: str) -> None:
+    check(lib().aqgpu_profile_tag(tag.encode()))
+
+
+def profile_report() -> dict[str, tuple[int, float]]:
+    """{"tag:kernel": (calls, total_ms)} since the last report (synchronises the stream)."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    check(lib().aqgpu_profile_report(buf, ctypes.c_size_t(len(buf))))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, calls, ms = line.rsplit("\t", 2)
+        out[name] = (int(calls), float(ms))
+    return out
+
+
+class DeviceColumn:
+    """One HBM-resident column of the column store (what a device ColRef::container points at)."""
+
+    def __init__(self, n: int, code: int):
+        self.n, self.code = int(n), int(code)
+        self.itemsize = CODE_SIZE[code]
+        p = ctypes.c_void_p(0)
+        check(lib().aqgpu_col_alloc(ctypes.c_size_t(max(self.nbytes, 16)), ctypes.byref(p)))
+        self.ptr = p.value
+
+    @property
+    def nbytes(self) -> int:
+        return self.n * self.itemsize
+
+    @classmethod
+    def from_numpy(cls, a: np.ndarray) -> "DeviceColumn":
+        a = np.ascontiguousarray(a)
+        if a.ndim == 2 and a.shape[1] == 2 and a.dtype == np.int64:
+            c = cls(a.shape[0], INT128)
+        else:
+            c = cls(a.size, NP2CODE[a.dtype])
+        if c.nbytes:
+            check(lib().aqgpu_col_upload(ctypes.c_void_p(c.ptr), a.ctypes.data_as(ctypes.c_void_p),
+                                         ctypes.c_size_t(c.nbytes)))
+        return c
+
+    def upload(self, a: np.ndarray) -> None:
+        a = np.ascontiguousarray(a)
+        assert a.nbytes <= self.nbytes
+        check(lib().aqgpu_col_upload(ctypes.c_void_p(self.ptr), a.ctypes.data_as(ctypes.c_void_p),
+                                     ctypes.c_size_t(a.nbytes)))
+
+    def numpy(self, n: int | None = None) -> np.ndarray:
+        n = self.n if n is None else int(n)
+        out = np.empty((n, 2), np.int64) if self.code == INT128 else np.empty(n, CODE2NP[self.code])
+        if n:
+            check(lib().aqgpu_col_download(out.ctypes.data_as(ctypes.c_void_p), ctypes.c_void_p(self.ptr),
+                                           ctypes.c_size_t(n * self.itemsize)))
+        return out
+
+    def free(self) -> None:
+        if getattr(self, "ptr", None):
+            lib().aqgpu_col_free(ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def _col(x):
+    """(pointer, dtype code, keepalive) of a numpy array or DeviceColumn."""
+    if isinstance(x, DeviceColumn):
+        return x.ptr, x.code, x
+    a = np.ascontiguousarray(x)
+    return a.ctypes.data, NP2CODE[a.dtype], a
+
+
+def _out_buf(code: int, n: int, device: bool):
+    if device:
+        return DeviceColumn(n, code)
+    return np.zeros((n, 2), np.int64) if code == INT128 else np.zeros(n, CODE2NP[code])
+
+
+def _out_ptr(b):
+    return b.ptr if isinstance(b, DeviceColumn) else b.ctypes.data
+
+
+def i128_to_int64(cells: np.ndarray) -> np.ndarray:
+    cells = cells.reshape(-1, 2)
+    lo, hi = cells[:, 0], cells[:, 1]
+    if not np.array_equal(hi, lo >> 63):
+        raise OverflowError("__int128 result does not fit in int64")
+    return lo.copy()
+
+
+def reduce_out_type(op: int, vtype: int) -> int:
+    return int(lib().aqgpu_reduce_out_type(op, vtype))
+
+
+def scan_out_type(op: int, vtype: int) -> int:
+    return int(lib().aqgpu_scan_out_type(op, vtype))
+
+
+def col_minmax(col) -> tuple[int, int]:
+    p, code, keep = _col(col)
+    n = col.n if isinstance(col, DeviceColumn) else keep.size
+    lo, hi = ctypes.c_int64(0), ctypes.c_int64(0)
+    check(lib().aqgpu_col_minmax(code, ctypes.c_void_p(p), ctypes.c_uint32(n), ctypes.byref(lo), ctypes.byref(hi)))
+    return lo.value, hi.value
+
+
+class GroupByResult:
+    def __init__(self, ngroups, keys, first_row, aggs):
+        self.ngroups, self.keys, self.first_row, self.aggs = ngroups, keys, first_row, aggs
+
+
+def groupby_agg(keys, aggs, row_order: int = ROWS_DESC, groups_hint: int = 0, max_groups: int = 0,
+                key_bounds=None, device_out: bool = False, want_keys: bool = True,
+                want_first_row: bool = True, out_types=None) -> GroupByResult:
+    """aqgpu_groupby_agg.  keys: list of columns; aggs: list of (op, v[, v2]) with op a name or code.
+
+    Columns are numpy arrays (host pointers: the call stages them itself) or DeviceColumn objects.
+    Results are numpy arrays (or DeviceColumn when device_out) sized max_groups, trimmed to ngroups
+    for numpy outputs.  __int128 cells come back as (n, 2) int64 [lo, hi].
+    """
+    L = lib()
+    nk = len(keys)
+    kc = [_col(k) for k in keys]
+    nrows = keys[0].n if isinstance(keys[0], DeviceColumn) else kc[0][2].size
+    kp = (ctypes.c_void_p * nk)(*[c[0] for c in kc])
+    kt = (ctypes.c_int * nk)(*[c[1] for c in kc])
+    cap = max_groups or nrows
+    na = len(aggs)
+    specs = (AggSpec * max(na, 1))()
+    keep, outs = [], []
+    for a, agg in enumerate(aggs):
+        op = REDUCE_NAMES[agg[0]] if isinstance(agg[0], str) else int(agg[0])
+        v = agg[1] if len(agg) > 1 else None
+        v2 = agg[2] if len(agg) > 2 else None
+        vt, vp, v2p = INT32, None, None
+        if op != COUNT:
+            vp, vt, k1 = _col(v)
+            keep.append(k1)
+            if v2 is not None:
+                v2p, _, k2 = _col(v2)
+                keep.append(k2)
+        ot = (out_types[a] if out_types and out_types[a] else 0) or reduce_out_type(op, vt)
+        if ot < 0:
+            raise AqgpuError(f"unsupported aggregate op={op} on dtype={vt}")
+        ob = _out_buf(ot, cap, device_out)
+        outs.append(ob)
+        specs[a].op, specs[a].vtype, specs[a].v, specs[a].v2 = op, vt, vp, v2p
+        specs[a].out_type, specs[a].out = ot, _out_ptr(ob)
+    kouts = [_out_buf(kc[k][1], cap, device_out) for k in range(nk)] if want_keys else []
+    okp = (ctypes.c_void_p * nk)(*[_out_ptr(b) for b in kouts]) if want_keys else None
+    fr = _out_buf(UINT32, cap, device_out) if want_first_row else None
+    kmin = kmax = None
+    if key_bounds is not None:
+        kmin = (ctypes.c_int64 * nk)(*[int(b[0]) for b in key_bounds])
+        kmax = (ctypes.c_int64 * nk)(*[int(b[1]) for b in key_bounds])
+    ng = ctypes.c_uint32(0)
+    check(L.aqgpu_groupby_agg(kp, kt, nk, ctypes.c_uint32(nrows), kmin, kmax, row_order,
+                              ctypes.c_uint32(groups_hint), specs, na, ctypes.c_uint32(cap), okp,
+                              ctypes.c_void_p(_out_ptr(fr)) if fr is not None else None, ctypes.byref(ng)))
+    n = ng.value
+    if not device_out:
+        outs = [o[:n] for o in outs]
+        kouts = [o[:n] for o in kouts]
+        fr = fr[:n] if fr is not None else None
+    return GroupByResult(n, kouts, fr, outs)
+
+
+class Groups:
+    """aqgpu_groups_t handle == the reference's HashTableComponents {size, keys, values, offsets}
+    (server/hasher.h:201-207), resident in HBM."""
+
+    def __init__(self, keys, row_order: int = ROWS_DESC, groups_hint: int = 0, key_bounds=None):
+        L = lib()
+        nk = len(keys)
+        kc = [_col(k) for k in keys]
+        self.nrows = keys[0].n if isinstance(keys[0], DeviceColumn) else kc[0][2].size
+        self.key_codes = [c[1] for c in kc]
+        kp = (ctypes.c_void_p * nk)(*[c[0] for c in kc])
+        kt = (ctypes.c_int * nk)(*self.key_codes)
+        kmin = kmax = None
+        if key_bounds is not None:
+            kmin = (ctypes.c_int64 * nk)(*[int(b[0]) for b in key_bounds])
+            kmax = (ctypes.c_int64 * nk)(*[int(b[1]) for b in key_bounds])
+        h = ctypes.c_void_p(0)
+        check(L.aqgpu_groupby_build(kp, kt, nk, ctypes.c_uint32(self.nrows), kmin, kmax, row_order,
+                                    ctypes.c_uint32(groups_hint), ctypes.byref(h)))
+        self.h = h
+        ng = ctypes.c_uint32(0)
+        check(L.aqgpu_groups_size(self.h, ctypes.byref(ng)))
+        self.ngroups = ng.value
+
+    def free(self):
+        if getattr(self, "h", None):
+            lib().aqgpu_groups_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def keys(self, k: int) -> np.ndarray:
+        out = np.empty(self.ngroups, CODE2NP[self.key_codes[k]])
+        if self.ngroups:
+            check(lib().aqgpu_groups_keys(self.h, k, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def first_row(self) -> np.ndarray:
+        out = np.empty(self.ngroups, np.uint32)
+        if self.ngroups:
+            check(lib().aqgpu_groups_first_row(self.h, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def gid(self) -> np.ndarray:
+        out = np.empty(self.nrows, np.uint32)
+        if self.nrows:
+            check(lib().aqgpu_groups_gid(self.h, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def csr(self):
+        off = np.zeros(self.ngroups + 1, np.uint32)
+        perm = np.empty(self.nrows, np.uint32)
+        check(lib().aqgpu_groups_csr(self.h, off.ctypes.data_as(ctypes.c_void_p),
+                                     perm.ctypes.data_as(ctypes.c_void_p) if self.nrows else None))
+        return off, perm
+
+    def reduce(self, op, v=None, v2=None, out_type: int = 0, device_out: bool = False):
+        op = REDUCE_NAMES[op] if isinstance(op, str) else int(op)
+        vt, vp, v2p, keep = INT32, None, None, []
+        if op != COUNT:
+            vp, vt, k1 = _col(v)
+            keep.append(k1)
+            if v2 is not None:
+                v2p, _, k2 = _col(v2)
+                keep.append(k2)
+        ot = out_type or reduce_out_type(op, vt)
+        if ot < 0:
+            raise AqgpuError(f"unsupported aggregate op={op} on dtype={vt}")
+        ob = _out_buf(ot, self.ngroups, device_out)
+        check(lib().aqgpu_group_reduce(self.h, op, vt, ctypes.c_void_p(vp), ctypes.c_void_p(v2p), ot,
+                                       ctypes.c_void_p(_out_ptr(ob))))
+        return ob
+
+    def scan(self, op, v, w: int = 0, out_type: int = 0, device_out: bool = False):
+        op = SCAN_NAMES[op] if isinstance(op, str) else int(op)
+        vp, vt, keep = _col(v)
+        ot = out_type or scan_out_type(op, vt)
+        if ot < 0:
+            raise AqgpuError(f"unsupported scan op={op} on dtype={vt}")
+        ob = _out_buf(ot, self.nrows, device_out)
+        check(lib().aqgpu_group_scan(self.h, op, ctypes.c_uint32(w), vt, ctypes.c_void_p(vp), ot,
+                                     ctypes.c_void_p(_out_ptr(ob))))
+        return ob
+
+    def order_by(self, cols, desc=None):
+        nc = len(cols)
+        cc = [_col(c) for c in cols]
+        cp = (ctypes.c_void_p * nc)(*[c[0] for c in cc])
+        ct = (ctypes.c_int * nc)(*[c[1] for c in cc])
+        d = (ctypes.c_int * nc)(*[int(bool(x)) for x in (desc or [0] * nc)])
+        check(lib().aqgpu_groups_order_by(self.h, cp, ct, d, nc))
+
+
+def synth_column(kind: int, key0: int, n: int, k: int, row_lo: int = 0, key1: int = 0, key2: int = 0,
+                 aux_k: int = 0, code: int = INT32) -> DeviceColumn:
+    out = DeviceColumn(n, code)
+    check(lib().aqgpu_synth_column(kind, ctypes.c_uint64(key0), ctypes.c_uint64(key1), ctypes.c_uint64(key2),
+                                   ctypes.c_uint32(k), ctypes.c_uint32(aux_k), ctypes.c_uint64(row_lo),
+                                   ctypes.c_uint32(n), ctypes.c_void_p(out.ptr)))
+    return out

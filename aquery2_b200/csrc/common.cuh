@@ -22,6 +22,7 @@ struct Context {
     cudaStream_t stream = nullptr;      // the stream every call works on
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::atomic<uint64_t> launches{0};
+    bool profiling = false;             // aqgpu_profile_enable
     // small device scratch reused by every call (flags, counters), and a pinned mirror
     uint32_t* d_flags = nullptr;        // 64 words
     uint32_t* h_flags = nullptr;        // pinned, 64 words
@@ -52,10 +53,16 @@ int fail(const char* fmt, ...);         // sets the message, returns -1
         }                                                                                   \
     } while (0)
 
+// Per-kernel CUDA-event timing on the launching stream (aqgpu_profile_*): off by default.
+void profile_pre(const char* kernel_name);
+void profile_post();
+
 // kernel launch with bookkeeping (gpu_launches in bench.py is this counter)
 #define AQ_LAUNCH(kernel, grid, block, smem, ...)                                           \
     do {                                                                                    \
+        if (::aq::ctx().profiling) ::aq::profile_pre(#kernel);                              \
         kernel<<<(grid), (block), (smem), ::aq::ctx().stream>>>(__VA_ARGS__);               \
+        if (::aq::ctx().profiling) ::aq::profile_post();                                    \
         ::aq::ctx().launches.fetch_add(1, std::memory_order_relaxed);                       \
         cudaError_t _e = cudaGetLastError();                                                \
         if (_e != cudaSuccess)                                                              \

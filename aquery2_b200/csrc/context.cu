@@ -52,6 +52,29 @@ void DevBuf::release() {
     bytes = 0;
 }
 
+// ---- per-kernel event timing ---------------------------------------------------------------------
+struct ProfRec { std::string name; cudaEvent_t e0, e1; };
+static std::vector<ProfRec> g_prof;
+static std::vector<cudaEvent_t> g_ev_pool;
+static std::string g_prof_tag;
+
+static cudaEvent_t prof_event() {
+    if (!g_ev_pool.empty()) { cudaEvent_t e = g_ev_pool.back(); g_ev_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+void profile_pre(const char* kernel_name) {
+    ProfRec r;
+    r.name = g_prof_tag.empty() ? std::string(kernel_name) : g_prof_tag + ":" + kernel_name;
+    r.e0 = prof_event(); r.e1 = prof_event();
+    cudaEventRecord(r.e0, ctx().stream);
+    g_prof.push_back(r);
+}
+void profile_post() {
+    if (!g_prof.empty()) cudaEventRecord(g_prof.back().e1, ctx().stream);
+}
+
 bool is_device_ptr(const void* p) {
     if (!p) return false;
     cudaPointerAttributes a;
@@ -179,6 +202,46 @@ int aqgpu_timer_end(float* ms) {
     return 0;
 }
 
+int aqgpu_profile_enable(int on) {
+    AQ_REQUIRE_INIT();
+    g_ctx.profiling = on != 0;
+    return 0;
+}
+
+int aqgpu_profile_tag(const char* tag) {
+    g_prof_tag = tag ? tag : "";
+    return 0;
+}
+
+/* Synchronises the stream and writes one line per (tag:kernel): "name calls total_ms\n". */
+int aqgpu_profile_report(char* buf, size_t cap) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    std::vector<std::string> names; std::vector<double> ms; std::vector<unsigned> calls;
+    for (auto& r : g_prof) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, r.e0, r.e1);
+        size_t i = 0;
+        for (; i < names.size(); ++i) if (names[i] == r.name) break;
+        if (i == names.size()) { names.push_back(r.name); ms.push_back(0.0); calls.push_back(0); }
+        ms[i] += t; calls[i] += 1;
+        g_ev_pool.push_back(r.e0); g_ev_pool.push_back(r.e1);
+    }
+    g_prof.clear();
+    std::string out;
+    char line[512];
+    for (size_t i = 0; i < names.size(); ++i) {
+        snprintf(line, sizeof(line), "%s\t%u\t%.6f\n", names[i].c_str(), calls[i], ms[i]);
+        out += line;
+    }
+    if (buf && cap) {
+        const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+        memcpy(buf, out.data(), n);
+        buf[n] = 0;
+    }
+    return 0;
+}
+
 int aqgpu_col_alloc(size_t bytes, void** dptr) {
     AQ_REQUIRE_INIT();
     if (!dptr) return fail("null dptr");
@@ -225,7 +288,7 @@ int aqgpu_reduce_out_type(int op, int vtype) {
     switch (op) {
     case AQ_SUM: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;     // types.h:205-210
     case AQ_AVG: case AQ_VAR: case AQ_STDDEV: case AQ_CORR: return AQ_DOUBLE;
-    case AQ_MIN: case AQ_MAX: case AQ_FIRST: case AQ_LAST: return vtype;
+    case AQ_MIN: case AQ_MAX: case AQ_FIRST: case AQ_LAST: case AQ_SECOND: return vtype;
     default: return -2;
     }
 }

@@ -51,7 +51,10 @@ enum aqgpu_reduce_op {
     AQ_LAST = 6,    /* aggregations.h:487-491 */
     AQ_VAR = 7,     /* aggregations.h:332-348 (divides by len+1, kept) */
     AQ_STDDEV = 8,  /* aggregations.h:413-415 */
-    AQ_CORR = 9     /* aggregations.h:383-407 integer inputs only */
+    AQ_CORR = 9,    /* aggregations.h:383-407 integer inputs only */
+    AQ_SECOND = 10  /* element [1] of the group's row list (0 when the group has one row): with
+                       AQ_FIRST this is subvec(v, 0, 2) of h2o q8 (benchmark/h2o/groupby.sql:17,
+                       server/vector_type.hpp:348-355) */
 };
 
 /* ---- per-group vector-valued aggregates, CSR output (engine/ast.py:696-718) ------------------ */
@@ -91,6 +94,13 @@ uint64_t aqgpu_launch_count(void);
 /* CUDA-event timing on the library stream: begin/end return elapsed milliseconds in *ms. */
 int aqgpu_timer_begin(void);
 int aqgpu_timer_end(float* ms);
+
+/* Per-kernel timing with CUDA events recorded on the library stream around every launch (off by
+ * default).  aqgpu_profile_tag prefixes subsequent records ("q3:k_probe_agg<true>");
+ * aqgpu_profile_report synchronises and writes "name<TAB>calls<TAB>total_ms" lines, then clears. */
+int aqgpu_profile_enable(int on);
+int aqgpu_profile_tag(const char* tag);
+int aqgpu_profile_report(char* buf, size_t cap);
 
 /* ---- HBM column store (replaces the malloc'ed / MonetDB-owned buffers ColRef points into:
  *      server/table.h:96-103 ColRef(size, void*), server/monetdb_conn.cpp:203-224 getCol) -------- */

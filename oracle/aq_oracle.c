@@ -121,7 +121,7 @@ int aqo_reduce_out_type(int op, int vtype) {
     switch (op) {
     case AQO_SUM: return is_int(vtype) ? AQO_INT128 : AQO_DOUBLE;
     case AQO_AVG: case AQO_VAR: case AQO_STDDEV: case AQO_CORR: return AQO_DOUBLE;
-    case AQO_MIN: case AQO_MAX: case AQO_FIRST: case AQO_LAST: return vtype;
+    case AQO_MIN: case AQO_MAX: case AQO_FIRST: case AQO_LAST: case AQO_SECOND: return vtype;
     case AQO_COUNT: return AQO_UINT32;
     default: return -2;
     }
@@ -185,6 +185,7 @@ static int reduce_##SFX(int op, const T* v, const T* v2, uint32_t ng, const uint
         case AQO_MAX: ((T*)out)[g] = max_##SFX(v, r, n); break;                                     \
         case AQO_FIRST: ((T*)out)[g] = n ? v[r[0]] : 0; break;        /* aggregations.h:493-497 */  \
         case AQO_LAST: ((T*)out)[g] = n ? v[r[n - 1]] : 0; break;     /* aggregations.h:487-491 */  \
+        case AQO_SECOND: ((T*)out)[g] = n > 1 ? v[r[1]] : 0; break;   /* vector_type.hpp:348-355 */ \
         case AQO_VAR: ((double*)out)[g] = var_##SFX(v, r, n); break;                                \
         case AQO_STDDEV: ((double*)out)[g] = sqrt(var_##SFX(v, r, n)); break; /* :413-415 */        \
         case AQO_CORR: ((double*)out)[g] = corr_##SFX(v, v2, r, n); break;                          \

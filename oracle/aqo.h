@@ -31,7 +31,8 @@ enum aqo_dtype {
 /* per-group scalar aggregates (server/aggregations.h:10-32,71-86,332-348,383-407,413-415,487-497) */
 enum aqo_reduce_op {
     AQO_SUM = 0, AQO_AVG = 1, AQO_MIN = 2, AQO_MAX = 3, AQO_COUNT = 4, AQO_FIRST = 5, AQO_LAST = 6,
-    AQO_VAR = 7, AQO_STDDEV = 8, AQO_CORR = 9
+    AQO_VAR = 7, AQO_STDDEV = 8, AQO_CORR = 9,
+    AQO_SECOND = 10   /* subvec(v, 0, 2)[1] (server/vector_type.hpp:348-355), 0 for one-row groups */
 };
 
 /* per-group vector-valued aggregates (server/aggregations.h:89-125 running min/max, :127-167 windowed

@@ -24,12 +24,12 @@ PORT_LIB = os.path.join(HERE, "libaqoracle.so")
 # dtype codes = reference types::Type_t (server/aquery_types.h:1-5)
 INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
 # aqo_reduce_op
-SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR = range(10)
+SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND = range(11)
 # aqo_scan_op
 SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
 
 REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
-                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR}
+                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR, "second": SECOND}
 SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
               "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
               "ratiow": RATIOW}

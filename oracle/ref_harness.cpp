@@ -126,6 +126,13 @@ int reduce_t(int op, const void* v, const void* v2, uint32_t ng, const uint32_t*
         per_group<T>(v, ng, off, perm, [&](uint32_t g, ColRef<T>& c, vector_type<uint32_t>& val) {
             static_cast<T*>(out)[g] = last(c[val]); });
         return 0;
+    case AQO_SECOND:                    /* subvec(v, 0, 2) of the gathered vector, element [1] */
+        per_group<T>(v, ng, off, perm, [&](uint32_t g, ColRef<T>& c, vector_type<uint32_t>& val) {
+            if (val.size < 2) { static_cast<T*>(out)[g] = 0; return; }
+            auto gathered = c[val];
+            auto sv = gathered.subvec_memcpy(0, 2);
+            static_cast<T*>(out)[g] = sv[1]; });
+        return 0;
     case AQO_VAR:
         per_group<T>(v, ng, off, perm, [&](uint32_t g, ColRef<T>& c, vector_type<uint32_t>& val) {
             static_cast<double*>(out)[g] = var(c[val]); });
@@ -189,7 +196,7 @@ template <class T> int reduce_out_t(int op) {
     switch (op) {
     case AQO_SUM: return code_of<types::GetLongType<T>>::v;
     case AQO_AVG: case AQO_VAR: case AQO_STDDEV: case AQO_CORR: return AQO_DOUBLE;
-    case AQO_MIN: case AQO_MAX: case AQO_FIRST: case AQO_LAST: return code_of<T>::v;
+    case AQO_MIN: case AQO_MAX: case AQO_FIRST: case AQO_LAST: case AQO_SECOND: return code_of<T>::v;
     case AQO_COUNT: return AQO_UINT32;
     default: return -2;
     }

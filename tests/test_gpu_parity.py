@@ -1,0 +1,213 @@
+"""Parity of the CUDA path (through the C ABI, include/aqgpu.h) with the CPU oracle and with the
+fixtures produced by the reference's own headers.  Bit-exact for keys, group order, counts, row lists
+and integer aggregates; FP64_RTOL (1e-12) for fp64 sums / averages / windowed means."""
+import numpy as np
+import pytest
+
+from aquery2_b200 import synth
+from oracle.gen_golden import H2O_QUERIES, SCAN_CASES, trade_values
+from util import assert_same
+
+pytestmark = pytest.mark.gpu
+
+
+def run_query(gpu, t, keys, aggs, **kw):
+    specs = []
+    for agg in aggs:
+        specs.append((agg[0],) + tuple(t[c] for c in agg[1:]))
+    return gpu.groupby_agg([t[c] for c in keys], specs, **kw)
+
+
+def check_query_vs_oracle(gpu, oracle, t, keys, aggs, **kw):
+    res = run_query(gpu, t, keys, aggs, **kw)
+    ng, gid, off, perm = oracle.groupby([t[c] for c in keys])
+    assert res.ngroups == ng
+    first = perm[off[1:] - 1] if ng else np.zeros(0, np.uint32)     # descending lists: last entry = first row
+    assert_same(res.first_row, first.astype(np.uint32), "first_row")
+    for k, c in enumerate(keys):
+        assert_same(res.keys[k], t[c][first], f"key {c}")
+    for a, agg in enumerate(aggs):
+        v = t[agg[1]] if len(agg) > 1 else None
+        v2 = t[agg[2]] if len(agg) > 2 else None
+        assert_same(res.aggs[a], oracle.reduce(agg[0], v, off, perm, v2=v2, raw128=True), f"{keys} {agg}")
+    return res
+
+
+# ---- golden fixtures (reference-built) ---------------------------------------------------------
+def test_h2o_golden(gpu, golden):
+    g = golden("h2o_small.npz")
+    t = synth.h2o_table(int(g["n"]), int(g["k"]), seed=int(g["seed"]))
+    for q, (keys, aggs) in H2O_QUERIES.items():
+        res = run_query(gpu, t, keys, aggs)
+        assert res.ngroups == int(g[f"{q}_ngroups"]), q
+        for a, agg in enumerate(aggs):
+            assert_same(res.aggs[a], g[f"{q}_agg{a}"], f"{q} {agg}")
+        h = gpu.Groups([t[c] for c in keys])
+        assert h.ngroups == int(g[f"{q}_ngroups"])
+        assert_same(h.gid(), g[f"{q}_gid"], f"{q} gid")
+        off, perm = h.csr()
+        assert_same(off, g[f"{q}_offsets"], f"{q} offsets")
+        assert_same(perm, g[f"{q}_perm"], f"{q} perm")
+        h.free()
+
+
+def test_trade_golden(gpu, golden):
+    g = golden("trade_small.npz")
+    t = synth.trade_table(int(g["n"]), int(g["nsym"]), seed=int(g["seed"]))
+    vals = trade_values(t)
+    h = gpu.Groups([t["sym"]])
+    assert h.ngroups == int(g["ngroups"])
+    assert_same(h.gid(), g["gid"])
+    off, perm = h.csr()
+    assert_same(off, g["offsets"]); assert_same(perm, g["perm"])
+    for vn, v in vals.items():
+        for op in ("sum", "avg", "min", "max", "first", "last", "var", "stddev"):
+            if vn == "big_i64" and op in ("var", "stddev"):
+                continue      # arr[i]*arr[i] overflows int64 in the reference (UB), not a parity case
+            assert_same(h.reduce(op, v), g[f"reduce_{op}_{vn}"], f"{op} {vn}")
+        for op, w in SCAN_CASES:
+            assert_same(h.scan(op, v, w=w), g[f"scan_{op}_{w}_{vn}"], f"{op}({w}) {vn}", scale=float(np.abs(v).max()))
+    assert_same(h.reduce("count"), g["reduce_count"])
+    assert_same(h.reduce("corr", vals["price_i32"], vals["qty_i32"]), g["reduce_corr_i32"])
+    h.free()
+
+
+def test_keys_golden(gpu, golden):
+    g = golden("keys_small.npz")
+    for name, keys in (("k64", [g["k64"]]), ("k64x2", [g["k64"], g["k64b"]]), ("kneg", [g["kneg"]])):
+        h = gpu.Groups(keys)
+        assert h.ngroups == int(g[f"{name}_ngroups"])
+        assert_same(h.gid(), g[f"{name}_gid"])
+        off, perm = h.csr()
+        assert_same(off, g[f"{name}_offsets"]); assert_same(perm, g[f"{name}_perm"])
+        h.free()
+
+
+# ---- oracle on the same seeded inputs -----------------------------------------------------------
+@pytest.mark.parametrize("q", list(H2O_QUERIES))
+@pytest.mark.parametrize("n,k", [(100_000, 100), (1_000_000, 100), (300_000, 3)])
+def test_h2o_vs_oracle(gpu, port, q, n, k):
+    keys, aggs = H2O_QUERIES[q]
+    cols = set(keys) | {c for a in aggs for c in a[1:]}
+    t = synth.h2o_table(n, k, seed=42, columns=sorted(cols))
+    check_query_vs_oracle(gpu, port, t, keys, aggs)
+
+
+def test_h2o_device_columns_and_bounds(gpu, port):
+    """device-resident columns (the HBM column store), key bounds (ColRef::stats), groups_hint"""
+    n, k = 500_000, 100
+    t = synth.h2o_table(n, k, seed=42, columns=["id1", "id2", "id4", "v1", "v3"])
+    d = {c: gpu.DeviceColumn.from_numpy(a) for c, a in t.items()}
+    ng, gid, off, perm = port.groupby([t["id1"], t["id2"]])
+    want = port.reduce("sum", t["v1"], off, perm, raw128=True)
+    for bounds in (None, [(1, k), (1, k)], [(1, k // 2), (1, k)]):      # last: wrong bounds -> silent retry
+        res = gpu.groupby_agg([d["id1"], d["id2"]], [("sum", d["v1"]), ("avg", d["v3"])], key_bounds=bounds, groups_hint=k * k)
+        assert res.ngroups == ng
+        assert_same(res.aggs[0], want)
+        assert_same(res.aggs[1], port.reduce("avg", t["v3"], off, perm))
+    res = gpu.groupby_agg([d["id1"], d["id2"]], [("sum", d["v1"])], device_out=True)
+    assert_same(res.aggs[0].numpy(res.ngroups), want)
+
+
+def test_synth_device_matches_host(gpu):
+    n, k = 100_003, 100
+    for name, kind, kk in (("id1", 0, k), ("id3", 0, n // k), ("v1", 0, 5), ("v2", 0, 15)):
+        dev = gpu.synth_column(kind, synth.stream_key(42, synth.STREAM[name]), n, kk)
+        assert_same(dev.numpy(), synth.h2o_column(name, n, k))
+    dev = gpu.synth_column(2, synth.stream_key(42, synth.STREAM["v3"]), n, 100_000_000, code=gpu.FLOAT)
+    assert_same(dev.numpy(), synth.h2o_column("v3", n, k))
+    # a shard [lo, hi) of the global table
+    lo, hi = 70_000, 90_001
+    dev = gpu.synth_column(0, synth.stream_key(42, synth.STREAM["id6"]), hi - lo, n // k, row_lo=lo)
+    assert_same(dev.numpy(), synth.h2o_column("id6", n, k, lo, hi))
+    for name, kind in (("sym", 1), ("quantity", 5)):
+        kk, aux = (1000, 0) if name == "sym" else (9901, 100)
+        dev = gpu.synth_column(kind, synth.stream_key(42, synth.STREAM[name]), n, kk, aux_k=aux)
+        assert_same(dev.numpy(), synth.trade_column(name, n, 1000))
+    dev = gpu.synth_column(4, synth.stream_key(42, synth.STREAM["price"]), n, 1000,
+                           key1=synth.stream_key(42, synth.STREAM["sym"]), key2=synth.stream_key(42, synth.STREAM["price_base"]))
+    assert_same(dev.numpy(), synth.trade_column("price", n, 1000))
+
+
+@pytest.mark.parametrize("n,nsym", [(200_000, 1000), (50_000, 20_000), (5000, 1)])
+def test_windowed_vs_oracle(gpu, port, n, nsym):
+    t = synth.trade_table(n, nsym, seed=9)
+    vals = trade_values(t)
+    h = gpu.Groups([t["sym"]])
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    assert h.ngroups == ng
+    assert_same(h.gid(), gid)
+    o2, p2 = h.csr()
+    assert_same(o2, off); assert_same(p2, perm)
+    for vn in ("price_i32", "price_f32", "big_i64", "qty_f64"):
+        v = vals[vn]
+        for op, w in SCAN_CASES + [("sumw", 100), ("avgw", 100), ("minw", 300), ("maxw", 10_000)]:
+            assert_same(h.scan(op, v, w=w), port.scan(op, v, off, perm, w=w, raw128=True), f"{op}({w}) {vn}", scale=float(np.abs(v).max()))
+    h.free()
+
+
+def test_row_order_asc_and_order_by(gpu, port):
+    """AQ_ROWS_ASC (legacy emplace_back order) and ASSUMING via order_by (common/groupby.py:54-59)."""
+    n, nsym = 60_000, 300
+    t = synth.trade_table(n, nsym, seed=5)
+    rng = np.random.default_rng(0)
+    tm = rng.permutation(n).astype(np.int32)          # unsorted time column
+    h = gpu.Groups([t["sym"]], row_order=gpu.ROWS_ASC)
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    o2, p2 = h.csr()
+    assert_same(o2, off)
+    asc = np.concatenate([perm[off[g]:off[g + 1]][::-1] for g in range(ng)]).astype(np.uint32)
+    assert_same(p2, asc)
+    h.order_by([tm], desc=[0])
+    o3, p3 = h.csr()
+    want = np.concatenate([np.sort(asc[off[g]:off[g + 1]], kind="stable")[np.argsort(tm[np.sort(asc[off[g]:off[g + 1]])], kind="stable")]
+                           for g in range(ng)]).astype(np.uint32)
+    assert_same(p3, want)
+    got = h.scan("avgw", t["price"], w=5)
+    assert_same(got, port.scan("avgw", t["price"], off, want, w=5))
+    h.order_by([tm], desc=[1])
+    _, p4 = h.csr()
+    want_d = np.concatenate([want[off[g]:off[g + 1]][::-1] for g in range(ng)]).astype(np.uint32)
+    assert_same(p4, want_d)
+    h.free()
+
+
+# ---- edge cases ----------------------------------------------------------------------------------
+def test_edge_cases(gpu, port):
+    # empty input
+    res = gpu.groupby_agg([np.zeros(0, np.int32)], [("sum", np.zeros(0, np.int32))])
+    assert res.ngroups == 0
+    h = gpu.Groups([np.zeros(0, np.int32)])
+    assert h.ngroups == 0 and h.csr()[0].tolist() == [0]
+    # a single row, a single group, all-distinct keys, ragged tails (n % 4 != 0)
+    for n, hi in ((1, 1), (2, 1), (3, 5), (5, 1), (1023, 7), (4097, 4097), (65537, 2)):
+        rng = np.random.default_rng(n)
+        key = rng.integers(0, hi, n).astype(np.int32) if hi < n else rng.permutation(n).astype(np.int32)
+        v = rng.integers(-1000, 1000, n).astype(np.int32)
+        t = {"k": key, "v": v, "f": v.astype(np.float32) / 3}
+        check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("min", "v"), ("max", "v"), ("count",), ("avg", "f"),
+                                                   ("first", "v"), ("last", "f")])
+    # all-negative fp max: the reference's numeric_limits<T>::min() identity (aggregations.h:73)
+    t = {"k": np.array([1, 1, 2], np.int32), "d": np.array([-1.0, -2.0, -3.0]), "f": np.array([-1.0, -2.0, -3.0], np.float32)}
+    res = check_query_vs_oracle(gpu, port, t, ["k"], [("max", "d"), ("max", "f"), ("min", "d")])
+    assert res.aggs[0].tolist() == [np.finfo(np.float64).tiny] * 2
+    # extreme int32 values and sums beyond int32
+    t = {"k": np.array([3, 3, 3, 4], np.int32), "v": np.array([2**31 - 1, 2**31 - 1, 2**31 - 1, -2**31], np.int32)}
+    res = check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "v"), ("min", "v"), ("max", "v")])
+    assert res.aggs[0][:, 0].tolist() == [3 * (2**31 - 1), -2**31]
+    # capacity error
+    with pytest.raises(gpu.AqgpuError, match="capacity"):
+        gpu.groupby_agg([np.arange(100, dtype=np.int32)], [("count",)], max_groups=10)
+
+
+def test_high_cardinality_and_collisions(gpu, port):
+    """G ~ N (q10 regime), keys that differ only in high words, 64-bit keys."""
+    n = 400_000
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 1 << 30, n).astype(np.int32)
+    b = (rng.integers(0, 4, n) << 28).astype(np.int32)
+    v = rng.integers(0, 100, n).astype(np.int32)
+    t = {"a": a, "b": b, "v": v, "k64": (a.astype(np.int64) << 20) ^ b.astype(np.int64)}
+    check_query_vs_oracle(gpu, port, t, ["a", "b"], [("sum", "v"), ("count",)])
+    check_query_vs_oracle(gpu, port, t, ["k64"], [("sum", "v")])
+    check_query_vs_oracle(gpu, port, t, ["b", "k64", "a"], [("max", "v")])

@@ -387,3 +387,104 @@ def synth_column(kind: int, key0: int, n: int, k: int, row_lo: int = 0, key1: in
                                    ctypes.c_uint32(k), ctypes.c_uint32(aux_k), ctypes.c_uint64(row_lo),
                                    ctypes.c_uint32(n), ctypes.c_void_p(out.ptr)))
     return out
+
+
+class PreparedQuery:
+    """One aqgpu_groupby_agg call with its argument block and output columns built once, so that a
+    timed loop does nothing but the C-ABI call.  Inputs/outputs may be DeviceColumn (HBM-resident
+    column store) or numpy arrays (host pointers: the call stages them itself, H2D + D2H)."""
+
+    def __init__(self, keys, aggs, max_groups: int, groups_hint: int = 0, key_bounds=None,
+                 row_order: int = ROWS_DESC, device_out: bool = True, out_types=None,
+                 want_keys: bool = True, want_first_row: bool = False, host_alloc=None):
+        self.nk = nk = len(keys)
+        self._keep = []
+        kc = [_col(k) for k in keys]
+        self._keep += [c[2] for c in kc]
+        self.nrows = keys[0].n if isinstance(keys[0], DeviceColumn) else kc[0][2].size
+        self.kp = (ctypes.c_void_p * nk)(*[c[0] for c in kc])
+        self.kt = (ctypes.c_int * nk)(*[c[1] for c in kc])
+        self.cap = int(max_groups)
+        self.groups_hint = int(groups_hint)
+        self.row_order = row_order
+        self.na = na = len(aggs)
+        self.specs = (AggSpec * max(na, 1))()
+        self.outs = []
+        self.in_bytes = sum(CODE_SIZE[c[1]] for c in kc) * self.nrows
+        mk = (lambda code, n: _out_buf(code, n, True)) if device_out else \
+             (host_alloc or (lambda code, n: _out_buf(code, n, False)))
+        seen = {c[0] for c in kc}
+        for a, agg in enumerate(aggs):
+            op = REDUCE_NAMES[agg[0]] if isinstance(agg[0], str) else int(agg[0])
+            vt, vp, v2p = INT32, None, None
+            if op != COUNT:
+                vp, vt, k1 = _col(agg[1])
+                self._keep.append(k1)
+                if vp not in seen:
+                    seen.add(vp); self.in_bytes += CODE_SIZE[vt] * self.nrows
+                if len(agg) > 2 and agg[2] is not None:
+                    v2p, _, k2 = _col(agg[2])
+                    self._keep.append(k2)
+                    if v2p not in seen:
+                        seen.add(v2p); self.in_bytes += CODE_SIZE[vt] * self.nrows
+            ot = (out_types[a] if out_types and out_types[a] else 0) or reduce_out_type(op, vt)
+            ob = mk(ot, self.cap)
+            self.outs.append(ob)
+            s = self.specs[a]
+            s.op, s.vtype, s.v, s.v2, s.out_type, s.out = op, vt, vp, v2p, ot, _out_ptr(ob)
+        self.kouts = [mk(kc[k][1], self.cap) for k in range(nk)] if want_keys else []
+        self.okp = (ctypes.c_void_p * nk)(*[_out_ptr(b) for b in self.kouts]) if want_keys else None
+        self.fr = mk(UINT32, self.cap) if want_first_row else None
+        self.kmin = self.kmax = None
+        if key_bounds is not None:
+            self.kmin = (ctypes.c_int64 * nk)(*[int(b[0]) for b in key_bounds])
+            self.kmax = (ctypes.c_int64 * nk)(*[int(b[1]) for b in key_bounds])
+        self.ng = ctypes.c_uint32(0)
+        self._fn = lib().aqgpu_groupby_agg
+
+    def out_bytes(self, ngroups: int) -> int:
+        b = sum(CODE_SIZE[self.specs[a].out_type] for a in range(self.na))
+        b += sum(CODE_SIZE[self.kt[k]] for k in range(self.nk)) if self.kouts else 0
+        b += 4 if self.fr is not None else 0
+        return b * ngroups
+
+    def run(self) -> int:
+        rc = self._fn(self.kp, self.kt, self.nk, ctypes.c_uint32(self.nrows), self.kmin, self.kmax,
+                      self.row_order, ctypes.c_uint32(self.groups_hint), self.specs, self.na,
+                      ctypes.c_uint32(self.cap), self.okp,
+                      ctypes.c_void_p(_out_ptr(self.fr)) if self.fr is not None else None,
+                      ctypes.byref(self.ng))
+        check(rc)
+        return self.ng.value
+
+
+def vec_sub(a, b, out, n: int, code: int) -> None:
+    check(lib().aqgpu_vec_sub(code, ctypes.c_void_p(_out_ptr(a)), ctypes.c_void_p(_out_ptr(b)),
+                              ctypes.c_void_p(_out_ptr(out)), ctypes.c_uint32(n)))
+
+
+def vec_pow(x, p: float, out, n: int) -> None:
+    check(lib().aqgpu_vec_pow(ctypes.c_void_p(_out_ptr(x)), ctypes.c_double(p), ctypes.c_void_p(_out_ptr(out)),
+                              ctypes.c_uint32(n)))
+
+
+class PinnedArray:
+    """numpy view of pinned host memory from aqgpu_host_alloc (host side of the e2e arm)."""
+
+    def __init__(self, n: int, code: int):
+        self.n, self.code = int(n), code
+        nbytes = max(self.n * CODE_SIZE[code], 16)
+        p = ctypes.c_void_p(0)
+        check(lib().aqgpu_host_alloc(ctypes.c_size_t(nbytes), ctypes.byref(p)))
+        self.ptr = p.value
+        buf = (ctypes.c_char * nbytes).from_address(self.ptr)
+        if code == INT128:
+            self.array = np.frombuffer(buf, np.int64, self.n * 2).reshape(self.n, 2)
+        else:
+            self.array = np.frombuffer(buf, CODE2NP[code], self.n)
+
+    def free(self):
+        if getattr(self, "ptr", None):
+            self.array = None
+            lib().aqgpu_host_free(ctypes.c_void_p(self.ptr))
+            self.ptr = None

@@ -105,7 +105,7 @@ int AggPlan::plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* d
     EmitAgg& e = emit.agg[emit.n];
     memset(&e, 0, sizeof(e));
     e.op = a.op; e.vtype = a.vtype; e.v = dv; e.out = dout;
-    e.cnt = e.maxrow = -1;
+    e.cnt = e.maxrow = e.top2 = -1;
     for (int i = 0; i < 5; ++i) e.a[i] = -1;
     const int def = aqgpu_reduce_out_type(a.op, a.vtype);
     if (def < 0) return fail("unsupported aggregate op %d on dtype %d", a.op, a.vtype);
@@ -127,6 +127,7 @@ int AggPlan::plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* d
         const bool need_max = (a.op == AQ_FIRST) == (emit.row_order == AQ_ROWS_DESC);
         if (need_max) ok = (e.maxrow = add_maxrow()) >= 0;
         break; }
+    case AQ_SECOND: ok = (e.top2 = add_top2(emit.row_order)) >= 0; break;
     case AQ_VAR: case AQ_STDDEV:
         ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0 &&
              (e.a[1] = add_acc(add, X_SQUARE, a.vtype, dv, nullptr)) >= 0 && (e.cnt = add_count()) >= 0;
@@ -214,6 +215,27 @@ __device__ __forceinline__ void acc_apply(const AccProg& p, int a, const uint32_
     if (o.kind == ACC_MAXROW) {
 #pragma unroll
         for (int r = 0; r < 4; ++r) if (r < cnt) atomicMax(slot_word(p, slot[r]) + 1 + a, (unsigned long long)(row0 + r));
+        return;
+    }
+    if (o.kind == ACC_TOP2ROW) {     // o.xform carries the row order
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (r >= cnt) continue;
+            const uint32_t row = row0 + r;
+            const unsigned long long k = o.xform == AQ_ROWS_DESC ? (unsigned long long)row + 1ull : (unsigned long long)(0xffffffffu - row);
+            unsigned long long* c = slot_word(p, slot[r]) + 1 + a;
+            unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(c);
+            for (;;) {
+                const unsigned long long best = old >> 32, second = old & 0xffffffffull;
+                unsigned long long nw;
+                if (k > best) nw = (k << 32) | best;
+                else if (k > second) nw = (best << 32) | k;
+                else break;
+                const unsigned long long seen = atomicCAS(c, old, nw);
+                if (seen == old) break;
+                old = seen;
+            }
+        }
         return;
     }
     long long xi[4]; double xd[4];
@@ -396,6 +418,13 @@ __device__ void emit_one(const EmitAgg& e, const unsigned long long* __restrict_
         const uint32_t r = want_max ? (uint32_t)cell(e.maxrow) : first_row;
         if (e.vtype == AQ_INT32 || e.vtype == AQ_FLOAT) static_cast<uint32_t*>(e.out)[gid] = static_cast<const uint32_t*>(e.v)[r];
         else static_cast<unsigned long long*>(e.out)[gid] = static_cast<const unsigned long long*>(e.v)[r];
+        break; }
+    case AQ_SECOND: {                // element [1] of the row list; 0 for one-row groups
+        const uint32_t k2 = (uint32_t)(cell(e.top2) & 0xffffffffull);
+        const bool have = k2 != 0;
+        const uint32_t r = row_order == AQ_ROWS_DESC ? k2 - 1u : 0xffffffffu - k2;
+        if (e.vtype == AQ_INT32 || e.vtype == AQ_FLOAT) static_cast<uint32_t*>(e.out)[gid] = have ? static_cast<const uint32_t*>(e.v)[r] : 0u;
+        else static_cast<unsigned long long*>(e.out)[gid] = have ? static_cast<const unsigned long long*>(e.v)[r] : 0ull;
         break; }
     case AQ_VAR: case AQ_STDDEV: {   // aggregations.h:332-348: (ssq - s*s/(len+1)) / (len+1)
         const double np1 = (double)(n + 1u);

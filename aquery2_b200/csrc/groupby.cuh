@@ -41,7 +41,9 @@ enum AccKind : int {
     ACC_ADD_F64 = 2,   // += (double) x
     ACC_MIN_I64 = 3,   // min of the int64 image (ints: value, fp: order-preserving bits of the double)
     ACC_MAX_I64 = 4,
-    ACC_MAXROW = 5     // max row id of the group
+    ACC_MAXROW = 5,    // max row id of the group
+    ACC_TOP2ROW = 6    // (best << 32 | second best) row keys; key = row + 1 (DESC lists: two largest
+                       // rows) or 0xffffffff - row (ASC lists: two smallest rows); 0 = none
 };
 enum AccXform : int {
     X_IDENT = 0,       // x = v[i]
@@ -78,6 +80,7 @@ struct EmitAgg {
     int a[5];          // accumulator indices (meaning depends on op)
     int cnt;           // index of the COUNT accumulator or -1
     int maxrow;        // index of the MAXROW accumulator or -1
+    int top2;          // index of the TOP2ROW accumulator or -1
     const void* v;     // value column for FIRST / LAST gathers
     void* out;
 };
@@ -111,6 +114,7 @@ struct AggPlan {
     int add_acc(int kind, int xform, int vtype, const void* v, const void* v2);
     int add_count() { return add_acc(ACC_COUNT, X_IDENT, 0, nullptr, nullptr); }
     int add_maxrow() { return add_acc(ACC_MAXROW, X_IDENT, 0, nullptr, nullptr); }
+    int add_top2(int row_order) { return add_acc(ACC_TOP2ROW, row_order, 0, nullptr, nullptr); }
     int find(int kind) const;
     int plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* dout);
 };

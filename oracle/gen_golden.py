@@ -30,7 +30,7 @@ H2O_QUERIES = {
     "q5": (["id6"], [("sum", "v1"), ("sum", "v2"), ("sum", "v3")]),
     "q6": (["id4", "id5"], [("stddev", "v3")]),
     "q7": (["id3"], [("max", "v1"), ("min", "v2")]),
-    "q8": (["id6"], [("first", "v3"), ("last", "v3")]),
+    "q8": (["id6"], [("first", "v3"), ("second", "v3")]),   # subvec(v3, 0, 2)
     "q9": (["id2", "id4"], [("corr", "v1", "v2")]),
     "q10": (["id1", "id2", "id3", "id4", "id5", "id6"], [("sum", "v3"), ("count",)]),
 }

@@ -56,7 +56,7 @@ int KeyCols::make_spec(const int64_t* key_min, const int64_t* key_max, KeySpec& 
     ks.nwords = w;
     ks.vec_ok = vec_ok;
     ks.exact = (w == 1) ? 1 : 0;
-    if (key_min && key_max && all32 && ks.exact == 0) {
+    if (key_min && key_max && all32) {
         // PerfectHashTable-style packing (hasher.h:226-243): sum of field widths must fit 32 bits
         int bits = 0;
         bool ok = true;
@@ -157,102 +157,6 @@ struct InitPattern { unsigned long long w[16]; };
 __global__ void k_init_table(unsigned long long* __restrict__ tab, size_t nwords, uint32_t sw, const InitPattern pat) {
     for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nwords; i += size_t(gridDim.x) * blockDim.x)
         tab[i] = pat.w[i & (sw - 1)];
-}
-
-// value column -> 4 (int64 image | double image) values
-__device__ __forceinline__ void load4_val(const void* v, int vtype, uint32_t row0, int cnt, bool vec,
-                                          long long iv[4], double dv[4], float fv[4]) {
-    if (vtype == AQ_INT32 || vtype == AQ_FLOAT) {
-        uint32_t u[4];
-        load4_b32(v, row0, cnt, vec, u);
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            if (vtype == AQ_INT32) { iv[r] = (long long)(int)u[r]; }
-            else { fv[r] = __uint_as_float(u[r]); dv[r] = (double)fv[r]; }
-        }
-    } else {
-        unsigned long long u[4];
-        load4_b64(v, row0, cnt, vec, u);
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            if (vtype == AQ_INT64) iv[r] = (long long)u[r];
-            else dv[r] = __longlong_as_double((long long)u[r]);
-        }
-    }
-}
-
-// x[r] for one accumulator: integer image in xi (int columns), double image in xd (fp columns)
-__device__ __forceinline__ void acc_inputs(const AccOp& o, uint32_t row0, int cnt, long long xi[4], double xd[4]) {
-    long long iv[4] = {0, 0, 0, 0}; double dv[4] = {0, 0, 0, 0}; float fv[4] = {0, 0, 0, 0};
-    load4_val(o.v, o.vtype, row0, cnt, o.vec_ok, iv, dv, fv);
-    if (o.xform == X_IDENT) {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) { xi[r] = iv[r]; xd[r] = dv[r]; }
-        return;
-    }
-    long long iw[4] = {0, 0, 0, 0}; double dw[4] = {0, 0, 0, 0}; float fw[4] = {0, 0, 0, 0};
-    if (o.xform == X_PRODUCT) {
-        load4_val(o.v2, o.vtype, row0, cnt, o.vec_ok, iw, dw, fw);
-    } else {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) { iw[r] = iv[r]; dw[r] = dv[r]; fw[r] = fv[r]; }
-    }
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        xi[r] = iv[r] * iw[r];
-        // the reference multiplies in the column's own type before widening (aggregations.h:339-345)
-        xd[r] = o.vtype == AQ_FLOAT ? (double)__fmul_rn(fv[r], fw[r]) : __dmul_rn(dv[r], dw[r]);
-    }
-}
-
-__device__ __forceinline__ void acc_apply(const AccProg& p, int a, const uint32_t slot[4], uint32_t row0, int cnt) {
-    const AccOp& o = p.op[a];
-    if (o.kind == ACC_COUNT) {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) if (r < cnt) atomicAdd(slot_word(p, slot[r]) + 1 + a, 1ull);
-        return;
-    }
-    if (o.kind == ACC_MAXROW) {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) if (r < cnt) atomicMax(slot_word(p, slot[r]) + 1 + a, (unsigned long long)(row0 + r));
-        return;
-    }
-    if (o.kind == ACC_TOP2ROW) {     // o.xform carries the row order
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            if (r >= cnt) continue;
-            const uint32_t row = row0 + r;
-            const unsigned long long k = o.xform == AQ_ROWS_DESC ? (unsigned long long)row + 1ull : (unsigned long long)(0xffffffffu - row);
-            unsigned long long* c = slot_word(p, slot[r]) + 1 + a;
-            unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(c);
-            for (;;) {
-                const unsigned long long best = old >> 32, second = old & 0xffffffffull;
-                unsigned long long nw;
-                if (k > best) nw = (k << 32) | best;
-                else if (k > second) nw = (best << 32) | k;
-                else break;
-                const unsigned long long seen = atomicCAS(c, old, nw);
-                if (seen == old) break;
-                old = seen;
-            }
-        }
-        return;
-    }
-    long long xi[4]; double xd[4];
-    acc_inputs(o, row0, cnt, xi, xd);
-    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        if (r >= cnt) continue;
-        unsigned long long* c = slot_word(p, slot[r]) + 1 + a;
-        switch (o.kind) {
-        case ACC_ADD_I64: atomicAdd(c, (unsigned long long)xi[r]); break;
-        case ACC_ADD_F64: atomicAdd(reinterpret_cast<double*>(c), isint ? (double)xi[r] : xd[r]); break;
-        case ACC_MIN_I64: atomicMin(reinterpret_cast<long long*>(c), isint ? xi[r] : f64_to_ordered(xd[r])); break;
-        case ACC_MAX_I64: atomicMax(reinterpret_cast<long long*>(c), isint ? xi[r] : f64_to_ordered(xd[r])); break;
-        default: break;
-        }
-    }
 }
 
 // One thread = 4 consecutive rows per iteration: 128-bit coalesced loads of every column.
@@ -451,29 +355,52 @@ __device__ void emit_one(const EmitAgg& e, const unsigned long long* __restrict_
     }
 }
 
+// Emit in ROW order: a warp walks 32 bitmap words (1024 rows) at a time; lane b of the warp owns row
+// 32*word + b.  A set bit = the first row of a group, whose gid is the rank of that bit.  The key
+// columns are read where they lie (coalesced for dense bitmaps), the group's slot is found again by
+// hashing the row's key (word 0 of the slot == tag << 32 | row exactly), and every output column is
+// written at consecutive gids by consecutive lanes.  One random 32-byte sector read per group.
 __global__ void __launch_bounds__(256)
-k_emit(const unsigned long long* __restrict__ tab, const uint32_t cap, const uint32_t sw,
-       const uint32_t* __restrict__ bitmap, const uint32_t* __restrict__ wordprefix, const KeyOut ko,
-       uint32_t* __restrict__ first_row_out, uint32_t* __restrict__ counts_out, uint32_t* __restrict__ last_row_out,
-       uint32_t* __restrict__ slot_gid, const EmitProg ep, const int cnt_acc, const int maxrow_acc,
-       const uint32_t max_groups, const uint32_t* __restrict__ flags) {
+k_emit_rows(const KeySpec ks, const unsigned long long* __restrict__ tab, const uint32_t mask, const uint32_t sw,
+            const uint32_t* __restrict__ bitmap, const uint32_t* __restrict__ wordprefix, const uint32_t nwords,
+            const KeyOut ko, uint32_t* __restrict__ first_row_out, uint32_t* __restrict__ counts_out,
+            uint32_t* __restrict__ last_row_out, uint32_t* __restrict__ slot_gid, const EmitProg ep,
+            const int cnt_acc, const int maxrow_acc, const uint32_t max_groups, const uint32_t* __restrict__ flags) {
     if (flags[FLAG_ABORT] != 0 || flags[FLAG_NGROUPS] > max_groups) return;   // host reports the error
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < cap; s += gridDim.x * blockDim.x) {
-        const unsigned long long* sl = tab + size_t(s) * sw;
-        const unsigned long long w = sl[0];
-        if (w == SLOT_EMPTY) continue;
-        const uint32_t fr = (uint32_t)w;
-        const uint32_t gid = wordprefix[fr >> 5] + __popc(bitmap[fr >> 5] & ((1u << (fr & 31)) - 1u));
-        if (slot_gid) slot_gid[s] = gid;
-        if (first_row_out) first_row_out[gid] = fr;
-        if (counts_out) counts_out[gid] = (uint32_t)sl[1 + cnt_acc];
-        if (last_row_out) last_row_out[gid] = (uint32_t)sl[1 + maxrow_acc];
-        for (int k = 0; k < ko.n; ++k) {
-            if (!ko.dst[k]) continue;
-            if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[gid] = static_cast<const uint32_t*>(ko.src[k])[fr];
-            else static_cast<unsigned long long*>(ko.dst[k])[gid] = static_cast<const unsigned long long*>(ko.src[k])[fr];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nchunks = (nwords + 31u) >> 5;
+    for (uint32_t chunk = gwarp; chunk < nchunks; chunk += nwarps) {
+        const uint32_t wi = chunk * 32u + lane;
+        const uint32_t word = wi < nwords ? bitmap[wi] : 0u;
+        const uint32_t pfx = wi < nwords ? wordprefix[wi] : 0u;
+        uint32_t m = __ballot_sync(0xffffffffu, word != 0u);
+        while (m) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1u;
+            const uint32_t w = __shfl_sync(0xffffffffu, word, j);
+            const uint32_t p = __shfl_sync(0xffffffffu, pfx, j);
+            if (!((w >> lane) & 1u)) continue;
+            const uint32_t fr = (chunk * 32u + j) * 32u + lane;
+            const uint32_t gid = p + __popc(w & ((1u << lane) - 1u));
+            uint32_t tag, hsh;
+            key_tag1(ks, fr, tag, hsh);
+            const unsigned long long want = ((unsigned long long)tag << 32) | fr;
+            uint32_t s = hsh & mask;
+            while (tab[size_t(s) * sw] != want) s = (s + 1u) & mask;
+            const unsigned long long* sl = tab + size_t(s) * sw;
+            if (slot_gid) slot_gid[s] = gid;
+            if (first_row_out) first_row_out[gid] = fr;
+            if (counts_out) counts_out[gid] = (uint32_t)sl[1 + cnt_acc];
+            if (last_row_out) last_row_out[gid] = (uint32_t)sl[1 + maxrow_acc];
+            for (int k = 0; k < ko.n; ++k) {
+                if (!ko.dst[k]) continue;
+                if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[gid] = static_cast<const uint32_t*>(ko.src[k])[fr];
+                else static_cast<unsigned long long*>(ko.dst[k])[gid] = static_cast<const unsigned long long*>(ko.src[k])[fr];
+            }
+            for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], sl, gid, fr, ep.row_order);
         }
-        for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], sl, gid, fr, ep.row_order);
     }
 }
 
@@ -541,7 +468,7 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
         AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         AQ_CUDA(cudaStreamSynchronize(c.stream));
         const uint32_t st = c.h_flags[FLAG_ABORT];
-        if (st == 0) { *ngroups = c.h_flags[FLAG_NGROUPS]; return 0; }
+        if (st == 0) { *ngroups = c.h_flags[FLAG_NGROUPS]; hr.ks = ks; return 0; }
         if (st == 2 || st == 4) { allow_smem = false; continue; }   // CTA-local overflow / inexact fp: global path
         if (st == 3) {                                              // a key outside the caller's bounds
             if (ks.exact != 2) return fail("internal: bounds flag without packed keys");
@@ -555,13 +482,14 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
     return fail("hash build did not converge");
 }
 
-int emit_groups(const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row, uint32_t* d_counts,
-                uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups) {
+int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
+                uint32_t* d_counts, uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups) {
     const int cnt_acc = plan.find(ACC_COUNT), maxrow_acc = plan.find(ACC_MAXROW);
     if (d_counts && cnt_acc < 0) return fail("internal: counts requested without a COUNT accumulator");
     if (d_last_row && maxrow_acc < 0) return fail("internal: last rows requested without a MAXROW accumulator");
-    AQ_LAUNCH(k_emit, grid_for(hr.cap, 256, 2), 256, 0, hr.tab.as<unsigned long long>(), hr.cap, hr.sw,
-              hr.bitmap.as<uint32_t>(), hr.wordprefix.as<uint32_t>(), ko, d_first_row, d_counts, d_last_row,
+    const uint32_t nwords = (nrows + 31) / 32;
+    AQ_LAUNCH(k_emit_rows, grid_for((nwords + 31) / 32, 8, 1, 8), 256, 0, ks, hr.tab.as<unsigned long long>(), hr.cap - 1, hr.sw,
+              hr.bitmap.as<uint32_t>(), hr.wordprefix.as<uint32_t>(), nwords, ko, d_first_row, d_counts, d_last_row,
               d_slot_gid, plan.emit, cnt_acc, maxrow_acc, max_groups, ctx().d_flags);
     return 0;
 }
@@ -630,7 +558,7 @@ extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, 
     uint32_t* d_fr = nullptr;
     if (out_first_row) { AQ_TRY(fr.bind(out_first_row, size_t(4) * max_groups)); d_fr = static_cast<uint32_t*>(fr.d); }
 
-    AQ_TRY(emit_groups(hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
+    AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
     bool any_host = false;
     for (int a = 0; a < n_aggs; ++a) { AQ_TRY(vout[a].finish(dtype_size(plan.emit.agg[a].out_type) * ng)); any_host |= vout[a].host != nullptr; }
     for (int k = 0; k < nkeys; ++k) if (ko.dst[k]) { AQ_TRY(kout[k].finish(size_t(ko.size[k]) * ng)); any_host |= kout[k].host != nullptr; }

@@ -123,6 +123,7 @@ struct AggPlan {
 struct HashResult {
     uint32_t cap = 0;
     uint32_t sw = 0;
+    KeySpec ks;                   // the key spec the table was finally built with (bounds may have been dropped)
     DevBuf tab;                   // cap x sw u64
     DevBuf bitmap;                // nrows bits: first-appearance rows
     DevBuf wordprefix;            // per bitmap word: number of groups before it
@@ -134,8 +135,8 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
                    uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups);
 
 // Writes keys / first rows / aggregates in first-appearance order (gid = rank of the first row).
-int emit_groups(const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row, uint32_t* d_counts,
-                uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups);
+int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
+                uint32_t* d_counts, uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups);
 
 // smem-privatised scan (groupby_smem.cu).  *used = false if the request does not qualify.
 int launch_smem_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t max_probe,
@@ -217,6 +218,23 @@ __device__ __forceinline__ bool key_tags4(const KeySpec& ks, uint32_t row0, int 
     return ok;
 }
 
+// tag / slot hash of ONE row (same values as key_tags4 produces for it); bounds are not re-checked.
+__device__ __forceinline__ void key_tag1(const KeySpec& ks, uint32_t row, uint32_t& tag, uint32_t& hsh) {
+    if (ks.exact) {
+        uint32_t t = 0;
+        for (int w = 0; w < ks.nwords; ++w) {
+            const uint32_t kw = __ldg(ks.base[w] + row);
+            if (ks.exact == 1) t = kw;
+            else t |= (kw - ks.pack_lo[w]) << ks.pack_shift[w];
+        }
+        tag = t; hsh = mix32(t);
+    } else {
+        uint64_t h = 0x9e3779b97f4a7c15ULL;
+        for (int w = 0; w < ks.nwords; ++w) h = mix64(h ^ __ldg(ks.base[w] + size_t(row) * ks.stride[w]));
+        tag = (uint32_t)(h >> 32); hsh = (uint32_t)h;
+    }
+}
+
 // find-or-insert in the global table; keeps the smallest row id in the low half of word 0.
 template <bool EXACT>
 __device__ __forceinline__ uint32_t probe_insert(const KeySpec& ks, unsigned long long* tab, uint32_t sw,
@@ -242,6 +260,97 @@ __device__ __forceinline__ uint32_t probe_insert(const KeySpec& ks, unsigned lon
     }
     return NOSLOT;
 }
+// value column -> 4 (int64 image | double image) values
+__device__ __forceinline__ void load4_val(const void* v, int vtype, uint32_t row0, int cnt, bool vec,
+                                          long long iv[4], double dv[4], float fv[4]) {
+    if (vtype == AQ_INT32 || vtype == AQ_FLOAT) {
+        uint32_t u[4];
+        load4_b32(v, row0, cnt, vec, u);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (vtype == AQ_INT32) { iv[r] = (long long)(int)u[r]; }
+            else { fv[r] = __uint_as_float(u[r]); dv[r] = (double)fv[r]; }
+        }
+    } else {
+        unsigned long long u[4];
+        load4_b64(v, row0, cnt, vec, u);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (vtype == AQ_INT64) iv[r] = (long long)u[r];
+            else dv[r] = __longlong_as_double((long long)u[r]);
+        }
+    }
+}
+
+// x[r] for one accumulator: integer image in xi (int columns), double image in xd (fp columns)
+__device__ __forceinline__ void acc_inputs(const AccOp& o, uint32_t row0, int cnt, long long xi[4], double xd[4]) {
+    long long iv[4] = {0, 0, 0, 0}; double dv[4] = {0, 0, 0, 0}; float fv[4] = {0, 0, 0, 0};
+    load4_val(o.v, o.vtype, row0, cnt, o.vec_ok, iv, dv, fv);
+    if (o.xform == X_IDENT) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { xi[r] = iv[r]; xd[r] = dv[r]; }
+        return;
+    }
+    long long iw[4] = {0, 0, 0, 0}; double dw[4] = {0, 0, 0, 0}; float fw[4] = {0, 0, 0, 0};
+    if (o.xform == X_PRODUCT) {
+        load4_val(o.v2, o.vtype, row0, cnt, o.vec_ok, iw, dw, fw);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { iw[r] = iv[r]; dw[r] = dv[r]; fw[r] = fv[r]; }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        xi[r] = iv[r] * iw[r];
+        // the reference multiplies in the column's own type before widening (aggregations.h:339-345)
+        xd[r] = o.vtype == AQ_FLOAT ? (double)__fmul_rn(fv[r], fw[r]) : __dmul_rn(dv[r], dw[r]);
+    }
+}
+
+// packed top-2 cell update (see ACC_TOP2ROW): k = row key, larger is better
+__device__ __forceinline__ void top2_update(unsigned long long* c, unsigned long long k) {
+    unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(c);
+    for (;;) {
+        const unsigned long long best = old >> 32, second = old & 0xffffffffull;
+        unsigned long long nw;
+        if (k > best) nw = (k << 32) | best;
+        else if (k > second && k != best) nw = (best << 32) | k;
+        else break;
+        const unsigned long long seen = atomicCAS(c, old, nw);
+        if (seen == old) break;
+        old = seen;
+    }
+}
+__device__ __forceinline__ unsigned long long top2_key(int row_order, uint32_t row) {
+    return row_order == AQ_ROWS_DESC ? (unsigned long long)row + 1ull : (unsigned long long)(0xffffffffu - row);
+}
+
+// one row's contribution to accumulator cell c of the GLOBAL table
+__device__ __forceinline__ void acc_global_row(const AccOp& o, unsigned long long* c, uint32_t row, long long xi, double xd) {
+    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
+    switch (o.kind) {
+    case ACC_COUNT: atomicAdd(c, 1ull); break;
+    case ACC_MAXROW: atomicMax(c, (unsigned long long)row); break;
+    case ACC_TOP2ROW: top2_update(c, top2_key(o.xform, row)); break;
+    case ACC_ADD_I64: atomicAdd(c, (unsigned long long)xi); break;
+    case ACC_ADD_F64: atomicAdd(reinterpret_cast<double*>(c), isint ? (double)xi : xd); break;
+    case ACC_MIN_I64: atomicMin(reinterpret_cast<long long*>(c), isint ? xi : f64_to_ordered(xd)); break;
+    case ACC_MAX_I64: atomicMax(reinterpret_cast<long long*>(c), isint ? xi : f64_to_ordered(xd)); break;
+    default: break;
+    }
+}
+__device__ __forceinline__ bool acc_needs_value(const AccOp& o) {
+    return o.kind != ACC_COUNT && o.kind != ACC_MAXROW && o.kind != ACC_TOP2ROW;
+}
+
+__device__ __forceinline__ void acc_apply(const AccProg& p, int a, const uint32_t slot[4], uint32_t row0, int cnt) {
+    const AccOp& o = p.op[a];
+    long long xi[4] = {0, 0, 0, 0}; double xd[4] = {0, 0, 0, 0};
+    if (acc_needs_value(o)) acc_inputs(o, row0, cnt, xi, xd);
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        if (r < cnt) acc_global_row(o, slot_word(p, slot[r]) + 1 + a, row0 + r, xi[r], xd[r]);
+}
+
 #endif
 
 } // namespace aq

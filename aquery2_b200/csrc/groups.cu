@@ -162,7 +162,7 @@ int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys
     AQ_TRY(g->counts.alloc_zero(size_t(ng + 1) * 4));
     DevBuf slot_gid;
     AQ_TRY(slot_gid.alloc(size_t(hr.cap) * 4));
-    AQ_TRY(emit_groups(hr, ko, g->first_row.as<uint32_t>(), g->counts.as<uint32_t>(), g->last_row.as<uint32_t>(),
+    AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, g->first_row.as<uint32_t>(), g->counts.as<uint32_t>(), g->last_row.as<uint32_t>(),
                        slot_gid.as<uint32_t>(), plan, ng));
     AQ_TRY(g->gid.alloc(size_t(nrows) * 4));
     AQ_LAUNCH(k_map_gid, grid_for(nrows, 256, 1, 32), 256, 0, row_slot.as<uint32_t>(), slot_gid.as<uint32_t>(), nrows,

@@ -91,6 +91,14 @@ int AggPlan::add_acc(int kind, int xform, int vtype, const void* v, const void* 
     AccOp& o = prog.op[n_acc];
     o.kind = kind; o.xform = xform; o.vtype = vtype; o.v = v; o.v2 = v2;
     o.vec_ok = ((reinterpret_cast<uintptr_t>(v) & 15) == 0) && ((reinterpret_cast<uintptr_t>(v2) & 15) == 0);
+    auto col_index = [&](const void* p) -> int {
+        if (!p || prog.nv < 0) return -1;
+        for (int j = 0; j < prog.nv; ++j) if (prog.vcol[j] == p) return j;
+        if (prog.nv >= MAX_VCOL) { prog.nv = -1; return -1; }
+        prog.vcol[prog.nv] = p; prog.vctype[prog.nv] = vtype;
+        return prog.nv++;
+    };
+    o.ci = col_index(v); o.ci2 = col_index(v2);
     prog.n = ++n_acc;
     return n_acc - 1;
 }

@@ -58,7 +58,9 @@ struct AccOp {
     int vec_ok;        // v (and v2) 16-byte aligned
     const void* v;
     const void* v2;
+    int ci, ci2;       // index of v / v2 in AccProg::vcol (-1: none or table full)
 };
+constexpr int MAX_VCOL = 4;
 // Global table: cap slots of `sw` 64-bit words; word 0 = (tag << 32 | min row) or SLOT_EMPTY,
 // word 1 + a = accumulator a.  sw is a power of two so that a slot never straddles a 32 B sector
 // boundary more than necessary (sw = 4 -> exactly one sector).
@@ -67,6 +69,10 @@ struct AccProg {
     int n;
     unsigned long long* tab;
     uint32_t sw;
+    // distinct value columns (kernels that load every column once per row batch, up front)
+    const void* vcol[MAX_VCOL];
+    int vctype[MAX_VCOL];
+    int nv;            // -1: more than MAX_VCOL distinct columns
 };
 __host__ __device__ __forceinline__ unsigned long long* slot_word(const AccProg& p, uint32_t slot) {
     return p.tab + size_t(slot) * p.sw;

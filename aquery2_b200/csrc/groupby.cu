@@ -448,7 +448,7 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
     for (int i = 0; i < 16; ++i) pat.w[i] = 0;
     pat.w[0] = SLOT_EMPTY;
     for (int a = 0; a < plan.n_acc; ++a) pat.w[1 + a] = acc_identity(plan.prog.op[a].kind);
-    bool allow_smem = d_row_slot == nullptr;
+    bool allow_smem = d_row_slot == nullptr, allow_part = d_row_slot == nullptr;
 
     for (int attempt = 0; attempt < 16; ++attempt) {
         hr.cap = cap;
@@ -461,9 +461,10 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
         AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
         AQ_CUDA(cudaMemsetAsync(hr.bitmap.p, 0, size_t(nwords_bm) * 4, c.stream));
 
-        bool used_smem = false;
+        bool used_smem = false, used_part = false;
         if (allow_smem && nrows) AQ_TRY(launch_smem_probe(ks, nrows, cap, max_probe, plan.prog, groups_hint, &used_smem));
-        if (!used_smem && nrows) {
+        if (!used_smem && allow_part && nrows) AQ_TRY(launch_part_probe(ks, nrows, cap, max_probe, plan.prog, groups_hint, &used_part));
+        if (!used_smem && !used_part && nrows) {
             const int grid = grid_for((nrows + 3) / 4, 256, 1, 16);
             if (ks.exact) AQ_LAUNCH(k_probe_agg<true>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
             else AQ_LAUNCH(k_probe_agg<false>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
@@ -477,7 +478,7 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
         AQ_CUDA(cudaStreamSynchronize(c.stream));
         const uint32_t st = c.h_flags[FLAG_ABORT];
         if (st == 0) { *ngroups = c.h_flags[FLAG_NGROUPS]; hr.ks = ks; return 0; }
-        if (st == 2 || st == 4) { allow_smem = false; continue; }   // CTA-local overflow / inexact fp: global path
+        if (st == 2 || st == 4) { if (used_part) allow_part = false; else allow_smem = false; continue; }   // CTA-local overflow / inexact fp: global path
         if (st == 3) {                                              // a key outside the caller's bounds
             if (ks.exact != 2) return fail("internal: bounds flag without packed keys");
             ks.exact = 0; ks.pack_bits = 0;

@@ -147,6 +147,9 @@ int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const K
 // smem-privatised scan (groupby_smem.cu).  *used = false if the request does not qualify.
 int launch_smem_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t max_probe,
                       const AccProg& prog, uint32_t groups_hint, bool* used);
+// partitioned aggregation (groupby_part.cu) for groups beyond one SM's shared memory; same contract.
+int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t max_probe,
+                      const AccProg& prog, uint32_t groups_hint, bool* used);
 
 #ifdef __CUDACC__
 // ---- device helpers shared by the probe kernels ------------------------------------------------

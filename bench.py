@@ -233,7 +233,7 @@ def run_b200(args, queries):
     top = max(prof.items(), key=lambda kv: kv[1][1]) if prof else None
     roofline = None
     kernels = {}
-    for name, (calls, tot_ms) in sorted(prof.items(), key=lambda kv: -kv[1][1])[:12]:
+    for name, (calls, tot_ms) in sorted(prof.items(), key=lambda kv: -kv[1][1])[:80]:
         kernels[name] = {"calls": calls, "ms_per_launch": tot_ms / calls}
     if top:
         name, (calls, tot_ms) = top

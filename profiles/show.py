@@ -6,4 +6,4 @@ for f in sys.argv[1:]:
     if d.get("e2e"): print("  e2e %.3e"%d["e2e"]["value"])
     if d.get("cpu_baseline"): print("  cpu %.3e"%d["cpu_baseline"]["value"])
     for q,v in d["per_query"].items(): print("  %-4s %9.2f ms %10.3e rows/s  hbm_frac %.3f groups %d"%(q, v["ms"], v["rows_per_s"], v["hbm_frac"], v["groups"]))
-    for k,v in list(d["kernels"].items())[:10]: print("   ", k, v)
+    for k,v in list(d["kernels"].items())[:14]: print("   ", k, v)

@@ -211,3 +211,46 @@ def test_high_cardinality_and_collisions(gpu, port):
     check_query_vs_oracle(gpu, port, t, ["a", "b"], [("sum", "v"), ("count",)])
     check_query_vs_oracle(gpu, port, t, ["k64"], [("sum", "v")])
     check_query_vs_oracle(gpu, port, t, ["b", "k64", "a"], [("max", "v")])
+
+
+# ---- partitioned path (groupby_part.cu): groups beyond one SM's shared memory ---------------------
+ALL_AGGS = [("sum", "v1"), ("avg", "v3"), ("min", "v2"), ("max", "v3"), ("count",), ("first", "v3"), ("last", "v1"),
+            ("second", "v3")]
+
+
+@pytest.mark.parametrize("n,k", [(1_000_000, 20), (300_003, 3)])
+def test_partitioned_one_key(gpu, port, n, k):
+    """id3 has n/k distinct values: with a groups_hint the library hash-partitions the rows
+    (HASH32 tables without bounds, directly indexed tables with bounds); all three must agree."""
+    t = synth.h2o_table(n, k, seed=7, columns=["id3", "id6", "v1", "v2", "v3"])
+    g = n // k
+    for bounds in (None, [(1, g)], [(1, g // 2)]):            # last: wrong bounds -> silent retry without them
+        for aggs in (ALL_AGGS[:2], ALL_AGGS[2:5], ALL_AGGS[5:], [("sum", "v1"), ("sum", "v2"), ("sum", "v3")],
+                     [("var", "v3"), ("stddev", "v1")]):
+            check_query_vs_oracle(gpu, port, t, ["id3"], aggs, groups_hint=g, key_bounds=bounds)
+
+
+def test_partitioned_two_keys(gpu, port):
+    """two key columns: bit-packed tag with bounds (q6 / q9 shape), 64-bit shared-memory keys without"""
+    n, k = 600_000, 200
+    t = synth.h2o_table(n, k, seed=11, columns=["id2", "id4", "v1", "v2", "v3"])
+    rng = np.random.default_rng(1)
+    t["wide"] = (rng.integers(0, 30_000, n).astype(np.int64) * 70_001 - 1_000_000_000).astype(np.int32)
+    for keys, bounds, hint in ((["id2", "id4"], [(1, k), (1, k)], k * k), (["id2", "id4"], None, k * k),
+                               (["wide", "id4"], None, 200_000)):
+        check_query_vs_oracle(gpu, port, t, keys, [("corr", "v1", "v2"), ("stddev", "v3")], groups_hint=hint, key_bounds=bounds)
+        check_query_vs_oracle(gpu, port, t, keys, [("sum", "v1"), ("max", "v2"), ("count",), ("first", "v3")], groups_hint=hint, key_bounds=bounds)
+
+
+def test_partitioned_hint_too_small_and_special_keys(gpu, port):
+    """a hint far below the real group count (tables overflow into the global table) and keys equal
+    to the EMPTY markers of the shared-memory tables"""
+    n = 500_000
+    rng = np.random.default_rng(5)
+    key = rng.integers(0, 200_000, n).astype(np.int32)
+    key[::1000] = -1                                          # 0xffffffff == EMPTY32
+    t = {"k": key, "k2": np.where(key == -1, -1, key % 7).astype(np.int32), "v": rng.integers(-5, 50, n).astype(np.int32),
+         "f": rng.random(n).astype(np.float32)}
+    check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "f"), ("count",)], groups_hint=20_000)
+    check_query_vs_oracle(gpu, port, t, ["k", "k2"], [("sum", "v"), ("min", "f")], groups_hint=20_000)
+    check_query_vs_oracle(gpu, port, t, ["k", "k2"], [("sum", "v"), ("min", "f")], groups_hint=400_000)

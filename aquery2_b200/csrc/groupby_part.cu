@@ -7,31 +7,40 @@
 // memory (one streaming read of the needed columns, one write and one read of 16..32-byte tuples), and
 // every bucket is then aggregated exactly like groupby_smem.cu does, in shared memory.
 //
-//   k_part_hist     per-partition row counts (one pass over the key columns)
-//   k_part_scan     exclusive scan -> partition offsets, write cursors, work units of <= chunk tuples
-//   k_part_scatter  tuple [row, tag | k0 k1, v0..] of every row -> its partition's range
+//   k_part_hist     row counts per (partition, scatter CTA): one pass over the key columns
+//   k_part_pad, exclusive_scan_u32, k_part_units
+//                   fixed tuple range of every (partition, CTA), partition offsets, work units
+//   k_part_scatter  tuple [row, tag | k0 k1, v0..] of every row -> staged in shared memory per
+//                   partition, written out in whole sector-aligned blocks only
 //   k_part_agg      one CTA per work unit: shared-memory table, merged into the global table of
 //                   groupby.cu (which then ranks the groups by first row and emits, unchanged)
 //
 // Replaces the same reference loops as groupby.cu (server/hasher.h:176-198, server/table.h:184-189,
 // server/aggregations.h scalar aggregates); the partitioning itself has no reference counterpart.
 #include "groupby_smem.cuh"
+#include "sort.cuh"
 #include <cstring>
 
 namespace aq {
 
 enum PartMode : int { PM_DIRECT = 0, PM_HASH32 = 1, PM_HASH64 = 2 };
 constexpr int PART_THREADS = 512;
-constexpr int PART_MAX = 8192;            // partitions (shared histogram of the scatter kernel)
-constexpr int PART_TILE_QUADS = 2;        // quads of rows per thread per scatter tile
+constexpr int PART_MAX = 8192;            // partitions
+constexpr int PART_TILE_QUADS = 2;        // quads of rows per thread per tile
+constexpr int PART_TILE_ROWS = PART_THREADS * 4 * PART_TILE_QUADS;
+constexpr int PART_HIST_SPLIT = 4;        // CTAs of k_part_hist that share the tiles of one scatter CTA
 constexpr int PART_UNR = 4;               // tuples per thread per iteration of k_part_agg
+constexpr uint32_t PAD_ROW = 0xffffffffu; // row id of a padding tuple
 
 struct PartSpec {
     int mode;
     uint32_t nparts;
-    uint32_t dbits;        // PM_DIRECT: slot = tag & ((1 << dbits) - 1), partition = tag >> dbits
-    uint32_t chunk;        // tuples per work unit
-    int nkw;               // key words read from the columns (1 or 2)
+    uint32_t range;                 // PM_DIRECT: tags per partition; slot = tag - partition * range
+    unsigned long long magic;       // ceil(2^48 / range): partition = (tag * magic) >> 48, exact for tag < 2^31
+    uint32_t chunk;                 // tuples per work unit of k_part_agg
+    int nkw;                        // key words read from the columns (1 or 2)
+    uint32_t bsz;                   // tuples per staging block (one flush = bsz tuples = a whole number of sectors)
+    uint32_t ncta;                  // CTAs of k_part_scatter; (partition, CTA) owns a fixed range of tuples
 };
 
 __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) { return __umulhi(a, b); }
@@ -57,33 +66,37 @@ __device__ __forceinline__ void part_tag(const KeySpec& ks, uint32_t k0, uint32_
 }
 template <int MODE>
 __device__ __forceinline__ uint32_t part_of(const PartSpec& ps, uint32_t tag, uint32_t hsh) {
-    if (MODE == PM_DIRECT) return tag >> ps.dbits;
+    if (MODE == PM_DIRECT) return (uint32_t)(((unsigned long long)tag * ps.magic) >> 48);
     return mulhi32(hsh, ps.nparts);
 }
 __device__ __forceinline__ uint32_t local_start(uint32_t hsh, uint32_t cap) { return mulhi32(hsh * 0x9E3779B1u, cap); }
 
-// ---- phase 0: histogram ---------------------------------------------------------------------------
+// ---- phase 0: per-(partition, scatter CTA) row counts ------------------------------------------------
+// Tile t (PART_TILE_ROWS consecutive rows) belongs to scatter CTA t % ncta; the PART_HIST_SPLIT hist
+// CTAs of one scatter CTA take its tiles round robin and add their counts into cnt[p * ncta + c].
 template <int MODE>
 __global__ void __launch_bounds__(PART_THREADS)
-k_part_hist(const KeySpec ks, const uint32_t nrows, const PartSpec ps, uint32_t* __restrict__ ghist, uint32_t* __restrict__ flags) {
+k_part_hist(const KeySpec ks, const uint32_t nrows, const PartSpec ps, uint32_t* __restrict__ cnt, uint32_t* __restrict__ flags) {
     extern __shared__ uint32_t hist[];
     for (uint32_t b = threadIdx.x; b < ps.nparts; b += PART_THREADS) hist[b] = 0;
     __syncthreads();
+    const uint32_t c = blockIdx.x % ps.ncta, h = blockIdx.x / ps.ncta;
     const uint32_t nquad = (nrows + 3u) >> 2;
-    const uint32_t stride = gridDim.x * PART_THREADS;
+    const uint32_t tile_quads = PART_THREADS * PART_TILE_QUADS;
+    const uint32_t ntiles = (nquad + tile_quads - 1) / tile_quads;
     bool bad = false;
-    for (uint32_t q0 = blockIdx.x * PART_THREADS + threadIdx.x; q0 < nquad; q0 += 2 * stride) {
-        uint4 kr[2][2]; int cnts[2];
+    for (uint32_t tile = c + h * ps.ncta; tile < ntiles; tile += ps.ncta * PART_HIST_SPLIT) {
+        uint4 kr[PART_TILE_QUADS][2]; int cnts[PART_TILE_QUADS];
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const uint32_t q = q0 + i * stride;
+        for (int i = 0; i < PART_TILE_QUADS; ++i) {
+            const uint32_t q = tile * tile_quads + i * PART_THREADS + threadIdx.x;
             cnts[i] = q < nquad ? (int)min(4u, nrows - (q << 2)) : 0;
 #pragma unroll
             for (int w = 0; w < 2; ++w)
                 kr[i][w] = (w < ps.nkw && cnts[i]) ? load_quad(ks.base[w], q << 2, cnts[i], ks.vec_ok) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < PART_TILE_QUADS; ++i)
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 if (r >= cnts[i]) continue;
@@ -97,12 +110,18 @@ k_part_hist(const KeySpec ks, const uint32_t nrows, const PartSpec ps, uint32_t*
     if (bad) atomicExch(flags + FLAG_ABORT, 3u);      // a key outside the caller's bounds
     __syncthreads();
     for (uint32_t b = threadIdx.x; b < ps.nparts; b += PART_THREADS) {
-        const uint32_t c = hist[b];
-        if (c) atomicAdd(ghist + b, c);
+        const uint32_t v = hist[b];
+        if (v) atomicAdd(cnt + size_t(b) * ps.ncta + c, v);
     }
 }
 
-// ---- phase 0b: offsets, cursors, work units (single CTA) --------------------------------------------
+// counts -> sizes of the (partition, CTA) ranges: rounded up to whole staging blocks
+__global__ void k_part_pad(uint32_t* __restrict__ cnt, uint32_t n, uint32_t bsz) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        cnt[i] = (cnt[i] + bsz - 1u) / bsz * bsz;
+}
+
+// ---- phase 0b: partition offsets and work units (single CTA) ------------------------------------------
 constexpr int PSCAN_THREADS = 1024;
 __device__ __forceinline__ uint32_t pscan_block_excl(uint32_t v, uint32_t* sm /* 33 words */) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -122,42 +141,36 @@ __device__ __forceinline__ uint32_t pscan_block_excl(uint32_t v, uint32_t* sm /*
     __syncthreads();
     return r;
 }
+// pos = exclusive scan of the padded counts (nparts * ncta + 1 entries, partition-major)
 __global__ void __launch_bounds__(PSCAN_THREADS)
-k_part_scan(const uint32_t* __restrict__ ghist, uint32_t nparts, uint32_t chunk, uint32_t* __restrict__ offsets,
-            uint32_t* __restrict__ cursor, uint32_t* __restrict__ unit_off) {
+k_part_units(const uint32_t* __restrict__ pos, uint32_t nparts, uint32_t ncta, uint32_t chunk,
+             uint32_t* __restrict__ offsets, uint32_t* __restrict__ unit_off) {
     __shared__ uint32_t sm[33];
     constexpr int PER = PART_MAX / PSCAN_THREADS;
-    uint32_t c[PER], u[PER], sc = 0, su = 0;
+    uint32_t u[PER], su = 0;
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const uint32_t b = threadIdx.x * PER + i;
-        c[i] = b < nparts ? ghist[b] : 0u;
-        u[i] = (c[i] + chunk - 1u) / chunk;
-        sc += c[i]; su += u[i];
+        u[i] = 0;
+        if (b < nparts) {
+            const uint32_t lo = pos[size_t(b) * ncta], hi = pos[size_t(b + 1) * ncta];
+            offsets[b] = lo;
+            if (b + 1 == nparts) offsets[nparts] = hi;
+            u[i] = (hi - lo + chunk - 1u) / chunk;
+        }
+        su += u[i];
     }
-    uint32_t ec = pscan_block_excl(sc, sm);
     uint32_t eu = pscan_block_excl(su, sm);
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const uint32_t b = threadIdx.x * PER + i;
-        if (b < nparts) { offsets[b] = ec; cursor[b] = ec; unit_off[b] = eu; }
-        ec += c[i]; eu += u[i];
-        if (b + 1 == nparts) { offsets[nparts] = ec; unit_off[nparts] = eu; }
+        if (b < nparts) unit_off[b] = eu;
+        eu += u[i];
+        if (b + 1 == nparts) unit_off[nparts] = eu;
     }
 }
 
 // ---- phase 1: scatter -------------------------------------------------------------------------------
-template <int TW>
-__device__ __forceinline__ void store_tuple(uint32_t* __restrict__ dst, const uint32_t (&w)[TW]) {
-    if (TW == 4) *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
-    else if (TW == 8) {
-        reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
-        reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4 % TW], w[5 % TW], w[6 % TW], w[7 % TW]);
-    } else {
-#pragma unroll
-        for (int i = 0; i < TW; i += 2) reinterpret_cast<uint2*>(dst)[i >> 1] = make_uint2(w[i], w[(i + 1) % TW]);
-    }
-}
 template <int TW>
 __device__ __forceinline__ void load_tuple(const uint32_t* __restrict__ src, uint32_t (&w)[TW]) {
     if (TW == 4) { const int4 t = ld_stream_v4(src); w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w; }
@@ -170,79 +183,154 @@ __device__ __forceinline__ void load_tuple(const uint32_t* __restrict__ src, uin
     }
 }
 
-// One tile = PART_THREADS * 4 * PART_TILE_QUADS consecutive rows.  rank inside (tile, partition) = value
-// returned by the shared atomicAdd; one global atomicAdd per non-empty (tile, partition) reserves
-// the run in the partition's range.  NKT = key words carried in the tuple.
+// Random 16-byte stores reach 23 Gtuples/s on B200 (partial sectors are read back from DRAM), whole
+// 128-byte lines 286 Gtuples/s (profiles/r01/microbench.txt: mb_scatter).  So every CTA stages the
+// tuples per partition in shared memory, bsz tuples per partition, and only ever writes whole blocks
+// (bsz * TW * 4 bytes, a multiple of 32 and sector-aligned) to the range it owns inside the partition
+// (fixed by k_part_hist + scan: no cursors, no global atomics, deterministic layout).  The row that
+// takes the last position of a block puts the partition on a work list; after a barrier the warps
+// copy the listed blocks out.  Rows that found their block full wait for the next round of the same
+// tile.  The last, partly filled block of every (partition, CTA) is completed with padding tuples
+// (row = PAD_ROW).  The columns of the next tile are loaded while the current one is staged.
 template <int MODE, int TW>
-__global__ void __launch_bounds__(PART_THREADS, 2)
+__global__ void __launch_bounds__(PART_THREADS, 1)
 k_part_scatter(const KeySpec ks, const AccProg prog, const uint32_t nrows, const PartSpec ps,
-               uint32_t* __restrict__ cursor, uint32_t* __restrict__ tuples, const uint32_t* __restrict__ flags) {
+               const uint32_t* __restrict__ pos, uint32_t* __restrict__ tuples, const uint32_t* __restrict__ flags) {
     constexpr int NKT = MODE == PM_HASH64 ? 2 : 1;
     constexpr int VB = 1 + NKT;
+    constexpr int NV = TW - VB < MAX_VCOL ? TW - VB : MAX_VCOL;     // value columns a tuple can carry
     constexpr int NQ = PART_TILE_QUADS;
-    extern __shared__ uint32_t hist[];
+    constexpr int NW = PART_THREADS / 32;
+    extern __shared__ __align__(16) uint32_t psm[];
+    __shared__ uint32_t wl_n[2];
     if (flags[FLAG_ABORT]) return;
-    for (uint32_t b = threadIdx.x; b < ps.nparts; b += PART_THREADS) hist[b] = 0;
+    const uint32_t P = ps.nparts, B = ps.bsz;
+    uint32_t* const fill = psm;
+    uint32_t* const wpos = psm + P;
+    uint32_t* const wl = psm + 2 * P;                           // work list: partitions with a complete block
+    uint32_t* const stage = psm + ((3 * P + 3) & ~3u);          // [P][B][TW] words, 16-byte aligned
+    for (uint32_t b = threadIdx.x; b < P; b += PART_THREADS) { fill[b] = 0; wpos[b] = pos[size_t(b) * ps.ncta + blockIdx.x]; }
+    if (threadIdx.x < 2) wl_n[threadIdx.x] = 0;
     __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t U = B * TW / 4;                              // 16-byte units per block
+    const uint32_t G = U <= 32 ? 32 / U : 1;                    // blocks a warp copies per step
+    const uint32_t lane_b = U <= 32 ? lane / U : 0, lane_u = U <= 32 ? lane % U : lane;
+    // copies block `b` (whole) to its place; lanes [0, U) of the group (or the whole warp, strided)
+    auto copy_block = [&](uint32_t b, bool act) {
+        uint32_t dst = 0;
+        if (act) {
+            dst = wpos[b];
+            const uint4* s4 = reinterpret_cast<const uint4*>(stage) + size_t(b) * U;
+            uint4* d4 = reinterpret_cast<uint4*>(tuples + size_t(dst) * TW);
+            if (U <= 32) d4[lane_u] = s4[lane_u];
+            else for (uint32_t u = lane; u < U; u += 32) d4[u] = s4[u];
+        }
+        __syncwarp();
+        if (act && lane_u == 0) { const uint32_t f = fill[b]; fill[b] = f >= B ? f - B : 0u; wpos[b] = dst + B; }
+    };
     const uint32_t nquad = (nrows + 3u) >> 2;
     const uint32_t tile_quads = PART_THREADS * NQ;
     const uint32_t ntiles = (nquad + tile_quads - 1) / tile_quads;
-    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        uint4 kr[NQ][2], vr[NQ][MAX_VCOL];
-        int cnts[NQ];
+    uint4 kr[NQ][2], vr[NQ][NV > 0 ? NV : 1];
+    int cnts[NQ];
+    auto load_tile = [&](uint32_t tile, uint4 (&k)[NQ][2], uint4 (&v)[NQ][NV > 0 ? NV : 1], int (&c)[NQ]) {
 #pragma unroll
         for (int i = 0; i < NQ; ++i) {
             const uint32_t q = tile * tile_quads + i * PART_THREADS + threadIdx.x;
-            cnts[i] = q < nquad ? (int)min(4u, nrows - (q << 2)) : 0;
+            c[i] = (tile < ntiles && q < nquad) ? (int)min(4u, nrows - (q << 2)) : 0;
 #pragma unroll
             for (int w = 0; w < 2; ++w)
-                kr[i][w] = (w < ps.nkw && cnts[i]) ? load_quad(ks.base[w], q << 2, cnts[i], ks.vec_ok) : make_uint4(0, 0, 0, 0);
+                k[i][w] = (w < ps.nkw && c[i]) ? load_quad(ks.base[w], q << 2, c[i], ks.vec_ok) : make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (int j = 0; j < MAX_VCOL; ++j)
-                vr[i][j] = (j < prog.nv && j < TW - VB && cnts[i])
-                    ? load_quad(prog.vcol[j], q << 2, cnts[i], (reinterpret_cast<uintptr_t>(prog.vcol[j]) & 15) == 0) : make_uint4(0, 0, 0, 0);
+            for (int j = 0; j < (NV > 0 ? NV : 1); ++j)
+                v[i][j] = (j < prog.nv && j < NV && c[i])
+                    ? load_quad(prog.vcol[j], q << 2, c[i], (reinterpret_cast<uintptr_t>(prog.vcol[j]) & 15) == 0) : make_uint4(0, 0, 0, 0);
         }
-        uint32_t part[NQ][4], rank[NQ][4], ktag[NQ][4];
+    };
+    load_tile(blockIdx.x, kr, vr, cnts);
+    uint32_t round = 0;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        // partition and position inside the partition's staging sequence (carries over between tiles)
+        uint32_t part[NQ][4], spos[NQ][4], ktag[NQ][4];
 #pragma unroll
         for (int i = 0; i < NQ; ++i)
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                part[i][r] = 0xffffffffu; rank[i][r] = 0; ktag[i][r] = 0;
+                part[i][r] = 0; spos[i][r] = PAD_ROW; ktag[i][r] = 0;       // PAD_ROW = nothing (left) to place
                 if (r >= cnts[i]) continue;
                 uint32_t tag, hsh; bool oob = false;
                 part_tag(ks, lane4(kr[i][0], r), lane4(kr[i][1], r), tag, hsh, oob);
                 const uint32_t p = part_of<MODE>(ps, tag, hsh);
-                if (oob || p >= ps.nparts) continue;              // k_part_hist already raised the flag
+                if (oob || p >= P) continue;                              // k_part_hist already raised the flag
                 part[i][r] = p; ktag[i][r] = tag;
-                rank[i][r] = atomicAdd(&hist[p], 1u);
+                spos[i][r] = atomicAdd(&fill[p], 1u);
             }
-        __syncthreads();
-        for (uint32_t b = threadIdx.x; b < ps.nparts; b += PART_THREADS) {
-            const uint32_t c = hist[b];
-            if (c) hist[b] = atomicAdd(cursor + b, c);
+        uint4 nkr[NQ][2], nvr[NQ][NV > 0 ? NV : 1];
+        int ncnts[NQ];
+        load_tile(tile + gridDim.x, nkr, nvr, ncnts);                     // in flight while this tile is staged
+        for (;;) {
+            bool deferred = false;
+            uint32_t* const my_n = &wl_n[round & 1];
+#pragma unroll
+            for (int i = 0; i < NQ; ++i) {
+                const uint32_t row0 = (tile * tile_quads + i * PART_THREADS + threadIdx.x) << 2;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const uint32_t sp = spos[i][r];
+                    if (sp == PAD_ROW) continue;
+                    if (sp >= B) { spos[i][r] = sp - B; deferred = true; continue; }
+                    uint32_t w[TW];
+#pragma unroll
+                    for (int x = 0; x < TW; ++x) w[x] = 0;
+                    w[0] = row0 + r;
+                    if (MODE == PM_HASH64) { w[1] = lane4(kr[i][0], r); w[2 % TW] = lane4(kr[i][1], r); }
+                    else w[1] = ktag[i][r];
+#pragma unroll
+                    for (int j = 0; j < NV; ++j) w[(VB + j) % TW] = lane4(vr[i][j], r);
+                    uint32_t* d = stage + (size_t(part[i][r]) * B + sp) * TW;
+                    if (TW % 4 == 0) {
+#pragma unroll
+                        for (int x = 0; x < TW; x += 4) *reinterpret_cast<uint4*>(d + x) = make_uint4(w[x], w[(x + 1) % TW], w[(x + 2) % TW], w[(x + 3) % TW]);
+                    } else {
+#pragma unroll
+                        for (int x = 0; x < TW; x += 2) *reinterpret_cast<uint2*>(d + x) = make_uint2(w[x], w[(x + 1) % TW]);
+                    }
+                    if (sp == B - 1u) wl[atomicAdd(my_n, 1u)] = part[i][r];   // this row completes the block
+                    spos[i][r] = PAD_ROW;
+                }
+            }
+            const int more = __syncthreads_or(deferred ? 1 : 0);          // staged tuples + work list visible
+            const uint32_t n = *reinterpret_cast<volatile uint32_t*>(my_n);
+            if (threadIdx.x == 0) wl_n[(round + 1) & 1] = 0;
+            for (uint32_t e0 = wid * G; e0 < n; e0 += NW * G) {
+                const uint32_t e = e0 + lane_b;
+                const bool act = lane_b < G && e < n;
+                copy_block(act ? wl[e] : 0u, act);
+            }
+            __syncthreads();
+            ++round;
+            if (!more) break;
         }
-        __syncthreads();
 #pragma unroll
         for (int i = 0; i < NQ; ++i) {
-            const uint32_t row0 = (tile * tile_quads + i * PART_THREADS + threadIdx.x) << 2;
+            cnts[i] = ncnts[i];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                if (part[i][r] == 0xffffffffu) continue;
-                uint32_t w[TW];
+            for (int w = 0; w < 2; ++w) kr[i][w] = nkr[i][w];
 #pragma unroll
-                for (int x = 0; x < TW; ++x) w[x] = 0;
-                w[0] = row0 + r;
-                if (MODE == PM_HASH64) { w[1] = lane4(kr[i][0], r); w[2] = lane4(kr[i][1], r); }
-                else w[1] = ktag[i][r];
-#pragma unroll
-                for (int j = 0; j < MAX_VCOL; ++j) if (j < TW - VB) w[VB + (j < TW - VB ? j : 0)] = lane4(vr[i][j], r);
-                const uint32_t pos = hist[part[i][r]] + rank[i][r];
-                store_tuple<TW>(tuples + size_t(pos) * TW, w);
-            }
+            for (int j = 0; j < (NV > 0 ? NV : 1); ++j) vr[i][j] = nvr[i][j];
         }
-        __syncthreads();
-        for (uint32_t b = threadIdx.x; b < ps.nparts; b += PART_THREADS) hist[b] = 0;
-        __syncthreads();
+    }
+    // ---- the partly filled blocks: complete with padding tuples, then write them out
+    for (uint32_t i = threadIdx.x; i < P * B; i += PART_THREADS) {
+        const uint32_t b = i / B, t = i % B;
+        if (t >= fill[b]) stage[size_t(i) * TW] = PAD_ROW;
+    }
+    __syncthreads();
+    for (uint32_t b0 = wid * G; b0 < P; b0 += NW * G) {
+        const uint32_t b = b0 + lane_b;
+        const bool act = lane_b < G && b < P && fill[b < P ? b : 0] > 0;
+        copy_block(b, act);
     }
 }
 
@@ -318,7 +406,7 @@ k_part_agg(const KeySpec ks, const uint32_t* __restrict__ tuples, const uint32_t
     const uint32_t part = s_part;
     const uint32_t t_lo = offsets[part] + (unit - unit_off[part]) * ps.chunk;
     const uint32_t t_hi = min(offsets[part + 1], t_lo + ps.chunk);
-    const uint32_t dmask = (1u << ps.dbits) - 1u;
+    const uint32_t part_base = part * ps.range;      // PM_DIRECT: first tag of this partition
     bool dead = false;
 
     for (uint32_t base = t_lo; base < t_hi && !dead; base += PART_THREADS * UNR) {
@@ -329,7 +417,8 @@ k_part_agg(const KeySpec ks, const uint32_t* __restrict__ tuples, const uint32_t
             const uint32_t t = base + j * PART_THREADS + threadIdx.x;
             valid[j] = t < t_hi;
             if (valid[j]) load_tuple<TW>(tuples + size_t(t) * TW, w[j]);
-            else {
+            valid[j] = valid[j] && w[j][0] != PAD_ROW;
+            if (!valid[j]) {
 #pragma unroll
                 for (int x = 0; x < TW; ++x) w[j][x] = 0;
             }
@@ -342,7 +431,7 @@ k_part_agg(const KeySpec ks, const uint32_t* __restrict__ tuples, const uint32_t
             const uint32_t row = w[j][0];
             uint32_t s = NOSLOT, tag = w[j][1], hsh = 0;
             if (MODE == PM_DIRECT) {
-                s = tag & dmask;
+                s = tag - part_base;
             } else if (MODE == PM_HASH32) {
                 hsh = mix32(tag);
                 if (tag != EMPTY32) {
@@ -480,7 +569,7 @@ k_part_agg(const KeySpec ks, const uint32_t* __restrict__ tuples, const uint32_t
         const uint32_t row = minrow[s];
         if (row == EMPTY32) continue;
         uint32_t t, h;
-        if (MODE == PM_DIRECT) { t = (part << ps.dbits) | s; h = mix32(t); }
+        if (MODE == PM_DIRECT) { t = part_base + s; h = mix32(t); }
         else if (MODE == PM_HASH32) { t = key32[s]; h = mix32(t); }
         else { const unsigned long long k = key64[s]; bool oob = false; part_tag(ks, (uint32_t)k, (uint32_t)(k >> 32), t, h, oob); }
         const uint32_t g = probe_insert<EXACT>(ks, prog.tab, prog.sw, gmask, max_probe, h, t, row);
@@ -493,32 +582,30 @@ k_part_agg(const KeySpec ks, const uint32_t* __restrict__ tuples, const uint32_t
 // ---- host ---------------------------------------------------------------------------------------------
 template <int MODE, int TW>
 static int run_part(const KeySpec& ks, uint32_t nrows, const PartSpec& ps, const AccProg& prog, const SmemLayout& lay,
-                    uint32_t gmask, uint32_t max_probe) {
+                    uint32_t gmask, uint32_t max_probe, size_t stage_bytes) {
     Context& c = ctx();
-    DevBuf tuples, small;
-    AQ_TRY(tuples.alloc(size_t(nrows) * TW * 4));
-    const size_t P = ps.nparts;
-    AQ_TRY(small.alloc_zero((P + (P + 1) + P + (P + 1)) * 4));
-    uint32_t* ghist = small.as<uint32_t>();
-    uint32_t* offsets = ghist + P;
-    uint32_t* cursor = offsets + P + 1;
-    uint32_t* unit_off = cursor + P;
-    const size_t hist_bytes = P * 4;
-    const uint32_t nquad = (nrows + 3) / 4;
-    int grid_h = (int)((nquad + PART_THREADS - 1) / PART_THREADS);
-    if (grid_h > c.sm_count * 4) grid_h = c.sm_count * 4;
-    AQ_LAUNCH((k_part_hist<MODE>), grid_h, PART_THREADS, hist_bytes, ks, nrows, ps, ghist, c.d_flags);
-    AQ_LAUNCH(k_part_scan, 1, PSCAN_THREADS, 0, ghist, ps.nparts, ps.chunk, offsets, cursor, unit_off);
-    const uint32_t tile_quads = PART_THREADS * PART_TILE_QUADS;
-    int grid_s = (int)((nquad + tile_quads - 1) / tile_quads);
-    if (grid_s > c.sm_count * 3) grid_s = c.sm_count * 3;
-    AQ_LAUNCH((k_part_scatter<MODE, TW>), grid_s, PART_THREADS, hist_bytes, ks, prog, nrows, ps, cursor, tuples.as<uint32_t>(), c.d_flags);
+    const size_t P = ps.nparts, C = ps.ncta;
+    const size_t cap_tuples = size_t(nrows) + P * C * (ps.bsz - 1);           // every (partition, CTA) range is padded to whole blocks
+    if (cap_tuples >= 0xffffffffull) return fail("partitioned group-by: %zu tuples exceed the 32-bit index space", cap_tuples);
+    DevBuf tuples, cnt, small;
+    AQ_TRY(tuples.alloc(cap_tuples * TW * 4));
+    AQ_TRY(cnt.alloc_zero((P * C + 1) * 4));
+    AQ_TRY(small.alloc((2 * P + 2) * 4));
+    uint32_t* offsets = small.as<uint32_t>();
+    uint32_t* unit_off = offsets + P + 1;
+    AQ_LAUNCH((k_part_hist<MODE>), (unsigned)(C * PART_HIST_SPLIT), PART_THREADS, P * 4, ks, nrows, ps, cnt.as<uint32_t>(), c.d_flags);
+    AQ_LAUNCH(k_part_pad, grid_for(P * C, 256), 256, 0, cnt.as<uint32_t>(), (uint32_t)(P * C), ps.bsz);
+    AQ_TRY(exclusive_scan_u32(cnt.as<uint32_t>(), cnt.as<uint32_t>(), P * C + 1, nullptr));
+    AQ_LAUNCH(k_part_units, 1, PSCAN_THREADS, 0, cnt.as<uint32_t>(), ps.nparts, ps.ncta, ps.chunk, offsets, unit_off);
     static bool attr_done = false;
     if (!attr_done) {
+        AQ_CUDA(cudaFuncSetAttribute(k_part_scatter<MODE, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(c.smem_optin - 1024)));
         AQ_CUDA(cudaFuncSetAttribute(k_part_agg<MODE, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(c.smem_optin - 1024)));
         attr_done = true;
     }
-    const uint32_t max_units = nrows / ps.chunk + ps.nparts + 1;
+    AQ_LAUNCH((k_part_scatter<MODE, TW>), (unsigned)C, PART_THREADS, stage_bytes, ks, prog, nrows, ps, cnt.as<uint32_t>(),
+              tuples.as<uint32_t>(), c.d_flags);
+    const uint32_t max_units = (uint32_t)(cap_tuples / ps.chunk + P + 1);
     AQ_LAUNCH((k_part_agg<MODE, TW>), max_units, PART_THREADS, lay.total_bytes, ks, tuples.as<uint32_t>(), offsets, unit_off, ps,
               gmask, max_probe, prog, lay, c.d_flags);
     return 0;
@@ -532,10 +619,11 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t gcap, uint32_t
     if (ks.nwords < 1 || ks.nwords > 2 || ks.stride[0] != 1 || (ks.nwords == 2 && ks.stride[1] != 1)) return 0;
     if (prog.nv < 0) return 0;
     for (int j = 0; j < prog.nv; ++j) if (prog.vctype[j] != AQ_INT32 && prog.vctype[j] != AQ_FLOAT) return 0;
-    if (c.smem_optin < 64 * 1024) return 0;
+    if (c.smem_optin < 96 * 1024) return 0;
     PartSpec ps;
     memset(&ps, 0, sizeof(ps));
     ps.nkw = ks.nwords;
+    ps.ncta = (uint32_t)c.sm_count;
     ps.mode = ks.exact ? PM_HASH32 : PM_HASH64;
     if (!ks.exact && ks.nwords != 2) return 0;
     SmemLayout lay;
@@ -558,17 +646,25 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t gcap, uint32_t
         bps += cell_bytes[a];
     }
     const size_t budget = c.smem_optin - 1024 - 64;
+    // ---- tuple width
+    const int nkt = ps.mode == PM_HASH64 ? 2 : 1;
+    if (1 + nkt + prog.nv > 8) return 0;
+    int tw = 1 + nkt + prog.nv;
+    tw = tw <= 4 ? 4 : (tw <= 6 ? 6 : 8);
     // ---- partitions and table capacity
     bool direct = false;
     if (ks.exact == 2 && ks.pack_bits >= 1 && ks.pack_bits <= 31) {
-        uint32_t dbits = 0;
-        while (dbits < 20 && (size_t(bps) * ((size_t(2) << dbits) + 8)) <= budget) ++dbits;   // largest 2^dbits that fits
-        if (dbits > (uint32_t)ks.pack_bits) dbits = ks.pack_bits;
-        const uint64_t np = (uint64_t(1) << ks.pack_bits) >> dbits;
-        if (dbits >= 8 && np <= PART_MAX) {
+        uint64_t max_tag = 0;                                     // largest tag the bounds allow
+        for (int w = 0; w < ks.nwords; ++w) max_tag |= uint64_t(ks.pack_range[w]) << ks.pack_shift[w];
+        uint32_t range = (uint32_t)(budget / bps);
+        range = (range - 8) & ~7u;
+        if (range > 65536) range = 65536;
+        const uint64_t np = max_tag / range + 1;
+        if (range >= 256 && np <= PART_MAX) {
             direct = true;
-            ps.mode = PM_DIRECT; ps.dbits = dbits; ps.nparts = (uint32_t)(np ? np : 1);
-            lay.cap = 1u << dbits; lay.limit = lay.cap;
+            ps.mode = PM_DIRECT; ps.range = range; ps.nparts = (uint32_t)np;
+            ps.magic = ((1ull << 48) + range - 1) / range;
+            lay.cap = range; lay.limit = range;
         }
     }
     if (!direct) {
@@ -583,13 +679,25 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t gcap, uint32_t
         if (np > PART_MAX) return 0;
         ps.nparts = (uint32_t)(np ? np : 1);
     }
-    {   // work-unit size: a few waves of units, but few enough that merging stays cheap
+    // ---- staging blocks of the scatter kernel: bsz tuples = a whole number of 32-byte sectors; as large as
+    // shared memory allows (few partitions: long blocks, so that a tile rarely overflows a block twice)
+    uint32_t bsz = 0;
+    size_t stage_bytes = 0;
+    for (uint32_t b = 2048; b >= 1; b >>= 1) {
+        const size_t blk = size_t(b) * tw * 4;
+        if (blk % 32 != 0) continue;
+        const size_t need = ((3 * size_t(ps.nparts) + 3) & ~size_t(3)) * 4 + size_t(ps.nparts) * blk;
+        if (need <= budget) { bsz = b; stage_bytes = need; break; }
+    }
+    if (bsz == 0) return 0;                                       // too many partitions for one SM's staging area
+    ps.bsz = bsz;
+    {   // work-unit size: a few waves of units, but few enough that merging stays cheap; whole blocks
         uint64_t chunk = uint64_t(nrows) / (uint64_t(c.sm_count) * 6);
         if (chunk < 16384) chunk = 16384;
         if (chunk > (1u << 20)) chunk = 1u << 20;
-        ps.chunk = (uint32_t)chunk;
+        ps.chunk = (uint32_t)(chunk / 8 * 8);
     }
-    // ---- shared-memory layout: every array has cap + 8 entries (trash slot at index cap)
+    // ---- shared-memory layout of k_part_agg: every array has cap + 8 entries (trash slot at index cap)
     const uint32_t capa = lay.cap + 8;
     lay.mode = ps.mode; lay.mask = 0; lay.reps = 1;
     uint32_t off = 0;
@@ -600,13 +708,8 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t gcap, uint32_t
     for (int a = 0; a < prog.n; ++a) if (cell_bytes[a] == 4) { lay.off_cell[a] = off; off += 4 * capa; }
     lay.total_bytes = off;
     if (off > c.smem_optin - 1024) return 0;
-    // ---- tuple width
-    const int nkt = ps.mode == PM_HASH64 ? 2 : 1;
-    int tw = 1 + nkt + prog.nv;
-    tw = tw <= 4 ? 4 : (tw <= 6 ? 6 : 8);
-    if (1 + nkt + prog.nv > 8) return 0;
     const uint32_t gmask = gcap - 1;
-#define AQ_PART_CASE(M, T) if (ps.mode == M && tw == T) { AQ_TRY((run_part<M, T>(ks, nrows, ps, prog, lay, gmask, max_probe))); *used = true; return 0; }
+#define AQ_PART_CASE(M, T) if (ps.mode == M && tw == T) { AQ_TRY((run_part<M, T>(ks, nrows, ps, prog, lay, gmask, max_probe, stage_bytes))); *used = true; return 0; }
     AQ_PART_CASE(PM_DIRECT, 4) AQ_PART_CASE(PM_DIRECT, 6) AQ_PART_CASE(PM_DIRECT, 8)
     AQ_PART_CASE(PM_HASH32, 4) AQ_PART_CASE(PM_HASH32, 6) AQ_PART_CASE(PM_HASH32, 8)
     AQ_PART_CASE(PM_HASH64, 4) AQ_PART_CASE(PM_HASH64, 6) AQ_PART_CASE(PM_HASH64, 8)

@@ -38,7 +38,7 @@ EXPORTS = [
     "aqgpu_sync", "aqgpu_launch_count", "aqgpu_timer_begin", "aqgpu_timer_end",
     "aqgpu_profile_enable", "aqgpu_profile_tag", "aqgpu_profile_report",
     "aqgpu_col_alloc", "aqgpu_col_free", "aqgpu_col_upload", "aqgpu_col_download",
-    "aqgpu_host_alloc", "aqgpu_host_free",
+    "aqgpu_host_alloc", "aqgpu_host_free", "aqgpu_ptr_is_device", "aqgpu_group_gather",
     "aqgpu_reduce_out_type", "aqgpu_scan_out_type", "aqgpu_dtype_size",
     "aqgpu_groupby_agg", "aqgpu_groupby_build", "aqgpu_col_minmax", "aqgpu_groups_free",
     "aqgpu_groups_size", "aqgpu_groups_keys", "aqgpu_groups_first_row", "aqgpu_groups_gid",

@@ -275,6 +275,8 @@ int aqgpu_host_alloc(size_t bytes, void** hptr) {
     return 0;
 }
 
+int aqgpu_ptr_is_device(const void* p) { return aq::is_device_ptr(p) ? 1 : 0; }
+
 int aqgpu_host_free(void* hptr) {
     if (hptr) AQ_CUDA(cudaFreeHost(hptr));
     return 0;

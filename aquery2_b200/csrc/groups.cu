@@ -264,6 +264,22 @@ int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const voi
     return 0;
 }
 
+int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out) {
+    AQ_REQUIRE_INIT();
+    if (!g) return fail("null handle");
+    if (g->nrows == 0) return 0;
+    const size_t esz = dtype_size(vtype);
+    if (esz != 4 && esz != 8) return fail("gather: 4- or 8-byte cells only");
+    AQ_TRY(ensure_perm(g));
+    InCol in; OutCol oc;
+    AQ_TRY(in.bind(v, esz * g->nrows));
+    AQ_TRY(oc.bind(out, esz * g->nrows));
+    AQ_TRY(gather_rows(in.d, (int)esz, g->perm.as<uint32_t>(), g->nrows, oc.d));
+    AQ_TRY(oc.finish(esz * g->nrows));
+    if (oc.host || in.tmp.p) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
 // TableInfo::order_by per group (table.h:447-461, common/groupby.py:54-59) as one segmented sort:
 // stable LSD passes over the order columns (last column first), then over gid.
 int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int* col_types,

@@ -1,0 +1,605 @@
+// aqgpu_host.hpp -- drop-in host side of AQuery++'s post-processor API over libaqgpu (include/aqgpu.h).
+//
+// The generated post-processor (reference engine/ast.py:334-460, 620-793; sample mem_opt.cpp:16-71)
+// and SDK modules compile against the reference's headers server/{vector_type.hpp, table.h, hasher.h,
+// aggregations.h, types.h, gc.h, libaquery.h}.  The files of the same names next to this one forward
+// here; this header keeps the reference's identifiers and argument meaning:
+//
+//   vector_type<T>, ColRef<T>, TableInfo<Ts...>        server/vector_type.hpp:30-431, table.h:68-258, 380-617
+//   record<>, decays<>, transTypes<,hasher>, value_type<>   server/types.h:356-450, hasher.h:66-140
+//   HashTableFactory<K,H>::get(cols...) -> {size, keys, values, offsets}   server/hasher.h:201-207, 324-357
+//   AQHashTable<K,H>: hashtable_push / hashtable_push_all / ht_postproc    server/hasher.h:146-199
+//   count sum avg min max first last, sums avgs mins maxs, sumw avgw minw maxw (SQL sums(w,x) ...),
+//   deltas prev aggnext ratios ratiow, var stddev corr     server/aggregations.h
+//
+// A column's `container` may point to host memory or into the HBM column store (ColRef::to_device());
+// every library call accepts both.  Two ways to use it:
+//   (1) unchanged generated code: the per-group loop `col[i] = sum(v[vecs[i]])` keeps compiling; `vecs[i]`
+//       is a proxy of group i and the FIRST call of an aggregate over a column evaluates it for ALL
+//       groups on the GPU (one aqgpu_group_reduce / aqgpu_group_scan) and memoises the result column, so
+//       the loop degenerates into reads of that column;
+//   (2) whole-column code (what the GPU variant of the emitter produces):
+//       `auto g = aq::group_by(id1, id2); out0 = g.key<0>(); out1 = sum(v1[g]); out2 = avgs(5, price[g]);`
+//
+// Errors: a failed library call throws aq::error (the reference has no error path inside c(cxt);
+// the exported function may catch and return non-zero).  There is no CPU evaluation path in here:
+// without libaqgpu and a CUDA device every aggregate throws.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <memory>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <type_traits>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+#include <iostream>
+#include "../../include/aqgpu.h"
+
+#ifndef __AQEXPORT__
+#define __AQEXPORT__(_Ty) extern "C" _Ty __attribute__((visibility("default")))      // server/libaquery.h:184
+#endif
+
+// ---- types (server/types.h, server/aquery_types.h) -------------------------------------------------
+namespace types {
+enum Type_t { AINT32, AFLOAT, ASTR, ADOUBLE, ALDOUBLE, AINT64, AINT128, AINT16, ADATE, ATIME, AINT8, AUINT32, AUINT64,
+              AUINT128, AUINT16, AUINT8, ABOOL, VECTOR, ATIMESTAMP, ACHAR, ASV, NONE, ERROR };
+template <class T> struct Types { static constexpr Type_t getType() { return ERROR; } };
+#define AQ_TYPE(T, E) template <> struct Types<T> { static constexpr Type_t getType() { return E; } };
+AQ_TYPE(int, AINT32) AQ_TYPE(float, AFLOAT) AQ_TYPE(double, ADOUBLE) AQ_TYPE(long long, AINT64) AQ_TYPE(long, AINT64)
+AQ_TYPE(__int128, AINT128) AQ_TYPE(unsigned int, AUINT32) AQ_TYPE(unsigned long, AUINT64) AQ_TYPE(unsigned long long, AUINT64)
+#undef AQ_TYPE
+// server/types.h:199-210: sum(int) is __int128, sum(fp) is double; avg is double; ratios(int32) is float
+template <class T> using GetLongType = std::conditional_t<std::is_floating_point<std::decay_t<T>>::value, double,
+                                       std::conditional_t<std::is_unsigned<std::decay_t<T>>::value, unsigned __int128, __int128>>;
+template <class T> using GetFPType = std::conditional_t<sizeof(std::decay_t<T>) == sizeof(float), float, double>;
+}  // namespace types
+
+// ---- error handling -----------------------------------------------------------------------------------
+namespace aq {
+struct error : std::runtime_error { using std::runtime_error::runtime_error; };
+inline void check(int rc) { if (rc != 0) throw error(std::string("aqgpu: ") + aqgpu_last_error()); }
+template <class T> constexpr int dtype_of() {
+    using D = std::decay_t<T>;
+    return std::is_same<D, int>::value ? AQ_INT32 : std::is_same<D, unsigned>::value ? AQ_UINT32
+         : std::is_same<D, float>::value ? AQ_FLOAT : std::is_same<D, double>::value ? AQ_DOUBLE
+         : (std::is_same<D, long long>::value || std::is_same<D, long>::value) ? AQ_INT64
+         : (std::is_same<D, __int128>::value || std::is_same<D, unsigned __int128>::value) ? AQ_INT128 : -1;
+}
+struct GroupsHandle;
+struct GroupRows;
+template <class T> struct GroupVec;
+template <class T> struct GroupedCol;
+}  // namespace aq
+
+// ---- GC shim (server/gc.h:7-106): the generated code sets / releases GC::scratch_space --------------------
+struct ScratchSpace { void release() {} void reset() {} };
+struct GC {
+    static inline ScratchSpace* scratch_space = nullptr;
+    static inline GC* gc_handle = nullptr;
+    ScratchSpace scratch;
+};
+
+// ---- vector_type (server/vector_type.hpp:25-431) ----------------------------------------------------------
+struct vectortype_cstorage { void* container; unsigned int size, capacity; };
+
+template <class _Ty> class vector_type {
+public:
+    typedef _Ty value_t;
+    typedef vector_type<_Ty> Decayed_t;
+    _Ty* container;
+    uint32_t size, capacity;                    // capacity > 0: owns `container` (host malloc or HBM)
+    constexpr vector_type() noexcept : container(nullptr), size(0), capacity(0) {}
+    explicit vector_type(const uint32_t& n) : container(static_cast<_Ty*>(malloc(sizeof(_Ty) * (n ? n : 1)))), size(n), capacity(n ? n : 1) {}
+    vector_type(const uint32_t n, void* data) : container(static_cast<_Ty*>(data)), size(n), capacity(0) {}
+    constexpr vector_type(_Ty* data, uint32_t n) noexcept : container(data), size(n), capacity(0) {}
+    vector_type(std::initializer_list<_Ty> l) : vector_type((uint32_t)l.size()) { uint32_t i = 0; for (const auto& x : l) container[i++] = x; }
+    vector_type(vector_type<_Ty>& o) noexcept : container(o.container), size(o.size), capacity(0) {}         // reference semantics (:96-98)
+    vector_type(const vector_type<_Ty>& o) : container(o.container), size(o.size), capacity(0) {
+        if (o.capacity) { alloc_like(o); copy_from(o); }
+    }
+    vector_type(vector_type<_Ty>&& o) noexcept : container(o.container), size(o.size), capacity(o.capacity) { o.container = nullptr; o.size = o.capacity = 0; }
+    explicit vector_type(vectortype_cstorage s) noexcept : container(static_cast<_Ty*>(s.container)), size(s.size), capacity(s.capacity) {}
+    ~vector_type() { release(); }
+    vector_type<_Ty>& operator=(const vector_type<_Ty>& o) {
+        if (this == &o) return *this;
+        release(); container = o.container; size = o.size; capacity = 0;
+        if (o.capacity) { alloc_like(o); copy_from(o); }
+        return *this;
+    }
+    vector_type<_Ty>& operator=(vector_type<_Ty>&& o) noexcept {
+        if (this == &o) return *this;
+        release(); container = o.container; size = o.size; capacity = o.capacity;
+        o.container = nullptr; o.size = o.capacity = 0;
+        return *this;
+    }
+    void init_from(const uint32_t n, void* data) { release(); container = static_cast<_Ty*>(data); size = n; capacity = 0; }
+    bool on_device() const { return container && aqgpu_ptr_is_device(container) == 1; }
+    _Ty& operator[](const uint32_t i) const { return container[i]; }            // host-resident vectors only
+    _Ty* begin() const { return container; }
+    _Ty* end() const { return container + size; }
+    _Ty& back() { return container[size - 1]; }
+    void reserve(uint32_t n) { if (n > capacity_or_size()) grow_to(n); }
+    void resize(uint32_t n) {                                                   // zero-fills (server/vector_type.hpp:205-207)
+        const uint32_t old = size;
+        if (n > capacity_or_size() || capacity == 0) grow_to(n > 1 ? n : 1);
+        if (n > old) memset((void*)(container + old), 0, sizeof(_Ty) * (n - old));
+        size = n;
+    }
+    void emplace_back(const _Ty& v) { if (capacity == 0 || size >= capacity) grow_to(size ? size * 2 : 8); container[size++] = v; }
+    void clear() { size = 0; }
+    vector_type<_Ty> subvec(uint32_t start, uint32_t end) const { return vector_type<_Ty>(container + start, end - start); }   // :348-355
+    vector_type<_Ty> subvec(uint32_t start = 0) const { return subvec(start, size); }
+    vector_type<_Ty> subvec_deep(uint32_t start, uint32_t end) const { vector_type<_Ty> r(end - start); memcpy(r.container, container + start, sizeof(_Ty) * (end - start)); return r; }
+    vector_type<_Ty> getRef() { return vector_type<_Ty>(container, size); }
+    vectortype_cstorage s() const { return vectortype_cstorage{container, size, capacity}; }
+    // host copy of a column that may live in HBM
+    std::vector<_Ty> to_host() const {
+        std::vector<_Ty> h(size);
+        if (size) { if (on_device()) aq::check(aqgpu_col_download(h.data(), container, sizeof(_Ty) * size)); else memcpy(h.data(), container, sizeof(_Ty) * size); }
+        return h;
+    }
+    void out(uint32_t n = 4000, const char* sep = " ") const {
+        const auto h = to_host();
+        n = n < size ? n : size;
+        std::cout << '(';
+        for (uint32_t i = 0; i < n; ++i) { if (i) std::cout << sep; print_cell(h[i]); }
+        std::cout << (n < size ? " ... )" : ")");
+    }
+    static void print_cell(const _Ty& v) {
+        if constexpr (std::is_same<_Ty, __int128>::value || std::is_same<_Ty, unsigned __int128>::value) std::cout << (long long)v;
+        else std::cout << v;
+    }
+protected:
+    uint32_t capacity_or_size() const { return capacity ? capacity : 0; }
+    void alloc_like(const vector_type<_Ty>& o) {
+        if (o.on_device()) { void* p = nullptr; aq::check(aqgpu_col_alloc(sizeof(_Ty) * (o.size ? o.size : 1), &p)); container = static_cast<_Ty*>(p); }
+        else container = static_cast<_Ty*>(malloc(sizeof(_Ty) * (o.size ? o.size : 1)));
+        capacity = o.size ? o.size : 1;
+    }
+    void copy_from(const vector_type<_Ty>& o) {
+        if (!o.size) return;
+        if (o.on_device()) { std::vector<_Ty> h = o.to_host(); aq::check(aqgpu_col_upload(container, h.data(), sizeof(_Ty) * o.size)); }
+        else memcpy(container, o.container, sizeof(_Ty) * o.size);
+    }
+    void grow_to(uint32_t n) {
+        _Ty* p = static_cast<_Ty*>(malloc(sizeof(_Ty) * n));
+        if (size && container) { if (on_device()) aq::check(aqgpu_col_download(p, container, sizeof(_Ty) * size)); else memcpy((void*)p, (const void*)container, sizeof(_Ty) * size); }
+        release_storage();
+        container = p; capacity = n;
+    }
+    void release_storage() {
+        if (capacity && container) { if (on_device()) aqgpu_col_free(container); else free(container); }
+    }
+    void release() { release_storage(); container = nullptr; size = capacity = 0; }
+};
+
+// ---- column statistics kept out of line (server/table.h:60-91 TableStats / populate_stats) -------------
+// The reference embeds TableStats<T> in ColRef, which breaks get_col<i> for non-4-byte types
+// (SURVEY.md section 7 "ABI"); here ColRef is 32 bytes for every T and statistics live in a side table.
+namespace aq {
+struct ColStats { long long lo, hi; };
+inline std::unordered_map<const void*, ColStats>& col_stats() { static std::unordered_map<const void*, ColStats> m; return m; }
+}
+
+struct ColRef_cstorage { void* container; unsigned int size, capacity; const char* name; int ty; };   // server/table.h:34-39
+
+template <class _Ty> class ColRef : public vector_type<_Ty> {
+public:
+    typedef ColRef<_Ty> Decayed_t;
+    const char* name = "";
+    types::Type_t ty = types::Types<_Ty>::getType();
+    ColRef() : vector_type<_Ty>() {}
+    ColRef(const uint32_t& n, const char* name = "") : vector_type<_Ty>(n), name(name) {}
+    ColRef(const char* name) : vector_type<_Ty>(), name(name) {}
+    ColRef(const uint32_t n, void* data, const char* name = "") : vector_type<_Ty>(n, data), name(name) {}     // table.h:101
+    ColRef(const ColRef<_Ty>& o) : vector_type<_Ty>(static_cast<const vector_type<_Ty>&>(o)), name(o.name), ty(o.ty) {}
+    ColRef(ColRef<_Ty>& o) : vector_type<_Ty>(static_cast<vector_type<_Ty>&>(o)), name(o.name), ty(o.ty) {}
+    ColRef(ColRef<_Ty>&& o) noexcept : vector_type<_Ty>(std::move(static_cast<vector_type<_Ty>&>(o))), name(o.name), ty(o.ty) {}
+    ColRef(vector_type<_Ty>&& v, const char* name = "") : vector_type<_Ty>(std::move(v)), name(name) {}
+    ColRef<_Ty>& operator=(const ColRef<_Ty>& o) { vector_type<_Ty>::operator=(static_cast<const vector_type<_Ty>&>(o)); return *this; }
+    ColRef<_Ty>& operator=(ColRef<_Ty>&& o) noexcept { vector_type<_Ty>::operator=(std::move(static_cast<vector_type<_Ty>&>(o))); return *this; }
+    ColRef<_Ty>& operator=(vector_type<_Ty>&& o) noexcept { vector_type<_Ty>::operator=(std::move(o)); return *this; }
+    void init(const char* nm = "") { this->container = nullptr; this->size = this->capacity = 0; name = nm; ty = types::Types<_Ty>::getType(); }
+    void initfrom(uint32_t sz, void* data, const char* nm = "") { this->init_from(sz, data); name = nm; ty = types::Types<_Ty>::getType(); }
+    template <class V> void initfrom(V&& v, const char* nm = "") {                                            // table.h:104-133
+        this->init_from(v.size, v.container);
+        if (!std::is_lvalue_reference<V>::value) { this->capacity = v.capacity; v.capacity = 0; }
+        name = nm; ty = types::Types<_Ty>::getType();
+    }
+    ColRef<_Ty>* rename(const char* nm) { name = nm; return this; }
+    ColRef_cstorage s() { return ColRef_cstorage{this->container, this->size, this->capacity, name, (int)ty}; }
+    using vector_type<_Ty>::operator[];
+    // statistics (ColRef::populate_stats, table.h:76-91): one streaming pass on the GPU
+    bool populate_stats() {
+        if constexpr (std::is_integral<_Ty>::value && (sizeof(_Ty) == 4 || sizeof(_Ty) == 8)) {
+            if (aq::col_stats().count(this->container)) return true;
+            long long lo = 0, hi = -1;
+            aq::check(aqgpu_col_minmax(aq::dtype_of<_Ty>(), this->container, this->size, (int64_t*)&lo, (int64_t*)&hi));
+            aq::col_stats()[this->container] = aq::ColStats{lo, hi};
+            return true;
+        }
+        return false;
+    }
+    void set_stats(long long lo, long long hi) { aq::col_stats()[this->container] = aq::ColStats{lo, hi}; }
+    // a copy of this column in the HBM column store
+    ColRef<_Ty> to_device() const {
+        ColRef<_Ty> d;
+        if (this->on_device()) { d.init_from(this->size, this->container); d.name = name; return d; }
+        void* p = nullptr;
+        aq::check(aqgpu_col_alloc(sizeof(_Ty) * (this->size ? this->size : 1), &p));
+        if (this->size) aq::check(aqgpu_col_upload(p, this->container, sizeof(_Ty) * this->size));
+        d.container = static_cast<_Ty*>(p); d.size = this->size; d.capacity = this->size ? this->size : 1; d.name = name;
+        return d;
+    }
+    // gather col[vecs[g]] (table.h:184-189): a proxy, evaluated by the aggregate that consumes it
+    aq::GroupVec<_Ty> operator[](const aq::GroupRows& rows) const;
+    template <class G, class = decltype(std::declval<const G&>().handle)> aq::GroupedCol<_Ty> operator[](const G& groups) const;
+};
+template <> class ColRef<void> : public ColRef<int> {};
+
+template <class T> struct is_vector_type_impl : std::false_type {};
+template <class T> struct is_vector_type_impl<vector_type<T>> : std::true_type {};
+template <class T> struct is_vector_type_impl<ColRef<T>> : std::true_type {};
+
+// ---- TableInfo (server/table.h:380-617) -----------------------------------------------------------------------
+template <class... Types> struct TableInfo {
+    const char* name;
+    ColRef<void>* colrefs;
+    uint32_t n_cols;
+    typedef std::tuple<Types...> tuple_type;
+    TableInfo(const char* name, const char** col_names) : name(name), n_cols(sizeof...(Types)) {
+        colrefs = static_cast<ColRef<void>*>(malloc(sizeof(ColRef<void>) * (n_cols ? n_cols : 1)));
+        for (uint32_t i = 0; i < n_cols; ++i) new (colrefs + i) ColRef<void>();
+        init_cols(col_names, std::index_sequence_for<Types...>());
+    }
+    template <int i> auto& get_col() {
+        static_assert(sizeof(ColRef<std::tuple_element_t<i, tuple_type>>) == sizeof(ColRef<void>), "one ColRef layout for every cell type");
+        return *reinterpret_cast<ColRef<std::tuple_element_t<i, tuple_type>>*>(colrefs + i);
+    }
+    void print(const char* sep = ",", const char* end = "\n", uint32_t limit = 0xffffffffu) {
+        print_impl(sep, end, limit, std::index_sequence_for<Types...>());
+    }
+    void printall(const char* sep = ",", const char* end = "\n", const char* = nullptr, FILE* = nullptr, uint32_t limit = 0xffffffffu) { print(sep, end, limit); }
+private:
+    template <size_t... I> void init_cols(const char** names, std::index_sequence<I...>) { ((get_col<(int)I>().init(names ? names[I] : "")), ...); }
+    template <class C> static void print_one(const std::vector<C>& h, uint32_t r) {
+        if constexpr (is_vector_type_impl<C>::value) h[r].out(8);
+        else vector_type<C>::print_cell(h[r]);
+    }
+    template <size_t... I> void print_impl(const char* sep, const char* end, uint32_t limit, std::index_sequence<I...>) {
+        auto hosts = std::make_tuple(host_cells(get_col<(int)I>())...);
+        uint32_t rows = n_cols ? colrefs[0].size : 0;
+        if (rows > limit) rows = limit;
+        for (uint32_t i = 0; i < n_cols; ++i) std::cout << colrefs[i].name << (i + 1 < n_cols ? sep : end);
+        for (uint32_t r = 0; r < rows; ++r) { ((print_one(std::get<I>(hosts), r), std::cout << (I + 1 < sizeof...(I) ? sep : end)), ...); }
+    }
+    template <class C> static std::vector<C> host_cells(ColRef<C>& c) {
+        if constexpr (is_vector_type_impl<C>::value) { std::vector<C> h; h.reserve(c.size); for (uint32_t i = 0; i < c.size; ++i) h.emplace_back(c.container[i].container, c.container[i].size); return h; }
+        else return c.to_host();
+    }
+};
+template <class... Types> void print(TableInfo<Types...>& t, const char* sep = " ", const char* end = "\n") { t.print(sep, end); }
+
+// ---- key records (server/types.h:356-450, server/hasher.h:66-140) -------------------------------------------
+template <class... T> using record = std::tuple<T...>;
+template <class T> struct decayS { typedef typename std::decay<T>::type type; };
+template <class T> struct decayS<ColRef<T>> { typedef ColRef<T> type; };
+template <class T> using decays = typename decayS<typename std::decay<T>::type>::type;
+template <class T> struct value_type_impl { typedef T type; };
+template <template <class...> class VT, class V0, class... V> struct value_type_impl<VT<V0, V...>> { typedef V0 type; };
+template <class T> using value_type = typename value_type_impl<T>::type;
+template <class... T> struct hasher {};                       // hashing happens on the GPU; kept for the template spelling
+template <class Rec, template <class...> class H> struct transTypes_s { typedef H<Rec> type; };
+template <class Rec, template <class...> class H> using transTypes = typename transTypes_s<Rec, H>::type;
+
+// ---- group handle shared by the proxies -------------------------------------------------------------------------
+namespace aq {
+struct GroupRows {                 // `vecs[i]` of the generated loop: the row list of group i, unevaluated
+    GroupsHandle* g; uint32_t gid; uint32_t size;     // .size: count(*) is emitted as val.size (engine/ast.py:763)
+};
+struct GroupsHandle {
+    aqgpu_groups_t* h = nullptr;
+    uint32_t nrows = 0, ngroups = 0;
+    std::vector<uint32_t> offsets;                    // host copy of ht_base + terminal (ngroups + 1)
+    std::vector<GroupRows> rows;                      // backing store of HashTableComponents::values
+    std::shared_ptr<void> keys;                       // backing store of HashTableComponents::keys
+    std::map<std::tuple<int, const void*, const void*, uint32_t>, std::shared_ptr<void>> memo;
+    ~GroupsHandle() { if (h) aqgpu_groups_free(h); }
+    void fetch_offsets() {
+        if (!offsets.empty()) return;
+        offsets.assign(size_t(ngroups) + 1, 0u);
+        check(aqgpu_groups_csr(h, offsets.data(), nullptr));
+        rows.resize(ngroups);
+        for (uint32_t i = 0; i < ngroups; ++i) rows[i] = GroupRows{this, i, offsets[i + 1] - offsets[i]};
+    }
+    // op(v) for ALL groups, evaluated once on the GPU, kept as a host column of ngroups cells of R
+    template <class R> const R* reduce_all(int op, int vtype, const void* v, const void* v2 = nullptr) {
+        auto key = std::make_tuple(op, v, v2, 0u);
+        auto it = memo.find(key);
+        if (it == memo.end()) {
+            std::shared_ptr<void> buf(malloc(sizeof(R) * (ngroups ? ngroups : 1)), free);
+            check(aqgpu_group_reduce(h, op, vtype, v, v2, dtype_of<R>(), buf.get()));
+            it = memo.emplace(key, buf).first;
+        }
+        return static_cast<const R*>(it->second.get());
+    }
+    // scan op(w, v) for ALL groups: nrows cells of R in the CSR order of the row lists
+    template <class R> const R* scan_all(int op, uint32_t w, int vtype, const void* v) {
+        auto key = std::make_tuple(100 + op, v, (const void*)nullptr, w);
+        auto it = memo.find(key);
+        if (it == memo.end()) {
+            std::shared_ptr<void> buf(malloc(sizeof(R) * (nrows ? nrows : 1)), free);
+            check(aqgpu_group_scan(h, op, w, vtype, v, dtype_of<R>(), buf.get()));
+            it = memo.emplace(key, buf).first;
+        }
+        return static_cast<const R*>(it->second.get());
+    }
+    template <class T> const T* gather_all(const T* v) {          // col[vecs[g]] for all groups, CSR order
+        auto key = std::make_tuple(200, (const void*)v, (const void*)nullptr, 0u);
+        auto it = memo.find(key);
+        if (it == memo.end()) {
+            std::shared_ptr<void> buf(malloc(sizeof(T) * (nrows ? nrows : 1)), free);
+            check(aqgpu_group_gather(h, dtype_of<T>(), v, buf.get()));
+            it = memo.emplace(key, buf).first;
+        }
+        return static_cast<const T*>(it->second.get());
+    }
+};
+template <class T> struct GroupVec {       // col[vecs[i]]: the values of one group, unevaluated
+    const T* col; GroupsHandle* g; uint32_t gid; uint32_t size;
+    operator vector_type<T>() const {      // materialised only when generated code does arithmetic on it
+        g->fetch_offsets();
+        return vector_type<T>(const_cast<T*>(g->gather_all(col)) + g->offsets[gid], size);
+    }
+};
+template <class T> struct GroupedCol {     // col[g]: a column seen through ALL groups (whole-column code)
+    const T* col; uint32_t n; std::shared_ptr<GroupsHandle> handle;
+};
+
+template <class... Ts, size_t... I>
+inline std::shared_ptr<GroupsHandle> build_groups(std::index_sequence<I...>, int row_order, const ColRef<Ts>&... cols) {
+    constexpr int nk = sizeof...(Ts);
+    static_assert(nk >= 1, "group by needs at least one key column");
+    static_assert(((dtype_of<Ts>() >= 0) && ...), "key columns: int32 / uint32 / int64");
+    const void* kp[nk] = { cols.container... };
+    const int kt[nk] = { dtype_of<Ts>()... };
+    const uint32_t n = std::get<0>(std::tie(cols...)).size;
+    int64_t lo[nk], hi[nk];
+    bool have = true;
+    double prod = 1.0;
+    int k = 0;
+    (void)std::initializer_list<int>{ ([&] {
+        auto it = col_stats().find(cols.container);
+        if (it == col_stats().end()) have = false; else { lo[k] = it->second.lo; hi[k] = it->second.hi; prod *= double(hi[k] - lo[k] + 1); }
+        ++k; }(), 0)... };
+    auto g = std::make_shared<GroupsHandle>();
+    const uint32_t hint = have ? (uint32_t)std::min<double>(prod, double(n)) : 0u;
+    check(aqgpu_groupby_build(kp, kt, nk, n, have ? lo : nullptr, have ? hi : nullptr, row_order, hint, &g->h));
+    g->nrows = n;
+    check(aqgpu_groups_size(g->h, &g->ngroups));
+    return g;
+}
+
+// Whole-column group-by: keys stay in HBM until asked for.
+template <class... Ts> struct Groups {
+    std::shared_ptr<GroupsHandle> handle;
+    uint32_t size = 0;
+    template <int i> ColRef<std::tuple_element_t<i, std::tuple<Ts...>>> key() const {
+        typedef std::tuple_element_t<i, std::tuple<Ts...>> K;
+        ColRef<K> out(handle->ngroups);
+        if (handle->ngroups) check(aqgpu_groups_keys(handle->h, i, out.container));
+        return out;
+    }
+    ColRef<uint32_t> offsets() const { handle->fetch_offsets(); ColRef<uint32_t> o((uint32_t)handle->offsets.size()); std::copy(handle->offsets.begin(), handle->offsets.end(), o.container); return o; }
+    ColRef<uint32_t> counts() const {
+        ColRef<uint32_t> c(handle->ngroups);
+        if (handle->ngroups) check(aqgpu_group_reduce(handle->h, AQ_COUNT, AQ_INT32, nullptr, nullptr, AQ_UINT32, c.container));
+        return c;
+    }
+};
+template <class... Ts> Groups<Ts...> group_by(const ColRef<Ts>&... cols) {
+    Groups<Ts...> g;
+    g.handle = build_groups<Ts...>(std::index_sequence_for<Ts...>(), AQ_ROWS_DESC, cols...);
+    g.size = g.handle->ngroups;
+    return g;
+}
+}  // namespace aq
+
+template <class _Ty> aq::GroupVec<_Ty> ColRef<_Ty>::operator[](const aq::GroupRows& r) const { return aq::GroupVec<_Ty>{this->container, r.g, r.gid, r.size}; }
+template <class _Ty> template <class G, class> aq::GroupedCol<_Ty> ColRef<_Ty>::operator[](const G& g) const { return aq::GroupedCol<_Ty>{this->container, this->size, g.handle}; }
+
+// ---- HashTableComponents / HashTableFactory / AQHashTable (server/hasher.h:146-357) --------------------------------
+template <class... Ty> struct HashTableComponents {
+    uint32_t size;
+    std::vector<std::tuple<Ty...>>* keys;
+    aq::GroupRows* values;                 // reference: vector_type<uint32_t>*; here proxies of the row lists
+    uint32_t* offsets;
+    std::shared_ptr<aq::GroupsHandle> handle;     // extension: keeps the HBM-resident groups alive
+};
+
+namespace aq {
+template <class... Ts, size_t... I>
+inline HashTableComponents<Ts...> make_components(std::index_sequence<I...>, std::shared_ptr<GroupsHandle> g) {
+    g->fetch_offsets();
+    auto keys = std::make_shared<std::vector<std::tuple<Ts...>>>(g->ngroups);
+    std::tuple<std::vector<Ts>...> cols{ std::vector<Ts>(g->ngroups)... };
+    if (g->ngroups) (check(aqgpu_groups_keys(g->h, (int)I, std::get<I>(cols).data())), ...);
+    for (uint32_t i = 0; i < g->ngroups; ++i) (*keys)[i] = std::make_tuple(std::get<I>(cols)[i]...);
+    g->keys = keys;
+    return HashTableComponents<Ts...>{g->ngroups, keys.get(), g->rows.data(), g->offsets.data(), g};
+}
+}  // namespace aq
+
+template <class Key, class Hash = void> struct HashTableFactory {
+    // the emitter spells explicit template arguments (engine/ast.py:668-670); they are accepted and ignored
+    template <class... Ignored, class... Ts> static HashTableComponents<Ts...> get(const ColRef<Ts>&... cols) {
+        auto g = aq::build_groups<Ts...>(std::index_sequence_for<Ts...>(), AQ_ROWS_DESC, cols...);
+        return aq::make_components<Ts...>(std::index_sequence_for<Ts...>(), g);
+    }
+};
+
+// The previous generation of the emitted code (engine/ast.py:664-676, mem_opt.cpp:31-52):
+//   AQHashTable<rec_t, ...> g{total}; g.hashtable_push_all<...>(cols..., total) | g.hashtable_push(key, i) per row;
+//   vecs = g.ht_postproc(total); g.size(); g.values()[i]; g.ht_base
+template <class Key, class Hash = void> class AQHashTable;
+template <class... Ks, class Hash> class AQHashTable<std::tuple<Ks...>, Hash> {
+public:
+    uint32_t *reversemap = nullptr, *mapbase = nullptr, *ht_base = nullptr;
+    AQHashTable() = default;
+    explicit AQHashTable(uint32_t sz) { init(sz); }
+    void init(uint32_t sz) { std::apply([&](auto&... v) { (v.reserve(sz), ...); }, pushed); }
+    template <class... Ignored> void hashtable_push_all(const ColRef<Ks>&... cols, uint32_t len) {
+        (void)len;
+        g = aq::build_groups<Ks...>(std::index_sequence_for<Ks...>(), AQ_ROWS_DESC, cols...);
+    }
+    template <class Tup> void hashtable_push(Tup&& k, uint32_t) { push_impl(k, std::index_sequence_for<Ks...>()); }   // key tuple of row i
+    aq::GroupRows* ht_postproc(uint32_t sz) {
+        if (!g) {          // per-row pushes: the buffered key columns are grouped now, in one call
+            g = std::apply([&](auto&... v) {
+                return aq::build_groups<Ks...>(std::index_sequence_for<Ks...>(), AQ_ROWS_DESC, ColRef<Ks>((uint32_t)v.size(), v.data())...); }, pushed);
+        }
+        (void)sz;
+        comp = aq::make_components<Ks...>(std::index_sequence_for<Ks...>(), g);
+        ht_base = comp.offsets;
+        return comp.values;
+    }
+    uint32_t size() const { return g ? g->ngroups : 0; }
+    std::vector<std::tuple<Ks...>>& values() { return *comp.keys; }
+    std::shared_ptr<aq::GroupsHandle> handle() const { return g; }
+private:
+    template <class Tup, size_t... I> void push_impl(const Tup& k, std::index_sequence<I...>) { (std::get<I>(pushed).push_back(std::get<I>(k)), ...); }
+    std::tuple<std::vector<Ks>...> pushed;
+    std::shared_ptr<aq::GroupsHandle> g;
+    HashTableComponents<Ks...> comp{};
+};
+
+// ---- aggregates (server/aggregations.h) -------------------------------------------------------------------------
+// (1) per-group proxies: the value for group gid of a column evaluated once for all groups
+template <class T> types::GetLongType<T> sum(const aq::GroupVec<T>& v) { return v.g->template reduce_all<types::GetLongType<T>>(AQ_SUM, aq::dtype_of<T>(), v.col)[v.gid]; }   // :19-27
+template <class T> double avg(const aq::GroupVec<T>& v) { return v.g->template reduce_all<double>(AQ_AVG, aq::dtype_of<T>(), v.col)[v.gid]; }                              // :28-32
+template <class T> T max(const aq::GroupVec<T>& v) { return v.g->template reduce_all<T>(AQ_MAX, aq::dtype_of<T>(), v.col)[v.gid]; }                                       // :71-78
+template <class T> T min(const aq::GroupVec<T>& v) { return v.g->template reduce_all<T>(AQ_MIN, aq::dtype_of<T>(), v.col)[v.gid]; }                                       // :79-86
+template <class T> T first(const aq::GroupVec<T>& v) { return v.g->template reduce_all<T>(AQ_FIRST, aq::dtype_of<T>(), v.col)[v.gid]; }                                   // :493-497
+template <class T> T last(const aq::GroupVec<T>& v) { return v.g->template reduce_all<T>(AQ_LAST, aq::dtype_of<T>(), v.col)[v.gid]; }                                     // :487-491
+template <class T> uint32_t count(const aq::GroupVec<T>& v) { return v.size; }                                                                                          // :10-16
+inline uint32_t count(const aq::GroupRows& r) { return r.size; }
+template <class T> double var(const aq::GroupVec<T>& v) { return v.g->template reduce_all<double>(AQ_VAR, aq::dtype_of<T>(), v.col)[v.gid]; }                              // :332-348
+template <class T> double stddev(const aq::GroupVec<T>& v) { return v.g->template reduce_all<double>(AQ_STDDEV, aq::dtype_of<T>(), v.col)[v.gid]; }                        // :413-415
+template <class T> double corr(const aq::GroupVec<T>& a, const aq::GroupVec<T>& b) { return a.g->template reduce_all<double>(AQ_CORR, aq::dtype_of<T>(), a.col, b.col)[a.gid]; }   // :383-407
+
+namespace aq {
+template <class R, class T> vector_type<R> scan_view(const GroupVec<T>& v, int op, uint32_t w) {
+    v.g->fetch_offsets();
+    const R* flat = v.g->template scan_all<R>(op, w, dtype_of<T>(), v.col);
+    return vector_type<R>(const_cast<R*>(flat) + v.g->offsets[v.gid], v.size);
+}
+template <class R, class T, class Ret> void scan_into(const GroupVec<T>& v, int op, uint32_t w, Ret& ret) {
+    const vector_type<R> s = scan_view<R, T>(v, op, w);
+    if (ret.size < s.size) ret.resize(s.size);
+    for (uint32_t i = 0; i < s.size; ++i) ret.container[i] = s.container[i];
+}
+}  // namespace aq
+// running / windowed / neighbour aggregates: 1-argument form returns the group's slice of the memoised
+// CSR result, the "write into ret" form (engine/expr.py:373-385, mem_opt.cpp:60) copies it into the cell
+#define AQ_SCAN0(NAME, OP, RT)                                                                                      \
+    template <class T> vector_type<RT> NAME(const aq::GroupVec<T>& v) { return aq::scan_view<RT, T>(v, OP, 0); }      \
+    template <class T, class Ret> void NAME(const aq::GroupVec<T>& v, Ret& ret) { aq::scan_into<RT, T>(v, OP, 0, ret); }
+#define AQ_SCANW(NAME, OP, RT)                                                                                      \
+    template <class T> vector_type<RT> NAME(uint32_t w, const aq::GroupVec<T>& v) { return aq::scan_view<RT, T>(v, OP, w); } \
+    template <class T, class Ret> void NAME(uint32_t w, const aq::GroupVec<T>& v, Ret& ret) { aq::scan_into<RT, T>(v, OP, w, ret); }
+AQ_SCAN0(sums, AQ_SUMS, types::GetLongType<T>)      // :203-217
+AQ_SCAN0(avgs, AQ_AVGS, double)                     // :219-236
+AQ_SCAN0(mins, AQ_MINS, T)                          // :89-106
+AQ_SCAN0(maxs, AQ_MAXS, T)                          // :108-125
+AQ_SCAN0(deltas, AQ_DELTAS, T)                      // :439-453
+AQ_SCAN0(prev, AQ_PREV, T)                          // :455-469
+AQ_SCAN0(aggnext, AQ_NEXT, T)                       // :471-485
+AQ_SCANW(sumw, AQ_SUMW, types::GetLongType<T>)      // :238-256
+AQ_SCANW(avgw, AQ_AVGW, double)                     // :258-281
+AQ_SCANW(minw, AQ_MINW, T)                          // :127-146
+AQ_SCANW(maxw, AQ_MAXW, T)                          // :148-167
+AQ_SCANW(ratiow, AQ_RATIOW, types::GetFPType<T>)    // :169-201
+template <class T> vector_type<types::GetFPType<T>> ratios(const aq::GroupVec<T>& v) { return aq::scan_view<types::GetFPType<T>, T>(v, AQ_RATIOW, 1); }
+// SQL spellings with a window argument (common/types.py:285-290, 349-352): sums(w, x) == sumw(w, x) ...
+template <class T> auto sums(uint32_t w, const aq::GroupVec<T>& v) { return sumw(w, v); }
+template <class T> auto avgs(uint32_t w, const aq::GroupVec<T>& v) { return avgw(w, v); }
+template <class T> auto mins(uint32_t w, const aq::GroupVec<T>& v) { return minw(w, v); }
+template <class T> auto maxs(uint32_t w, const aq::GroupVec<T>& v) { return maxw(w, v); }
+
+// (2) whole-column forms: result columns for all groups in one call.  The result lives where the input
+// column lives (HBM for device-resident inputs, host otherwise).
+namespace aq {
+template <class R> ColRef<R> alloc_like_input(const void* input, uint32_t n) {
+    ColRef<R> out;
+    if (input && aqgpu_ptr_is_device(input) == 1) {
+        void* p = nullptr;
+        check(aqgpu_col_alloc(sizeof(R) * (n ? n : 1), &p));
+        out.container = static_cast<R*>(p); out.size = n; out.capacity = n ? n : 1;
+    } else out = ColRef<R>(n);
+    return out;
+}
+template <class R, class T> ColRef<R> reduce_col(const GroupedCol<T>& c, int op, const T* v2 = nullptr) {
+    ColRef<R> out = alloc_like_input<R>(c.col, c.handle->ngroups);
+    if (c.handle->ngroups) check(aqgpu_group_reduce(c.handle->h, op, dtype_of<T>(), c.col, v2, dtype_of<R>(), out.container));
+    return out;
+}
+// vector-valued result: flat values in the CSR order of the row lists + the groups' offsets (engine/ast.py:696-718)
+template <class R> struct VecCol {
+    ColRef<R> flat;
+    std::shared_ptr<GroupsHandle> handle;
+    // per-group views for a TableInfo column of vector_type<R> cells (host-resident results only)
+    ColRef<vector_type<R>> views() {
+        handle->fetch_offsets();
+        ColRef<vector_type<R>> v(handle->ngroups);
+        for (uint32_t i = 0; i < handle->ngroups; ++i) new (v.container + i) vector_type<R>(flat.container + handle->offsets[i], handle->offsets[i + 1] - handle->offsets[i]);
+        return v;
+    }
+};
+template <class R, class T> VecCol<R> scan_col(const GroupedCol<T>& c, int op, uint32_t w) {
+    VecCol<R> out{alloc_like_input<R>(c.col, c.handle->nrows), c.handle};
+    if (c.handle->nrows) check(aqgpu_group_scan(c.handle->h, op, w, dtype_of<T>(), c.col, dtype_of<R>(), out.flat.container));
+    return out;
+}
+}  // namespace aq
+template <class T> ColRef<types::GetLongType<T>> sum(const aq::GroupedCol<T>& c) { return aq::reduce_col<types::GetLongType<T>, T>(c, AQ_SUM); }
+template <class T> ColRef<double> avg(const aq::GroupedCol<T>& c) { return aq::reduce_col<double, T>(c, AQ_AVG); }
+template <class T> ColRef<T> max(const aq::GroupedCol<T>& c) { return aq::reduce_col<T, T>(c, AQ_MAX); }
+template <class T> ColRef<T> min(const aq::GroupedCol<T>& c) { return aq::reduce_col<T, T>(c, AQ_MIN); }
+template <class T> ColRef<T> first(const aq::GroupedCol<T>& c) { return aq::reduce_col<T, T>(c, AQ_FIRST); }
+template <class T> ColRef<T> last(const aq::GroupedCol<T>& c) { return aq::reduce_col<T, T>(c, AQ_LAST); }
+template <class T> ColRef<uint32_t> count(const aq::GroupedCol<T>& c) { return aq::reduce_col<uint32_t, T>(c, AQ_COUNT); }
+template <class T> ColRef<double> var(const aq::GroupedCol<T>& c) { return aq::reduce_col<double, T>(c, AQ_VAR); }
+template <class T> ColRef<double> stddev(const aq::GroupedCol<T>& c) { return aq::reduce_col<double, T>(c, AQ_STDDEV); }
+template <class T> ColRef<double> corr(const aq::GroupedCol<T>& a, const aq::GroupedCol<T>& b) { return aq::reduce_col<double, T>(a, AQ_CORR, b.col); }
+#define AQ_WSCAN0(NAME, OP, RT) template <class T> aq::VecCol<RT> NAME(const aq::GroupedCol<T>& c) { return aq::scan_col<RT, T>(c, OP, 0); }
+#define AQ_WSCANW(NAME, OP, RT) template <class T> aq::VecCol<RT> NAME(uint32_t w, const aq::GroupedCol<T>& c) { return aq::scan_col<RT, T>(c, OP, w); }
+AQ_WSCAN0(sums, AQ_SUMS, types::GetLongType<T>) AQ_WSCAN0(avgs, AQ_AVGS, double) AQ_WSCAN0(mins, AQ_MINS, T) AQ_WSCAN0(maxs, AQ_MAXS, T)
+AQ_WSCAN0(deltas, AQ_DELTAS, T) AQ_WSCAN0(prev, AQ_PREV, T) AQ_WSCAN0(aggnext, AQ_NEXT, T)
+AQ_WSCANW(sumw, AQ_SUMW, types::GetLongType<T>) AQ_WSCANW(avgw, AQ_AVGW, double) AQ_WSCANW(minw, AQ_MINW, T) AQ_WSCANW(maxw, AQ_MAXW, T)
+AQ_WSCANW(ratiow, AQ_RATIOW, types::GetFPType<T>)
+AQ_WSCANW(sums, AQ_SUMW, types::GetLongType<T>) AQ_WSCANW(avgs, AQ_AVGW, double) AQ_WSCANW(mins, AQ_MINW, T) AQ_WSCANW(maxs, AQ_MAXW, T)
+template <class T> aq::VecCol<types::GetFPType<T>> ratios(const aq::GroupedCol<T>& c) { return aq::scan_col<types::GetFPType<T>, T>(c, AQ_RATIOW, 1); }
+#undef AQ_SCAN0
+#undef AQ_SCANW
+#undef AQ_WSCAN0
+#undef AQ_WSCANW
+
+// ---- Context / DataSource (server/libaquery.h:118-160, server/DataSource_conn.h:27-46): what c(cxt) touches ---------
+struct DataSource {
+    long long cnt = 0;
+    virtual void* getCol(int col_idx, int type) = 0;
+    virtual ~DataSource() = default;
+};
+struct Context {
+    void* curr_server = nullptr;
+    void* alt_server[8] = {nullptr};
+    void* gc = nullptr;
+    std::unordered_map<std::string, void*> tables;      // cached tables: TableInfo<...>* whose containers may live in HBM
+};

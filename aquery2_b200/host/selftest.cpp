@@ -1,0 +1,175 @@
+// selftest.cpp -- compiles and runs code shaped like the reference emitter's output against the drop-in
+// headers (aquery2_b200/host/server/*.h) and libaqgpu.so.  Three post-processors:
+//   dll_unchanged   the per-group loop exactly as engine/ast.py:334-460, 620-793 emits it
+//                   (HashTableFactory::get, g.keys / g.values / g.offsets, col[i] = sum(v[val]), 3-argument avgw)
+//   dll_legacy      the previous generation (mem_opt.cpp:31-63): AQHashTable + hashtable_push + ht_postproc
+//   dll_whole       the whole-column form the GPU variant of the emitter produces
+// The expected values are computed here with plain loops over the reference semantics (first-appearance
+// group order, descending row order inside a group).  Needs a CUDA device: exits 2 without one.
+#include "./server/libaquery.h"
+#include "./server/hasher.h"
+#include "./server/monetdb_conn.h"
+#include "./server/aggregations.h"
+#include <cassert>
+#include <map>
+
+struct VecSource : DataSource {
+    std::vector<void*> cols;
+    void* getCol(int i, int) override { return cols[i]; }
+};
+
+static int fails = 0;
+#define EXPECT(c) do { if (!(c)) { printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); ++fails; } } while (0)
+
+static TableInfo<int, __int128_t, double, int, vector_type<double>>* g_out1 = nullptr;
+
+// ---- (1) unchanged emitter output -----------------------------------------------------------------
+__AQEXPORT__(int) dll_unchanged(Context* cxt) {
+    using namespace std;
+    using namespace types;
+    auto server = static_cast<DataSource*>(cxt->curr_server);
+    auto len = server->cnt;
+    auto id1_a = ColRef<int>(len, server->getCol(0, AINT32));
+    auto v1_b = ColRef<int>(len, server->getCol(1, AINT32));
+    auto v3_c = ColRef<float>(len, server->getCol(2, AFLOAT));
+    const char* names[] = {"id1", "sumv1", "avgv3", "maxv1", "avgs3v1"};
+    auto out = new TableInfo<int, __int128_t, double, int, vector_type<double>>("out_x", names);
+    decltype(auto) col0 = out->get_col<0>();
+    decltype(auto) col1 = out->get_col<1>();
+    decltype(auto) col2 = out->get_col<2>();
+    decltype(auto) col3 = out->get_col<3>();
+    decltype(auto) col4 = out->get_col<4>();
+    uint32_t total = id1_a.size;
+    typedef record<decays<decltype(id1_a)>::value_t> rec_t;
+    auto g = HashTableFactory<rec_t, transTypes<rec_t, hasher>>::get<decays<decltype(id1_a)>>(id1_a);
+    auto sz = g.size;
+    auto vecs = g.values;
+    col0.resize(sz); col1.resize(sz); col2.resize(sz); col3.resize(sz); col4.resize(sz);
+    auto buf_col4 = static_cast<double*>(calloc(total, sizeof(double)));
+    for (uint32_t i = 0; i < sz; ++i) col4[i].init_from(vecs[i].size, buf_col4 + g.offsets[i]);
+    GC::scratch_space = GC::gc_handle ? &(GC::gc_handle->scratch) : nullptr;
+    for (uint32_t i = 0; i < sz; ++i) {
+        auto& key = (*g.keys)[i];
+        auto& val = vecs[i];
+        col0[i] = (get<0>(key));
+        col1[i] = (sum(v1_b[val]));
+        col2[i] = (avg(v3_c[val]));
+        col3[i] = (max(v1_b[val]));
+        avgw(3, v1_b[val], col4[i]);
+        if (GC::scratch_space) GC::scratch_space->release();
+    }
+    GC::scratch_space = nullptr;
+    g_out1 = out;
+    return 0;
+}
+
+// ---- (2) previous generation: AQHashTable -----------------------------------------------------------
+static std::vector<int> g_legacy_keys;
+static std::vector<long long> g_legacy_sums;
+static std::vector<uint32_t> g_legacy_cnt;
+__AQEXPORT__(int) dll_legacy(Context* cxt) {
+    using namespace std;
+    auto server = static_cast<DataSource*>(cxt->curr_server);
+    auto len = server->cnt;
+    auto id1_a = ColRef<int>(len, server->getCol(0, types::AINT32));
+    auto id2_a = ColRef<int>(len, server->getCol(3, types::AINT32));
+    auto v1_b = ColRef<int>(len, server->getCol(1, types::AINT32));
+    uint32_t total = id1_a.size;
+    typedef record<decays<decltype(id1_a)>::value_t, decays<decltype(id2_a)>::value_t> rec_t;
+    AQHashTable<rec_t, transTypes<rec_t, hasher>> g{total};
+    for (uint32_t i = 0; i < total; ++i) g.hashtable_push(forward_as_tuple(id1_a[i], id2_a[i]), i);
+    auto vecs = g.ht_postproc(total);
+    for (uint32_t i = 0; i < g.size(); ++i) {
+        auto& key = g.values()[i];
+        auto& val = vecs[i];
+        g_legacy_keys.push_back(get<0>(key) * 1000 + get<1>(key));
+        g_legacy_sums.push_back((long long)sum(v1_b[val]));
+        g_legacy_cnt.push_back(val.size);
+    }
+    return 0;
+}
+
+// ---- (3) whole-column code, device-resident columns ---------------------------------------------------
+static std::vector<int> g_w_keys, g_w_min;
+static std::vector<__int128> g_w_sum;
+static std::vector<double> g_w_avgs;
+static std::vector<uint32_t> g_w_off;
+__AQEXPORT__(int) dll_whole(Context* cxt) {
+    auto server = static_cast<DataSource*>(cxt->curr_server);
+    auto len = server->cnt;
+    auto id1 = ColRef<int>(len, server->getCol(0, types::AINT32)).to_device();      // the HBM column store
+    auto v1 = ColRef<int>(len, server->getCol(1, types::AINT32)).to_device();
+    id1.populate_stats();
+    auto g = aq::group_by(id1);
+    auto k0 = g.key<0>();
+    auto s1 = sum(v1[g]);
+    auto m1 = min(v1[g]);
+    auto a3 = avgs(3, v1[g]);
+    g_w_keys = k0.to_host(); g_w_sum = s1.to_host(); g_w_min = m1.to_host(); g_w_avgs = a3.flat.to_host();
+    g_w_off = g.offsets().to_host();
+    EXPECT(s1.on_device() && a3.flat.on_device());
+    return 0;
+}
+
+int main() {
+    if (aqgpu_init(0) != 0) { printf("no CUDA device: %s\n", aqgpu_last_error()); return 2; }
+    const uint32_t n = 100003;
+    std::vector<int> id1(n), id2(n), v1(n);
+    std::vector<float> v3(n);
+    uint64_t x = 88172645463325252ull;
+    auto rnd = [&] { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return x; };
+    for (uint32_t i = 0; i < n; ++i) { id1[i] = 1 + rnd() % 100; id2[i] = 1 + rnd() % 7; v1[i] = (int)(rnd() % 11) - 3; v3[i] = (float)(rnd() % 100000) / 1000.f; }
+    VecSource src;
+    src.cnt = n;
+    src.cols = { id1.data(), v1.data(), v3.data(), id2.data() };
+    Context cxt;
+    cxt.curr_server = &src;
+
+    // expected: first-appearance order, rows of a group in descending order
+    std::vector<int> order; std::map<int, std::vector<uint32_t>> rows;
+    for (uint32_t i = 0; i < n; ++i) { if (!rows.count(id1[i])) order.push_back(id1[i]); rows[id1[i]].push_back(i); }
+
+    EXPECT(dll_unchanged(&cxt) == 0);
+    auto& o = *g_out1;
+    EXPECT(o.get_col<0>().size == order.size());
+    for (size_t gi = 0; gi < order.size() && fails < 5; ++gi) {
+        const auto& r = rows[order[gi]];
+        long long s = 0; double fs = 0; int mx = -1000;
+        std::vector<int> desc(r.rbegin(), r.rend());
+        for (uint32_t i : desc) { s += v1[i]; fs += (double)v3[i]; mx = std::max(mx, v1[i]); }
+        EXPECT(o.get_col<0>()[gi] == order[gi]);
+        EXPECT((long long)o.get_col<1>()[gi] == s);
+        EXPECT(std::fabs(o.get_col<2>()[gi] - fs / r.size()) <= 1e-12 * std::fabs(fs / r.size()));
+        EXPECT(o.get_col<3>()[gi] == mx);
+        auto& cell = o.get_col<4>()[gi];
+        EXPECT(cell.size == r.size());
+        for (uint32_t j = 0; j < cell.size && fails < 5; ++j) {          // avgw(3, .) over the descending row list
+            double w = 0; uint32_t c = 0;
+            for (uint32_t t = (j >= 2 ? j - 2 : 0); t <= j; ++t) { w += v1[desc[t]]; ++c; }
+            EXPECT(std::fabs(cell[j] - w / c) <= 1e-12 * (std::fabs(w / c) + 10));
+        }
+    }
+    o.print(",", "\n", 3);
+
+    EXPECT(dll_legacy(&cxt) == 0);
+    {
+        std::vector<int> ord2; std::map<int, std::pair<long long, uint32_t>> acc;
+        for (uint32_t i = 0; i < n; ++i) { const int k = id1[i] * 1000 + id2[i]; if (!acc.count(k)) ord2.push_back(k); acc[k].first += v1[i]; acc[k].second++; }
+        EXPECT(g_legacy_keys == ord2);
+        for (size_t i = 0; i < ord2.size() && fails < 5; ++i) { EXPECT(g_legacy_sums[i] == acc[ord2[i]].first); EXPECT(g_legacy_cnt[i] == acc[ord2[i]].second); }
+    }
+
+    EXPECT(dll_whole(&cxt) == 0);
+    EXPECT(g_w_keys == order);
+    for (size_t gi = 0; gi < order.size() && fails < 5; ++gi) {
+        const auto& r = rows[order[gi]];
+        long long s = 0; int mn = 1000;
+        for (uint32_t i : r) { s += v1[i]; mn = std::min(mn, v1[i]); }
+        EXPECT((long long)g_w_sum[gi] == s);
+        EXPECT(g_w_min[gi] == mn);
+        EXPECT(g_w_off[gi + 1] - g_w_off[gi] == r.size());
+        EXPECT(std::fabs(g_w_avgs[g_w_off[gi]] - (double)v1[r.back()]) < 1e-12);       // first cell = last row of the group
+    }
+    printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
+    return fails ? 1 : 0;
+}

@@ -1,0 +1,3 @@
+// drop-in for the reference header server/table.h: everything lives in ../aqgpu_host.hpp
+#pragma once
+#include "../aqgpu_host.hpp"

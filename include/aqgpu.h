@@ -110,6 +110,8 @@ int aqgpu_col_upload(void* dptr, const void* host, size_t bytes);
 int aqgpu_col_download(void* host, const void* dptr, size_t bytes);
 int aqgpu_host_alloc(size_t bytes, void** hptr);      /* pinned host memory for staging */
 int aqgpu_host_free(void* hptr);
+/* 1 if p points into device memory (a column of the HBM store), 0 for host memory. */
+int aqgpu_ptr_is_device(const void* p);
 
 /* ---- fused group-by + scalar aggregation -----------------------------------------------------
  * Replaces, in one pass over the columns and without materialising row lists:
@@ -184,6 +186,9 @@ int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, cons
  * the CSR layout of engine/ast.py:696-718.  out has nrows cells of out_type. */
 int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const void* v,
                      int out_type, void* out);
+/* out[offsets[g] + j] = v[row j of group g]  -- the gather col[vecs[g]] of server/table.h:184-189 for
+ * ALL groups at once, in the CSR order of the row lists.  out has nrows cells of vtype. */
+int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out);
 /* ASSUMING-ordered evaluation for unsorted input (common/groupby.py:54-59 ->
  * TableInfo::order_by, server/table.h:447-461): re-orders every group's row list by the given
  * columns (desc[c] != 0 = descending), ties by the current order.  Integer / float keys. */

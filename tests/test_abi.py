@@ -73,3 +73,13 @@ def test_product_does_not_touch_oracle():
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 for needle in needles:
                     assert needle not in txt, f"{os.path.join(dp, f)} mentions {needle}"
+
+
+def test_host_headers_compile():
+    """the drop-in C++ headers (aquery2_b200/host/server/*.h) compile emitter-shaped code against the C ABI"""
+    import subprocess
+    host = os.path.join(ROOT, "aquery2_b200", "host")
+    subprocess.run(["make", "-s", "-C", host], check=True)
+    assert os.path.exists(os.path.join(host, "selftest"))
+    for h in ("vector_type.hpp", "table.h", "hasher.h", "aggregations.h", "types.h", "gc.h", "libaquery.h"):
+        assert os.path.exists(os.path.join(host, "server", h)), h

@@ -254,3 +254,15 @@ def test_partitioned_hint_too_small_and_special_keys(gpu, port):
     check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "f"), ("count",)], groups_hint=20_000)
     check_query_vs_oracle(gpu, port, t, ["k", "k2"], [("sum", "v"), ("min", "f")], groups_hint=20_000)
     check_query_vs_oracle(gpu, port, t, ["k", "k2"], [("sum", "v"), ("min", "f")], groups_hint=400_000)
+
+
+def test_host_header_selftest(gpu):
+    """emitter-shaped C++ (unchanged per-group loop, AQHashTable generation, whole-column form) compiled
+    against the drop-in headers and run on the device: aquery2_b200/host/selftest.cpp"""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "aquery2_b200", "host", "selftest")
+    assert os.path.exists(exe), "run __graft_entry__.build() first"
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "selftest ok" in r.stdout

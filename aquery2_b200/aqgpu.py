@@ -17,12 +17,13 @@ LIB_PATH = os.path.join(HERE, "libaqgpu.so")
 
 # dtype codes = reference types::Type_t (server/aquery_types.h:1-5)
 INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
-SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND = range(11)
+SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND, SUMSQ, SUMXY = range(13)
 SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
 ROWS_DESC, ROWS_ASC = 0, 1
 
 REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
-                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR, "second": SECOND}
+                "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR, "second": SECOND, "sumsq": SUMSQ,
+                "sumxy": SUMXY}
 SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
               "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
               "ratiow": RATIOW}
@@ -43,7 +44,8 @@ EXPORTS = [
     "aqgpu_groupby_agg", "aqgpu_groupby_build", "aqgpu_col_minmax", "aqgpu_groups_free",
     "aqgpu_groups_size", "aqgpu_groups_keys", "aqgpu_groups_first_row", "aqgpu_groups_gid",
     "aqgpu_groups_csr", "aqgpu_groups_device_views", "aqgpu_group_reduce", "aqgpu_group_scan",
-    "aqgpu_groups_order_by", "aqgpu_vec_sub", "aqgpu_avg_finalize", "aqgpu_vec_pow",
+    "aqgpu_groups_order_by", "aqgpu_vec_sub", "aqgpu_avg_finalize", "aqgpu_vec_pow", "aqgpu_finalize",
+    "aqgpu_rows_to_global", "aqgpu_key_owner", "aqgpu_second_merge",
     "aqgpu_synth_column",
 ]
 

@@ -288,7 +288,7 @@ int aqgpu_reduce_out_type(int op, int vtype) {
     if (op == AQ_COUNT) return AQ_UINT32;
     if (!is_val_type(vtype)) return -2;
     switch (op) {
-    case AQ_SUM: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;     // types.h:205-210
+    case AQ_SUM: case AQ_SUMSQ: case AQ_SUMXY: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;     // types.h:205-210
     case AQ_AVG: case AQ_VAR: case AQ_STDDEV: case AQ_CORR: return AQ_DOUBLE;
     case AQ_MIN: case AQ_MAX: case AQ_FIRST: case AQ_LAST: case AQ_SECOND: return vtype;
     default: return -2;

@@ -126,6 +126,10 @@ int AggPlan::plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* d
     bool ok = true;
     switch (a.op) {
     case AQ_SUM: ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
+    case AQ_SUMSQ: ok = (e.a[0] = add_acc(add, X_SQUARE, a.vtype, dv, nullptr)) >= 0; break;
+    case AQ_SUMXY:
+        if (!dv2) return fail("sumxy needs a second column");
+        ok = (e.a[0] = add_acc(add, X_PRODUCT, a.vtype, dv, dv2)) >= 0; break;
     case AQ_AVG: ok = (e.a[0] = add_acc(add, X_IDENT, a.vtype, dv, nullptr)) >= 0 && (e.cnt = add_count()) >= 0; break;
     case AQ_MIN: ok = (e.a[0] = add_acc(ACC_MIN_I64, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
     case AQ_MAX: ok = (e.a[0] = add_acc(ACC_MAX_I64, X_IDENT, a.vtype, dv, nullptr)) >= 0; break;
@@ -291,7 +295,7 @@ __device__ void emit_one(const EmitAgg& e, const unsigned long long* __restrict_
     const bool isint = (e.vtype == AQ_INT32 || e.vtype == AQ_INT64);
     const uint32_t n = e.cnt >= 0 ? (uint32_t)cell(e.cnt) : 0u;
     switch (e.op) {
-    case AQ_SUM:
+    case AQ_SUM: case AQ_SUMSQ: case AQ_SUMXY:
         if (isint) {
             const long long s = (long long)cell(e.a[0]);
             if (e.out_type == AQ_INT128) { I128 v; v.lo = (unsigned long long)s; v.hi = s >> 63; static_cast<I128*>(e.out)[gid] = v; }

@@ -1,0 +1,414 @@
+"""Multi-GPU group-by: row shards, local partial aggregation, NCCL exchange, merge.
+
+One process per GPU (``torch.distributed``, NCCL over NVLink; gloo for the CPU tests).  Rank r owns the
+contiguous global rows [lo_r, hi_r).  A query runs as
+
+  1. local:    ``aqgpu_groupby_agg`` over the shard with DECOMPOSABLE partial aggregates (``decompose``)
+  2. exchange: the partial tables (key columns, partial states, global first rows) are all-gathered when
+               small, or hash-partitioned by key (``aqgpu_key_owner``) and sent to the owning rank with one
+               all-to-all when large
+  3. merge:    a second ``aqgpu_groupby_agg`` over the concatenation of the partial tables in rank order.
+               Shards are contiguous row ranges, so first appearance in that concatenation IS the
+               reference's first-appearance group order (server/unordered_dense.h:1142-1146), and the
+               largest row of the concatenation is the largest global row (FIRST / LAST / SECOND keep
+               their meaning, server/hasher.h:193-196)
+  4. finalize: avg / var / stddev / corr / count / second from the merged states (``aqgpu_finalize``)
+
+The reference is single-process (no distributed backend); this file has no
+counterpart there.  Compute goes through an *engine* (``GpuEngine`` = libaqgpu; the CPU tests plug in an
+oracle-backed engine) and bytes through ``Comm``; nothing here touches oracle/.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from . import aqgpu as aq
+
+INT_CODES = (aq.INT32, aq.INT64)
+
+
+# ------------------------------------------------------------------------------------------------
+# algebra: requested aggregates -> partial aggregates, merge aggregates, finalisation
+# ------------------------------------------------------------------------------------------------
+def decompose(aggs, codes):
+    """aggs: [(op name, column name[, second column])]; codes: {column name: dtype code}.
+
+    Returns (partials, merges, finals):
+      partials  [(op, col, col2, out_code)]               run on the shard (deduplicated)
+      merges    [(op, ("p", i) | ("grow",), out_code)]    run on the concatenated partial tables; ("p", i) =
+                                                          output i of `partials`
+      finals    [(kind, ...)] one per requested aggregate, indices into `merges`
+    """
+    partials, merges = [], []
+
+    def part(op, col=None, col2=None, out=0):
+        e = (op, col, col2, out)
+        if e not in partials:
+            partials.append(e)
+        return partials.index(e)
+
+    def merge(op, src, out=0):
+        e = (op, src, out)
+        if e not in merges:
+            merges.append(e)
+        return merges.index(e)
+
+    def sum_of(op, col, col2=None):
+        isint = codes[col] in INT_CODES
+        p = part(op, col, col2, aq.INT64 if isint else aq.DOUBLE)
+        return merge("sum", ("p", p), aq.INT128 if isint else aq.DOUBLE), (aq.INT128 if isint else aq.DOUBLE)
+
+    def count_of():
+        return merge("sum", ("p", part("count", out=aq.INT64)), aq.INT64)
+
+    finals = []
+    for a in aggs:
+        op = a[0]
+        if op == "sum":
+            finals.append(("col", sum_of("sum", a[1])[0]))
+        elif op == "count":
+            finals.append(("fin", aq.COUNT, count_of(), 0, []))
+        elif op == "avg":
+            s, st = sum_of("sum", a[1])
+            finals.append(("fin", aq.AVG, count_of(), st, [s]))
+        elif op in ("min", "max", "first", "last"):
+            finals.append(("col", merge(op, ("p", part(op, a[1])))))
+        elif op in ("var", "stddev"):
+            s, st = sum_of("sum", a[1])
+            q, _ = sum_of("sumsq", a[1])
+            finals.append(("fin", aq.VAR if op == "var" else aq.STDDEV, count_of(), st, [s, q]))
+        elif op == "corr":
+            x, y = a[1], a[2]
+            cols = [sum_of("sum", x), sum_of("sum", y), sum_of("sumxy", x, y), sum_of("sumsq", x), sum_of("sumsq", y)]
+            finals.append(("fin", aq.CORR, count_of(), cols[0][1], [c[0] for c in cols]))
+        elif op == "second":
+            pf, ps, pc = part("first", a[1]), part("second", a[1]), part("count", out=aq.INT64)
+            finals.append(("second", codes[a[1]], merge("first", ("p", pc)), merge("count", None, aq.INT64),
+                           merge("first", ("p", ps)), merge("second", ("p", pf))))
+        else:
+            raise ValueError(f"aggregate {op!r} has no multi-GPU decomposition")
+    return partials, merges, finals
+
+
+# ------------------------------------------------------------------------------------------------
+# communication
+# ------------------------------------------------------------------------------------------------
+class Comm:
+    """torch.distributed process group: NCCL when CUDA is there, gloo otherwise (CPU tests)."""
+
+    def __init__(self, local_rank: int = 0, backend: str | None = None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        cuda = torch.cuda.is_available()
+        backend = backend or ("nccl" if cuda else "gloo")
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if cuda:
+            torch.cuda.set_device(local_rank)
+        self.device = torch.device("cuda", local_rank) if cuda else torch.device("cpu")
+        if not dist.is_initialized():
+            kw = {"device_id": self.device} if backend == "nccl" else {}
+            dist.init_process_group(backend, **kw)
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        if cuda:      # the library works on torch's current stream: one ordering for kernels and collectives
+            aq.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def barrier(self):
+        self.dist.barrier()
+
+    def _reduce(self, x: float, op):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max_float(self, x: float) -> float:
+        return self._reduce(x, self.dist.ReduceOp.MAX)
+
+    def sum_float(self, x: float) -> float:
+        return self._reduce(x, self.dist.ReduceOp.SUM)
+
+    def all_counts(self, n: int) -> list[int]:
+        t = self.torch.zeros(self.world, dtype=self.torch.int64, device=self.device)
+        t[self.rank] = n
+        self.dist.all_reduce(t)
+        return [int(x) for x in t.tolist()]
+
+    def count_matrix(self, row: list[int]) -> list[list[int]]:
+        """m[src][dst] from every rank's row of per-destination counts"""
+        t = self.torch.zeros(self.world, self.world, dtype=self.torch.int64, device=self.device)
+        t[self.rank] = self.torch.tensor(row, dtype=self.torch.int64)
+        self.dist.all_reduce(t)
+        return [[int(x) for x in r] for r in t.tolist()]
+
+    def allgather_bytes(self, buf, counts: list[int], itemsize: int):
+        """buf: uint8 tensor of counts[rank] * itemsize bytes -> concatenation over ranks (rank order)"""
+        out = self.torch.empty(sum(counts) * itemsize, dtype=self.torch.uint8, device=self.device)
+        off = 0
+        for r, c in enumerate(counts):
+            sl = out[off * itemsize:(off + c) * itemsize]
+            if r == self.rank and c:
+                sl.copy_(buf[:c * itemsize])
+            if c:
+                self.dist.broadcast(sl, src=r)
+            off += c
+        return out
+
+    def alltoall_bytes(self, buf, send_counts: list[int], recv_counts: list[int], itemsize: int):
+        """buf holds the rows for rank 0, 1, ... back to back; returns what the others sent, in rank order"""
+        out = self.torch.empty(sum(recv_counts) * itemsize, dtype=self.torch.uint8, device=self.device)
+        ins = [c * itemsize for c in send_counts]
+        outs = [c * itemsize for c in recv_counts]
+        if self.dist.get_backend() == "gloo":      # gloo has no all_to_all_single on every build: pairwise
+            offs_in = np.concatenate([[0], np.cumsum(ins)]).astype(int)
+            offs_out = np.concatenate([[0], np.cumsum(outs)]).astype(int)
+            for step in range(self.world):
+                dst, src = (self.rank + step) % self.world, (self.rank - step) % self.world
+                send = buf[offs_in[dst]:offs_in[dst + 1]]
+                recv = out[offs_out[src]:offs_out[src + 1]]
+                if dst == self.rank:
+                    recv.copy_(send)
+                    continue
+                reqs = []
+                if len(send):
+                    reqs.append(self.dist.isend(send.contiguous(), dst))
+                if len(recv):
+                    reqs.append(self.dist.irecv(recv, src))
+                for rq in reqs:
+                    rq.wait()
+        else:
+            self.dist.all_to_all_single(out, buf[:sum(ins)], output_split_sizes=outs, input_split_sizes=ins)
+        return out
+
+    def close(self):
+        if self.dist.is_initialized():
+            self.dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# compute engine over libaqgpu (the CPU tests substitute an oracle-backed engine with the same methods)
+# ------------------------------------------------------------------------------------------------
+class _CudaBytes:
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class WrappedColumn(aq.DeviceColumn):
+    """non-owning DeviceColumn over memory of a torch tensor (exchange buffers)"""
+
+    def __init__(self, tensor, n: int, code: int):       # noqa: super().__init__ allocates; this one must not
+        self.n, self.code, self.itemsize = int(n), int(code), aq.CODE_SIZE[code]
+        self.keep, self.ptr = tensor, tensor.data_ptr()
+
+    def free(self):
+        self.ptr, self.keep = None, None
+
+
+class GpuEngine:
+    def __init__(self, comm: Comm):
+        self.comm, self.torch = comm, comm.torch
+
+    def local_prepare(self, keys, partials, cols, max_groups, hint, bounds):
+        specs = [(p[0],) + tuple(cols[c] for c in p[1:3] if c is not None) for p in partials]
+        return aq.PreparedQuery(keys, specs, max_groups=max_groups, groups_hint=hint, key_bounds=bounds, device_out=True,
+                                out_types=[p[3] for p in partials], want_keys=True, want_first_row=True)
+
+    def rows_to_global(self, fr, n, add):
+        out = aq.DeviceColumn(max(n, 1), aq.INT64)
+        aq.check(aq.lib().aqgpu_rows_to_global(aq.ctypes.c_void_p(fr.ptr), aq.ctypes.c_int64(add), aq.ctypes.c_void_p(out.ptr),
+                                               aq.ctypes.c_uint32(n)))
+        return out
+
+    def bytes_of(self, col, n):
+        nb = n * col.itemsize
+        if nb == 0:
+            return self.torch.empty(0, dtype=self.torch.uint8, device=self.comm.device)
+        return self.torch.as_tensor(_CudaBytes(col.ptr, nb), device=self.comm.device)
+
+    def from_bytes(self, t, n, code):
+        return WrappedColumn(t, n, code)
+
+    def groupby(self, keys, specs, hint, bounds, max_groups):
+        res = aq.groupby_agg(keys, [(s[0],) + tuple(c for c in s[1:3] if c is not None) for s in specs], groups_hint=hint,
+                             max_groups=max_groups, key_bounds=bounds, device_out=True, want_first_row=False,
+                             out_types=[s[3] for s in specs])
+        return res.ngroups, res.keys, res.aggs
+
+    def finalize(self, op, n, count, s_code, s_cols):
+        out = aq.DeviceColumn(max(n, 1), aq.UINT32 if op == aq.COUNT else aq.DOUBLE)
+        sp = (aq.ctypes.c_void_p * 5)(*([c.ptr for c in s_cols] + [None] * (5 - len(s_cols))))
+        aq.check(aq.lib().aqgpu_finalize(op, aq.ctypes.c_uint32(n), aq.ctypes.c_void_p(count.ptr), s_code, sp, aq.ctypes.c_void_p(out.ptr)))
+        return out
+
+    def second_merge(self, code, n, cnt_top, nparts, second_top, first_prev):
+        out = aq.DeviceColumn(max(n, 1), code)
+        aq.check(aq.lib().aqgpu_second_merge(code, aq.ctypes.c_void_p(cnt_top.ptr), aq.ctypes.c_void_p(nparts.ptr),
+                                             aq.ctypes.c_void_p(second_top.ptr), aq.ctypes.c_void_p(first_prev.ptr),
+                                             aq.ctypes.c_void_p(out.ptr), aq.ctypes.c_uint32(n)))
+        return out
+
+    def partition(self, keys, n, nparts, cols):
+        """rows grouped by owner rank, original order kept inside an owner: (rows per owner, the columns in that order)"""
+        if n == 0:
+            return [0] * nparts, cols
+        owner = aq.DeviceColumn(n, aq.UINT32)
+        kp = (aq.ctypes.c_void_p * len(keys))(*[k.ptr for k in keys])
+        kt = (aq.ctypes.c_int * len(keys))(*[k.code for k in keys])
+        aq.check(aq.lib().aqgpu_key_owner(kp, kt, len(keys), aq.ctypes.c_uint32(n), aq.ctypes.c_uint32(nparts), aq.ctypes.c_void_p(owner.ptr)))
+        g = aq.Groups([owner], row_order=aq.ROWS_ASC, groups_hint=nparts, key_bounds=[(0, nparts - 1)])
+        ranks = g.keys(0)                       # owners present, in first-appearance order = CSR block order
+        off = self._offsets(g)
+        counts = [0] * nparts
+        for i, r in enumerate(ranks):
+            counts[int(r)] = int(off[i + 1] - off[i])
+        out = []
+        for c in cols:
+            gathered = aq.DeviceColumn(n, c.code)
+            self._gather(g, c, gathered, n)
+            out.append(gathered)
+        order = np.argsort(ranks, kind="stable")            # the exchange wants the blocks in ascending owner order
+        if not np.array_equal(order, np.arange(len(ranks))):
+            out = [self._reorder_blocks(c, off, order, n) for c in out]
+        g.free()
+        return counts, out
+
+    @staticmethod
+    def _offsets(g):
+        off = np.zeros(g.ngroups + 1, np.uint32)
+        aq.check(aq.lib().aqgpu_groups_csr(g.h, off.ctypes.data_as(aq.ctypes.c_void_p), None))
+        return off
+
+    def _gather(self, g, src, dst, n):
+        if src.itemsize in (4, 8):
+            code = aq.INT32 if src.itemsize == 4 else aq.INT64
+            aq.check(aq.lib().aqgpu_group_gather(g.h, code, aq.ctypes.c_void_p(src.ptr), aq.ctypes.c_void_p(dst.ptr)))
+        else:           # 16-byte cells: two 8-byte halves through torch views would need strides; not exchanged today
+            raise aq.AqgpuError("16-byte partial cells are not exchanged (partials are <= 8 bytes wide)")
+
+    def _reorder_blocks(self, col, off, order, n):
+        t = self.bytes_of(col, n)
+        out = self.torch.empty_like(t)
+        pos = 0
+        for i in order:
+            a, b = int(off[i]) * col.itemsize, int(off[i + 1]) * col.itemsize
+            out[pos:pos + b - a].copy_(t[a:b])
+            pos += b - a
+        return self.from_bytes(out, n, col.code)
+
+    def to_numpy(self, col, n):
+        return col.numpy(n)
+
+
+# ------------------------------------------------------------------------------------------------
+# one distributed query
+# ------------------------------------------------------------------------------------------------
+GATHER_LIMIT = 4_000_000        # partial rows over all ranks up to which every rank merges everything
+
+
+class DistQuery:
+    """keys / aggs name columns of `cols` (this rank's shard, rows [lo, lo + n) of the global table)."""
+
+    def __init__(self, comm: Comm, engine, cols: dict, codes: dict, keys, aggs, lo: int, max_groups: int,
+                 hint: int = 0, bounds=None, gather_limit: int = GATHER_LIMIT):
+        self.comm, self.eng, self.lo = comm, engine, int(lo)
+        self.key_names, self.aggs = list(keys), list(aggs)
+        self.key_codes = [codes[k] for k in keys]
+        self.hint, self.bounds, self.gather_limit = hint, bounds, gather_limit
+        self.partials, self.merges, self.finals = decompose(aggs, codes)
+        self.pcodes = [p[3] or aq.reduce_out_type(aq.REDUCE_NAMES[p[0]], codes[p[1]] if p[1] else aq.INT32) for p in self.partials]
+        self.local = engine.local_prepare([cols[k] for k in keys], self.partials, cols, max_groups, hint, bounds)
+        self.strategy = None
+        self.exchanged_bytes = 0
+
+    def run(self):
+        """returns (ngroups on this rank, key columns, result columns, first global rows); with the gather
+        strategy every rank holds all groups in the reference's order, with the partitioned strategy
+        rank r holds the groups it owns, each rank's in ascending first-global-row order"""
+        c, e = self.comm, self.eng
+        ng = self.local.run()
+        grow = e.rows_to_global(self.local.fr, ng, self.lo)
+        table = list(self.local.kouts) + list(self.local.outs) + [grow]
+        tcodes = self.key_codes + self.pcodes + [aq.INT64]
+        counts = c.all_counts(ng)
+        total = sum(counts)
+        self.exchanged_bytes = 0
+        if total <= self.gather_limit:
+            self.strategy = "allgather"
+            recv = []
+            for col, code in zip(table, tcodes):
+                sz = aq.CODE_SIZE[code]
+                recv.append(e.from_bytes(c.allgather_bytes(e.bytes_of(col, ng), counts, sz), total, code))
+                self.exchanged_bytes += (total - ng) * sz
+            nmerge = total
+        else:
+            self.strategy = "alltoall"
+            send, parted = e.partition(table[:len(self.key_names)], ng, c.world, table)
+            m = c.count_matrix(send)
+            rcounts = [m[src][c.rank] for src in range(c.world)]
+            nmerge = sum(rcounts)
+            recv = []
+            for col, code in zip(parted, tcodes):
+                sz = aq.CODE_SIZE[code]
+                recv.append(e.from_bytes(c.alltoall_bytes(e.bytes_of(col, ng), send, rcounts, sz), nmerge, code))
+                self.exchanged_bytes += (ng - send[c.rank]) * sz
+        nk = len(self.key_names)
+        rkeys, rparts, rgrow = recv[:nk], recv[nk:-1], recv[-1]
+        specs = []
+        for op, src, out in self.merges:
+            specs.append((op, rparts[src[1]] if src else None, None, out))
+        specs.append(("min", rgrow, None, aq.INT64))
+        hint = min(nmerge, self.hint) if self.hint else 0
+        ngm, mkeys, mouts = e.groupby(rkeys, specs, hint, self.bounds, max(nmerge, 1))
+        first_global = mouts[-1]
+        results = []
+        for f in self.finals:
+            if f[0] == "col":
+                results.append(mouts[f[1]])
+            elif f[0] == "fin":
+                _, op, cnt, st, ss = f
+                results.append(e.finalize(op, ngm, mouts[cnt], st, [mouts[i] for i in ss]))
+            else:
+                _, code, cnt_top, nparts, second_top, first_prev = f
+                results.append(e.second_merge(code, ngm, mouts[cnt_top], mouts[nparts], mouts[second_top], mouts[first_prev]))
+        return ngm, mkeys, results, first_global
+
+
+class DistPlan:
+    """the h2o queries of bench.py over row shards (one DistQuery each); mirrors h2o.Plan"""
+
+    def __init__(self, comm: Comm, table: dict, queries, n_total: int, k: int, lo: int, use_bounds: bool = True):
+        from . import h2o
+        self.comm, self.queries = comm, list(queries)
+        self.eng = GpuEngine(comm)
+        codes = {c: d.code for c, d in table.items()}
+        nrows = next(iter(table.values())).n
+        self.dq, self.epilogue, self.extra = {}, {}, {}
+        for q in self.queries:
+            keys, aggs, epi = h2o.QUERIES[q]
+            mg = h2o.max_groups(q, n_total, k, nrows)
+            bounds = [h2o.key_bound(c, n_total, k) for c in keys] if use_bounds else None
+            self.dq[q] = DistQuery(comm, self.eng, table, codes, keys, aggs, lo, mg, hint=mg, bounds=bounds)
+            self.epilogue[q] = epi
+
+    def run(self, q: str) -> int:
+        ng, keys, res, _ = self.dq[q].run()
+        epi = self.epilogue[q]
+        if epi == "sub":
+            out = aq.DeviceColumn(max(ng, 1), aq.INT32)
+            aq.vec_sub(res[0], res[1], out, ng, aq.INT32)
+        elif epi == "pow2":
+            out = aq.DeviceColumn(max(ng, 1), aq.DOUBLE)
+            aq.vec_pow(res[0], 2.0, out, ng)
+        self.last = (ng, keys, res)
+        return ng
+
+    def step(self) -> dict:
+        return {q: self.run(q) for q in self.queries}
+
+    def total_groups(self, ngs: dict) -> dict:
+        """groups over all ranks: the gather strategy replicates them, the partitioned one splits them"""
+        out = {}
+        for q, ng in ngs.items():
+            out[q] = ng if self.dq[q].strategy == "allgather" else int(self.comm.sum_float(float(ng)))
+        return out

@@ -185,8 +185,12 @@ def run_b200(args, queries):
     cols = h2o.columns_of(queries)
     table = h2o.device_table(aq, n_total, args.k, lo, hi, cols)
     aq.sync()
-    plan = h2o.Plan(aq, table, queries, n_total, args.k, device_out=True, use_bounds=not args.no_bounds)
-    runner = plan if comm is None else dist.DistPlan(comm, plan, n_total, args.k)
+    if comm is None:
+        plan = h2o.Plan(aq, table, queries, n_total, args.k, device_out=True, use_bounds=not args.no_bounds)
+        runner = plan
+    else:
+        plan = None
+        runner = dist.DistPlan(comm, table, queries, n_total, args.k, lo, use_bounds=not args.no_bounds)
 
     def barrier():
         if comm is not None:
@@ -213,6 +217,10 @@ def run_b200(args, queries):
         launches = int(comm.sum_float(float(launches)))
     ms_per_step = ms / args.steps
     value = len(queries) * n_total / (ms_per_step * 1e-3)
+    exchange = None
+    if comm is not None:
+        ngs = runner.total_groups(ngs)
+        exchange = {q: {"strategy": runner.dq[q].strategy, "bytes_in_per_rank": runner.dq[q].exchanged_bytes} for q in queries}
 
     # ---- per-kernel / per-query breakdown (separate pass, CUDA events around every launch)
     aq.profile_enable(True)
@@ -253,9 +261,6 @@ def run_b200(args, queries):
     e2e = None
     if not args.no_e2e and comm is None:
         e2e = run_e2e(args, aq, h2o, table, plan, queries, n_total)
-    elif not args.no_e2e:
-        e2e = runner.e2e(args)
-
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, queries, args.cpu_rows)
@@ -269,7 +274,7 @@ def run_b200(args, queries):
                            "l2": "inputs (>= 8 B/row x rows) far larger than the 126 MB L2; no flush needed",
                            "parallelism": "1 GPU" if world == 1 else f"{world} GPUs: row-range shards, local partial aggregation, NCCL merge"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches // max(args.steps, 1) * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "per_query": per_query, "kernels": kernels}
+                "roofline": roofline, "cpu_baseline": cpu, "per_query": per_query, "kernels": kernels, "exchange": exchange}
         print(json.dumps(line), flush=True)
     if comm is not None:
         comm.close()

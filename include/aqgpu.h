@@ -52,9 +52,14 @@ enum aqgpu_reduce_op {
     AQ_VAR = 7,     /* aggregations.h:332-348 (divides by len+1, kept) */
     AQ_STDDEV = 8,  /* aggregations.h:413-415 */
     AQ_CORR = 9,    /* aggregations.h:383-407 integer inputs only */
-    AQ_SECOND = 10  /* element [1] of the group's row list (0 when the group has one row): with
+    AQ_SECOND = 10, /* element [1] of the group's row list (0 when the group has one row): with
                        AQ_FIRST this is subvec(v, 0, 2) of h2o q8 (benchmark/h2o/groupby.sql:17,
                        server/vector_type.hpp:348-355) */
+    /* partial moments, the decomposable halves of VAR / STDDEV / CORR for multi-GPU merges
+     * (result cells like AQ_SUM): sum of v*v and of v*v2, products formed in the column's own type as
+     * aggregations.h:339-345, 392-398 do */
+    AQ_SUMSQ = 11,
+    AQ_SUMXY = 12
 };
 
 /* ---- per-group vector-valued aggregates, CSR output (engine/ast.py:696-718) ------------------ */
@@ -201,6 +206,23 @@ int aqgpu_vec_sub(int dtype, const void* a, const void* b, void* out, uint32_t n
 /* out[i] = sum[i] / double(count[i]): AVG finalisation after a multi-GPU merge. sum is AQ_INT64,
  * AQ_INT128 or AQ_DOUBLE. */
 int aqgpu_avg_finalize(int sum_type, const void* sum, const uint32_t* count, double* out, uint32_t n);
+/* Finalisation of merged partial states (multi-GPU); n cells each.
+ *   AQ_AVG     out f64 = s[0] / count                                  aggregations.h:28-32
+ *   AQ_VAR / AQ_STDDEV   from s[0] = sum, s[1] = sum of squares        aggregations.h:332-348, 413-415
+ *   AQ_CORR    from s = {sum x, sum y, sum xy, sum xx, sum yy}          aggregations.h:383-407
+ *   AQ_COUNT   out u32 = count
+ * count is AQ_INT64; every s[k] has dtype s_type (AQ_INT64, AQ_INT128 or AQ_DOUBLE). */
+int aqgpu_finalize(int op, uint32_t n, const int64_t* count, int s_type, const void* const* s, void* out);
+/* out[i] = (int64) in[i] + add: local first rows -> global row ids of a shard. */
+int aqgpu_rows_to_global(const uint32_t* in, int64_t add, int64_t* out, uint32_t n);
+/* owner[i] = hash(key tuple of row i) % nparts: the rank that merges the group (hash-partitioned
+ * exchange of partial aggregates). */
+int aqgpu_key_owner(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                    uint32_t nparts, uint32_t* owner);
+/* AQ_SECOND across shards: out = cnt_top >= 2 ? second_top : (nparts >= 2 ? first_prev : 0), cells of
+ * vtype; cnt_top and nparts are AQ_INT64 columns. */
+int aqgpu_second_merge(int vtype, const int64_t* cnt_top, const int64_t* nparts, const void* second_top,
+                       const void* first_prev, void* out, uint32_t n);
 /* out[i] = pow(x[i], p) in fp64 (q9 pow(corr, 2); aggregations.h:409-411). */
 int aqgpu_vec_pow(const double* x, double p, double* out, uint32_t n);
 

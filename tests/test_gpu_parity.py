@@ -266,3 +266,69 @@ def test_host_header_selftest(gpu):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "selftest ok" in r.stdout
+
+
+# ---- multi-GPU path on one device: the GPU engine of aquery2_b200/dist.py ---------------------------
+@pytest.fixture(scope="module")
+def comm1(gpu):
+    import os
+    import socket
+    from aquery2_b200 import dist
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK="0", WORLD_SIZE="1")
+    c = dist.Comm(0)
+    yield c
+    gpu.set_stream(None)
+    c.close()
+
+
+def test_dist_engine_single_rank(gpu, port, comm1):
+    """local partial aggregation -> exchange (world size 1) -> merge -> finalize on the device, both
+    exchange strategies, against the oracle on the same table"""
+    from aquery2_b200 import dist
+    n, k = 300_000, 50
+    t = synth.h2o_table(n, k, seed=33)
+    d = {c: gpu.DeviceColumn.from_numpy(a) for c, a in t.items()}
+    codes = {c: x.code for c, x in d.items()}
+    eng = dist.GpuEngine(comm1)
+    for keys, aggs in ((["id1"], [("sum", "v1"), ("avg", "v3"), ("count",)]),
+                       (["id1", "id2"], [("stddev", "v3"), ("corr", "v1", "v2"), ("var", "v1")]),
+                       (["id3"], [("max", "v1"), ("min", "v2"), ("first", "v3"), ("second", "v3"), ("last", "v1")]),
+                       (["id6"], [("sum", "v1"), ("sum", "v3"), ("second", "v1")])):
+        ng, gid, off, perm = port.groupby([t[c] for c in keys])
+        first = perm[off[1:] - 1]
+        for limit in (10**9, 0):
+            q = dist.DistQuery(comm1, eng, d, codes, keys, aggs, 0, max_groups=n, gather_limit=limit)
+            ngm, mkeys, res, fg = q.run()
+            assert ngm == ng and q.strategy == ("allgather" if limit else "alltoall")
+            assert_same(fg.numpy(ngm).astype(np.uint32), first.astype(np.uint32), "first global row")
+            for i, c in enumerate(keys):
+                assert_same(mkeys[i].numpy(ngm), t[c][first], f"key {c}")
+            for j, a in enumerate(aggs):
+                want = port.reduce(a[0], t[a[1]] if len(a) > 1 else None, off, perm, v2=t[a[2]] if len(a) > 2 else None, raw128=True)
+                assert_same(res[j].numpy(ngm), want, f"{keys} {a} limit={limit}")
+
+
+def test_dist_partition_by_owner(gpu, comm1):
+    """rows grouped by owner rank with their order kept (the send buffers of the all-to-all)"""
+    from aquery2_b200 import dist
+    n, parts = 200_001, 4
+    rng = np.random.default_rng(2)
+    key = rng.integers(0, 50_000, n).astype(np.int32)
+    val = rng.random(n)
+    idx = np.arange(n, dtype=np.int64)
+    eng = dist.GpuEngine(comm1)
+    cols = [gpu.DeviceColumn.from_numpy(a) for a in (key, val, idx)]
+    counts, out = eng.partition([cols[0]], n, parts, cols)
+    assert sum(counts) == n and len(counts) == parts and min(counts) > 0
+    k2, v2, i2 = (c.numpy(n) for c in out)
+    assert_same(k2, key[i2]); assert_same(v2, val[i2])
+    bounds = np.concatenate([[0], np.cumsum(counts)])
+    owners = []
+    for r in range(parts):
+        blk = i2[bounds[r]:bounds[r + 1]]
+        assert np.all(np.diff(blk) > 0)                           # stable inside an owner
+        owners.append(set(np.unique(k2[bounds[r]:bounds[r + 1]]).tolist()))
+    for a in range(parts):
+        for b in range(a + 1, parts):
+            assert not (owners[a] & owners[b])                    # a key has exactly one owner

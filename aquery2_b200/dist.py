@@ -97,6 +97,7 @@ def decompose(aggs, codes):
 # ------------------------------------------------------------------------------------------------
 class Comm:
     """torch.distributed process group: NCCL when CUDA is there, gloo otherwise (CPU tests)."""
+    CHUNK = 256 << 20          # bytes per peer and all-to-all call
 
     def __init__(self, local_rank: int = 0, backend: str | None = None):
         import torch
@@ -109,8 +110,9 @@ class Comm:
             torch.cuda.set_device(local_rank)
         self.device = torch.device("cuda", local_rank) if cuda else torch.device("cpu")
         if not dist.is_initialized():
+            import datetime
             kw = {"device_id": self.device} if backend == "nccl" else {}
-            dist.init_process_group(backend, **kw)
+            dist.init_process_group(backend, timeout=datetime.timedelta(seconds=int(os.environ.get("AQ_DIST_TIMEOUT", "180"))), **kw)
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         if cuda:      # the library works on torch's current stream: one ordering for kernels and collectives
             aq.set_stream(torch.cuda.current_stream().cuda_stream)
@@ -142,6 +144,15 @@ class Comm:
         self.dist.all_reduce(t)
         return [[int(x) for x in r] for r in t.tolist()]
 
+    def _wide(self, t, itemsize: int):
+        """the same bytes as 8- or 4-byte elements where the cell size allows: element counts of NCCL
+        calls stay far below 2^31 (a 4e9-element uint8 all-to-all hung on B200 / NCCL 2.28)"""
+        if itemsize % 8 == 0 and t.data_ptr() % 8 == 0:
+            return t.view(self.torch.int64), 8
+        if itemsize % 4 == 0 and t.data_ptr() % 4 == 0:
+            return t.view(self.torch.int32), 4
+        return t, 1
+
     def allgather_bytes(self, buf, counts: list[int], itemsize: int):
         """buf: uint8 tensor of counts[rank] * itemsize bytes -> concatenation over ranks (rank order)"""
         out = self.torch.empty(sum(counts) * itemsize, dtype=self.torch.uint8, device=self.device)
@@ -151,11 +162,11 @@ class Comm:
             if r == self.rank and c:
                 sl.copy_(buf[:c * itemsize])
             if c:
-                self.dist.broadcast(sl, src=r)
+                self.dist.broadcast(self._wide(sl, itemsize)[0], src=r)
             off += c
         return out
 
-    def alltoall_bytes(self, buf, send_counts: list[int], recv_counts: list[int], itemsize: int):
+    def alltoall_bytes(self, buf, send_counts: list[int], recv_counts: list[int], itemsize: int, max_count: int | None = None):
         """buf holds the rows for rank 0, 1, ... back to back; returns what the others sent, in rank order"""
         out = self.torch.empty(sum(recv_counts) * itemsize, dtype=self.torch.uint8, device=self.device)
         ins = [c * itemsize for c in send_counts]
@@ -178,7 +189,20 @@ class Comm:
                 for rq in reqs:
                     rq.wait()
         else:
-            self.dist.all_to_all_single(out, buf[:sum(ins)], output_split_sizes=outs, input_split_sizes=ins)
+            # pieces of <= CHUNK bytes per peer: one 4 GB all_to_all_single (2 GB per peer) never completed on
+            # B200 / NCCL 2.28, 1 GB per peer did
+            offs_in = np.concatenate([[0], np.cumsum(ins)]).astype(np.int64)
+            offs_out = np.concatenate([[0], np.cumsum(outs)]).astype(np.int64)
+            step = max(self.CHUNK // itemsize, 1) * itemsize
+            if max_count is None:       # every rank must issue the same number of calls
+                max_count = int(self.max_float(float(max(send_counts + recv_counts, default=0))))
+            dt = self.torch.int64 if itemsize % 8 == 0 else self.torch.int32 if itemsize % 4 == 0 else self.torch.uint8
+            done = 0
+            while done < max_count * itemsize:
+                send = [buf[offs_in[d] + min(done, ins[d]):offs_in[d] + min(done + step, ins[d])].view(dt) for d in range(self.world)]
+                recv = [out[offs_out[r] + min(done, outs[r]):offs_out[r] + min(done + step, outs[r])].view(dt) for r in range(self.world)]
+                self.dist.all_to_all(recv, send)
+                done += step
         return out
 
     def close(self):
@@ -346,11 +370,12 @@ class DistQuery:
             send, parted = e.partition(table[:len(self.key_names)], ng, c.world, table)
             m = c.count_matrix(send)
             rcounts = [m[src][c.rank] for src in range(c.world)]
+            mmax = max(max(r) for r in m)
             nmerge = sum(rcounts)
             recv = []
             for col, code in zip(parted, tcodes):
                 sz = aq.CODE_SIZE[code]
-                recv.append(e.from_bytes(c.alltoall_bytes(e.bytes_of(col, ng), send, rcounts, sz), nmerge, code))
+                recv.append(e.from_bytes(c.alltoall_bytes(e.bytes_of(col, ng), send, rcounts, sz, mmax), nmerge, code))
                 self.exchanged_bytes += (ng - send[c.rank]) * sz
         nk = len(self.key_names)
         rkeys, rparts, rgrow = recv[:nk], recv[nk:-1], recv[-1]

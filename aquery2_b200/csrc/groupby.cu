@@ -73,6 +73,28 @@ int KeyCols::make_spec(const int64_t* key_min, const int64_t* key_max, KeySpec& 
             if (bits > 32) ok = false;
         }
         if (ok) { ks.exact = 2; ks.pack_bits = bits; }
+        else if (n <= MAX_KEY_WORDS) {
+            // wide image: first-fit of whole columns into the 32-bit tag or the 64-bit second word
+            uint32_t used[2] = {0, 0};
+            const uint32_t room[2] = {32, 64};
+            bool wide = true;
+            for (int k = 0; k < n && wide; ++k) {
+                const int64_t lo = key_min[k], hi = key_max[k];
+                if (hi < lo || hi - lo > 0xffffffffLL) { wide = false; break; }
+                const uint64_t range = uint64_t(hi - lo);
+                uint32_t b = 0;
+                while (b < 32 && (range >> b) != 0) ++b;
+                const int part = used[0] + b <= room[0] ? 0 : (used[1] + b <= room[1] ? 1 : -1);
+                if (part < 0) { wide = false; break; }
+                ks.pack_lo[k] = (uint32_t)lo;
+                ks.pack_range[k] = (uint32_t)range;
+                ks.wide_part[k] = (uint32_t)part;
+                ks.wide_shift[k] = used[part];
+                used[part] += b;
+            }
+            // all-ones in the second word marks an empty slot: keep one bit of it clear
+            ks.wide = (wide && used[1] < 64) ? 1 : 0;
+        }
     }
     return 0;
 }
@@ -198,6 +220,71 @@ k_probe_agg(const KeySpec ks, const uint32_t nrows, const uint32_t mask, const u
             else for (int r = 0; r < cnt; ++r) row_slot[row0 + r] = slot[r];
         }
         for (int a = 0; a < prog.n; ++a) acc_apply(prog, a, slot, row0, cnt);
+    }
+}
+
+// ---- wide exact keys: slot words (0, 1) = (tag << 32 | min row, second key word), accumulators from word 2
+// one thread = 4 consecutive rows, every key column read once with a 128-bit load
+__global__ void __launch_bounds__(256)
+k_probe_wide(const KeySpec ks, const uint32_t nrows, const uint32_t mask, const uint32_t max_probe,
+             const AccProg prog, uint32_t* __restrict__ row_slot, uint32_t* __restrict__ flags) {
+    const uint32_t nquad = (nrows + 3u) >> 2;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nquad; q += gridDim.x * blockDim.x) {
+        if (*reinterpret_cast<volatile uint32_t*>(flags + FLAG_ABORT)) return;
+        const uint32_t row0 = q << 2;
+        const int cnt = min(4u, nrows - row0);
+        uint32_t tag[4], slot[4];
+        unsigned long long hi[4];
+        const bool ok = wide_pack4(ks, row0, cnt, tag, hi);
+        if (!ok) { atomicExch(flags + FLAG_ABORT, 3u); return; }
+        // first probe of all four rows in flight together
+        uint32_t s0[4];
+        unsigned long long c0[4], c1[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            s0[r] = wide_hash(tag[r], hi[r]) & mask;
+            if (r < cnt) ld128_volatile(prog.tab + size_t(s0[r]) * prog.sw, c0[r], c1[r]);
+        }
+        bool bad = false;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            slot[r] = 0;
+            if (r >= cnt) continue;
+            const uint32_t row = row0 + r;
+            const unsigned long long mine = ((unsigned long long)tag[r] << 32) | row;
+            uint32_t s = s0[r], found = NOSLOT;
+            unsigned long long a = c0[r], b = c1[r];
+            for (uint32_t step = 0; step <= max_probe; ++step) {
+                unsigned long long* w0 = prog.tab + size_t(s) * prog.sw;
+                if (step) ld128_volatile(w0, a, b);
+                if (a == SLOT_EMPTY) {
+                    unsigned long long o0, o1;
+                    cas128(w0, SLOT_EMPTY, SLOT_EMPTY, mine, hi[r], o0, o1);
+                    if (o0 == SLOT_EMPTY) { found = s; break; }
+                    a = o0; b = o1;
+                }
+                if ((uint32_t)(a >> 32) == tag[r] && b == hi[r]) {
+                    if (row < (uint32_t)a) atomicMin(w0, mine);
+                    found = s; break;
+                }
+                s = (s + 1) & mask;
+            }
+            slot[r] = found;
+            bad |= found == NOSLOT;
+        }
+        if (bad) { atomicCAS(flags + FLAG_ABORT, 0u, 1u); return; }
+        if (row_slot) {
+            if (cnt == 4) *reinterpret_cast<uint4*>(row_slot + row0) = make_uint4(slot[0], slot[1], slot[2], slot[3]);
+            else for (int r = 0; r < cnt; ++r) row_slot[row0 + r] = slot[r];
+        }
+        for (int a = 0; a < prog.n; ++a) {
+            const AccOp& o = prog.op[a];
+            long long xi[4] = {0, 0, 0, 0}; double xd[4] = {0, 0, 0, 0};
+            if (acc_needs_value(o)) acc_inputs(o, row0, cnt, xi, xd);
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                if (r < cnt) acc_global_row(o, slot_word(prog, slot[r]) + 2 + a, row0 + r, xi[r], xd[r]);
+        }
     }
 }
 
@@ -416,6 +503,102 @@ k_emit_rows(const KeySpec ks, const unsigned long long* __restrict__ tab, const 
     }
 }
 
+// ---- fused rank + emit (global-table path): ONE pass in row order ---------------------------------------
+// row_slot[i] is row i's slot; row i is its group's first appearance iff the slot's min row == i.  A
+// tile of EF_ROWS rows counts its first rows, gets the number of first rows before it by decoupled
+// look-back over per-tile states (tiles are handed out by a ticket counter, so a tile's predecessors
+// have always started), and writes keys / first rows / aggregates at gid = that rank: the insertion
+// index of m_values in the reference (server/unordered_dense.h:1142-1146).  One random 32-byte sector
+// read per ROW replaces k_mark + k_rank_* + the re-probe of k_emit_rows when groups ~ rows (h2o q10).
+constexpr int EF_THREADS = 256;
+constexpr int EF_ROWS = EF_THREADS * 4;
+constexpr unsigned long long EF_AGG = 1ull << 62, EF_PREFIX = 2ull << 62, EF_VAL = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(EF_THREADS)
+k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, const int acc_off,
+             const uint32_t* __restrict__ row_slot, const uint32_t nrows, const uint32_t ntiles,
+             unsigned long long* __restrict__ tile_state, uint32_t* __restrict__ ticket,
+             const KeyOut ko, uint32_t* __restrict__ first_row_out, const EmitProg ep,
+             const uint32_t max_groups, uint32_t* __restrict__ flags) {
+    __shared__ uint32_t s_tile, s_excl, warp_sums[EF_THREADS / 32];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (;;) {
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= ntiles) return;
+        const uint32_t row0 = tile * EF_ROWS + threadIdx.x * 4;
+        const int cnt = row0 < nrows ? (int)min(4u, nrows - row0) : 0;
+        uint32_t sl[4] = {0, 0, 0, 0};
+        if (!row_slot) { for (int r = 0; r < 4; ++r) sl[r] = row0 + r; }          // one record per row (groupby_hc.cu)
+        else if (cnt == 4) { const int4 t = ld_stream_v4(row_slot + row0); sl[0] = t.x; sl[1] = t.y; sl[2] = t.z; sl[3] = t.w; }
+        else for (int r = 0; r < cnt; ++r) sl[r] = row_slot[row0 + r];
+        unsigned long long w0[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) w0[r] = r < cnt ? tab[size_t(sl[r]) * sw] : SLOT_EMPTY;
+        uint32_t fl = 0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) if (r < cnt && (uint32_t)w0[r] == row0 + r) fl |= 1u << r;
+        const uint32_t mine = __popc(fl);
+        // block exclusive scan of `mine`
+        uint32_t x = mine;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) warp_sums[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t v = lane < EF_THREADS / 32 ? warp_sums[lane] : 0u, sc = v;
+#pragma unroll
+            for (int d = 1; d < EF_THREADS / 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, d); if (lane >= d) sc += y; }
+            if (lane < EF_THREADS / 32) warp_sums[lane] = sc - v;            // exclusive per warp
+            const uint32_t total = __shfl_sync(0xffffffffu, sc, EF_THREADS / 32 - 1);
+            // ---- decoupled look-back
+            volatile unsigned long long* st = tile_state;
+            if (lane == 0) st[tile] = (tile == 0 ? EF_PREFIX : EF_AGG) | total;
+            uint32_t excl = 0;
+            if (tile > 0) {
+                long long look = (long long)tile - 1;
+                for (;;) {
+                    const long long idx = look - lane;
+                    unsigned long long v2 = EF_PREFIX;
+                    if (idx >= 0) { do { v2 = st[idx]; } while ((v2 >> 62) == 0); }
+                    const uint32_t pm = __ballot_sync(0xffffffffu, (v2 >> 62) == 2);
+                    const int first = pm ? __ffs(pm) - 1 : 32;
+                    uint32_t part = ((int)lane <= first) ? (uint32_t)(v2 & EF_VAL) : 0u;
+#pragma unroll
+                    for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+                    excl += part;
+                    if (pm) break;
+                    look -= 32;
+                }
+                if (lane == 0) st[tile] = EF_PREFIX | (unsigned long long)(excl + total);
+            }
+            if (lane == 0) {
+                s_excl = excl;
+                if (tile + 1 == ntiles) flags[FLAG_NGROUPS] = excl + total;
+            }
+        }
+        __syncthreads();
+        uint32_t gid = s_excl + warp_sums[wid] + x - mine;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (!((fl >> r) & 1u)) continue;
+            const uint32_t g = gid++;
+            if (g >= max_groups) continue;                                    // the host reports the overflow
+            const uint32_t fr = row0 + r;
+            const unsigned long long* slp = tab + size_t(sl[r]) * sw + (acc_off - 1);
+            if (first_row_out) first_row_out[g] = fr;
+            for (int k = 0; k < ko.n; ++k) {
+                if (!ko.dst[k]) continue;
+                if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[g] = static_cast<const uint32_t*>(ko.src[k])[fr];
+                else static_cast<unsigned long long*>(ko.dst[k])[g] = static_cast<const unsigned long long*>(ko.src[k])[fr];
+            }
+            for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], slp, g, fr, ep.row_order);
+        }
+        __syncthreads();                                                      // s_tile / warp_sums reused
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host pipeline
 // ------------------------------------------------------------------------------------------------
@@ -434,27 +617,46 @@ static unsigned long long acc_identity(int kind) {
 }
 
 int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& plan,
-                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups) {
+                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups, bool allow_fused) {
     Context& c = ctx();
     const uint32_t max_cap = pow2_ceil(2ull * (nrows ? nrows : 1));
     uint32_t cap = groups_hint ? pow2_ceil(2ull * groups_hint) : (1u << 16);
     if (cap > max_cap) cap = max_cap;
+    if (d_row_slot) allow_fused = false;
     uint32_t sw = 1;
-    while (sw < uint32_t(1 + plan.n_acc)) sw <<= 1;
-    hr.sw = sw;
     const uint32_t nwords_bm = (nrows + 31) / 32 + 1;
     const uint32_t rank_blocks = (nwords_bm + RANK_WORDS - 1) / RANK_WORDS;
     DevBuf blocksum;
     AQ_TRY(hr.bitmap.alloc(size_t(nwords_bm) * 4));
     AQ_TRY(hr.wordprefix.alloc(size_t(nwords_bm) * 4));
     AQ_TRY(blocksum.alloc(size_t(rank_blocks) * 4));
-    InitPattern pat;
-    for (int i = 0; i < 16; ++i) pat.w[i] = 0;
-    pat.w[0] = SLOT_EMPTY;
-    for (int a = 0; a < plan.n_acc; ++a) pat.w[1 + a] = acc_identity(plan.prog.op[a].kind);
-    bool allow_smem = d_row_slot == nullptr, allow_part = d_row_slot == nullptr;
+    bool allow_smem = d_row_slot == nullptr, allow_part = d_row_slot == nullptr, allow_hc = true;
 
     for (int attempt = 0; attempt < 16; ++attempt) {
+        // wide exact keys (only the fused path knows the shifted slot layout; the shared-memory and
+        // partitioned kernels never take more than 2 key words, so they cannot meet such a table)
+        const bool wide = allow_fused && ks.exact == 0 && ks.wide && ks.nwords > 2 && plan.n_acc + 2 <= 16;
+        const int acc_off = wide ? 2 : 1;
+        for (sw = 1; sw < uint32_t(acc_off + plan.n_acc); sw <<= 1) {}
+        hr.sw = sw; hr.acc_off = acc_off;
+        InitPattern pat;
+        for (int i = 0; i < 16; ++i) pat.w[i] = 0;
+        pat.w[0] = SLOT_EMPTY;
+        if (wide) pat.w[1] = SLOT_EMPTY;
+        for (int a = 0; a < plan.n_acc; ++a) pat.w[acc_off + a] = acc_identity(plan.prog.op[a].kind);
+        if (wide && allow_hc && nrows) {                       // partitioned, L2-resident tables, one record per row
+            bool used_hc = false;
+            AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
+            AQ_TRY(launch_hc(ks, nrows, plan.prog, sw, pat.w, groups_hint, hr.tab, &used_hc));
+            if (used_hc) {
+                AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+                AQ_CUDA(cudaStreamSynchronize(c.stream));
+                const uint32_t st = c.h_flags[FLAG_ABORT];
+                if (st == 0) { *ngroups = 0; hr.ks = ks; hr.fused = true; hr.cap = nrows; hr.row_slot.release(); return 0; }
+                if (st == 3) ks.wide = 0; else allow_hc = false;
+                continue;
+            }
+        }
         hr.cap = cap;
         const uint32_t max_probe = cap == max_cap ? cap : 256u;
         const size_t tab_words = size_t(cap) * sw;
@@ -468,24 +670,30 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
         bool used_smem = false, used_part = false;
         if (allow_smem && nrows) AQ_TRY(launch_smem_probe(ks, nrows, cap, max_probe, plan.prog, groups_hint, &used_smem));
         if (!used_smem && allow_part && nrows) AQ_TRY(launch_part_probe(ks, nrows, cap, max_probe, plan.prog, groups_hint, &used_part));
+        const bool fused = allow_fused && !used_smem && !used_part && nrows;
+        uint32_t* rs = d_row_slot;
+        if (fused) { AQ_TRY(hr.row_slot.alloc(size_t(nrows) * 4)); rs = hr.row_slot.as<uint32_t>(); }
         if (!used_smem && !used_part && nrows) {
             const int grid = grid_for((nrows + 3) / 4, 256, 1, 16);
-            if (ks.exact) AQ_LAUNCH(k_probe_agg<true>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
-            else AQ_LAUNCH(k_probe_agg<false>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, d_row_slot, c.d_flags);
+            if (wide) AQ_LAUNCH(k_probe_wide, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, rs, c.d_flags);
+            else if (ks.exact) AQ_LAUNCH(k_probe_agg<true>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, rs, c.d_flags);
+            else AQ_LAUNCH(k_probe_agg<false>, grid, 256, 0, ks, nrows, cap - 1, max_probe, plan.prog, rs, c.d_flags);
         }
+        if (!fused) {
         AQ_LAUNCH(k_mark, grid_for(cap, 256, 4), 256, 0, plan.prog.tab, cap, sw, hr.bitmap.as<uint32_t>());
         AQ_LAUNCH(k_rank_blocksum, rank_blocks, RANK_THREADS, 0, hr.bitmap.as<uint32_t>(), nwords_bm, blocksum.as<uint32_t>());
         AQ_LAUNCH(k_rank_scan_blocks, 1, RANK_THREADS, 0, blocksum.as<uint32_t>(), rank_blocks, c.d_flags);
         AQ_LAUNCH(k_rank_wordprefix, rank_blocks, RANK_THREADS, 0, hr.bitmap.as<uint32_t>(), nwords_bm,
                   blocksum.as<uint32_t>(), hr.wordprefix.as<uint32_t>());
+        }
         AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
         AQ_CUDA(cudaStreamSynchronize(c.stream));
         const uint32_t st = c.h_flags[FLAG_ABORT];
-        if (st == 0) { *ngroups = c.h_flags[FLAG_NGROUPS]; hr.ks = ks; return 0; }
+        if (st == 0) { *ngroups = fused ? 0u : c.h_flags[FLAG_NGROUPS]; hr.ks = ks; hr.fused = fused; return 0; }
         if (st == 2 || st == 4) { if (used_part) allow_part = false; else allow_smem = false; continue; }   // CTA-local overflow / inexact fp: global path
         if (st == 3) {                                              // a key outside the caller's bounds
-            if (ks.exact != 2) return fail("internal: bounds flag without packed keys");
-            ks.exact = 0; ks.pack_bits = 0;
+            if (ks.exact != 2 && !wide) return fail("internal: bounds flag without packed keys");
+            if (wide) ks.wide = 0; else { ks.exact = 0; ks.pack_bits = 0; }
             continue;
         }
         if (cap == max_cap) return fail("hash table overflow at maximum capacity (%u slots)", cap);
@@ -504,6 +712,24 @@ int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const K
     AQ_LAUNCH(k_emit_rows, grid_for((nwords + 31) / 32, 8, 1, 8), 256, 0, ks, hr.tab.as<unsigned long long>(), hr.cap - 1, hr.sw,
               hr.bitmap.as<uint32_t>(), hr.wordprefix.as<uint32_t>(), nwords, ko, d_first_row, d_counts, d_last_row,
               d_slot_gid, plan.emit, cnt_acc, maxrow_acc, max_groups, ctx().d_flags);
+    return 0;
+}
+
+int emit_fused(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
+               const AggPlan& plan, uint32_t max_groups, uint32_t* ngroups) {
+    (void)ks;
+    Context& c = ctx();
+    const uint32_t ntiles = (nrows + EF_ROWS - 1) / EF_ROWS;
+    DevBuf state;
+    AQ_TRY(state.alloc_zero(size_t(ntiles) * 8 + 8));
+    unsigned long long* st = state.as<unsigned long long>();
+    uint32_t* ticket = reinterpret_cast<uint32_t*>(st + ntiles);
+    const int grid = (int)std::min<uint64_t>(ntiles, uint64_t(c.sm_count) * 8);
+    AQ_LAUNCH(k_emit_fused, grid, EF_THREADS, 0, hr.tab.as<unsigned long long>(), hr.sw, hr.acc_off, hr.row_slot.as<uint32_t>(),
+              nrows, ntiles, st, ticket, ko, d_first_row, plan.emit, max_groups, c.d_flags);
+    AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    *ngroups = c.h_flags[FLAG_NGROUPS];
     return 0;
 }
 
@@ -552,8 +778,8 @@ extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, 
 
     HashResult hr;
     uint32_t ng = 0;
-    AQ_TRY(hash_aggregate(ks, nrows, groups_hint, plan, nullptr, hr, &ng));
-    if (ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
+    AQ_TRY(hash_aggregate(ks, nrows, groups_hint, plan, nullptr, hr, &ng, true));
+    if (!hr.fused && ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
 
     KeyOut ko;
     memset(&ko, 0, sizeof(ko));
@@ -571,7 +797,12 @@ extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, 
     uint32_t* d_fr = nullptr;
     if (out_first_row) { AQ_TRY(fr.bind(out_first_row, size_t(4) * max_groups)); d_fr = static_cast<uint32_t*>(fr.d); }
 
-    AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
+    if (hr.fused) {
+        AQ_TRY(emit_fused(hr.ks, nrows, hr, ko, d_fr, plan, max_groups, &ng));
+        if (ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
+    } else {
+        AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
+    }
     bool any_host = false;
     for (int a = 0; a < n_aggs; ++a) { AQ_TRY(vout[a].finish(dtype_size(plan.emit.agg[a].out_type) * ng)); any_host |= vout[a].host != nullptr; }
     for (int k = 0; k < nkeys; ++k) if (ko.dst[k]) { AQ_TRY(kout[k].finish(size_t(ko.size[k]) * ng)); any_host |= kout[k].host != nullptr; }

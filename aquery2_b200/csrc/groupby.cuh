@@ -32,6 +32,13 @@ struct KeySpec {
     uint32_t pack_range[MAX_KEY_WORDS];   // hi - lo
     uint32_t pack_shift[MAX_KEY_WORDS];
     int pack_bits;
+    // "wide" exact image for tuples whose packed fields exceed 32 bits but fit 96 (h2o q10: 76 bits):
+    // every column goes whole into the 32-bit tag (wide_part = 0) or into a 64-bit second word kept in
+    // slot word 1 (wide_part = 1), so membership is decided by the slot's first 16 bytes alone
+    // (k_probe_wide: one 128-bit CAS inserts both) -- no gathers from the key columns.
+    int wide;
+    uint32_t wide_part[MAX_KEY_WORDS];
+    uint32_t wide_shift[MAX_KEY_WORDS];
 };
 
 // One 64-bit accumulator cell per group and AccOp.
@@ -133,12 +140,20 @@ struct HashResult {
     DevBuf tab;                   // cap x sw u64
     DevBuf bitmap;                // nrows bits: first-appearance rows
     DevBuf wordprefix;            // per bitmap word: number of groups before it
+    // fused path (global table only): every row's slot, ranked and emitted by ONE row-order pass
+    // (k_emit_fused) instead of k_mark / k_rank_* / k_emit_rows; ngroups is known after the emit.
+    bool fused = false;
+    int acc_off = 1;              // accumulator a lives in slot word acc_off + a (2 for wide keys)
+    DevBuf row_slot;
 };
 
 // Hash build + fused accumulation + ranking of the groups by first row.  Synchronises once to
 // return *ngroups.  d_row_slot (optional, nrows) receives every row's table slot.
 int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& plan,
-                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups);
+                   uint32_t* d_row_slot, HashResult& hr, uint32_t* ngroups, bool allow_fused = false);
+// fused rank + emit of a HashResult with hr.fused set; synchronises to return *ngroups
+int emit_fused(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
+               const AggPlan& plan, uint32_t max_groups, uint32_t* ngroups);
 
 // Writes keys / first rows / aggregates in first-appearance order (gid = rank of the first row).
 int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
@@ -150,6 +165,11 @@ int launch_smem_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t 
 // partitioned aggregation (groupby_part.cu) for groups beyond one SM's shared memory; same contract.
 int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t max_probe,
                       const AccProg& prog, uint32_t groups_hint, bool* used);
+// high-cardinality path for wide exact keys (groupby_hc.cu): rows -> hash partitions -> per-CTA
+// L2-resident tables -> one record per ROW (rec[i] = the slot of the group whose first row is i,
+// else all ones), which k_emit_fused then ranks and emits.  *used = false if it does not qualify.
+int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
+              uint32_t groups_hint, DevBuf& rec, bool* used);
 
 #ifdef __CUDACC__
 // ---- device helpers shared by the probe kernels ------------------------------------------------
@@ -242,6 +262,38 @@ __device__ __forceinline__ void key_tag1(const KeySpec& ks, uint32_t row, uint32
         for (int w = 0; w < ks.nwords; ++w) h = mix64(h ^ __ldg(ks.base[w] + size_t(row) * ks.stride[w]));
         tag = (uint32_t)(h >> 32); hsh = (uint32_t)h;
     }
+}
+
+__device__ __forceinline__ void cas128(unsigned long long* p, unsigned long long c0, unsigned long long c1,
+                                       unsigned long long n0, unsigned long long n1,
+                                       unsigned long long& o0, unsigned long long& o1) {
+    asm volatile("{\n\t.reg .b128 c, n, o;\n\tmov.b128 c, {%2, %3};\n\tmov.b128 n, {%4, %5};\n\t"
+                 "atom.relaxed.gpu.global.cas.b128 o, [%6], c, n;\n\tmov.b128 {%0, %1}, o;\n\t}"
+                 : "=l"(o0), "=l"(o1) : "l"(c0), "l"(c1), "l"(n0), "l"(n1), "l"(p) : "memory");
+}
+__device__ __forceinline__ void ld128_volatile(const unsigned long long* p, unsigned long long& a, unsigned long long& b) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ uint32_t wide_hash(uint32_t tag, unsigned long long hi) {
+    return (uint32_t)(mix64(hi * 0x9e3779b97f4a7c15ULL + tag) >> 16);
+}
+// wide exact image of 4 consecutive rows (KeySpec::wide): false if a key lies outside the bounds
+__device__ __forceinline__ bool wide_pack4(const KeySpec& ks, uint32_t row0, int cnt, uint32_t tag[4], unsigned long long hi[4]) {
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) { tag[r] = 0; hi[r] = 0; }
+    for (int w = 0; w < ks.nwords; ++w) {
+        uint32_t kw[4];
+        load4_b32(ks.base[w], row0, cnt, ks.vec_ok, kw);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const uint32_t d = kw[r] - ks.pack_lo[w];
+            ok &= (r >= cnt) || (d <= ks.pack_range[w]);
+            if (ks.wide_part[w]) hi[r] |= (unsigned long long)d << ks.wide_shift[w];
+            else tag[r] |= d << ks.wide_shift[w];
+        }
+    }
+    return ok;
 }
 
 // find-or-insert in the global table; keeps the smallest row id in the low half of word 0.

@@ -213,6 +213,47 @@ def test_high_cardinality_and_collisions(gpu, port):
     check_query_vs_oracle(gpu, port, t, ["b", "k64", "a"], [("max", "v")])
 
 
+def test_wide_exact_keys_fused_emit(gpu, port):
+    """q10 shape: six bounded key columns whose packed image needs 76 bits -> wide exact slots
+    (k_probe_wide, 128-bit CAS) + the fused look-back rank/emit; right bounds, wrong bounds (silent
+    retry without them), duplicates-heavy and all-distinct inputs, several tile counts."""
+    for n, k in ((300_007, 100), (5_000, 3), (1023, 100), (1025, 2), (1_300_001, 100)):   # last: groupby_hc.cu path
+        t = synth.h2o_table(n, k, seed=13, columns=["id1", "id2", "id3", "id4", "id5", "id6", "v1", "v3"])
+        t["id3"] = (t["id3"].astype(np.int64) * 1_000 % 10_000_000 + 1).astype(np.int32)   # 24-bit fields
+        t["id6"] = (t["id6"].astype(np.int64) * 777 % 10_000_000 + 1).astype(np.int32)
+        keys = ["id1", "id2", "id3", "id4", "id5", "id6"]
+        good = [(1, k), (1, k), (1, 10_000_000), (1, k), (1, k), (1, 10_000_000)]
+        wrong = [(1, k), (1, k), (1, 10), (1, k), (1, k), (1, 10_000_000)]
+        for bounds in (good, wrong, None):
+            check_query_vs_oracle(gpu, port, t, keys, [("sum", "v3"), ("count",)], groups_hint=n, key_bounds=bounds)
+        check_query_vs_oracle(gpu, port, t, keys[:4], [("sum", "v1"), ("avg", "v3"), ("max", "v1"), ("first", "v3"), ("second", "v1")],
+                              groups_hint=n, key_bounds=good[:4])
+    # groupby_hc.cu with a skewed key: one group holds a third of the rows -> its partition overflows ->
+    # silent fallback to the global table; and a moderately duplicated one that stays on the path
+    n = 1_500_000
+    rng = np.random.default_rng(23)
+    t = {c: rng.integers(0, 1 << 20, n).astype(np.int32) for c in ("a", "b", "c")}
+    t["v"] = rng.integers(-50, 50, n).astype(np.int32); t["f"] = rng.random(n).astype(np.float32)
+    b3 = [(0, (1 << 20) - 1)] * 3
+    dup = rng.integers(0, n, n // 4)
+    for c in ("a", "b", "c"):
+        t[c][dup] = t[c][(dup * 7) % 1000]                    # ~1000 hot keys share a quarter of the rows
+    check_query_vs_oracle(gpu, port, t, ["a", "b", "c"], [("sum", "v"), ("avg", "f"), ("count",), ("min", "v"), ("first", "f")],
+                          key_bounds=b3, groups_hint=n)
+    for c in ("a", "b", "c"):
+        t[c][::3] = 5
+    check_query_vs_oracle(gpu, port, t, ["a", "b", "c"], [("sum", "v"), ("count",)], key_bounds=b3, groups_hint=n)
+    # few groups over many rows: most rows are NOT first rows; full-range fields fill the 64-bit word
+    n = 200_000
+    rng = np.random.default_rng(17)
+    t = {"a": rng.integers(-2**31, 2**31 - 1, 50).astype(np.int32)[rng.integers(0, 50, n)],
+         "b": rng.integers(0, 2**31 - 1, 40).astype(np.int32)[rng.integers(0, 40, n)],
+         "c": rng.integers(0, 1 << 20, n).astype(np.int32) >> 12, "v": rng.integers(-9, 9, n).astype(np.int32)}
+    b3 = [(-2**31, 2**31 - 1), (0, 2**31 - 1), (0, 255)]
+    check_query_vs_oracle(gpu, port, t, ["a", "b", "c"], [("sum", "v"), ("count",), ("min", "v")], key_bounds=b3)
+    check_query_vs_oracle(gpu, port, t, ["c", "a", "b"], [("sum", "v"), ("last", "v")], key_bounds=[b3[2], b3[0], b3[1]], groups_hint=1000)
+
+
 # ---- partitioned path (groupby_part.cu): groups beyond one SM's shared memory ---------------------
 ALL_AGGS = [("sum", "v1"), ("avg", "v3"), ("min", "v2"), ("max", "v3"), ("count",), ("first", "v3"), ("last", "v1"),
             ("second", "v3")]

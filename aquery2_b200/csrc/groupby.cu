@@ -93,7 +93,7 @@ int KeyCols::make_spec(const int64_t* key_min, const int64_t* key_max, KeySpec& 
                 used[part] += b;
             }
             // all-ones in the second word marks an empty slot: keep one bit of it clear
-            ks.wide = (wide && used[1] < 64) ? 1 : 0;
+            ks.wide = (wide && used[1] < 64 && n <= WIDE_MAX_COLS) ? 1 : 0;
         }
     }
     return 0;
@@ -580,6 +580,7 @@ k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, cons
         }
         __syncthreads();
         uint32_t gid = s_excl + warp_sums[wid] + x - mine;
+        const uint32_t gid0 = gid;
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
             if (!((fl >> r) & 1u)) continue;
@@ -588,12 +589,37 @@ k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, cons
             const uint32_t fr = row0 + r;
             const unsigned long long* slp = tab + size_t(sl[r]) * sw + (acc_off - 1);
             if (first_row_out) first_row_out[g] = fr;
-            for (int k = 0; k < ko.n; ++k) {
-                if (!ko.dst[k]) continue;
-                if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[g] = static_cast<const uint32_t*>(ko.src[k])[fr];
-                else static_cast<unsigned long long*>(ko.dst[k])[g] = static_cast<const unsigned long long*>(ko.src[k])[fr];
-            }
             for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], slp, g, fr, ep.row_order);
+        }
+        // key columns: all loads of a batch of 4 columns in flight before the first store
+        for (int k0 = 0; k0 < ko.n; k0 += 4) {
+            unsigned long long kv[4][4];
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const int k = k0 + kk;
+                if (k >= ko.n || !ko.dst[k]) continue;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if (!((fl >> r) & 1u)) continue;
+                    kv[kk][r] = ko.size[k] == 4 ? (unsigned long long)static_cast<const uint32_t*>(ko.src[k])[row0 + r]
+                                                : static_cast<const unsigned long long*>(ko.src[k])[row0 + r];
+                }
+            }
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const int k = k0 + kk;
+                if (k >= ko.n || !ko.dst[k]) continue;
+                uint32_t g = gid0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if (!((fl >> r) & 1u)) continue;
+                    if (g < max_groups) {
+                        if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[g] = (uint32_t)kv[kk][r];
+                        else static_cast<unsigned long long*>(ko.dst[k])[g] = kv[kk][r];
+                    }
+                    ++g;
+                }
+            }
         }
         __syncthreads();                                                      // s_tile / warp_sums reused
     }

@@ -277,17 +277,25 @@ __device__ __forceinline__ void ld128_volatile(const unsigned long long* p, unsi
 __device__ __forceinline__ uint32_t wide_hash(uint32_t tag, unsigned long long hi) {
     return (uint32_t)(mix64(hi * 0x9e3779b97f4a7c15ULL + tag) >> 16);
 }
-// wide exact image of 4 consecutive rows (KeySpec::wide): false if a key lies outside the bounds
+// wide exact image of 4 consecutive rows (KeySpec::wide, at most WIDE_MAX_COLS columns): every column's
+// 128-bit load is issued before the first one is used.  false if a key lies outside the bounds.
+constexpr int WIDE_MAX_COLS = 8;
 __device__ __forceinline__ bool wide_pack4(const KeySpec& ks, uint32_t row0, int cnt, uint32_t tag[4], unsigned long long hi[4]) {
+    uint32_t kw[WIDE_MAX_COLS][4];
+#pragma unroll
+    for (int w = 0; w < WIDE_MAX_COLS; ++w) {
+        if (w < ks.nwords) load4_b32(ks.base[w], row0, cnt, ks.vec_ok, kw[w]);
+        else { kw[w][0] = kw[w][1] = kw[w][2] = kw[w][3] = 0u; }
+    }
     bool ok = true;
 #pragma unroll
     for (int r = 0; r < 4; ++r) { tag[r] = 0; hi[r] = 0; }
-    for (int w = 0; w < ks.nwords; ++w) {
-        uint32_t kw[4];
-        load4_b32(ks.base[w], row0, cnt, ks.vec_ok, kw);
+#pragma unroll
+    for (int w = 0; w < WIDE_MAX_COLS; ++w) {
+        if (w >= ks.nwords) break;
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const uint32_t d = kw[r] - ks.pack_lo[w];
+            const uint32_t d = kw[w][r] - ks.pack_lo[w];
             ok &= (r >= cnt) || (d <= ks.pack_range[w]);
             if (ks.wide_part[w]) hi[r] |= (unsigned long long)d << ks.wide_shift[w];
             else tag[r] |= d << ks.wide_shift[w];

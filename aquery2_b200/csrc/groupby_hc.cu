@@ -187,6 +187,118 @@ k_hc_agg(const AccProg prog, const uint32_t sw, const HcPattern pat, const uint3
     }
 }
 
+// ---- phase 2, shared-memory tables (slots of 4 words: h2o q10) ------------------------------------------
+// Same protocol as k_hc_agg with the table in the CTA's shared memory (HC_SM_SLOTS x 32 B = 192 KB): the
+// L2 then only carries the two streams (tuples in, records out).
+constexpr uint32_t HC_SM_SLOTS = 6144;
+constexpr uint32_t HC_SM_SW = 4;
+
+__device__ __forceinline__ void cas128_shared(uint32_t saddr, unsigned long long c0, unsigned long long c1,
+                                              unsigned long long n0, unsigned long long n1,
+                                              unsigned long long& o0, unsigned long long& o1) {
+    asm volatile("{\n\t.reg .b128 c, n, o;\n\tmov.b128 c, {%2, %3};\n\tmov.b128 n, {%4, %5};\n\t"
+                 "atom.relaxed.cta.shared.cas.b128 o, [%6], c, n;\n\tmov.b128 {%0, %1}, o;\n\t}"
+                 : "=l"(o0), "=l"(o1) : "l"(c0), "l"(c1), "l"(n0), "l"(n1), "r"(saddr) : "memory");
+}
+__device__ __forceinline__ void ld128_shared_volatile(uint32_t saddr, unsigned long long& a, unsigned long long& b) {
+    asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(saddr) : "memory");
+}
+
+__global__ void __launch_bounds__(HC_THREADS, 1)
+k_hc_agg_smem(const AccProg prog, const HcPattern pat, const uint32_t nparts,
+              const uint32_t* __restrict__ cursor, const uint32_t* __restrict__ tuples,
+              unsigned long long* __restrict__ rec, uint32_t* __restrict__ flags) {
+    extern __shared__ __align__(16) unsigned long long tab[];          // HC_SM_SLOTS x 4 words
+    if (flags[FLAG_ABORT]) return;
+    const unsigned long long p0 = pat.w[0], p1 = pat.w[1], p2 = pat.w[2], p3 = pat.w[3];
+    for (uint32_t i = threadIdx.x; i < HC_SM_SLOTS; i += HC_THREADS) {
+        tab[i * 4 + 0] = p0; tab[i * 4 + 1] = p1; tab[i * 4 + 2] = p2; tab[i * 4 + 3] = p3;
+    }
+    __syncthreads();
+    const uint32_t tab_s = (uint32_t)__cvta_generic_to_shared(tab);
+    uint32_t p = blockIdx.x;
+    // tuples of the first partition
+    int4 ta[HC_TPT], tb[HC_TPT];
+    uint32_t n = p < nparts ? min(cursor[p], HC_CAP) : 0u;
+#pragma unroll
+    for (int j = 0; j < HC_TPT; ++j) {
+        const uint32_t t = j * HC_THREADS + threadIdx.x;
+        if (t < n) {
+            const uint32_t* src = tuples + (size_t(p) * HC_CAP + t) * HC_TW;
+            ta[j] = ld_stream_v4(src); tb[j] = ld_stream_v4(src + 4);
+        }
+    }
+    for (; p < nparts; p += gridDim.x) {
+        uint32_t row[HC_TPT], slot[HC_TPT];
+#pragma unroll
+        for (int j = 0; j < HC_TPT; ++j) {
+            const uint32_t t = j * HC_THREADS + threadIdx.x;
+            slot[j] = NOSLOT; row[j] = 0;
+            if (t >= n) continue;
+            row[j] = (uint32_t)ta[j].x;
+            const uint32_t tag = (uint32_t)ta[j].y;
+            const unsigned long long hi = (unsigned long long)(uint32_t)ta[j].z | ((unsigned long long)(uint32_t)ta[j].w << 32);
+            const unsigned long long mine = ((unsigned long long)tag << 32) | row[j];
+            uint32_t sh;
+            hc_part(tag, hi, nparts, sh);
+            uint32_t s = __umulhi(sh, HC_SM_SLOTS);
+            for (uint32_t step = 0; step < HC_SM_SLOTS; ++step) {
+                const uint32_t sa = tab_s + s * 32u;
+                unsigned long long a, b;
+                ld128_shared_volatile(sa, a, b);
+                if (a == SLOT_EMPTY) {
+                    unsigned long long o0, o1;
+                    cas128_shared(sa, SLOT_EMPTY, SLOT_EMPTY, mine, hi, o0, o1);
+                    if (o0 == SLOT_EMPTY) { slot[j] = s; break; }
+                    a = o0; b = o1;
+                }
+                if ((uint32_t)(a >> 32) == tag && b == hi) {
+                    if (row[j] < (uint32_t)a) atomicMin(tab + s * 4, mine);
+                    slot[j] = s; break;
+                }
+                s = s + 1 == HC_SM_SLOTS ? 0u : s + 1;
+            }
+            const uint32_t v[MAX_VCOL] = {(uint32_t)tb[j].x, (uint32_t)tb[j].y, (uint32_t)tb[j].z, (uint32_t)tb[j].w};
+            for (int a2 = 0; a2 < prog.n; ++a2) {
+                long long xi; double xd;
+                hc_x(prog.op[a2], v, xi, xd);
+                acc_global_row(prog.op[a2], tab + slot[j] * 4 + 2 + a2, row[j], xi, xd);
+            }
+        }
+        // the next partition's tuples travel while this one is finished
+        const uint32_t pn = p + gridDim.x;
+        const uint32_t nn = pn < nparts ? min(cursor[pn], HC_CAP) : 0u;
+#pragma unroll
+        for (int j = 0; j < HC_TPT; ++j) {
+            const uint32_t t = j * HC_THREADS + threadIdx.x;
+            if (t < nn) {
+                const uint32_t* src = tuples + (size_t(pn) * HC_CAP + t) * HC_TW;
+                ta[j] = ld_stream_v4(src); tb[j] = ld_stream_v4(src + 4);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < HC_TPT; ++j) {
+            if (slot[j] == NOSLOT) continue;
+            unsigned long long* const sl = tab + slot[j] * 4;
+            unsigned long long* const out = rec + size_t(row[j]) * 4;
+            const unsigned long long a = *reinterpret_cast<volatile unsigned long long*>(sl);
+            if ((uint32_t)a == row[j]) {
+                const unsigned long long b = sl[1], c2 = sl[2], d = sl[3];
+                st_stream_v4(out, (uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+                st_stream_v4(out + 2, (uint32_t)c2, (uint32_t)(c2 >> 32), (uint32_t)d, (uint32_t)(d >> 32));
+                sl[3] = p3; sl[2] = p2; sl[1] = p1;
+                *reinterpret_cast<volatile unsigned long long*>(sl) = p0;
+            } else {
+                st_stream_v4(out, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+                st_stream_v4(out + 2, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+            }
+        }
+        __syncthreads();
+        n = nn;
+    }
+}
+
 // ---- host ---------------------------------------------------------------------------------------------
 int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
               uint32_t groups_hint, DevBuf& rec, bool* used) {
@@ -208,6 +320,15 @@ int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t s
     for (int i = 0; i < 16; ++i) pat.w[i] = pattern[i];
     AQ_LAUNCH(k_hc_scatter, grid_for((nrows + 3) / 4, HC_SCATTER_THREADS, 1, 16), HC_SCATTER_THREADS, 0, ks, prog, nrows, nparts,
               cursor.as<uint32_t>(), tuples.as<uint32_t>(), c.d_flags);
+    if (sw == HC_SM_SW && c.smem_optin >= HC_SM_SLOTS * 32 + 1024) {
+        const size_t smem = size_t(HC_SM_SLOTS) * 32;
+        static bool attr_done = false;
+        if (!attr_done) { AQ_CUDA(cudaFuncSetAttribute(k_hc_agg_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
+        AQ_LAUNCH(k_hc_agg_smem, grid, HC_THREADS, smem, prog, pat, nparts, cursor.as<uint32_t>(), tuples.as<uint32_t>(),
+                  rec.as<unsigned long long>(), c.d_flags);
+        *used = true;
+        return 0;
+    }
     AQ_LAUNCH(k_hc_agg, grid, HC_THREADS, 0, prog, sw, pat, nparts, cursor.as<uint32_t>(), tuples.as<uint32_t>(),
               scratch.as<unsigned long long>(), rec.as<unsigned long long>(), c.d_flags);
     *used = true;

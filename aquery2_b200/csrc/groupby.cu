@@ -661,7 +661,15 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
     for (int attempt = 0; attempt < 16; ++attempt) {
         // wide exact keys (only the fused path knows the shifted slot layout; the shared-memory and
         // partitioned kernels never take more than 2 key words, so they cannot meet such a table)
-        const bool wide = allow_fused && ks.exact == 0 && ks.wide && ks.nwords > 2 && plan.n_acc + 2 <= 16;
+        // ... and only when the second key word is free (the slot does not grow) or the partitioned path
+        // takes the query, which needs no table at all: a 2^30-slot table must not double to 64 GB
+        bool wide = allow_fused && ks.exact == 0 && ks.wide && ks.nwords > 2 && plan.n_acc + 2 <= 16;
+        if (wide) {
+            uint32_t sw1 = 1, sw2 = 1;
+            while (sw1 < uint32_t(1 + plan.n_acc)) sw1 <<= 1;
+            while (sw2 < uint32_t(2 + plan.n_acc)) sw2 <<= 1;
+            if (sw2 != sw1 && !(allow_hc && hc_qualifies(ks, nrows, plan.prog, sw2, groups_hint))) wide = false;
+        }
         const int acc_off = wide ? 2 : 1;
         for (sw = 1; sw < uint32_t(acc_off + plan.n_acc); sw <<= 1) {}
         hr.sw = sw; hr.acc_off = acc_off;

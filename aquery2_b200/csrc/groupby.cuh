@@ -168,6 +168,7 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t 
 // high-cardinality path for wide exact keys (groupby_hc.cu): rows -> hash partitions -> per-CTA
 // L2-resident tables -> one record per ROW (rec[i] = the slot of the group whose first row is i,
 // else all ones), which k_emit_fused then ranks and emits.  *used = false if it does not qualify.
+bool hc_qualifies(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, uint32_t groups_hint);
 int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
               uint32_t groups_hint, DevBuf& rec, bool* used);
 

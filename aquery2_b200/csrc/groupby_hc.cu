@@ -300,15 +300,20 @@ k_hc_agg_smem(const AccProg prog, const HcPattern pat, const uint32_t nparts,
 }
 
 // ---- host ---------------------------------------------------------------------------------------------
+bool hc_qualifies(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, uint32_t groups_hint) {
+    if (!ks.wide || ks.exact != 0 || nrows < (1u << 20)) return false;
+    if (groups_hint < nrows / 8) return false;             // few groups: tables elsewhere are small and cheap
+    if (sw < 2 || sw > 16 || prog.nv < 0 || prog.nv > MAX_VCOL) return false;
+    for (int j = 0; j < prog.nv; ++j) if (prog.vctype[j] != AQ_INT32 && prog.vctype[j] != AQ_FLOAT) return false;
+    for (int w = 0; w < ks.nwords; ++w) if (ks.stride[w] != 1) return false;
+    return true;
+}
+
 int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
               uint32_t groups_hint, DevBuf& rec, bool* used) {
     *used = false;
     Context& c = ctx();
-    if (!ks.wide || ks.exact != 0 || nrows < (1u << 20)) return 0;
-    if (groups_hint < nrows / 8) return 0;                 // few groups: tables elsewhere are small and cheap
-    if (sw < 2 || sw > 16 || prog.nv < 0 || prog.nv > MAX_VCOL) return 0;
-    for (int j = 0; j < prog.nv; ++j) if (prog.vctype[j] != AQ_INT32 && prog.vctype[j] != AQ_FLOAT) return 0;
-    for (int w = 0; w < ks.nwords; ++w) if (ks.stride[w] != 1) return 0;
+    if (!hc_qualifies(ks, nrows, prog, sw, groups_hint)) return 0;
     const uint32_t nparts = (nrows + HC_MEAN - 1) / HC_MEAN;
     const int grid = c.sm_count;
     DevBuf tuples, cursor, scratch;

@@ -45,7 +45,7 @@ EXPORTS = [
     "aqgpu_groups_size", "aqgpu_groups_keys", "aqgpu_groups_first_row", "aqgpu_groups_gid",
     "aqgpu_groups_csr", "aqgpu_groups_device_views", "aqgpu_group_reduce", "aqgpu_group_scan",
     "aqgpu_groups_order_by", "aqgpu_vec_sub", "aqgpu_avg_finalize", "aqgpu_vec_pow", "aqgpu_finalize",
-    "aqgpu_rows_to_global", "aqgpu_key_owner", "aqgpu_second_merge",
+    "aqgpu_rows_to_global", "aqgpu_key_owner", "aqgpu_second_merge", "aqgpu_partition_rows",
     "aqgpu_synth_column",
 ]
 

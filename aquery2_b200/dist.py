@@ -21,6 +21,8 @@ oracle-backed engine) and bytes through ``Comm``; nothing here touches oracle/.
 from __future__ import annotations
 
 import os
+import sys
+import time
 
 import numpy as np
 
@@ -114,8 +116,14 @@ class Comm:
             kw = {"device_id": self.device} if backend == "nccl" else {}
             dist.init_process_group(backend, timeout=datetime.timedelta(seconds=int(os.environ.get("AQ_DIST_TIMEOUT", "180"))), **kw)
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
-        if cuda:      # the library works on torch's current stream: one ordering for kernels and collectives
-            aq.set_stream(torch.cuda.current_stream().cuda_stream)
+        self.stream = None
+        if cuda:
+            # ONE stream for the library's kernels, torch's indexing and the NCCL collectives.  torch's default
+            # stream has handle 0, which aqgpu_set_stream reads as "use your own stream", so a real stream
+            # is made current instead (kept alive by this object).
+            self.stream = torch.cuda.Stream(device=self.device)
+            torch.cuda.set_stream(self.stream)
+            aq.set_stream(self.stream.cuda_stream)
 
     def barrier(self):
         self.dist.barrier()
@@ -206,6 +214,11 @@ class Comm:
         return out
 
     def close(self):
+        if self.stream is not None:
+            self.stream.synchronize()
+            aq.set_stream(None)
+            self.torch.cuda.set_stream(self.torch.cuda.default_stream(self.device))
+            self.stream = None
         if self.dist.is_initialized():
             self.dist.destroy_process_group()
 
@@ -280,22 +293,33 @@ class GpuEngine:
         kp = (aq.ctypes.c_void_p * len(keys))(*[k.ptr for k in keys])
         kt = (aq.ctypes.c_int * len(keys))(*[k.code for k in keys])
         aq.check(aq.lib().aqgpu_key_owner(kp, kt, len(keys), aq.ctypes.c_uint32(n), aq.ctypes.c_uint32(nparts), aq.ctypes.c_void_p(owner.ptr)))
-        g = aq.Groups([owner], row_order=aq.ROWS_ASC, groups_hint=nparts, key_bounds=[(0, nparts - 1)])
-        ranks = g.keys(0)                       # owners present, in first-appearance order = CSR block order
-        off = self._offsets(g)
-        counts = [0] * nparts
-        for i, r in enumerate(ranks):
-            counts[int(r)] = int(off[i + 1] - off[i])
-        out = []
-        for c in cols:
-            gathered = aq.DeviceColumn(n, c.code)
-            self._gather(g, c, gathered, n)
-            out.append(gathered)
-        order = np.argsort(ranks, kind="stable")            # the exchange wants the blocks in ascending owner order
-        if not np.array_equal(order, np.arange(len(ranks))):
-            out = [self._reorder_blocks(c, off, order, n) for c in out]
-        g.free()
-        return counts, out
+        out = [aq.DeviceColumn(n, c.code) for c in cols]
+        cp = (aq.ctypes.c_void_p * len(cols))(*[c.ptr for c in cols])
+        op = (aq.ctypes.c_void_p * len(cols))(*[c.ptr for c in out])
+        eb = (aq.ctypes.c_int * len(cols))(*[c.itemsize for c in cols])
+        counts = (aq.ctypes.c_uint32 * nparts)()
+        aq.check(aq.lib().aqgpu_partition_rows(aq.ctypes.c_void_p(owner.ptr), aq.ctypes.c_uint32(n), aq.ctypes.c_uint32(nparts),
+                                               cp, eb, len(cols), op, counts))
+        owner.free()
+        return [int(x) for x in counts], out
+
+    def groupby_rows(self, keys, aggs, hint, bounds, max_groups):
+        """whole groups on this rank (row exchange): the requested aggregates themselves, plus first rows"""
+        res = aq.groupby_agg(keys, aggs, groups_hint=hint, max_groups=max_groups, key_bounds=bounds, device_out=True,
+                             want_first_row=True)
+        return res.ngroups, res.keys, res.aggs, res.first_row
+
+    def take(self, col, idx, n):
+        """col[idx[0..n)]: global row ids of the groups' first rows (n is G-sized; torch indexing is plumbing)"""
+        t = self.torch
+        src = self.bytes_of(col, col.n).view(t.int64 if col.itemsize == 8 else t.int32)
+        ix = self.bytes_of(idx, n).view(t.int32).to(t.int64) & 0xffffffff
+        return self.from_bytes(src[ix].contiguous().view(t.uint8), n, col.code)
+
+    def global_rows(self, lo, n):
+        """int64 column lo, lo + 1, ..., lo + n - 1"""
+        t = self.torch
+        return self.from_bytes(t.arange(lo, lo + n, dtype=t.int64, device=self.comm.device).view(t.uint8), n, aq.INT64)
 
     @staticmethod
     def _offsets(g):
@@ -344,12 +368,69 @@ class DistQuery:
         self.local = engine.local_prepare([cols[k] for k in keys], self.partials, cols, max_groups, hint, bounds)
         self.strategy = None
         self.exchanged_bytes = 0
+        # groups ~ rows (h2o q10): local aggregation cannot shrink anything, so the ROWS are exchanged by key
+        # owner and every group is aggregated whole on its owner (any aggregate, no merge algebra)
+        self.cols = cols
+        k0 = cols[keys[0]]
+        self.nrows = int(k0.n) if hasattr(k0, "n") else len(k0)
+        total_rows = sum(comm.all_counts(self.nrows))
+        self.by_rows = comm.world > 1 and hint > 0 and 2 * hint >= total_rows and total_rows > gather_limit
+
+    def run_rows(self):
+        c, e = self.comm, self.eng
+        trace = os.environ.get("AQ_DIST_TRACE") and c.rank == 0
+        t0 = [time.perf_counter()]
+
+        def mark(what):
+            if trace:
+                if c.stream is not None:
+                    c.stream.synchronize()
+                t1 = time.perf_counter()
+                print(f"[dist rows] {what}: {1e3 * (t1 - t0[0]):.1f} ms", file=sys.stderr, flush=True)
+                t0[0] = t1
+        nk = len(self.key_names)
+        vnames = []
+        for a in self.aggs:
+            for name in a[1:]:
+                if name not in vnames:
+                    vnames.append(name)
+        grow = e.global_rows(self.lo, self.nrows)
+        table = [self.cols[k] for k in self.key_names] + [self.cols[v] for v in vnames] + [grow]
+        tcodes = self.key_codes + [self.cols[v].code if hasattr(self.cols[v], "code") else aq.NP2CODE[self.cols[v].dtype] for v in vnames] + [aq.INT64]
+        self.strategy = "alltoall-rows"
+        mark("global rows")
+        send, parted = e.partition(table[:nk], self.nrows, c.world, table)
+        del grow, table
+        mark("partition")
+        m = c.count_matrix(send)
+        rcounts = [m[src][c.rank] for src in range(c.world)]
+        mmax = max(max(r) for r in m)
+        nmerge = sum(rcounts)
+        recv = []
+        self.exchanged_bytes = 0
+        for i, code in enumerate(tcodes):
+            sz = aq.CODE_SIZE[code]
+            recv.append(e.from_bytes(c.alltoall_bytes(e.bytes_of(parted[i], self.nrows), send, rcounts, sz, mmax), nmerge, code))
+            parted[i] = None                                  # the send copy of this column is released
+            self.exchanged_bytes += (self.nrows - send[c.rank]) * sz
+        mark("all-to-all")
+        rkeys, rgrow = recv[:nk], recv[-1]
+        rv = dict(zip(vnames, recv[nk:-1]))
+        aggs = [(a[0],) + tuple(rv[x] for x in a[1:]) for a in self.aggs]
+        hint = min(nmerge, self.hint) if self.hint else 0
+        ngm, mkeys, results, fr = e.groupby_rows(rkeys, aggs, hint, self.bounds, max(nmerge, 1))
+        mark("group-by")
+        fg = e.take(rgrow, fr, ngm)
+        mark("take")
+        return ngm, mkeys, results, fg
 
     def run(self):
         """returns (ngroups on this rank, key columns, result columns, first global rows); with the gather
         strategy every rank holds all groups in the reference's order, with the partitioned strategy
         rank r holds the groups it owns, each rank's in ascending first-global-row order"""
         c, e = self.comm, self.eng
+        if self.by_rows:
+            return self.run_rows()
         ng = self.local.run()
         grow = e.rows_to_global(self.local.fr, ng, self.lo)
         table = list(self.local.kouts) + list(self.local.outs) + [grow]

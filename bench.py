@@ -243,6 +243,9 @@ def run_b200(args, queries):
     kernels = {}
     for name, (calls, tot_ms) in sorted(prof.items(), key=lambda kv: -kv[1][1])[:80]:
         kernels[name] = {"calls": calls, "ms_per_launch": tot_ms / calls}
+    # DRAM bytes per row of the kernels captured with `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum
+    # per launch / rows of that launch; profiles/r01/ncu_full_hc_scatter.csv), scaled to this launch's rows
+    NCU_DRAM_BYTES_PER_ROW = {"k_hc_scatter": (28.133142e9 + 31.992585e9) / 1e9}
     if top:
         name, (calls, tot_ms) = top
         q = name.split(":")[0]
@@ -250,7 +253,9 @@ def run_b200(args, queries):
         avg_ms = tot_ms / calls
         achieved = alg / (avg_ms * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak,
+                    "traffic": next((v * nrows_local for k, v in NCU_DRAM_BYTES_PER_ROW.items() if k in name), None),
+                    "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg, "ms_per_launch": avg_ms,
                     "share_of_step": tot_ms / prof_steps / max(sum(per_query_ms.values()), 1e-9)}
     per_query = {q: {"ms": per_query_ms[q], "rows_per_s": n_total / (per_query_ms[q] * 1e-3),

@@ -219,6 +219,11 @@ int aqgpu_rows_to_global(const uint32_t* in, int64_t add, int64_t* out, uint32_t
  * exchange of partial aggregates). */
 int aqgpu_key_owner(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
                     uint32_t nparts, uint32_t* owner);
+/* Stable split of device-resident columns by owner[i] in [0, nparts), nparts <= 64: out_cols[k] receives
+ * column k with the rows of owner 0 first, then owner 1, ..., each in their original order; counts[p]
+ * (host) = rows of owner p.  elem_bytes[k] in {4, 8, 16}.  The step before the all-to-all exchange. */
+int aqgpu_partition_rows(const uint32_t* owner, uint32_t nrows, uint32_t nparts, const void* const* cols,
+                         const int* elem_bytes, int ncols, void* const* out_cols, uint32_t* counts);
 /* AQ_SECOND across shards: out = cnt_top >= 2 ? second_top : (nparts >= 2 ? first_prev : 0), cells of
  * vtype; cnt_top and nparts are AQ_INT64 columns. */
 int aqgpu_second_merge(int vtype, const int64_t* cnt_top, const int64_t* nparts, const void* second_top,

@@ -127,5 +127,16 @@ class CpuEngine:
         counts = np.bincount(owner, minlength=nparts).tolist()
         return counts, [np.ascontiguousarray(np.asarray(c[:n])[order]) for c in cols]
 
+    def groupby_rows(self, keys, aggs, hint, bounds, max_groups):
+        specs = [(a[0], a[1] if len(a) > 1 else None, a[2] if len(a) > 2 else None, 0) for a in aggs]
+        ng, k, outs, first = self._groupby(keys, specs)
+        return ng, k, outs, first.astype(np.uint32)
+
+    def take(self, col, idx, n):
+        return np.asarray(col)[np.asarray(idx[:n], np.int64)]
+
+    def global_rows(self, lo, n):
+        return np.arange(lo, lo + n, dtype=np.int64)
+
     def to_numpy(self, col, n):
         return np.asarray(col[:n])

@@ -49,10 +49,11 @@ def _worker(rank, world, port, n, k, out_dir):
         want_keys = [full[c][first] for c in keys]
         want = [port_o.reduce(a[0], full[a[1]] if len(a) > 1 else None, off, perm, v2=full[a[2]] if len(a) > 2 else None, raw128=True)
                 for a in aggs]
-        for limit in (10**9, 0):                     # all-gather, then hash-partitioned all-to-all
-            q = dist.DistQuery(comm, eng, shard, codes, keys, aggs, lo, max_groups=max(hi - lo, 1), gather_limit=limit)
+        # all-gather of partials, hash-partitioned all-to-all of partials, all-to-all of the rows themselves
+        for limit, hint in ((10**9, 0), (0, 0), (0, n)):
+            q = dist.DistQuery(comm, eng, shard, codes, keys, aggs, lo, max_groups=max(hi - lo, 1), hint=hint, gather_limit=limit)
             ngm, mkeys, res, fg = q.run()
-            assert q.strategy == ("allgather" if limit else "alltoall")
+            assert q.strategy == ("allgather" if limit else ("alltoall-rows" if hint else "alltoall"))
             cols = [np.asarray(x[:ngm]) for x in mkeys + res] + [np.asarray(fg[:ngm])]
             if limit == 0:                           # bring the owners' groups together, order by first global row
                 counts = comm.all_counts(ngm)

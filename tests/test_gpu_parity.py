@@ -338,10 +338,11 @@ def test_dist_engine_single_rank(gpu, port, comm1):
                        (["id6"], [("sum", "v1"), ("sum", "v3"), ("second", "v1")])):
         ng, gid, off, perm = port.groupby([t[c] for c in keys])
         first = perm[off[1:] - 1]
-        for limit in (10**9, 0):
-            q = dist.DistQuery(comm1, eng, d, codes, keys, aggs, 0, max_groups=n, gather_limit=limit)
+        for limit, rows in ((10**9, False), (0, False), (0, True)):
+            q = dist.DistQuery(comm1, eng, d, codes, keys, aggs, 0, max_groups=n, hint=n if rows else 0, gather_limit=limit)
+            q.by_rows = rows                     # world size 1 never chooses the row exchange by itself
             ngm, mkeys, res, fg = q.run()
-            assert ngm == ng and q.strategy == ("allgather" if limit else "alltoall")
+            assert ngm == ng and q.strategy == ("allgather" if limit else ("alltoall-rows" if rows else "alltoall"))
             assert_same(fg.numpy(ngm).astype(np.uint32), first.astype(np.uint32), "first global row")
             for i, c in enumerate(keys):
                 assert_same(mkeys[i].numpy(ngm), t[c][first], f"key {c}")

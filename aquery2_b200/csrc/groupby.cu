@@ -519,6 +519,7 @@ k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, cons
              const uint32_t* __restrict__ row_slot, const uint32_t nrows, const uint32_t ntiles,
              unsigned long long* __restrict__ tile_state, uint32_t* __restrict__ ticket,
              const KeyOut ko, uint32_t* __restrict__ first_row_out, const EmitProg ep,
+             const unsigned char* __restrict__ rflags, const AccProg prog,
              const uint32_t max_groups, uint32_t* __restrict__ flags) {
     __shared__ uint32_t s_tile, s_excl, warp_sums[EF_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -533,12 +534,25 @@ k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, cons
         if (!row_slot) { for (int r = 0; r < 4; ++r) sl[r] = row0 + r; }          // one record per row (groupby_hc.cu)
         else if (cnt == 4) { const int4 t = ld_stream_v4(row_slot + row0); sl[0] = t.x; sl[1] = t.y; sl[2] = t.z; sl[3] = t.w; }
         else for (int r = 0; r < cnt; ++r) sl[r] = row_slot[row0 + r];
-        unsigned long long w0[4];
+        uint32_t fl = 0, single = 0;
+        if (rflags) {
+            // groupby_hc.cu: one byte per row -- 0 first row of a one-row group (cells rebuilt below from the
+            // row's own values, nothing was written for it), 1 first row with a record, 2 not a first row
+            uint32_t rf = 0x02020202u;
+            if (cnt == 4) rf = *reinterpret_cast<const uint32_t*>(rflags + row0);
+            else for (int r = 0; r < cnt; ++r) rf = (rf & ~(0xffu << (8 * r))) | ((uint32_t)rflags[row0 + r] << (8 * r));
 #pragma unroll
-        for (int r = 0; r < 4; ++r) w0[r] = r < cnt ? tab[size_t(sl[r]) * sw] : SLOT_EMPTY;
-        uint32_t fl = 0;
+            for (int r = 0; r < 4; ++r) {
+                const uint32_t b = (rf >> (8 * r)) & 0xffu;
+                if (r < cnt && b != 2u) { fl |= 1u << r; if (b == 0u) single |= 1u << r; }
+            }
+        } else {
+            unsigned long long w0[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) if (r < cnt && (uint32_t)w0[r] == row0 + r) fl |= 1u << r;
+            for (int r = 0; r < 4; ++r) w0[r] = r < cnt ? tab[size_t(sl[r]) * sw] : SLOT_EMPTY;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) if (r < cnt && (uint32_t)w0[r] == row0 + r) fl |= 1u << r;
+        }
         const uint32_t mine = __popc(fl);
         // block exclusive scan of `mine`
         uint32_t x = mine;
@@ -588,11 +602,42 @@ k_emit_fused(const unsigned long long* __restrict__ tab, const uint32_t sw, cons
             if (g >= max_groups) continue;                                    // the host reports the overflow
             const uint32_t fr = row0 + r;
             const unsigned long long* slp = tab + size_t(sl[r]) * sw + (acc_off - 1);
+            unsigned long long one[1 + MAX_ACC];
+            if ((single >> r) & 1u) {
+                for (int a = 0; a < prog.n; ++a) one[1 + a] = acc_single_row(prog.op[a], fr);
+                slp = one;
+            }
             if (first_row_out) first_row_out[g] = fr;
             for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], slp, g, fr, ep.row_order);
         }
-        // key columns: all loads of a batch of 4 columns in flight before the first store
-        for (int k0 = 0; k0 < ko.n; k0 += 4) {
+        // key columns.  4-byte keys (the usual case): ONE 128-bit load per column for the thread's four
+        // rows, up to 8 columns in flight before the first store
+        bool keys32 = cnt == 4 && fl != 0;
+        for (int k = 0; k < ko.n; ++k) keys32 &= ko.size[k] == 4 && (reinterpret_cast<uintptr_t>(ko.src[k]) & 15) == 0;
+        for (int k0 = 0; keys32 && k0 < ko.n; k0 += 8) {
+            uint32_t kv[8][4];
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int k = k0 + kk;
+                if (k >= ko.n || !ko.dst[k]) continue;
+                const int4 t = ld_stream_v4(static_cast<const uint32_t*>(ko.src[k]) + row0);
+                kv[kk][0] = t.x; kv[kk][1] = t.y; kv[kk][2] = t.z; kv[kk][3] = t.w;
+            }
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int k = k0 + kk;
+                if (k >= ko.n || !ko.dst[k]) continue;
+                uint32_t g = gid0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if (!((fl >> r) & 1u)) continue;
+                    if (g < max_groups) static_cast<uint32_t*>(ko.dst[k])[g] = kv[kk][r];
+                    ++g;
+                }
+            }
+        }
+        // general case: all loads of a batch of 4 columns in flight before the first store
+        for (int k0 = 0; !keys32 && k0 < ko.n; k0 += 4) {
             unsigned long long kv[4][4];
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
@@ -681,12 +726,13 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
         if (wide && allow_hc && nrows) {                       // partitioned, L2-resident tables, one record per row
             bool used_hc = false;
             AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
-            AQ_TRY(launch_hc(ks, nrows, plan.prog, sw, pat.w, groups_hint, hr.tab, &used_hc));
+            AQ_TRY(launch_hc(ks, nrows, plan.prog, sw, pat.w, groups_hint, hr.tab, hr.rflags, &used_hc));
             if (used_hc) {
                 AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
                 AQ_CUDA(cudaStreamSynchronize(c.stream));
                 const uint32_t st = c.h_flags[FLAG_ABORT];
                 if (st == 0) { *ngroups = 0; hr.ks = ks; hr.fused = true; hr.cap = nrows; hr.row_slot.release(); return 0; }
+                hr.rflags.release(); hr.tab.release();
                 if (st == 3) ks.wide = 0; else allow_hc = false;
                 continue;
             }
@@ -760,7 +806,7 @@ int emit_fused(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const Ke
     uint32_t* ticket = reinterpret_cast<uint32_t*>(st + ntiles);
     const int grid = (int)std::min<uint64_t>(ntiles, uint64_t(c.sm_count) * 8);
     AQ_LAUNCH(k_emit_fused, grid, EF_THREADS, 0, hr.tab.as<unsigned long long>(), hr.sw, hr.acc_off, hr.row_slot.as<uint32_t>(),
-              nrows, ntiles, st, ticket, ko, d_first_row, plan.emit, max_groups, c.d_flags);
+              nrows, ntiles, st, ticket, ko, d_first_row, plan.emit, hr.rflags.as<unsigned char>(), plan.prog, max_groups, c.d_flags);
     AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
     AQ_CUDA(cudaStreamSynchronize(c.stream));
     *ngroups = c.h_flags[FLAG_NGROUPS];

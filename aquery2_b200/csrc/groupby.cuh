@@ -145,6 +145,8 @@ struct HashResult {
     bool fused = false;
     int acc_off = 1;              // accumulator a lives in slot word acc_off + a (2 for wide keys)
     DevBuf row_slot;
+    DevBuf rflags;                // groupby_hc.cu: per row 0 = first row of a one-row group (no record written),
+                                  // 1 = first row with a record in tab, 2 = not a first row; empty = records only
 };
 
 // Hash build + fused accumulation + ranking of the groups by first row.  Synchronises once to
@@ -170,7 +172,7 @@ int launch_part_probe(const KeySpec& ks, uint32_t nrows, uint32_t cap, uint32_t 
 // else all ones), which k_emit_fused then ranks and emits.  *used = false if it does not qualify.
 bool hc_qualifies(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, uint32_t groups_hint);
 int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
-              uint32_t groups_hint, DevBuf& rec, bool* used);
+              uint32_t groups_hint, DevBuf& rec, DevBuf& rflags, bool* used);
 
 #ifdef __CUDACC__
 // ---- device helpers shared by the probe kernels ------------------------------------------------
@@ -406,6 +408,37 @@ __device__ __forceinline__ void acc_global_row(const AccOp& o, unsigned long lon
     case ACC_MIN_I64: atomicMin(reinterpret_cast<long long*>(c), isint ? xi : f64_to_ordered(xd)); break;
     case ACC_MAX_I64: atomicMax(reinterpret_cast<long long*>(c), isint ? xi : f64_to_ordered(xd)); break;
     default: break;
+    }
+}
+// the cell of accumulator o after exactly ONE row (a one-row group): identity (+) that row, no atomics
+__device__ __forceinline__ unsigned long long acc_single_row(const AccOp& o, uint32_t row) {
+    if (o.kind == ACC_COUNT) return 1ull;
+    if (o.kind == ACC_MAXROW) return (unsigned long long)row;
+    if (o.kind == ACC_TOP2ROW) return top2_key(o.xform, row) << 32;
+    long long xi = 0; double xd = 0.0;
+    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
+    auto ld = [&](const void* v, long long& i, double& d, float& f) {
+        i = 0; d = 0.0; f = 0.f;
+        switch (o.vtype) {
+        case AQ_INT32: i = (long long)static_cast<const int*>(v)[row]; break;
+        case AQ_INT64: i = static_cast<const long long*>(v)[row]; break;
+        case AQ_FLOAT: f = static_cast<const float*>(v)[row]; d = (double)f; break;
+        default: d = static_cast<const double*>(v)[row]; break;
+        }
+    };
+    long long i1, i2; double d1, d2; float f1, f2;
+    ld(o.v, i1, d1, f1);
+    if (o.xform == X_IDENT) { xi = i1; xd = d1; }
+    else {
+        if (o.xform == X_PRODUCT) ld(o.v2, i2, d2, f2); else { i2 = i1; d2 = d1; f2 = f1; }
+        xi = i1 * i2;
+        xd = o.vtype == AQ_FLOAT ? (double)__fmul_rn(f1, f2) : __dmul_rn(d1, d2);
+    }
+    switch (o.kind) {
+    case ACC_ADD_I64: return (unsigned long long)xi;
+    case ACC_ADD_F64: return (unsigned long long)__double_as_longlong(0.0 + (isint ? (double)xi : xd));
+    case ACC_MIN_I64: case ACC_MAX_I64: return (unsigned long long)(isint ? xi : f64_to_ordered(xd));
+    default: return 0ull;
     }
 }
 __device__ __forceinline__ bool acc_needs_value(const AccOp& o) {

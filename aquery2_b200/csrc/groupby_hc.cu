@@ -207,7 +207,8 @@ __device__ __forceinline__ void ld128_shared_volatile(uint32_t saddr, unsigned l
 __global__ void __launch_bounds__(HC_THREADS, 1)
 k_hc_agg_smem(const AccProg prog, const HcPattern pat, const uint32_t nparts,
               const uint32_t* __restrict__ cursor, const uint32_t* __restrict__ tuples,
-              unsigned long long* __restrict__ rec, uint32_t* __restrict__ flags) {
+              unsigned long long* __restrict__ rec, unsigned char* __restrict__ rflags, const int cnt_acc,
+              uint32_t* __restrict__ flags) {
     extern __shared__ __align__(16) unsigned long long tab[];          // HC_SM_SLOTS x 4 words
     if (flags[FLAG_ABORT]) return;
     const unsigned long long p0 = pat.w[0], p1 = pat.w[1], p2 = pat.w[2], p3 = pat.w[3];
@@ -285,10 +286,18 @@ k_hc_agg_smem(const AccProg prog, const HcPattern pat, const uint32_t nparts,
             const unsigned long long a = *reinterpret_cast<volatile unsigned long long*>(sl);
             if ((uint32_t)a == row[j]) {
                 const unsigned long long b = sl[1], c2 = sl[2], d = sl[3];
-                st_stream_v4(out, (uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
-                st_stream_v4(out + 2, (uint32_t)c2, (uint32_t)(c2 >> 32), (uint32_t)d, (uint32_t)(d >> 32));
+                // rflags (needs a COUNT accumulator): a one-row group writes NOTHING -- k_emit_fused rebuilds
+                // its cells from the row's own values; rflags[row] stays 0 = "first row, singleton"
+                const bool single = rflags && (cnt_acc == 0 ? c2 : d) == 1ull;
+                if (!single) {
+                    st_stream_v4(out, (uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+                    st_stream_v4(out + 2, (uint32_t)c2, (uint32_t)(c2 >> 32), (uint32_t)d, (uint32_t)(d >> 32));
+                    if (rflags) rflags[row[j]] = 1;
+                }
                 sl[3] = p3; sl[2] = p2; sl[1] = p1;
                 *reinterpret_cast<volatile unsigned long long*>(sl) = p0;
+            } else if (rflags) {
+                rflags[row[j]] = 2;
             } else {
                 st_stream_v4(out, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
                 st_stream_v4(out + 2, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
@@ -310,7 +319,7 @@ bool hc_qualifies(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32
 }
 
 int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t sw, const unsigned long long* pattern,
-              uint32_t groups_hint, DevBuf& rec, bool* used) {
+              uint32_t groups_hint, DevBuf& rec, DevBuf& rflags, bool* used) {
     *used = false;
     Context& c = ctx();
     if (!hc_qualifies(ks, nrows, prog, sw, groups_hint)) return 0;
@@ -329,8 +338,11 @@ int launch_hc(const KeySpec& ks, uint32_t nrows, const AccProg& prog, uint32_t s
         const size_t smem = size_t(HC_SM_SLOTS) * 32;
         static bool attr_done = false;
         if (!attr_done) { AQ_CUDA(cudaFuncSetAttribute(k_hc_agg_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
+        int cnt_acc = -1;
+        for (int a = 0; a < prog.n && a < 2; ++a) if (prog.op[a].kind == ACC_COUNT) cnt_acc = a;
+        if (cnt_acc >= 0) AQ_TRY(rflags.alloc_zero(size_t(nrows)));
         AQ_LAUNCH(k_hc_agg_smem, grid, HC_THREADS, smem, prog, pat, nparts, cursor.as<uint32_t>(), tuples.as<uint32_t>(),
-                  rec.as<unsigned long long>(), c.d_flags);
+                  rec.as<unsigned long long>(), cnt_acc >= 0 ? rflags.as<unsigned char>() : nullptr, cnt_acc, c.d_flags);
         *used = true;
         return 0;
     }

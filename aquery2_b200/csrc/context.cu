@@ -245,12 +245,14 @@ int aqgpu_profile_report(char* buf, size_t cap) {
 int aqgpu_col_alloc(size_t bytes, void** dptr) {
     AQ_REQUIRE_INIT();
     if (!dptr) return fail("null dptr");
-    AQ_CUDA(cudaMalloc(dptr, bytes ? bytes : 16));
+    // stream-ordered pool (the one DevBuf uses): no device-wide synchronisation, no ms-scale cudaMalloc /
+    // cudaFree per column -- the multi-GPU flows allocate and drop dozens of GB-sized columns per query
+    AQ_CUDA(cudaMallocAsync(dptr, bytes ? bytes : 16, g_ctx.stream));
     return 0;
 }
 
 int aqgpu_col_free(void* dptr) {
-    if (dptr) AQ_CUDA(cudaFree(dptr));
+    if (dptr) AQ_CUDA(cudaFreeAsync(dptr, g_ctx.stream));
     return 0;
 }
 

@@ -102,6 +102,9 @@ class Comm:
     CHUNK = 256 << 20          # bytes per peer and all-to-all call
 
     def __init__(self, local_rank: int = 0, backend: str | None = None):
+        # the exchange buffers are multi-GB torch tensors next to the library's own cudaMallocAsync pool:
+        # expandable segments keep torch's cache from fragmenting into cudaFree / cudaMalloc retries
+        os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -510,7 +513,18 @@ class DistPlan:
         return ng
 
     def step(self) -> dict:
-        return {q: self.run(q) for q in self.queries}
+        if not (os.environ.get("AQ_DIST_TRACE") and self.comm.rank == 0):
+            return {q: self.run(q) for q in self.queries}
+        out, line = {}, []
+        for q in self.queries:                                # per-query wall time inside a step (debug aid)
+            self.comm.stream.synchronize()
+            t0 = time.perf_counter()
+            out[q] = self.run(q)
+            self.comm.stream.synchronize()
+            line.append(f"{q} {1e3 * (time.perf_counter() - t0):.1f}")
+        t = self.comm.torch
+        print("[dist step] " + "  ".join(line) + f"  | torch reserved {t.cuda.memory_reserved() / 2**30:.1f} GiB", file=sys.stderr, flush=True)
+        return out
 
     def total_groups(self, ngs: dict) -> dict:
         """groups over all ranks: the gather strategy replicates them, the partitioned one splits them"""

@@ -99,7 +99,7 @@ def decompose(aggs, codes):
 # ------------------------------------------------------------------------------------------------
 class Comm:
     """torch.distributed process group: NCCL when CUDA is there, gloo otherwise (CPU tests)."""
-    CHUNK = 256 << 20          # bytes per peer and all-to-all call
+    CHUNK = 1 << 30            # bytes per peer and all-to-all call
 
     def __init__(self, local_rank: int = 0, backend: str | None = None):
         # the exchange buffers are multi-GB torch tensors next to the library's own cudaMallocAsync pool:
@@ -201,7 +201,7 @@ class Comm:
                     rq.wait()
         else:
             # pieces of <= CHUNK bytes per peer: one 4 GB all_to_all_single (2 GB per peer) never completed on
-            # B200 / NCCL 2.28, 1 GB per peer did
+            # B200 / NCCL 2.28, 1 GB per peer did (and 1 GiB pieces move at 430 GB/s against 325 for 256 MiB)
             offs_in = np.concatenate([[0], np.cumsum(ins)]).astype(np.int64)
             offs_out = np.concatenate([[0], np.cumsum(outs)]).astype(np.int64)
             step = max(self.CHUNK // itemsize, 1) * itemsize

@@ -46,7 +46,9 @@ EXPORTS = [
     "aqgpu_groups_csr", "aqgpu_groups_device_views", "aqgpu_group_reduce", "aqgpu_group_scan",
     "aqgpu_groups_order_by", "aqgpu_vec_sub", "aqgpu_avg_finalize", "aqgpu_vec_pow", "aqgpu_finalize",
     "aqgpu_rows_to_global", "aqgpu_key_owner", "aqgpu_second_merge", "aqgpu_partition_rows",
-    "aqgpu_synth_column",
+    "aqgpu_synth_column", "aqgpu_groupby_run", "aqgpu_result_size", "aqgpu_result_key", "aqgpu_result_agg",
+    "aqgpu_result_first_row", "aqgpu_result_free", "aqgpu_trim_pool", "aqgpu_col_upload_async",
+    "aqgpu_col_download_async",
 ]
 
 
@@ -91,6 +93,11 @@ def init(device: int = -1) -> None:
 
 def sync() -> None:
     check(lib().aqgpu_sync())
+
+
+def trim_pool() -> None:
+    """give the unused memory of the library's stream-ordered pool back to the device (synchronises)"""
+    check(lib().aqgpu_trim_pool())
 
 
 def launch_count() -> int:
@@ -458,6 +465,89 @@ class PreparedQuery:
                       ctypes.byref(self.ng))
         check(rc)
         return self.ng.value
+
+
+class ColumnView(DeviceColumn):
+    """non-owning DeviceColumn over memory that belongs to something else (a result set)"""
+
+    def __init__(self, ptr: int, n: int, code: int, keep=None):   # noqa: super().__init__ allocates; this must not
+        self.n, self.code, self.itemsize = int(n), int(code), CODE_SIZE[code]
+        self.ptr, self.keep = ptr, keep
+
+    def free(self):
+        self.ptr, self.keep = None, None
+
+
+class AutoQuery:
+    """aqgpu_groupby_run with its argument block built once: no bounds, no hints, no capacities -- the library
+    samples the key columns inside the call, picks a path and allocates the result columns itself.  After
+    run(), ``kouts`` / ``outs`` / ``fr`` are views of the result set (valid until the next run / free)."""
+
+    def __init__(self, keys, aggs, row_order: int = ROWS_DESC, want_first_row: bool = False, key_bounds=None,
+                 groups_hint: int = 0):
+        self.nk = nk = len(keys)
+        self._keep = []
+        kc = [_col(k) for k in keys]
+        self._keep += [c[2] for c in kc]
+        self.nrows = keys[0].n if isinstance(keys[0], DeviceColumn) else kc[0][2].size
+        self.kp = (ctypes.c_void_p * nk)(*[c[0] for c in kc])
+        self.kt = (ctypes.c_int * nk)(*[c[1] for c in kc])
+        self.key_codes = [c[1] for c in kc]
+        self.row_order, self.want_fr, self.groups_hint = row_order, int(want_first_row), int(groups_hint)
+        self.na = na = len(aggs)
+        self.specs = (AggSpec * max(na, 1))()
+        for a, agg in enumerate(aggs):
+            op = REDUCE_NAMES[agg[0]] if isinstance(agg[0], str) else int(agg[0])
+            vt, vp, v2p = INT32, None, None
+            if op != COUNT:
+                vp, vt, k1 = _col(agg[1])
+                self._keep.append(k1)
+                if len(agg) > 2 and agg[2] is not None:
+                    v2p, _, k2 = _col(agg[2])
+                    self._keep.append(k2)
+            s = self.specs[a]
+            s.op, s.vtype, s.v, s.v2, s.out_type, s.out = op, vt, vp, v2p, 0, None
+        self.kmin = self.kmax = None
+        if key_bounds is not None:
+            self.kmin = (ctypes.c_int64 * nk)(*[int(b[0]) for b in key_bounds])
+            self.kmax = (ctypes.c_int64 * nk)(*[int(b[1]) for b in key_bounds])
+        self.h = None
+        self.kouts, self.outs, self.fr, self.ngroups = [], [], None, 0
+        self._fn = lib().aqgpu_groupby_run
+
+    def free(self):
+        if self.h is not None:
+            lib().aqgpu_result_free(self.h)
+            self.h = None
+        self.kouts, self.outs, self.fr = [], [], None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def run(self) -> int:
+        self.free()
+        h = ctypes.c_void_p(0)
+        check(self._fn(self.kp, self.kt, self.nk, ctypes.c_uint32(self.nrows), self.kmin, self.kmax, self.row_order,
+                       ctypes.c_uint32(self.groups_hint), self.specs, self.na, self.want_fr, ctypes.byref(h)))
+        self.h = h
+        L = lib()
+        ng = ctypes.c_uint32(0)
+        check(L.aqgpu_result_size(h, ctypes.byref(ng)))
+        n = self.ngroups = ng.value
+        p, t = ctypes.c_void_p(0), ctypes.c_int(0)
+        for k in range(self.nk):
+            check(L.aqgpu_result_key(h, k, ctypes.byref(p), ctypes.byref(t)))
+            self.kouts.append(ColumnView(p.value, n, t.value))
+        for a in range(self.na):
+            check(L.aqgpu_result_agg(h, a, ctypes.byref(p), ctypes.byref(t)))
+            self.outs.append(ColumnView(p.value, n, t.value))
+        if self.want_fr:
+            check(L.aqgpu_result_first_row(h, ctypes.byref(p)))
+            self.fr = ColumnView(p.value, n, UINT32)
+        return n
 
 
 def vec_sub(a, b, out, n: int, code: int) -> None:

@@ -270,6 +270,27 @@ int aqgpu_col_download(void* host, const void* dptr, size_t bytes) {
     return 0;
 }
 
+int aqgpu_col_upload_async(void* dptr, const void* host, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaMemcpyAsync(dptr, host, bytes, cudaMemcpyHostToDevice, g_ctx.stream));
+    return 0;
+}
+
+int aqgpu_col_download_async(void* host, const void* dptr, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaMemcpyAsync(host, dptr, bytes, cudaMemcpyDeviceToHost, g_ctx.stream));
+    return 0;
+}
+
+int aqgpu_trim_pool(void) {
+    AQ_REQUIRE_INIT();
+    AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    cudaMemPool_t pool;
+    AQ_CUDA(cudaDeviceGetDefaultMemPool(&pool, g_ctx.device));
+    AQ_CUDA(cudaMemPoolTrimTo(pool, 0));
+    return 0;
+}
+
 int aqgpu_host_alloc(size_t bytes, void** hptr) {
     AQ_REQUIRE_INIT();
     if (!hptr) return fail("null hptr");

@@ -16,6 +16,7 @@
 // row among all first rows -- a prefix-popcount over an nrows-bit bitmap, no sort of the groups --
 // which is exactly the insertion index m_values gives (server/unordered_dense.h:1142-1146).
 #include "groupby.cuh"
+#include <algorithm>
 #include <cstring>
 
 namespace aq {
@@ -817,30 +818,94 @@ int emit_fused(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const Ke
 
 using namespace aq;
 
-extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
-                                 const int64_t* key_min, const int64_t* key_max,
-                                 int row_order, uint32_t groups_hint,
-                                 const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
-                                 void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups) {
-    AQ_REQUIRE_INIT();
+// Result columns allocated by the library (aqgpu_groupby_run): the reference's order of events --
+// group build first, then col.resize(g.size) (engine/ast.py:681-701).
+struct aqgpu_result {
+    uint32_t ngroups = 0;
+    int nkeys = 0, naggs = 0;
+    int key_type[MAX_KEY_COLS];
+    int agg_type[MAX_AGGS];
+    DevBuf keys[MAX_KEY_COLS];
+    DevBuf aggs[MAX_AGGS];
+    DevBuf first_row;
+};
+
+namespace aq {
+
+int OutSink::prepare(uint32_t cap_cells, const AggPlan& plan) {
+    cap = cap_cells ? cap_cells : 1;
+    if (res) {
+        for (int a = 0; a < n_aggs; ++a) {
+            res->agg_type[a] = plan.emit.agg[a].out_type;
+            AQ_TRY(res->aggs[a].alloc(dtype_size(res->agg_type[a]) * size_t(cap)));
+            agg_dst[a] = res->aggs[a].p;
+        }
+        for (int k = 0; k < nkeys; ++k) {
+            AQ_TRY(res->keys[k].alloc(dtype_size(key_types[k]) * size_t(cap)));
+            key_dst[k] = res->keys[k].p;
+        }
+        fr_dst = nullptr;
+        if (want_first_row) { AQ_TRY(res->first_row.alloc(size_t(4) * cap)); fr_dst = res->first_row.as<uint32_t>(); }
+        return 0;
+    }
+    cap = max_groups;
+    vout.resize(n_aggs); kout.resize(nkeys);
+    for (int a = 0; a < n_aggs; ++a) {
+        AQ_TRY(vout[a].bind(aggs[a].out, dtype_size(plan.emit.agg[a].out_type) * size_t(cap)));
+        agg_dst[a] = vout[a].d;
+    }
+    for (int k = 0; k < nkeys; ++k) {
+        key_dst[k] = nullptr;
+        if (out_keys && out_keys[k]) {
+            AQ_TRY(kout[k].bind(out_keys[k], dtype_size(key_types[k]) * size_t(cap)));
+            key_dst[k] = kout[k].d;
+        }
+    }
+    fr_dst = nullptr;
+    if (out_first_row) { AQ_TRY(fr.bind(out_first_row, size_t(4) * cap)); fr_dst = static_cast<uint32_t*>(fr.d); }
+    return 0;
+}
+
+int OutSink::finish(uint32_t ng, const AggPlan& plan) {
+    if (res) { res->ngroups = ng; return 0; }
+    bool any_host = false;
+    for (int a = 0; a < n_aggs; ++a) { AQ_TRY(vout[a].finish(dtype_size(plan.emit.agg[a].out_type) * size_t(ng))); any_host |= vout[a].host != nullptr; }
+    for (int k = 0; k < nkeys; ++k) if (key_dst[k]) { AQ_TRY(kout[k].finish(dtype_size(key_types[k]) * size_t(ng))); any_host |= kout[k].host != nullptr; }
+    if (fr_dst) { AQ_TRY(fr.finish(size_t(4) * ng)); any_host |= fr.host != nullptr; }
+    // host outputs are complete on return; device outputs are stream-ordered
+    if (any_host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+// The whole fused group-by: bind inputs, plan, pick a path, emit into `sink`.
+static int groupby_core(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                        const int64_t* key_min, const int64_t* key_max, int row_order, uint32_t groups_hint,
+                        const aqgpu_agg_t* aggs, int n_aggs, OutSink& sink, uint32_t* ngroups) {
     if (n_aggs < 0 || n_aggs > MAX_AGGS || (n_aggs && !aggs)) return fail("need 0..%d aggregates", MAX_AGGS);
     if (!ngroups) return fail("ngroups must not be null");
     if (row_order != AQ_ROWS_DESC && row_order != AQ_ROWS_ASC) return fail("bad row_order %d", row_order);
     *ngroups = 0;
+    if (!keys || !key_types || nkeys < 1 || nkeys > MAX_KEY_COLS) return fail("need 1..%d key columns", MAX_KEY_COLS);
+    sink.n_aggs = n_aggs; sink.nkeys = nkeys; sink.key_types = key_types;
     KeyCols kc;
     if (nrows == 0) {
-        if (!keys || !key_types || nkeys < 1 || nkeys > MAX_KEY_COLS) return fail("need 1..%d key columns", MAX_KEY_COLS);
+        for (int k = 0; k < nkeys; ++k)
+            if (key_types[k] != AQ_INT32 && key_types[k] != AQ_UINT32 && key_types[k] != AQ_INT64)
+                return fail("unsupported key dtype %d (int32, uint32, int64 keys only)", key_types[k]);
+        if (sink.res) {
+            AggPlan plan0; plan0.emit.row_order = row_order;
+            for (int a = 0; a < n_aggs; ++a) AQ_TRY(plan0.plan(aggs[a], aggs[a].v, aggs[a].v2, nullptr));
+            AQ_TRY(sink.prepare(1, plan0));
+            AQ_TRY(sink.finish(0, plan0));
+        }
         return 0;
     }
     AQ_TRY(kc.bind(keys, key_types, nkeys, nrows));
-    if (max_groups == 0) max_groups = nrows;
-    KeySpec ks;
-    AQ_TRY(kc.make_spec(key_min, key_max, ks));
+    if (!sink.res && sink.max_groups == 0) sink.max_groups = nrows;
 
     AggPlan plan;
     plan.emit.row_order = row_order;
     std::vector<InCol> vin(n_aggs), vin2(n_aggs);
-    std::vector<OutCol> vout(n_aggs);
     for (int a = 0; a < n_aggs; ++a) {
         const aqgpu_agg_t& g = aggs[a];
         const void* dv = nullptr; const void* dv2 = nullptr;
@@ -852,43 +917,108 @@ extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, 
         }
         const int ot = g.out_type ? g.out_type : aqgpu_reduce_out_type(g.op, g.vtype);
         if (ot < 0 || dtype_size(ot) == 0) return fail("aggregate %d: bad output dtype", a);
-        AQ_TRY(vout[a].bind(g.out, dtype_size(ot) * max_groups));
-        AQ_TRY(plan.plan(g, dv, dv2, vout[a].d));
+        AQ_TRY(plan.plan(g, dv, dv2, nullptr));
+    }
+    auto set_outputs = [&](KeyOut& ko) {
+        for (int a = 0; a < n_aggs; ++a) plan.emit.agg[a].out = sink.agg_dst[a];
+        memset(&ko, 0, sizeof(ko));
+        ko.n = nkeys;
+        for (int k = 0; k < nkeys; ++k) {
+            ko.src[k] = kc.col[k].d;
+            ko.size[k] = (int)dtype_size(key_types[k]);
+            ko.dst[k] = sink.key_dst[k];
+        }
+    };
+
+    // ---- planned fast paths (plan.cu / lc.cu / hcfp.cu); each declines (used = false) or completes the query
+    {
+        bool used = false;
+        AQ_TRY(run_planned_paths(kc, nrows, key_min, key_max, groups_hint, plan, sink, ngroups, &used));
+        if (used) return 0;
     }
 
+    KeySpec ks;
+    AQ_TRY(kc.make_spec(key_min, key_max, ks));
     HashResult hr;
     uint32_t ng = 0;
     AQ_TRY(hash_aggregate(ks, nrows, groups_hint, plan, nullptr, hr, &ng, true));
-    if (!hr.fused && ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
-
+    if (!sink.res && !hr.fused && ng > sink.max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.max_groups);
+    AQ_TRY(sink.prepare(hr.fused ? nrows : ng, plan));
     KeyOut ko;
-    memset(&ko, 0, sizeof(ko));
-    ko.n = nkeys;
-    std::vector<OutCol> kout(nkeys);
-    for (int k = 0; k < nkeys; ++k) {
-        ko.src[k] = kc.col[k].d;
-        ko.size[k] = (int)dtype_size(key_types[k]);
-        if (out_keys && out_keys[k]) {
-            AQ_TRY(kout[k].bind(out_keys[k], size_t(ko.size[k]) * max_groups));
-            ko.dst[k] = kout[k].d;
-        }
-    }
-    OutCol fr;
-    uint32_t* d_fr = nullptr;
-    if (out_first_row) { AQ_TRY(fr.bind(out_first_row, size_t(4) * max_groups)); d_fr = static_cast<uint32_t*>(fr.d); }
-
+    set_outputs(ko);
     if (hr.fused) {
-        AQ_TRY(emit_fused(hr.ks, nrows, hr, ko, d_fr, plan, max_groups, &ng));
-        if (ng > max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, max_groups);
+        AQ_TRY(emit_fused(hr.ks, nrows, hr, ko, sink.fr_dst, plan, sink.cap, &ng));
+        if (ng > sink.cap) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.cap);
     } else {
-        AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, d_fr, nullptr, nullptr, nullptr, plan, max_groups));
+        AQ_TRY(emit_groups(hr.ks, nrows, hr, ko, sink.fr_dst, nullptr, nullptr, nullptr, plan, sink.cap));
     }
-    bool any_host = false;
-    for (int a = 0; a < n_aggs; ++a) { AQ_TRY(vout[a].finish(dtype_size(plan.emit.agg[a].out_type) * ng)); any_host |= vout[a].host != nullptr; }
-    for (int k = 0; k < nkeys; ++k) if (ko.dst[k]) { AQ_TRY(kout[k].finish(size_t(ko.size[k]) * ng)); any_host |= kout[k].host != nullptr; }
-    if (out_first_row) { AQ_TRY(fr.finish(size_t(4) * ng)); any_host |= fr.host != nullptr; }
+    AQ_TRY(sink.finish(ng, plan));
     *ngroups = ng;
-    // host outputs are complete on return; device outputs are stream-ordered
-    if (any_host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    bool staged = false;
+    for (int k = 0; k < kc.n; ++k) staged |= kc.col[k].tmp.p != nullptr;
+    if (staged || std::any_of(vin.begin(), vin.end(), [](const InCol& c) { return c.tmp.p != nullptr; }))
+        AQ_CUDA(cudaStreamSynchronize(ctx().stream));      // staged host inputs are released on return
+    return 0;
+}
+
+} // namespace aq
+
+extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                                 const int64_t* key_min, const int64_t* key_max,
+                                 int row_order, uint32_t groups_hint,
+                                 const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
+                                 void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups) {
+    AQ_REQUIRE_INIT();
+    OutSink sink;
+    sink.aggs = aggs; sink.out_keys = out_keys; sink.out_first_row = out_first_row; sink.max_groups = max_groups;
+    return groupby_core(keys, key_types, nkeys, nrows, key_min, key_max, row_order, groups_hint, aggs, n_aggs, sink, ngroups);
+}
+
+extern "C" int aqgpu_groupby_run(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                                 const int64_t* key_min, const int64_t* key_max,
+                                 int row_order, uint32_t groups_hint,
+                                 const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out) {
+    AQ_REQUIRE_INIT();
+    if (!out) return fail("null result pointer");
+    *out = nullptr;
+    aqgpu_result* r = new aqgpu_result();
+    struct Guard { aqgpu_result* r; ~Guard() { delete r; } } guard{r};
+    r->nkeys = nkeys > 0 && nkeys <= MAX_KEY_COLS ? nkeys : 0;
+    r->naggs = n_aggs > 0 && n_aggs <= MAX_AGGS ? n_aggs : 0;
+    for (int k = 0; k < r->nkeys; ++k) r->key_type[k] = key_types ? key_types[k] : 0;
+    OutSink sink;
+    sink.res = r; sink.want_first_row = want_first_row != 0;
+    uint32_t ng = 0;
+    AQ_TRY(groupby_core(keys, key_types, nkeys, nrows, key_min, key_max, row_order, groups_hint, aggs, n_aggs, sink, &ng));
+    r->ngroups = ng;
+    guard.r = nullptr;
+    *out = r;
+    return 0;
+}
+
+extern "C" int aqgpu_result_size(const aqgpu_result_t* r, uint32_t* ngroups) {
+    if (!r || !ngroups) return fail("null argument");
+    *ngroups = r->ngroups;
+    return 0;
+}
+extern "C" int aqgpu_result_key(const aqgpu_result_t* r, int k, void** dptr, int* dtype) {
+    if (!r || !dptr || k < 0 || k >= r->nkeys) return fail("bad key column index %d", k);
+    *dptr = r->keys[k].p;
+    if (dtype) *dtype = r->key_type[k];
+    return 0;
+}
+extern "C" int aqgpu_result_agg(const aqgpu_result_t* r, int a, void** dptr, int* dtype) {
+    if (!r || !dptr || a < 0 || a >= r->naggs) return fail("bad aggregate index %d", a);
+    *dptr = r->aggs[a].p;
+    if (dtype) *dtype = r->agg_type[a];
+    return 0;
+}
+extern "C" int aqgpu_result_first_row(const aqgpu_result_t* r, uint32_t** dptr) {
+    if (!r || !dptr) return fail("null argument");
+    *dptr = r->first_row.as<uint32_t>();
+    return 0;
+}
+extern "C" int aqgpu_result_free(aqgpu_result_t* r) {
+    delete r;
     return 0;
 }

@@ -2,6 +2,8 @@
 #pragma once
 #include "common.cuh"
 
+struct aqgpu_result;
+
 namespace aq {
 
 constexpr int MAX_KEY_COLS = 12;
@@ -131,6 +133,37 @@ struct AggPlan {
     int find(int kind) const;
     int plan(const aqgpu_agg_t& a, const void* dv, const void* dv2, void* dout);
 };
+
+// Where the result columns of one fused group-by go: caller-provided columns (aqgpu_groupby_agg: device or
+// host pointers with room for max_groups cells) or columns the library allocates once it knows the group
+// count (aqgpu_groupby_run -> struct aqgpu_result).  prepare() is called after the group count (or an upper
+// bound of it) is known and before anything is emitted.
+struct OutSink {
+    // caller-provided
+    const aqgpu_agg_t* aggs = nullptr;
+    void* const* out_keys = nullptr;
+    uint32_t* out_first_row = nullptr;
+    uint32_t max_groups = 0;
+    std::vector<OutCol> vout, kout;
+    OutCol fr;
+    // library-allocated
+    ::aqgpu_result* res = nullptr;
+    bool want_first_row = false;
+    // common
+    int n_aggs = 0, nkeys = 0;
+    const int* key_types = nullptr;
+    uint32_t cap = 0;                     // cells every destination below can hold
+    void* agg_dst[MAX_AGGS] = {};
+    void* key_dst[MAX_KEY_COLS] = {};
+    uint32_t* fr_dst = nullptr;
+    int prepare(uint32_t cap_cells, const AggPlan& plan);
+    int finish(uint32_t ngroups, const AggPlan& plan);
+};
+
+// Sampling planner + the fast paths it can choose (plan.cu): low-cardinality direct tables (lc.cu) and the
+// fingerprint-partitioned path for groups ~ rows (hcfp.cu).  *used = false: fall through to hash_aggregate.
+int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max,
+                      uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used);
 
 // Result of the hash phase, consumed by emit / handle construction.
 struct HashResult {

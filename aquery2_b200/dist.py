@@ -361,7 +361,7 @@ class DistQuery:
     """keys / aggs name columns of `cols` (this rank's shard, rows [lo, lo + n) of the global table)."""
 
     def __init__(self, comm: Comm, engine, cols: dict, codes: dict, keys, aggs, lo: int, max_groups: int,
-                 hint: int = 0, bounds=None, gather_limit: int = GATHER_LIMIT):
+                 hint: int = 0, bounds=None, gather_limit: int = GATHER_LIMIT, global_hint: int | None = None):
         self.comm, self.eng, self.lo = comm, engine, int(lo)
         self.key_names, self.aggs = list(keys), list(aggs)
         self.key_codes = [codes[k] for k in keys]
@@ -377,7 +377,9 @@ class DistQuery:
         k0 = cols[keys[0]]
         self.nrows = int(k0.n) if hasattr(k0, "n") else len(k0)
         total_rows = sum(comm.all_counts(self.nrows))
-        self.by_rows = comm.world > 1 and hint > 0 and 2 * hint >= total_rows and total_rows > gather_limit
+        # decided from the GLOBAL group estimate against the GLOBAL row count (hint itself is capped at the shard size)
+        ghint = hint if global_hint is None else global_hint
+        self.by_rows = comm.world > 1 and ghint > 0 and 2 * ghint >= total_rows and total_rows > gather_limit
 
     def run_rows(self):
         c, e = self.comm, self.eng
@@ -497,7 +499,8 @@ class DistPlan:
             keys, aggs, epi = h2o.QUERIES[q]
             mg = h2o.max_groups(q, n_total, k, nrows)
             bounds = [h2o.key_bound(c, n_total, k) for c in keys] if use_bounds else None
-            self.dq[q] = DistQuery(comm, self.eng, table, codes, keys, aggs, lo, mg, hint=mg, bounds=bounds)
+            self.dq[q] = DistQuery(comm, self.eng, table, codes, keys, aggs, lo, mg, hint=mg, bounds=bounds,
+                                   global_hint=h2o.max_groups(q, n_total, k, n_total))
             self.epilogue[q] = epi
 
     def run(self, q: str) -> int:
@@ -536,3 +539,9 @@ class DistPlan:
         for q, ng in ngs.items():
             out[q] = ng if self.dq[q].strategy == "allgather" else int(self.comm.sum_float(float(ng)))
         return out
+
+    def exchange_report(self) -> dict:
+        return {q: {"strategy": self.dq[q].strategy, "bytes_in_per_rank": self.dq[q].exchanged_bytes} for q in self.queries}
+
+    def verify(self, table, queries, args, n_total, ngs) -> dict:
+        return {"status": "skipped (multi-GPU result checks: tests/test_dist_gpu.py)"}

@@ -1,15 +1,28 @@
 #!/usr/bin/env python
-"""bench.py -- h2o group-by q1-q10 throughput (rows/s) of the B200 post-processor path.
+"""bench.py -- throughput (rows/s) of the B200 post-processor path on the reference's own workloads.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--rows R]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload h2o|trade] [--rows R] [--no-verify] [--hints]
 
-A step = one pass of the hot path over the synthetic table G1_{R}_1e2_0_0: the ten queries of the
-reference's benchmark/h2o/groupby.sql, each from "columns resident in HBM" to "result columns
-resident in HBM" (the reference's postproc_time bracket, server/server.cpp:303-305).
-value = (queries x rows) / time, whole job.  One JSON line on stdout (rank 0).
+--workload h2o (default; BASELINE.json configs[2]): a step = one pass of the hot path over the synthetic
+table G1_{R}_1e2_0_0: the ten queries of the reference's benchmark/h2o/groupby.sql, each from "columns
+resident in HBM" to "result columns resident in HBM" (the reference's postproc_time bracket,
+server/server.cpp:303-305).  value = (queries x rows) / time, whole job.
+--workload trade (configs[3]): ASSUMING-ordered windowed aggregates by sym over the trade table of
+datagen.cpp:90-107 (see aquery2_b200/trade.py, bench_trade.py).
 
---impl reference times the reference's own CPU post-processor (oracle/_ref/libaqref.so = the
-reference headers compiled here; else the C port) on a bounded sample of the same workload.
+By default the library is told NOTHING the reference's path would not know: no key bounds, no group-count
+hints, no output capacities (it samples the key columns itself inside the timed call and allocates the
+result columns once it knows the group count).  --hints passes the generator's exact statistics instead
+(the round-1 behaviour), for comparison only.
+
+After the last timed step the results left in HBM are VERIFIED (bench_verify.py): independent group counts,
+sum(count) = rows, first-appearance order, column-total identities, groups recomputed from scratch, and
+the same ten queries compared with the reference-built CPU oracle on the cpu_baseline table.  A failed
+check prints "verify": "FAILED: ..." and exits non-zero.
+
+--impl reference times the reference's own CPU post-processor (oracle/_ref/libaqref.so = the reference
+headers compiled here; else the C port) on a bounded sample of the same workload.
 """
 from __future__ import annotations
 
@@ -26,7 +39,6 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "h2o groupby rows/sec (q1-q10)"
 UNIT = "rows/s"
 
 
@@ -36,14 +48,17 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="h2o", choices=["h2o", "trade"])
     ap.add_argument("--rows", type=float, default=1e9, help="total rows of the table (all ranks)")
     ap.add_argument("--k", type=int, default=100, help="h2o K (id1,id2,id4,id5 cardinality)")
-    ap.add_argument("--queries", default="q1,q2,q3,q4,q5,q6,q7,q8,q9,q10")
+    ap.add_argument("--nsym", type=float, default=1e6, help="trade: number of symbols (groups)")
+    ap.add_argument("--queries", default="")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--cpu-rows", type=float, default=1e7, help="rows of the CPU-baseline sample table")
-    ap.add_argument("--no-bounds", action="store_true", help="do not pass key statistics to the library")
+    ap.add_argument("--hints", action="store_true", help="pass the generator's key bounds / group counts to the library")
     return ap.parse_args()
 
 
@@ -55,6 +70,16 @@ def load_peaks():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_ncu_traffic():
+    """{kernel name: {"bytes_per_row": .., "capture": file}} from an `ncu --set full` capture of THIS round
+    (profiles/r02/ncu_traffic.json); absent kernels report traffic null."""
+    p = os.path.join(ROOT, "profiles", "r02", "ncu_traffic.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
 
 
 class ClockSampler:
@@ -103,6 +128,14 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def workload_module(args):
+    if args.workload == "trade":
+        import bench_trade as wl
+    else:
+        import bench_h2o as wl
+    return wl
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU baseline: the reference's own post-processor (the ONLY place bench.py executes oracle/)
 # ------------------------------------------------------------------------------------------------
@@ -112,54 +145,36 @@ def load_cpu_impl():
     return ref if ref is not None else aqo.load_port()
 
 
-def cpu_step(impl, t, queries):
-    """one pass of the ten queries through hashtable_push / ht_postproc / per-group aggregates;
-    returns seconds inside the postproc bracket (aqo_time_groupby_reduce)"""
-    from aquery2_b200 import h2o
-    total = 0.0
-    for q in queries:
-        keys, aggs, _ = h2o.QUERIES[q]
-        specs = [(a[0],) + tuple(t[c] for c in a[1:]) for a in aggs]
-        sec, _ = impl.time_groupby_reduce([t[c] for c in keys], specs)
-        total += sec
-    return total
+def cpu_kind(impl):
+    return "reference" if impl.kind == "reference" else "port"
 
 
-def cpu_baseline(args, queries, rows):
-    from aquery2_b200 import h2o, synth
-    impl = load_cpu_impl()
-    n = int(rows)
-    t = synth.h2o_table(n, args.k, columns=h2o.columns_of(queries))
-    sec = cpu_step(impl, t, queries)
-    return {"value": len(queries) * n / sec, "unit": UNIT, "cores": 1,
-            "kind": "reference" if impl.kind == "reference" else "port",
-            "sample": f"G1_{n:.0e}_{args.k:.0e}_0_0 {queries[0]}-{queries[-1]} once ({sec:.1f} s), single thread "
-                      f"(the reference path has no threads); g++ -O3 -march=x86-64-v3 (no clang in the image)",
-            "host_cores": os.cpu_count()}
+CPU_NOTE = ("single thread (the reference path has no threads); g++ -O3 -march=x86-64-v3 (the reference wants "
+            "clang -Ofast, absent from the image)")
 
 
-def run_reference(args, queries):
+def run_reference(args, wl, queries):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from aquery2_b200 import h2o, synth
     impl = load_cpu_impl()
     total_steps = max(args.steps + args.warmup, 1)
-    n = int(min(args.cpu_rows, max(1e6, 1.2e8 / total_steps)))      # ~10 s per step at 1e7 rows
-    t = synth.h2o_table(n, args.k, columns=h2o.columns_of(queries))
+    n = int(min(args.cpu_rows, args.rows, max(1e6, 1.2e8 / total_steps)))      # ~10 s per step at 1e7 rows
+    t = wl.host_table(args, n)
     for _ in range(args.warmup):
-        cpu_step(impl, t, queries)
-    secs = [cpu_step(impl, t, queries) for _ in range(args.steps)]
+        wl.cpu_step(impl, t, queries)
+    secs = [wl.cpu_step(impl, t, queries) for _ in range(args.steps)]
     tot = sum(secs)
     value = args.steps * len(queries) * n / tot
-    sample = f"G1_{n:.0e}_{args.k:.0e}_0_0 q1-q10 per step, single thread (reference path is single-threaded)"
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+    sample = f"{wl.table_name(args, n)} {queries[0]}-{queries[-1]} per step, " + CPU_NOTE
+    line = {"impl": "reference", "metric": wl.METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int64/f64",
-            "data": "synthetic", "config": {"workload": f"h2o G1_{args.rows:.0e}_{args.k:.0e}_0_0 {','.join(queries)}",
-                                            "sample_rows": n},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1,
-                             "kind": "reference" if impl.kind == "reference" else "port", "sample": sample,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": wl.DTYPE,
+            "data": "synthetic",
+            "config": {"workload": f"{wl.table_name(args, n)} {','.join(queries)} -- a {n:.0e}-row SAMPLE of the b200 arm's "
+                                   f"{wl.table_name(args, int(args.rows))} (CPU time bound); group cardinalities shrink with the sample",
+                       "sample_rows": n, "same_config": False},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": cpu_kind(impl), "sample": sample,
                              "host_cores": os.cpu_count()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -169,11 +184,11 @@ def run_reference(args, queries):
 # ------------------------------------------------------------------------------------------------
 # the B200 arm
 # ------------------------------------------------------------------------------------------------
-def run_b200(args, queries):
+def run_b200(args, wl, queries):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    from aquery2_b200 import aqgpu as aq, h2o
+    from aquery2_b200 import aqgpu as aq
     aq.init(local_rank)                      # raises without the CUDA library / device: no fallback
     comm = None
     if world > 1:
@@ -182,15 +197,12 @@ def run_b200(args, queries):
 
     n_total = int(args.rows)
     lo, hi = rank * n_total // world, (rank + 1) * n_total // world
-    cols = h2o.columns_of(queries)
-    table = h2o.device_table(aq, n_total, args.k, lo, hi, cols)
+    table = wl.device_table(aq, args, n_total, lo, hi, queries)
     aq.sync()
     if comm is None:
-        plan = h2o.Plan(aq, table, queries, n_total, args.k, device_out=True, use_bounds=not args.no_bounds)
-        runner = plan
+        runner = wl.Plan(aq, table, queries, args, n_total, hints=args.hints)
     else:
-        plan = None
-        runner = dist.DistPlan(comm, table, queries, n_total, args.k, lo, use_bounds=not args.no_bounds)
+        runner = wl.dist_plan(comm, table, queries, args, n_total, lo, hints=args.hints)
 
     def barrier():
         if comm is not None:
@@ -219,8 +231,20 @@ def run_b200(args, queries):
     value = len(queries) * n_total / (ms_per_step * 1e-3)
     exchange = None
     if comm is not None:
-        ngs = runner.total_groups(ngs)
-        exchange = {q: {"strategy": runner.dq[q].strategy, "bytes_in_per_rank": runner.dq[q].exchanged_bytes} for q in queries}
+        ngs_total = runner.total_groups(ngs)
+        exchange = runner.exchange_report()
+    else:
+        ngs_total = ngs
+
+    # ---- verification of what the timed loop left in HBM (outside the timed region)
+    verify = None
+    if not args.no_verify:
+        try:
+            verify = wl.verify(aq, comm, runner, table, queries, args, n_total, ngs)
+        except Exception as e:      # VerifyError or anything the checker tripped over: never report a number as verified
+            import traceback
+            traceback.print_exc()
+            verify = {"status": f"FAILED: {type(e).__name__}: {e}"[:600]}
 
     # ---- per-kernel / per-query breakdown (separate pass, CUDA events around every launch)
     aq.profile_enable(True)
@@ -243,94 +267,77 @@ def run_b200(args, queries):
     kernels = {}
     for name, (calls, tot_ms) in sorted(prof.items(), key=lambda kv: -kv[1][1])[:80]:
         kernels[name] = {"calls": calls, "ms_per_launch": tot_ms / calls}
-    # DRAM bytes per row of the kernels captured with `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum
-    # per launch / rows of that launch; profiles/r01/ncu_full_hc_scatter.csv), scaled to this launch's rows
-    NCU_DRAM_BYTES_PER_ROW = {"k_hc_scatter": (28.133142e9 + 31.992585e9) / 1e9}
+    ncu = load_ncu_traffic()
     if top:
         name, (calls, tot_ms) = top
         q = name.split(":")[0]
-        alg = h2o.ALG_BYTES.get(q, 0) * nrows_local
+        alg = wl.ALG_BYTES.get(q, 0) * nrows_local
         avg_ms = tot_ms / calls
         achieved = alg / (avg_ms * 1e-3) / 1e9
+        kname = name.split(":", 1)[-1]
+        cap = next((v for k, v in ncu.items() if k in kname), None)
         roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak,
-                    "traffic": next((v * nrows_local for k, v in NCU_DRAM_BYTES_PER_ROW.items() if k in name), None),
+                    "traffic": cap["bytes_per_row"] * nrows_local if cap and world == 1 else None,
+                    "traffic_source": (f"ncu --set full capture {cap['capture']}, dram bytes/row x rows" if cap and world == 1
+                                       else "no capture of this kernel at this configuration"),
                     "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg, "ms_per_launch": avg_ms,
                     "share_of_step": tot_ms / prof_steps / max(sum(per_query_ms.values()), 1e-9)}
     per_query = {q: {"ms": per_query_ms[q], "rows_per_s": n_total / (per_query_ms[q] * 1e-3),
-                     "hbm_frac": h2o.ALG_BYTES[q] * nrows_local / (per_query_ms[q] * 1e-3) / 1e9 / peak,
-                     "groups": int(ngs[q])} for q in queries}
+                     "hbm_frac": wl.ALG_BYTES[q] * nrows_local / (per_query_ms[q] * 1e-3) / 1e9 / peak,
+                     "hbm_frac_in_out": (wl.ALG_BYTES[q] * nrows_local + wl.out_bytes(q, int(ngs[q]))) / (per_query_ms[q] * 1e-3) / 1e9 / peak,
+                     "groups": int(ngs_total[q])} for q in queries}
+    step_alg = sum(wl.ALG_BYTES[q] for q in queries) * nrows_local
+    step_frac = step_alg / (ms_per_step * 1e-3) / 1e9 / peak
 
-    # ---- e2e: the same step through the C ABI with HOST buffers (pinned), H2D + D2H inside
+    # ---- e2e: host-resident (pinned) columns -> HBM column store -> queries -> results back in pinned host memory
     e2e = None
     if not args.no_e2e and comm is None:
-        e2e = run_e2e(args, aq, h2o, table, plan, queries, n_total)
+        e2e = wl.run_e2e(aq, args, table, runner, queries, n_total)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(args, queries, args.cpu_rows)
+        try:
+            cpu = wl.cpu_baseline(aq, args, queries, load_cpu_impl(), CPU_NOTE, check=not args.no_verify)
+            if verify is not None and "oracle_parity" in cpu:
+                verify["oracle_parity"] = cpu.pop("oracle_parity")
+                if not verify["oracle_parity"]["status"].startswith("ok"):
+                    verify["status"] = "FAILED: " + verify["oracle_parity"]["status"]
+        except Exception as e:
+            import traceback
+            traceback.print_exc()
+            if verify is not None:
+                verify["status"] = f"FAILED: cpu parity leg: {type(e).__name__}: {e}"[:600]
 
     if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        line = {"metric": wl.METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "int64/f64", "data": "synthetic",
-                "config": {"workload": f"h2o G1_{n_total:.0e}_{args.k:.0e}_0_0 {','.join(queries)}",
+                "scaling": "strong", "vs_baseline": None, "dtype": wl.DTYPE, "data": "synthetic",
+                "config": {"workload": f"{wl.table_name(args, n_total)} {','.join(queries)}",
                            "rows_total": n_total, "rows_per_gpu": nrows_local, "queries": len(queries),
+                           "statistics_given_to_library": "generator bounds + group counts (--hints)" if args.hints
+                                                          else "none: the library samples keys inside the timed call",
                            "l2": "inputs (>= 8 B/row x rows) far larger than the 126 MB L2; no flush needed",
                            "parallelism": "1 GPU" if world == 1 else f"{world} GPUs: row-range shards, local partial aggregation, NCCL merge"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches // max(args.steps, 1) * args.steps,
-                "roofline": roofline, "cpu_baseline": cpu, "per_query": per_query, "kernels": kernels, "exchange": exchange}
+                "verify": verify["status"] if verify else "skipped (--no-verify)", "verify_detail": verify,
+                "roofline": roofline, "step_hbm_frac": step_frac, "cpu_baseline": cpu, "per_query": per_query,
+                "kernels": kernels, "exchange": exchange}
         print(json.dumps(line), flush=True)
     if comm is not None:
         comm.close()
-
-
-def run_e2e(args, aq, h2o, table, plan, queries, n_total):
-    """Host-resident columns in pinned memory -> aqgpu_groupby_agg stages them itself (H2D), results
-    land in pinned host columns (D2H): the call a reference user makes with MonetDB-owned buffers."""
-    pinned, host = [], {}
-    for c, d in table.items():
-        pa = aq.PinnedArray(d.n, d.code)
-        if d.nbytes:
-            aq.check(aq.lib().aqgpu_col_download(ctypes.c_void_p(pa.ptr), ctypes.c_void_p(d.ptr), ctypes.c_size_t(d.nbytes)))
-        pinned.append(pa)
-        host[c] = pa.array
-    del plan
-    for d in table.values():
-        d.free()                               # the e2e arm starts with nothing resident in HBM
-
-    def host_alloc(code, n):
-        pa = aq.PinnedArray(n, code)
-        pinned.append(pa)
-        return pa.array
-
-    hplan = h2o.Plan(aq, host, queries, n_total, args.k, device_out=False, host_alloc=host_alloc,
-                     use_bounds=not args.no_bounds)
-    hplan.step()                               # warm-up
-    aq.sync()
-    t0 = time.perf_counter()
-    aq.timer_begin()
-    for _ in range(args.e2e_steps):
-        ngs = hplan.step()
-    ms = aq.timer_end()
-    wall = time.perf_counter() - t0
-    bi, bo = hplan.io_bytes(ngs)
-    out = {"value": len(queries) * n_total / (ms * 1e-3 / args.e2e_steps), "unit": UNIT,
-           "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo, "steps": args.e2e_steps,
-           "ms_per_step": ms / args.e2e_steps, "wall_s_per_step": wall / args.e2e_steps,
-           "host_memory": "pinned (aqgpu_host_alloc)"}
-    for pa in pinned:
-        pa.free()
-    return out
+    if verify is not None and not str(verify.get("status", "")).startswith(("ok", "skipped")):
+        sys.exit(3)
 
 
 def main():
     args = parse_args()
-    queries = [q.strip() for q in args.queries.split(",") if q.strip()]
+    wl = workload_module(args)
+    queries = [q.strip() for q in args.queries.split(",") if q.strip()] or list(wl.ORDER)
     if args.impl == "reference":
-        run_reference(args, queries)
+        run_reference(args, wl, queries)
     else:
-        run_b200(args, queries)
+        run_b200(args, wl, queries)
 
 
 if __name__ == "__main__":

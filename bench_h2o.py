@@ -1,0 +1,128 @@
+"""bench_h2o.py -- bench.py's hooks for the h2o workload (aquery2_b200/h2o.py): verification of the timed
+results (bench_verify.py), the CPU baseline leg (the reference build, passed in by bench.py) and the e2e arm.
+Bench infrastructure, not product code."""
+from __future__ import annotations
+
+import ctypes
+import time
+
+from aquery2_b200.h2o import *          # noqa: F401,F403  (QUERIES, ORDER, ALG_BYTES, Plan, device_table, ...)
+from aquery2_b200.h2o import QUERIES, ORDER, key_bound, host_table, table_name
+
+
+# ------------------------------------------------------------------------------------------------
+# hooks for bench.py
+# ------------------------------------------------------------------------------------------------
+def verify(aq, comm, runner, table, queries, args, n_total, ngs) -> dict:
+    """size-independent checks of the results the timed loop left in HBM (bench_verify.py)"""
+    if comm is not None:
+        return runner.verify(table, queries, args, n_total, ngs)
+    import torch
+    import bench_verify as bv
+    aq.trim_pool()
+    report = {}
+    t0 = time.perf_counter()
+    for q in queries:
+        keys, aggs, epi = QUERIES[q]
+        ranges = [key_bound(c, n_total, args.k)[1] for c in keys]
+        bv.verify_query(torch, aq, q, keys, aggs, epi, table, runner.prepared[q], runner.extra[q], int(ngs[q]), ranges, report)
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        aq.trim_pool()
+    return {"status": "ok", "rows": n_total, "per_query": report, "seconds": round(time.perf_counter() - t0, 1),
+            "checks": "independent distinct count; sum(count)=rows; first rows ascending; key==col[first_row]; column-total "
+                      "identities; groups recomputed through row masks; epilogues"}
+
+
+def cpu_step(impl, t, queries) -> float:
+    """one pass of the queries through hashtable_push / ht_postproc / per-group aggregates; seconds
+    inside the postproc bracket (aqo_time_groupby_reduce)"""
+    total = 0.0
+    for q in queries:
+        keys, aggs, _ = QUERIES[q]
+        specs = [(a[0],) + tuple(t[c] for c in a[1:]) for a in aggs]
+        sec, _ = impl.time_groupby_reduce([t[c] for c in keys], specs)
+        total += sec
+    return total
+
+
+def cpu_baseline(aq, args, queries, impl, note, check=True) -> dict:
+    """the reference build timed on one host core over the cpu_baseline table; with check=True the very
+    results it produced are compared with the GPU's on the same table (bench_verify.verify_vs_oracle)"""
+    import os
+    n = int(min(args.cpu_rows, args.rows))
+    t = host_table(args, n, queries)
+    out = {}
+    if check:
+        import bench_verify as bv
+        rep = {}
+        try:
+            sec = bv.verify_vs_oracle(aq, impl, t, queries, QUERIES, rep)
+            out["oracle_parity"] = {"status": f"ok ({len(queries)} queries, {n:.0e} rows, bit-exact ints/order, fp64 <= {bv.FP_RTOL_ORACLE})",
+                                    "kind": impl.kind, "per_query": rep}
+        except bv.VerifyError as e:
+            out["oracle_parity"] = {"status": f"{e}"[:500], "kind": impl.kind}
+            sec = cpu_step(impl, t, queries)
+    else:
+        sec = cpu_step(impl, t, queries)
+    out.update({"value": len(queries) * n / sec, "unit": "rows/s", "cores": 1,
+                "kind": "reference" if impl.kind == "reference" else "port",
+                "sample": f"{table_name(args, n)} {queries[0]}-{queries[-1]} once ({sec:.1f} s), " + note,
+                "host_cores": os.cpu_count()})
+    return out
+
+
+def run_e2e(aq, args, table, runner, queries, n_total) -> dict:
+    """End to end with HOST buffers: the table lives in pinned host memory (the MonetDB-owned buffers of
+    the reference, server/monetdb_conn.cpp:203-224); a step ingests it into the HBM column store
+    (the 'C' cache message, server/server.cpp:552-583: one H2D copy per column), runs the queries on the
+    store and writes every result column back to pinned host memory.  H2D and D2H are inside the timed
+    region."""
+    L = aq.lib()
+    pinned, host = [], {}
+    for c, d in table.items():
+        pa = aq.PinnedArray(d.n, d.code)
+        if d.nbytes:
+            aq.check(L.aqgpu_col_download(ctypes.c_void_p(pa.ptr), ctypes.c_void_p(d.ptr), ctypes.c_size_t(d.nbytes)))
+        pinned.append(pa)
+        host[c] = pa
+    res_host = {}
+
+    def one_step():
+        bo = 0
+        for c, d in table.items():                 # ingest
+            aq.check(L.aqgpu_col_upload(ctypes.c_void_p(d.ptr), ctypes.c_void_p(host[c].ptr), ctypes.c_size_t(d.nbytes)))
+        ngs = {}
+        for q in queries:
+            ng = ngs[q] = runner.run(q)
+            for i, col in enumerate(runner.result_columns(q)):     # write-back
+                nb = ng * col.itemsize
+                key = (q, i)
+                if key not in res_host or res_host[key].n * res_host[key].itemsize < nb:
+                    if key in res_host:
+                        res_host[key].free()
+                    res_host[key] = aq.PinnedArray(max(ng, 1), col.code)
+                    res_host[key].itemsize = col.itemsize
+                    pinned.append(res_host[key])
+                if nb:
+                    aq.check(L.aqgpu_col_download(ctypes.c_void_p(res_host[key].ptr), ctypes.c_void_p(col.ptr), ctypes.c_size_t(nb)))
+                bo += nb
+        return ngs, bo
+
+    one_step()                                     # warm-up (also sizes the pinned result buffers)
+    aq.sync()
+    t0 = time.perf_counter()
+    aq.timer_begin()
+    for _ in range(args.e2e_steps):
+        ngs, bo = one_step()
+    ms = aq.timer_end()
+    wall = time.perf_counter() - t0
+    bi = sum(d.nbytes for d in table.values())
+    out = {"value": len(queries) * n_total / (ms * 1e-3 / args.e2e_steps), "unit": "rows/s",
+           "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo, "steps": args.e2e_steps,
+           "ms_per_step": ms / args.e2e_steps, "wall_s_per_step": wall / args.e2e_steps,
+           "host_memory": "pinned (aqgpu_host_alloc)",
+           "path": "ingest every column once per step (H2D) -> queries on the HBM store -> every result column D2H"}
+    for pa in pinned:
+        pa.free()
+    return out

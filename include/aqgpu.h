@@ -113,6 +113,11 @@ int aqgpu_col_alloc(size_t bytes, void** dptr);
 int aqgpu_col_free(void* dptr);
 int aqgpu_col_upload(void* dptr, const void* host, size_t bytes);
 int aqgpu_col_download(void* host, const void* dptr, size_t bytes);
+/* stream-ordered copies: return at once, complete in stream order (aqgpu_sync / the next synchronous call) */
+int aqgpu_col_upload_async(void* dptr, const void* pinned_host, size_t bytes);
+int aqgpu_col_download_async(void* pinned_host, const void* dptr, size_t bytes);
+/* Returns the unused memory of the library's stream-ordered pool to the device (synchronises). */
+int aqgpu_trim_pool(void);
 int aqgpu_host_alloc(size_t bytes, void** hptr);      /* pinned host memory for staging */
 int aqgpu_host_free(void* hptr);
 /* 1 if p points into device memory (a column of the HBM store), 0 for host memory. */
@@ -159,6 +164,24 @@ int aqgpu_groupby_agg(const void* const* keys, const int* key_types, int nkeys, 
                       int row_order, uint32_t groups_hint,
                       const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
                       void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups);
+
+/* Same computation with the result columns ALLOCATED BY THE LIBRARY in HBM once the number of groups is
+ * known -- the order of events of the generated code itself: group build, then col.resize(g.size), then the
+ * per-group loop (engine/ast.py:681-701, 720-790).  The caller passes no capacities; key_min / key_max /
+ * groups_hint may all be 0 / NULL, in which case the library samples the key columns (strided, ~1M rows)
+ * inside this call to choose between its low-cardinality, partitioned and groups ~ rows paths; everything it
+ * speculates from the sample is verified by the scan itself.  aggs[a].out is ignored.                      */
+typedef struct aqgpu_result aqgpu_result_t;
+int aqgpu_groupby_run(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
+                      const int64_t* key_min, const int64_t* key_max,
+                      int row_order, uint32_t groups_hint,
+                      const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out);
+int aqgpu_result_size(const aqgpu_result_t* r, uint32_t* ngroups);
+/* device pointers to ngroups cells each (owned by the result; valid until aqgpu_result_free) */
+int aqgpu_result_key(const aqgpu_result_t* r, int k, void** dptr, int* dtype);
+int aqgpu_result_agg(const aqgpu_result_t* r, int a, void** dptr, int* dtype);
+int aqgpu_result_first_row(const aqgpu_result_t* r, uint32_t** dptr);
+int aqgpu_result_free(aqgpu_result_t* r);
 
 /* ---- group handle: ids, row lists, per-group vectors ----------------------------------------
  * aqgpu_groupby_build replaces HashTableFactory<...>::get(cols...) / AQHashTable (server/hasher.h:

@@ -134,7 +134,7 @@ class Oracle:
         return out
 
     # -- the postproc_time bracket -----------------------------------------------------------
-    def time_groupby_reduce(self, keys, aggs):
+    def time_groupby_reduce(self, keys, aggs, want_outs=False):
         """aggs: list of (op, v[, v2]).  Returns (seconds, ngroups)."""
         keys = [np.ascontiguousarray(k) for k in keys]
         n = len(keys[0])
@@ -158,12 +158,28 @@ class Oracle:
             if len(agg) > 2 and agg[2] is not None:
                 v2 = np.ascontiguousarray(agg[2]); keep.append(v2)
                 vals2[a] = v2.ctypes.data
+        outs_p, outs = None, []
+        if want_outs:
+            outs_p = (ctypes.c_void_p * max(na, 1))()
+            for a in range(na):
+                ot = self.lib.aqo_reduce_out_type(ops[a], vts[a])
+                if ot < 0:
+                    raise RuntimeError(f"unsupported reduce op={ops[a]} vtype={vts[a]}")
+                o = np.zeros((n, 2), np.int64) if ot == INT128 else np.zeros(n, _CODE2NP[ot])
+                outs.append(o)
+                outs_p[a] = o.ctypes.data
         ng = ctypes.c_uint32(0)
         ns = self.lib.aqo_time_groupby_reduce(kp, kt, len(keys), ctypes.c_uint32(n), na, ops, vts,
-                                              vals, vals2, None, ctypes.byref(ng))
+                                              vals, vals2, outs_p, ctypes.byref(ng))
         if ns < 0:
             raise RuntimeError(f"aqo_time_groupby_reduce rc={ns}")
+        if want_outs:
+            return ns * 1e-9, ng.value, [o[: ng.value] for o in outs]
         return ns * 1e-9, ng.value
+
+    def time_groupby_reduce_out(self, keys, aggs):
+        """as time_groupby_reduce, also returning the aggregate columns (first-appearance group order)"""
+        return self.time_groupby_reduce(keys, aggs, want_outs=True)
 
 
 def load_port(build_if_missing: bool = True) -> Oracle:

@@ -162,8 +162,16 @@ struct OutSink {
 
 // Sampling planner + the fast paths it can choose (plan.cu): low-cardinality direct tables (lc.cu) and the
 // fingerprint-partitioned path for groups ~ rows (hcfp.cu).  *used = false: fall through to hash_aggregate.
+// AQGPU_DISABLE=lc,hcfp,plan,smem,part,hc switches paths off at run time (A/B measurements, fault isolation)
+bool path_disabled(const char* name);
+struct PlanHints {                        // what the generic paths get when the planner declines
+    uint32_t groups_hint = 0;
+    bool have_bounds = false;
+    int64_t kmin[MAX_KEY_COLS], kmax[MAX_KEY_COLS];
+};
 int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max,
-                      uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used);
+                      uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used,
+                      PlanHints* hints_out);
 
 // Result of the hash phase, consumed by emit / handle construction.
 struct HashResult {
@@ -443,13 +451,9 @@ __device__ __forceinline__ void acc_global_row(const AccOp& o, unsigned long lon
     default: break;
     }
 }
-// the cell of accumulator o after exactly ONE row (a one-row group): identity (+) that row, no atomics
-__device__ __forceinline__ unsigned long long acc_single_row(const AccOp& o, uint32_t row) {
-    if (o.kind == ACC_COUNT) return 1ull;
-    if (o.kind == ACC_MAXROW) return (unsigned long long)row;
-    if (o.kind == ACC_TOP2ROW) return top2_key(o.xform, row) << 32;
-    long long xi = 0; double xd = 0.0;
-    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
+// x of accumulator o for ONE row (same values acc_inputs produces for it): integer image xi, double image xd
+__device__ __forceinline__ void acc_row_x(const AccOp& o, uint32_t row, long long& xi, double& xd) {
+    xi = 0; xd = 0.0;
     auto ld = [&](const void* v, long long& i, double& d, float& f) {
         i = 0; d = 0.0; f = 0.f;
         switch (o.vtype) {
@@ -467,6 +471,15 @@ __device__ __forceinline__ unsigned long long acc_single_row(const AccOp& o, uin
         xi = i1 * i2;
         xd = o.vtype == AQ_FLOAT ? (double)__fmul_rn(f1, f2) : __dmul_rn(d1, d2);
     }
+}
+// the cell of accumulator o after exactly ONE row (a one-row group): identity (+) that row, no atomics
+__device__ __forceinline__ unsigned long long acc_single_row(const AccOp& o, uint32_t row) {
+    if (o.kind == ACC_COUNT) return 1ull;
+    if (o.kind == ACC_MAXROW) return (unsigned long long)row;
+    if (o.kind == ACC_TOP2ROW) return top2_key(o.xform, row) << 32;
+    long long xi = 0; double xd = 0.0;
+    const bool isint = (o.vtype == AQ_INT32 || o.vtype == AQ_INT64);
+    acc_row_x(o, row, xi, xd);
     switch (o.kind) {
     case ACC_ADD_I64: return (unsigned long long)xi;
     case ACC_ADD_F64: return (unsigned long long)__double_as_longlong(0.0 + (isint ? (double)xi : xd));

@@ -1,0 +1,523 @@
+// hcfp.cu -- group-by for groups ~ rows (h2o q10: six key columns, every row its own group): duplicate
+// detection by 64-bit fingerprint, partitioned so that every random access stays inside one SM.
+//
+// Replaces the reference's per-row hashtable_push / ht_postproc / gather / aggregate loops
+// (server/hasher.h:176-198, server/table.h:184-189, server/aggregations.h) for ANY key tuple (no bounds
+// needed: the columns are hashed, never packed).  A DRAM-resident table costs one random sector
+// read-modify-write per row (~2e10/s on B200, profiles/r01/microbench.txt); here the only per-row traffic
+// beyond the columns themselves is an 8-byte tuple (row id, 32-bit fingerprint) written and read twice:
+//
+//   k_fp_part1   rows -> tuples, split into P1 partitions by fingerprint bits.  A CTA sorts a tile of 8192
+//                tuples by partition in shared memory (histogram with returned ranks, scan, scatter) and
+//                writes every partition's run as whole 32-byte sectors (runs padded with invalid tuples, one
+//                L2 atomic per run reserves the space): DRAM sees full-sector, mostly full-line writes.
+//   k_fp_part2   the same split of every level-1 partition into P2 sub-partitions (~3800 tuples each).
+//   k_fp_agg     one CTA per final partition: a shared-memory table keyed by the fingerprint.  A fingerprint
+//                that is already present is verified against the key columns (gather of both rows' keys), so
+//                the result is exact whatever the hash does.  Rows that turn out to share their key tuple
+//                (rare by construction: the planner sends a query here only when its sample says groups ~
+//                rows) accumulate into a compact record list through global atomics; every other row writes
+//                NOTHING -- rflags[row] stays 0 = "first row of a one-row group".
+//   k_fp_emit    one pass in row order: a tile counts its first rows, gets the number of first rows before it
+//                by decoupled look-back, and every first row writes its keys (read where they lie, coalesced)
+//                and its aggregates (from its own values, or from its record) at gid = that rank: the
+//                insertion index m_values has in the reference (server/unordered_dense.h:1142-1146).
+#include "lc.cuh"
+#include "emit.cuh"
+#include <cmath>
+#include <cstring>
+
+namespace aq {
+
+constexpr int FP_THREADS = 1024;
+constexpr int FP_RPT = 8;                               // tuples per thread and tile
+constexpr int FP_T = FP_THREADS * FP_RPT;               // 8192
+constexpr int FP_PMAX = 1024;
+constexpr uint32_t FP_STAGE = FP_T + 3 * FP_PMAX;       // staged tuples incl. padding
+constexpr unsigned long long FP_INVALID = 0xffffffffffffffffULL;   // row = 0xffffffff
+constexpr uint32_t FP_NOPOS = 0xffffffffu;
+constexpr uint32_t FP_MEAN = 3800;                      // target tuples per final partition
+constexpr uint32_t FP_SLOTS = 8192;                     // table of k_fp_agg
+constexpr int FPA_THREADS = 512;
+constexpr int FPA_TPT = 10;                             // a final partition holds at most 5120 tuples
+
+struct FpSmem {
+    uint32_t hist[FP_PMAX];
+    uint32_t loff[FP_PMAX + 1];
+    uint32_t gpos[FP_PMAX];
+    uint32_t wsum[32];
+    uint32_t total;
+    unsigned short secp[FP_STAGE / 4];
+    alignas(16) unsigned long long stage[FP_STAGE];
+};
+
+__device__ __forceinline__ uint64_t fp_hash(const uint32_t* kw, int n) {
+    uint64_t h = 0x9e3779b97f4a7c15ULL;
+    for (int w = 0; w < n; ++w) { h = (h ^ kw[w]) * 0xff51afd7ed558ccdULL; h ^= h >> 32; }
+    h *= 0xc4ceb9fe1a85ec53ULL;
+    return h ^ (h >> 29);
+}
+
+// Sorts the CTA's tile (RPT tuples per thread, part[i] < P, valid bit i of vmask) by partition in shared
+// memory and appends every partition's run, padded to whole sectors, to its region out + p * cap.
+__device__ __forceinline__ void fp_tile_scatter(FpSmem& S, const unsigned long long (&tup)[FP_RPT], const uint32_t (&part)[FP_RPT],
+                                                uint32_t vmask, uint32_t P, uint32_t* __restrict__ cursor,
+                                                unsigned long long* __restrict__ out, uint32_t cap, uint32_t* __restrict__ flags) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    uint32_t pr[FP_RPT];
+#pragma unroll
+    for (int i = 0; i < FP_RPT; ++i) {
+        pr[i] = 0;
+        if (vmask & (1u << i)) pr[i] = (part[i] << 16) | atomicAdd(&S.hist[part[i]], 1u);
+    }
+    __syncthreads();
+    // ---- padded exclusive scan over the partitions (one per thread), space reservation, sector map
+    {
+        const uint32_t c = tid < P ? S.hist[tid] : 0u;
+        const uint32_t pc = (c + 3u) & ~3u;
+        uint32_t x = pc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= (uint32_t)d) x += y; }
+        if (lane == 31) S.wsum[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t v = S.wsum[lane], sc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, d); if (lane >= (uint32_t)d) sc += y; }
+            S.wsum[lane] = sc - v;
+            if (lane == 31) S.total = sc;
+        }
+        __syncthreads();
+        const uint32_t ex = S.wsum[wid] + x - pc;
+        if (tid < P) {
+            S.loff[tid] = ex;
+            uint32_t gp = FP_NOPOS;
+            if (pc) {
+                gp = atomicAdd(cursor + tid, pc);
+                if (gp + pc > cap) { gp = FP_NOPOS; atomicCAS(flags + FLAG_ABORT, 0u, 2u); }     // region full: not this path
+            }
+            S.gpos[tid] = gp;
+            for (uint32_t s = ex >> 2; s < (ex + pc) >> 2; ++s) S.secp[s] = (unsigned short)tid;
+            for (uint32_t i = c; i < pc; ++i) S.stage[ex + i] = FP_INVALID;
+            S.hist[tid] = 0u;                                   // ready for the next tile
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < FP_RPT; ++i)
+        if (vmask & (1u << i)) S.stage[S.loff[pr[i] >> 16] + (pr[i] & 0xffffu)] = tup[i];
+    __syncthreads();
+    // ---- copy out: one 32-byte sector per thread and step, consecutive threads = consecutive sectors
+    const uint32_t nsec = S.total >> 2;
+    for (uint32_t s = tid; s < nsec; s += FP_THREADS) {
+        const uint32_t p = S.secp[s];
+        const uint32_t gp = S.gpos[p];
+        if (gp == FP_NOPOS) continue;
+        const uint4* src = reinterpret_cast<const uint4*>(S.stage + size_t(s) * 4);
+        uint4* dst = reinterpret_cast<uint4*>(out + size_t(p) * cap + gp + (s * 4u - S.loff[p]));
+        const uint4 a = src[0], b = src[1];
+        dst[0] = a; dst[1] = b;
+    }
+    __syncthreads();
+}
+
+// ---- level 1: key columns -> (row, fingerprint) tuples in P1 partitions -------------------------------------
+__global__ void __launch_bounds__(FP_THREADS, 1)
+k_fp_part1(const KeySpec ks, const uint32_t nrows, const uint32_t P1, uint32_t* __restrict__ cursor,
+           unsigned long long* __restrict__ out, const uint32_t cap, uint32_t* __restrict__ flags) {
+    extern __shared__ __align__(16) unsigned char fp_sm[];
+    FpSmem& S = *reinterpret_cast<FpSmem*>(fp_sm);
+    for (uint32_t i = threadIdx.x; i < FP_PMAX; i += FP_THREADS) S.hist[i] = 0u;
+    __syncthreads();
+    const uint32_t ntiles = (nrows + FP_T - 1) / FP_T;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        unsigned long long tup[FP_RPT];
+        uint32_t part[FP_RPT];
+        uint32_t vmask = 0;
+        // two quads of consecutive rows per thread; the hash state of the eight rows lives in registers and the
+        // key words stream through it, two columns (four 128-bit loads) in flight at a time
+        uint64_t hs[FP_RPT];
+        uint32_t row0[2]; int cnt[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t q = tile * (FP_T / 4) + h * FP_THREADS + threadIdx.x;
+            row0[h] = q << 2;
+            cnt[h] = row0[h] < nrows ? (int)min(4u, nrows - row0[h]) : 0;
+        }
+#pragma unroll
+        for (int i = 0; i < FP_RPT; ++i) hs[i] = 0x9e3779b97f4a7c15ULL;
+#pragma unroll 2
+        for (int w = 0; w < ks.nwords; ++w) {
+            uint32_t kw[2][4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                kw[h][0] = kw[h][1] = kw[h][2] = kw[h][3] = 0u;
+                if (cnt[h] == 0) continue;
+                if (ks.stride[w] == 1) load4_b32(ks.base[w], row0[h], cnt[h], ks.vec_ok, kw[h]);
+                else {
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) if (r < cnt[h]) kw[h][r] = __ldg(ks.base[w] + size_t(row0[h] + r) * ks.stride[w]);
+                }
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    uint64_t x = (hs[h * 4 + r] ^ kw[h][r]) * 0xff51afd7ed558ccdULL;
+                    hs[h * 4 + r] = x ^ (x >> 32);
+                }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int i = h * 4 + r;
+                tup[i] = 0; part[i] = 0;
+                if (r >= cnt[h]) continue;
+                uint64_t hsh = hs[i] * 0xc4ceb9fe1a85ec53ULL;
+                hsh ^= hsh >> 29;
+                part[i] = __umulhi((uint32_t)(hsh >> 32), P1);
+                tup[i] = ((unsigned long long)(uint32_t)hsh << 32) | (unsigned long long)(row0[h] + r);
+                vmask |= 1u << i;
+            }
+        fp_tile_scatter(S, tup, part, vmask, P1, cursor, out, cap, flags);
+    }
+}
+
+// ---- level 2: every level-1 partition -> P2 sub-partitions ---------------------------------------------------
+__global__ void __launch_bounds__(FP_THREADS, 1)
+k_fp_part2(const unsigned long long* __restrict__ in, const uint32_t* __restrict__ cursor1, const uint32_t cap1,
+           const uint32_t P1, const uint32_t P2, uint32_t* __restrict__ cursor2, unsigned long long* __restrict__ out,
+           const uint32_t cap2, uint32_t* __restrict__ flags) {
+    extern __shared__ __align__(16) unsigned char fp_sm[];
+    FpSmem& S = *reinterpret_cast<FpSmem*>(fp_sm);
+    for (uint32_t i = threadIdx.x; i < FP_PMAX; i += FP_THREADS) S.hist[i] = 0u;
+    if (threadIdx.x == 0) S.total = *reinterpret_cast<volatile uint32_t*>(flags + FLAG_ABORT);
+    __syncthreads();
+    if (S.total) return;                                        // level 1 gave up (uniform: read once per CTA)
+    __syncthreads();
+    uint32_t tix = 0;                                           // running tile index over all level-1 partitions
+    for (uint32_t p1 = 0; p1 < P1; ++p1) {
+        const uint32_t n = min(__ldg(cursor1 + p1), cap1);
+        const uint32_t nt = (n + FP_T - 1) / FP_T;
+        uint32_t j = (blockIdx.x + gridDim.x - tix % gridDim.x) % gridDim.x;     // first tile of p1 that is mine
+        for (; j < nt; j += gridDim.x) {
+            const unsigned long long* src = in + size_t(p1) * cap1 + size_t(j) * FP_T;
+            const uint32_t left = n - j * FP_T;
+            unsigned long long tup[FP_RPT];
+            uint32_t part[FP_RPT];
+            uint32_t vmask = 0;
+#pragma unroll
+            for (int i = 0; i < FP_RPT / 2; ++i) {
+                const uint32_t idx = (i * FP_THREADS + threadIdx.x) * 2u;       // regions and caps are multiples of 4 tuples
+                uint4 v = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+                if (idx < left) v = *reinterpret_cast<const uint4*>(src + idx);
+                tup[2 * i] = (unsigned long long)v.x | ((unsigned long long)v.y << 32);
+                tup[2 * i + 1] = (unsigned long long)v.z | ((unsigned long long)v.w << 32);
+            }
+#pragma unroll
+            for (int i = 0; i < FP_RPT; ++i) {
+                part[i] = 0;
+                if ((uint32_t)tup[i] != 0xffffffffu) { part[i] = __umulhi((uint32_t)(tup[i] >> 32), P2); vmask |= 1u << i; }
+            }
+            fp_tile_scatter(S, tup, part, vmask, P2, cursor2 + size_t(p1) * P2, out + size_t(p1) * P2 * cap2, cap2, flags);
+        }
+        tix += nt;
+    }
+}
+
+// ---- level 3: per-partition duplicate detection ----------------------------------------------------------------
+struct FpAggArgs {
+    const unsigned long long* tuples;     // npart regions of cap tuples
+    const uint32_t* cursor;
+    uint32_t npart, cap;
+    unsigned char* rflags;                // nrows, zero-filled: 0 first row of a one-row group, 1 first row with a record, 2 not a first row
+    uint32_t* rec_of_row;                 // nrows, sparse: record index of a first row with a record
+    unsigned long long* rec;              // rec_cap records of nacc cells
+    uint32_t rec_cap;
+    uint32_t* nrec;
+    uint32_t* flags;
+};
+
+__global__ void __launch_bounds__(FPA_THREADS, 2)
+k_fp_agg(const KeySpec ks, const AccProg prog, const FpAggArgs A, const HcIdentity ident) {
+    extern __shared__ __align__(16) unsigned char fpa_sm[];
+    unsigned long long* const tab = reinterpret_cast<unsigned long long*>(fpa_sm);
+    uint32_t* const multi = reinterpret_cast<uint32_t*>(tab + FP_SLOTS);
+    __shared__ uint32_t s_abort;
+    if (threadIdx.x == 0) s_abort = *reinterpret_cast<volatile uint32_t*>(A.flags + FLAG_ABORT);
+    __syncthreads();
+    if (s_abort) return;
+    constexpr uint32_t mask = FP_SLOTS - 1;
+    for (uint32_t p = blockIdx.x; p < A.npart; p += gridDim.x) {
+        for (uint32_t i = threadIdx.x; i < FP_SLOTS; i += FPA_THREADS) tab[i] = FP_INVALID;
+        for (uint32_t i = threadIdx.x; i < FP_SLOTS / 32; i += FPA_THREADS) multi[i] = 0u;
+        const uint32_t n = min(__ldg(A.cursor + p), A.cap);
+        const unsigned long long* src = A.tuples + size_t(p) * A.cap;
+        unsigned long long tup[FPA_TPT];
+#pragma unroll
+        for (int j = 0; j < FPA_TPT; ++j) {
+            const uint32_t idx = j * FPA_THREADS + threadIdx.x;
+            tup[j] = idx < n ? __ldg(src + idx) : FP_INVALID;
+        }
+        __syncthreads();
+        uint32_t myslot[FPA_TPT];
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < FPA_TPT; ++j) {
+            myslot[j] = FP_NOPOS;
+            const uint32_t row = (uint32_t)tup[j];
+            if (row == 0xffffffffu) continue;
+            const uint32_t fp = (uint32_t)(tup[j] >> 32);
+            const unsigned long long mine = tup[j];
+            uint32_t s = (fp * 0x9E3779B1u) >> 19;                 // 13 bits
+            for (uint32_t step = 0; step < FP_SLOTS; ++step) {
+                unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(tab + s);
+                if (cur == FP_INVALID) {
+                    cur = atomicCAS(tab + s, FP_INVALID, mine);
+                    if (cur == FP_INVALID) { myslot[j] = s; break; }
+                }
+                if ((uint32_t)(cur >> 32) == fp && keys_equal(ks, row, (uint32_t)cur)) {
+                    atomicMin(tab + s, mine);                         // same fingerprint: orders by row
+                    atomicOr(multi + (s >> 5), 1u << (s & 31u));
+                    myslot[j] = s; any = true; break;
+                }
+                s = (s + 1u) & mask;
+            }
+        }
+        // ---- groups with more than one row (rare): records through global atomics
+        if (__syncthreads_or(any ? 1 : 0)) {
+            uint32_t role[FPA_TPT];                                // 0 none, 1 first row of a multi-row group, 2 other row of one
+#pragma unroll
+            for (int j = 0; j < FPA_TPT; ++j) {
+                role[j] = 0;
+                const uint32_t s = myslot[j];
+                if (s == FP_NOPOS || !((multi[s >> 5] >> (s & 31u)) & 1u)) continue;
+                role[j] = (uint32_t)tab[s] == (uint32_t)tup[j] ? 1u : 2u;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < FPA_TPT; ++j) {
+                if (role[j] != 1u) continue;
+                const uint32_t ridx = atomicAdd(A.nrec, 1u);
+                const uint32_t row = (uint32_t)tup[j];
+                if (ridx < A.rec_cap) {
+                    for (int a = 0; a < prog.n; ++a) A.rec[size_t(ridx) * prog.n + a] = ident.w[a];
+                    A.rec_of_row[row] = ridx;
+                    A.rflags[row] = 1;
+                } else {
+                    atomicCAS(A.flags + FLAG_ABORT, 0u, 2u);           // more duplicated groups than this path provides for
+                }
+                tab[myslot[j]] = (unsigned long long)ridx;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < FPA_TPT; ++j) {
+                if (role[j] == 0u) continue;
+                const uint32_t row = (uint32_t)tup[j];
+                const uint32_t ridx = (uint32_t)tab[myslot[j]];
+                if (role[j] == 2u) A.rflags[row] = 2;
+                if (ridx >= A.rec_cap) continue;
+                for (int a = 0; a < prog.n; ++a) {
+                    long long xi = 0; double xd = 0.0;
+                    if (acc_needs_value(prog.op[a])) acc_row_x(prog.op[a], row, xi, xd);
+                    acc_global_row(prog.op[a], A.rec + size_t(ridx) * prog.n + a, row, xi, xd);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---- emit: ranks by look-back, one pass in row order ----------------------------------------------------------
+constexpr int FPE_THREADS = 256;
+constexpr int FPE_ROWS = FPE_THREADS * 4;
+constexpr unsigned long long FPE_AGG = 1ull << 62, FPE_PREFIX = 2ull << 62, FPE_VAL = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(FPE_THREADS)
+k_fp_emit(const uint32_t nrows, const uint32_t ntiles, const unsigned char* __restrict__ rflags,
+          const uint32_t* __restrict__ rec_of_row, const unsigned long long* __restrict__ rec,
+          unsigned long long* __restrict__ tile_state, uint32_t* __restrict__ ticket,
+          const KeyOut ko, uint32_t* __restrict__ first_row_out, const EmitProg ep, const AccProg prog,
+          const uint32_t max_groups, uint32_t* __restrict__ flags) {
+    __shared__ uint32_t s_tile, s_excl, wcnt[4][FPE_THREADS / 32];
+    if (*reinterpret_cast<volatile uint32_t*>(flags + FLAG_ABORT)) return;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    constexpr int NW = FPE_THREADS / 32;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= ntiles) return;
+        const uint32_t base = tile * FPE_ROWS;
+        uint32_t fl[4], before[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t row = base + j * FPE_THREADS + threadIdx.x;
+            fl[j] = row < nrows ? (uint32_t)rflags[row] : 2u;
+            const uint32_t m = __ballot_sync(0xffffffffu, fl[j] != 2u);
+            before[j] = __popc(m & ((1u << lane) - 1u));
+            if (lane == 0) wcnt[j][wid] = __popc(m);
+        }
+        __syncthreads();
+        if (wid == 0) {
+            // exclusive scan of the 4 x NW warp counts (row order: j major, warp minor), then the look-back
+            const uint32_t v = lane < 4 * NW ? wcnt[lane / NW][lane % NW] : 0u;
+            uint32_t sc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, d); if (lane >= (uint32_t)d) sc += y; }
+            const uint32_t total = __shfl_sync(0xffffffffu, sc, 31);
+            if (lane < 4 * NW) wcnt[lane / NW][lane % NW] = sc - v;
+            volatile unsigned long long* st = tile_state;
+            if (lane == 0) st[tile] = (tile == 0 ? FPE_PREFIX : FPE_AGG) | total;
+            uint32_t excl = 0;
+            if (tile > 0) {
+                long long look = (long long)tile - 1;
+                for (;;) {
+                    const long long idx = look - lane;
+                    unsigned long long v2 = FPE_PREFIX;
+                    if (idx >= 0) { do { v2 = st[idx]; } while ((v2 >> 62) == 0); }
+                    const uint32_t pm = __ballot_sync(0xffffffffu, (v2 >> 62) == 2);
+                    const int first = pm ? __ffs(pm) - 1 : 32;
+                    uint32_t part = ((int)lane <= first) ? (uint32_t)(v2 & FPE_VAL) : 0u;
+#pragma unroll
+                    for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+                    excl += part;
+                    if (pm) break;
+                    look -= 32;
+                }
+                if (lane == 0) st[tile] = FPE_PREFIX | (unsigned long long)(excl + total);
+            }
+            if (lane == 0) {
+                s_excl = excl;
+                if (tile + 1 == ntiles) flags[FLAG_NGROUPS] = excl + total;
+            }
+        }
+        __syncthreads();
+        const uint32_t excl = s_excl;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (fl[j] == 2u) continue;
+            const uint32_t row = base + j * FPE_THREADS + threadIdx.x;
+            const uint32_t g = excl + wcnt[j][wid] + before[j];
+            if (g >= max_groups) continue;                         // the host reports the overflow
+            if (first_row_out) first_row_out[g] = row;
+            for (int k = 0; k < ko.n; ++k) {
+                if (!ko.dst[k]) continue;
+                if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[g] = ld_stream_u32(static_cast<const uint32_t*>(ko.src[k]) + row);
+                else static_cast<unsigned long long*>(ko.dst[k])[g] = static_cast<const unsigned long long*>(ko.src[k])[row];
+            }
+            unsigned long long one[1 + MAX_ACC];
+            const unsigned long long* cells = one;
+            if (fl[j] == 0u) {
+                for (int a = 0; a < prog.n; ++a) one[1 + a] = acc_single_row(prog.op[a], row);
+            } else {
+                cells = rec + size_t(rec_of_row[row]) * prog.n - 1;
+            }
+            for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], cells, g, row, ep.row_order);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host
+// ------------------------------------------------------------------------------------------------
+bool hcfp_qualifies(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st) {
+    (void)kc; (void)plan;
+    if (nrows < (1u << 21)) return false;
+    if (st.est_groups < 0.9 * (double)nrows) return false;
+    // the sample must itself be (nearly) duplicate free: S^2 / (2 G) collisions expected at G = 0.9 rows
+    return true;
+}
+
+static uint32_t region_cap(double mean, double runs) {
+    const double c = mean + 8.0 * std::sqrt(mean) + 1.5 * 1.25 * runs + 64.0;
+    return ((uint32_t)c + 3u) & ~3u;
+}
+
+int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used) {
+    Context& c = ctx();
+    *used = false;
+    KeySpec ks;
+    AQ_TRY(kc.make_spec(nullptr, nullptr, ks));
+    // ---- partitions
+    const double parts = std::ceil((double)nrows / FP_MEAN);
+    uint32_t P1, P2;
+    if (parts <= FP_PMAX) { P1 = (uint32_t)parts; P2 = 1; }
+    else {
+        P1 = (uint32_t)std::ceil(std::sqrt(parts));
+        if (P1 > FP_PMAX) return 0;                              // > 4e9 rows: not reachable with 32-bit row ids
+        P2 = (uint32_t)std::ceil(parts / P1);
+    }
+    if (P1 < 1) P1 = 1;
+    const double ntiles1 = std::ceil((double)nrows / FP_T);
+    const uint32_t cap1 = region_cap((double)nrows / P1, ntiles1);
+    const double tiles2 = std::ceil((double)cap1 / FP_T);       // tiles a level-1 partition is read in
+    const uint32_t cap2 = P2 > 1 ? region_cap((double)nrows / P1 / P2, tiles2) : cap1;
+    if (cap2 > (uint32_t)FPA_THREADS * FPA_TPT) return 0;
+    const uint32_t nfinal = P1 * P2;
+    DevBuf part1, part2, cur, rflags, rec_of_row, rec, state;
+    AQ_TRY(part1.alloc(size_t(P1) * cap1 * 8));
+    if (P2 > 1) AQ_TRY(part2.alloc(size_t(nfinal) * cap2 * 8));
+    AQ_TRY(cur.alloc_zero((size_t(P1) + nfinal + 4) * 4));
+    AQ_TRY(rflags.alloc_zero(size_t(nrows)));
+    AQ_TRY(rec_of_row.alloc(size_t(nrows) * 4));
+    const uint32_t rec_cap = std::max<uint32_t>(1u << 16, nrows / 16);
+    AQ_TRY(rec.alloc(size_t(rec_cap) * std::max(plan.n_acc, 1) * 8));
+    const uint32_t ntiles_e = (nrows + FPE_ROWS - 1) / FPE_ROWS;
+    AQ_TRY(state.alloc_zero(size_t(ntiles_e) * 8 + 8));
+    uint32_t* cursor1 = cur.as<uint32_t>();
+    uint32_t* cursor2 = cursor1 + P1;
+    uint32_t* nrec = cursor2 + nfinal;
+    AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
+    static bool attr_done = false;
+    if (!attr_done) {
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_part1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_part2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_agg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(size_t(FP_SLOTS) * 8 + FP_SLOTS / 8)));
+        attr_done = true;
+    }
+    AQ_LAUNCH(k_fp_part1, c.sm_count, FP_THREADS, sizeof(FpSmem), ks, nrows, P1, cursor1, part1.as<unsigned long long>(), cap1, c.d_flags);
+    const unsigned long long* fin = part1.as<unsigned long long>();
+    const uint32_t* fcur = cursor1;
+    if (P2 > 1) {
+        AQ_LAUNCH(k_fp_part2, c.sm_count, FP_THREADS, sizeof(FpSmem), part1.as<unsigned long long>(), cursor1, cap1, P1, P2, cursor2,
+                  part2.as<unsigned long long>(), cap2, c.d_flags);
+        fin = part2.as<unsigned long long>(); fcur = cursor2;
+    }
+    FpAggArgs A;
+    A.tuples = fin; A.cursor = fcur; A.npart = nfinal; A.cap = cap2;
+    A.rflags = rflags.as<unsigned char>(); A.rec_of_row = rec_of_row.as<uint32_t>();
+    A.rec = rec.as<unsigned long long>(); A.rec_cap = rec_cap; A.nrec = nrec; A.flags = c.d_flags;
+    HcIdentity ident;
+    for (int a = 0; a < MAX_ACC; ++a) ident.w[a] = 0ull;
+    for (int a = 0; a < plan.n_acc; ++a) {
+        if (plan.prog.op[a].kind == ACC_MIN_I64) ident.w[a] = 0x7fffffffffffffffULL;
+        if (plan.prog.op[a].kind == ACC_MAX_I64) ident.w[a] = 0x8000000000000000ULL;
+    }
+    const size_t agg_smem = size_t(FP_SLOTS) * 8 + FP_SLOTS / 8;
+    AQ_LAUNCH(k_fp_agg, (int)std::min<uint32_t>(nfinal, (uint32_t)c.sm_count * 2), FPA_THREADS, agg_smem, ks, plan.prog, A, ident);
+    // ---- emit (the kernel does nothing when an earlier stage gave up)
+    AQ_TRY(sink.prepare(sink.res ? nrows : sink.max_groups, plan));
+    KeyOut ko;
+    memset(&ko, 0, sizeof(ko));
+    ko.n = kc.n;
+    for (int k = 0; k < kc.n; ++k) { ko.src[k] = kc.col[k].d; ko.size[k] = (int)dtype_size(kc.type[k]); ko.dst[k] = sink.key_dst[k]; }
+    for (int a = 0; a < plan.emit.n; ++a) plan.emit.agg[a].out = sink.agg_dst[a];
+    unsigned long long* st = state.as<unsigned long long>();
+    AQ_LAUNCH(k_fp_emit, (int)std::min<uint64_t>(ntiles_e, uint64_t(c.sm_count) * 8), FPE_THREADS, 0, nrows, ntiles_e,
+              rflags.as<unsigned char>(), rec_of_row.as<uint32_t>(), rec.as<unsigned long long>(), st,
+              reinterpret_cast<uint32_t*>(st + ntiles_e), ko, sink.fr_dst, plan.emit, plan.prog, sink.cap, c.d_flags);
+    AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    if (c.h_flags[FLAG_ABORT] != 0) return 0;                     // a region or the record list overflowed: generic path
+    const uint32_t ng = c.h_flags[FLAG_NGROUPS];
+    if (ng > sink.cap) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.cap);
+    AQ_TRY(sink.finish(ng, plan));
+    *ngroups = ng;
+    *used = true;
+    return 0;
+}
+
+} // namespace aq

@@ -236,16 +236,6 @@ def run_b200(args, wl, queries):
     else:
         ngs_total = ngs
 
-    # ---- verification of what the timed loop left in HBM (outside the timed region)
-    verify = None
-    if not args.no_verify:
-        try:
-            verify = wl.verify(aq, comm, runner, table, queries, args, n_total, ngs)
-        except Exception as e:      # VerifyError or anything the checker tripped over: never report a number as verified
-            import traceback
-            traceback.print_exc()
-            verify = {"status": f"FAILED: {type(e).__name__}: {e}"[:600]}
-
     # ---- per-kernel / per-query breakdown (separate pass, CUDA events around every launch)
     aq.profile_enable(True)
     aq.profile_report()
@@ -260,6 +250,16 @@ def run_b200(args, wl, queries):
     aq.profile_tag("")
     prof = aq.profile_report()
     aq.profile_enable(False)
+    # ---- verification of what the timed loop left in HBM (outside the timed region)
+    verify = None
+    if not args.no_verify:
+        try:
+            verify = wl.verify(aq, comm, runner, table, queries, args, n_total, ngs)
+        except Exception as e:      # VerifyError or anything the checker tripped over: never report a number as verified
+            import traceback
+            traceback.print_exc()
+            verify = {"status": f"FAILED: {type(e).__name__}: {e}"[:600]}
+
     peak, peak_src = load_peaks()
     nrows_local = hi - lo
     top = max(prof.items(), key=lambda kv: kv[1][1]) if prof else None

@@ -374,3 +374,174 @@ def test_dist_partition_by_owner(gpu, comm1):
     for a in range(parts):
         for b in range(a + 1, parts):
             assert not (owners[a] & owners[b])                    # a key has exactly one owner
+
+
+# ---- round 2: planned paths (plan.cu -> lc.cu / hcfp.cu), no bounds, no hints ---------------------------
+def _lc_table(n, seed, ranges, neg=False):
+    rng = np.random.default_rng(seed)
+    t = {f"k{i}": (rng.integers(0, r, n) + (-7 if neg else 3)).astype(np.int32) for i, r in enumerate(ranges)}
+    t["v1"] = rng.integers(-50 if neg else 1, 60, n).astype(np.int32)
+    t["v2"] = rng.integers(1, 16, n).astype(np.int32)
+    t["f"] = np.round(rng.random(n) * 100, 6).astype(np.float32)
+    t["g"] = (rng.standard_normal(n) * 1000).astype(np.float32)        # signed floats, wide exponent spread
+    return t
+
+
+@pytest.mark.parametrize("n,ranges", [(4096, (7,)), (100_003, (100,)), (300_001, (100, 100)), (250_000, (13, 9, 11)),
+                                      (400_000, (150, 150)), (2_500_000, (100, 37))])
+def test_low_cardinality_direct_table(gpu, port, n, ranges):
+    """lc.cu: bulk-copy ring + direct shared-memory table, cluster split for fat tables, ragged tails"""
+    t = _lc_table(n, n, ranges, neg=(n % 2 == 1))
+    keys = [f"k{i}" for i in range(len(ranges))]
+    for aggs in ([("sum", "v1")], [("avg", "v1"), ("avg", "v2"), ("avg", "f")], [("stddev", "f")], [("corr", "v1", "v2")],
+                 [("sum", "g"), ("min", "g"), ("max", "g"), ("min", "v1"), ("max", "v1"), ("count",), ("var", "v1")],
+                 [("sum", "v1"), ("first", "f"), ("last", "v2")]):          # first / last: generic path
+        check_query_vs_oracle(gpu, port, t, keys, aggs)
+
+
+def test_low_cardinality_speculation_fails(gpu, port):
+    """a key the sample cannot see and a float the fixed point cannot hold: the scan notices, the query re-runs"""
+    n = 3_000_000
+    t = _lc_table(n, 5, (50,))
+    t["k0"][2_999_999] = 1_000_000                 # outside every sampled chunk's range
+    check_query_vs_oracle(gpu, port, t, ["k0"], [("sum", "v1"), ("avg", "f")])
+    t = _lc_table(n, 6, (50,))
+    t["f"][1_234_567] = np.float32(1e-30)          # 2^-100: below the fixed-point unit chosen from the sample
+    check_query_vs_oracle(gpu, port, t, ["k0"], [("sum", "f"), ("count",)])
+    t["f"][7] = np.float32(np.inf)
+    res = run_query(gpu, t, ["k0"], [("sum", "f")])
+    assert np.isinf(res.aggs[0]).sum() == 1
+
+
+def test_large_integer_sums_low_cardinality(gpu, port):
+    """values near the int32 limits and big products: spill words / two-word cells stay exact"""
+    n = 200_000
+    rng = np.random.default_rng(8)
+    t = {"k": rng.integers(0, 5, n).astype(np.int32), "v": rng.integers(-2**31, 2**31 - 1, n).astype(np.int32),
+         "w": rng.integers(-40_000, 40_000, n).astype(np.int32)}
+    check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "v"), ("min", "v"), ("max", "v")])
+    check_query_vs_oracle(gpu, port, t, ["k"], [("var", "w"), ("sum", "w")])
+
+
+@pytest.mark.parametrize("n", [2_200_000, 5_000_000])
+def test_groups_like_rows_fingerprint_path(gpu, port, n):
+    """hcfp.cu: all-distinct key tuples, a sprinkling of duplicates (records), 64-bit keys, one level and two"""
+    rng = np.random.default_rng(n)
+    t = {c: rng.integers(0, 1 << 30, n).astype(np.int32) for c in ("a", "b", "c")}
+    t["v"] = rng.integers(-50, 50, n).astype(np.int32); t["f"] = np.round(rng.random(n) * 100, 6).astype(np.float32)
+    t["k64"] = (t["a"].astype(np.int64) << 31) | t["b"].astype(np.int64)
+    aggs = [("sum", "f"), ("count",)]
+    check_query_vs_oracle(gpu, port, t, ["a", "b", "c"], aggs)
+    dup = rng.integers(0, n, n // 200)                                    # ~0.5 % of the rows repeat another row's key
+    for c in ("a", "b", "c"):
+        t[c][dup] = t[c][(dup * 13 + 5) % n]
+    t["k64"] = (t["a"].astype(np.int64) << 31) | t["b"].astype(np.int64)
+    check_query_vs_oracle(gpu, port, t, ["a", "b", "c"], aggs + [("min", "v"), ("first", "f"), ("sum", "v"), ("second", "v")])
+    check_query_vs_oracle(gpu, port, t, ["k64", "c"], [("sum", "v"), ("avg", "f"), ("max", "v")])
+
+
+def test_result_set_api(gpu, port):
+    """aqgpu_groupby_run: the library allocates the result columns; no capacities, bounds or hints"""
+    n, k = 700_000, 50
+    t = synth.h2o_table(n, k, seed=3, columns=["id1", "id3", "v1", "v3"])
+    d = {c: gpu.DeviceColumn.from_numpy(a) for c, a in t.items()}
+    for keys in (["id1"], ["id3"], ["id1", "id3"]):
+        q = gpu.AutoQuery([d[c] for c in keys], [("sum", d["v1"]), ("avg", d["v3"])], want_first_row=True)
+        for _ in range(2):
+            ng = q.run()
+            ngo, gid, off, perm = port.groupby([t[c] for c in keys])
+            assert ng == ngo
+            first = perm[off[1:] - 1]
+            assert_same(q.fr.numpy(ng), first.astype(np.uint32))
+            for i, c in enumerate(keys):
+                assert_same(q.kouts[i].numpy(ng), t[c][first])
+            assert_same(q.outs[0].numpy(ng), port.reduce("sum", t["v1"], off, perm, raw128=True))
+            assert_same(q.outs[1].numpy(ng), port.reduce("avg", t["v3"], off, perm))
+        q.free()
+    q = gpu.AutoQuery([np.zeros(0, np.int32)], [("count",)])
+    assert q.run() == 0
+
+
+# ---- BASELINE.json sizes against the C port ----------------------------------------------------------------
+def _check_h2o(gpu, port, n, k, queries):
+    from aquery2_b200 import h2o
+    cols = h2o.columns_of(queries)
+    t = synth.h2o_table(n, k, seed=42, columns=cols)
+    d = {c: gpu.DeviceColumn.from_numpy(a) for c, a in t.items()}
+    for q in queries:
+        keys, aggs, _ = h2o.QUERIES[q]
+        res = gpu.groupby_agg([d[c] for c in keys], [(a[0],) + tuple(d[c] for c in a[1:]) for a in aggs])
+        ng, gid, off, perm = port.groupby([t[c] for c in keys])
+        assert res.ngroups == ng, q
+        first = perm[off[1:] - 1]
+        assert_same(res.first_row, first.astype(np.uint32), f"{q} first_row")
+        for i, c in enumerate(keys):
+            assert_same(res.keys[i], t[c][first], f"{q} key {c}")
+        for a, agg in enumerate(aggs):
+            want = port.reduce(agg[0], t[agg[1]] if len(agg) > 1 else None, off, perm, v2=t[agg[2]] if len(agg) > 2 else None, raw128=True)
+            assert_same(res.aggs[a], want, f"{q} {agg}")
+    for c in d.values():
+        c.free()
+
+
+def test_h2o_config1_1e7_all_queries(gpu, port):
+    """BASELINE.json configs[0]: G1_1e7_1e2, q1-q10, the library on its own (no bounds, no hints)"""
+    from aquery2_b200 import h2o
+    _check_h2o(gpu, port, 10_000_000, 100, h2o.ORDER)
+
+
+def test_h2o_config2_1e8_size_dependent_paths(gpu, port):
+    """BASELINE.json configs[1] size: G1_1e8_1e2 -- one query per size-dependent path: direct table in a
+    cluster (q9), partitioned with 1e6 groups (q3), fingerprint-partitioned with two levels (q10)"""
+    _check_h2o(gpu, port, 100_000_000, 100, ["q9", "q3", "q10"])
+
+
+def test_generic_paths_at_1e8_without_planner(gpu, port, monkeypatch):
+    """the round-1 paths at BASELINE size, forced by switching the planner off: hash-partitioned aggregation
+    with bounds + hint (q5 shape), and the global-table path with nothing (q3 shape)"""
+    monkeypatch.setenv("AQGPU_DISABLE", "plan")
+    n, k = 100_000_000, 100
+    t = synth.h2o_table(n, k, seed=42, columns=["id6", "v1", "v3"])
+    d = {c: gpu.DeviceColumn.from_numpy(a) for c, a in t.items()}
+    ng, gid, off, perm = port.groupby([t["id6"]])
+    first = perm[off[1:] - 1]
+    want = [port.reduce("sum", t["v1"], off, perm, raw128=True), port.reduce("sum", t["v3"], off, perm), port.reduce("count", None, off, perm)]
+    for kw in (dict(key_bounds=[(1, n // k)], groups_hint=n // k), dict()):
+        res = gpu.groupby_agg([d["id6"]], [("sum", d["v1"]), ("sum", d["v3"]), ("count",)], **kw)
+        assert res.ngroups == ng
+        assert_same(res.first_row, first.astype(np.uint32))
+        for a in range(3):
+            assert_same(res.aggs[a], want[a], f"agg {a} {kw}")
+
+
+# ---- A4 / A10 helpers against numpy ------------------------------------------------------------------------
+def test_gather_and_elementwise_helpers(gpu, port):
+    n, nsym = 120_000, 700
+    t = synth.trade_table(n, nsym, seed=4)
+    h = gpu.Groups([t["sym"]])
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    import ctypes
+    L = gpu.lib()
+    for v in (t["price"], t["price"].astype(np.float64) / 3, t["quantity"].astype(np.int64) * 1_000_003):
+        out = np.empty_like(v)
+        gpu.check(L.aqgpu_group_gather(h.h, gpu.NP2CODE[v.dtype], v.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p)))
+        assert_same(out, v[perm], "gather col[vecs[g]]")                  # server/table.h:184-189
+    h.free()
+    assert gpu.col_minmax(t["price"]) == (int(t["price"].min()), int(t["price"].max()))
+    big = t["quantity"].astype(np.int64) * -3_000_000_007
+    assert gpu.col_minmax(big) == (int(big.min()), int(big.max()))
+    a, b = t["price"], t["quantity"]
+    for x, y in ((a, b), (a.astype(np.float32), b.astype(np.float32)), (a.astype(np.float64), b.astype(np.float64)), (a.astype(np.int64), b.astype(np.int64))):
+        o = np.empty_like(x)
+        gpu.vec_sub(gpu.DeviceColumn.from_numpy(x), gpu.DeviceColumn.from_numpy(y), dc := gpu.DeviceColumn(n, gpu.NP2CODE[x.dtype]), n, gpu.NP2CODE[x.dtype])
+        assert_same(dc.numpy(), x - y, "vec_sub")
+    x = np.linspace(-1, 1, 1001)
+    dx, do = gpu.DeviceColumn.from_numpy(x), gpu.DeviceColumn(1001, gpu.DOUBLE)
+    gpu.vec_pow(dx, 2.0, do, 1001)
+    assert_same(do.numpy(), np.power(x, 2.0), "vec_pow")
+    s = np.arange(1, 1001, dtype=np.float64) * 1.5
+    cnt = np.arange(1, 1001, dtype=np.uint32)
+    o = np.empty(1000)
+    gpu.check(L.aqgpu_avg_finalize(gpu.DOUBLE, s.ctypes.data_as(ctypes.c_void_p), cnt.ctypes.data_as(ctypes.c_void_p),
+                                   o.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(1000)))
+    assert_same(o, s / cnt, "avg_finalize")

@@ -73,19 +73,33 @@ void profile_post();
 // ------------------------------------------------------------------------------------------------
 // stream-ordered device temporaries (cudaMallocAsync pool, release threshold = never)
 // ------------------------------------------------------------------------------------------------
+// Scratch of one API call comes from a device ARENA (the device counterpart of the reference's per-query
+// ScratchSpace bump allocator, server/gc.h:7-35 / server/libaquery.cpp:464-494): one block that grows to the
+// largest call seen and is handed out by bumping an offset, reset when the outermost ArenaScope closes.
+// Work is stream-ordered, so the next call may reuse the bytes at once.  Buffers that outlive a call (result
+// sets, group handles) are marked persistent and come from the stream-ordered pool (cudaMallocAsync).
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    bool persistent = false;
+    bool from_arena = false;
     DevBuf() = default;
+    explicit DevBuf(bool persist) : persistent(persist) {}
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
-    DevBuf& operator=(DevBuf&& o) noexcept { release(); p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; return *this; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), persistent(o.persistent), from_arena(o.from_arena) { o.p = nullptr; o.bytes = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        release(); p = o.p; bytes = o.bytes; persistent = o.persistent; from_arena = o.from_arena; o.p = nullptr; o.bytes = 0; return *this;
+    }
     ~DevBuf() { release(); }
     int alloc(size_t n);                 // uninitialised
     int alloc_zero(size_t n);
     void release();
     template <class T> T* as() const { return static_cast<T*>(p); }
+};
+struct ArenaScope {                      // opened by the entry points of the C ABI that allocate scratch
+    ArenaScope();
+    ~ArenaScope();
 };
 
 bool is_device_ptr(const void* p);

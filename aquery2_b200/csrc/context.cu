@@ -28,15 +28,60 @@ int fail(const char* fmt, ...) {
     return -1;
 }
 
+// ---- scratch arena ---------------------------------------------------------------------------------
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0, off = 0;
+    size_t overflow = 0, need = 0;       // bytes served by the pool in this scope / high-water mark of the scope
+    int depth = 0;
+    std::vector<void*> spilled;
+};
+static Arena g_arena;
+static constexpr size_t ARENA_ALIGN = 256;
+
+ArenaScope::ArenaScope() { ++g_arena.depth; }
+ArenaScope::~ArenaScope() {
+    Arena& a = g_arena;
+    if (--a.depth > 0) return;
+    for (void* q : a.spilled) cudaFreeAsync(q, ctx().stream);
+    a.spilled.clear();
+    if (a.need > a.cap) {                // grow to what this call needed (stream-ordered: earlier work still sees the old block)
+        if (a.base) cudaFreeAsync(a.base, ctx().stream);
+        a.base = nullptr; a.cap = 0;
+        const size_t want = a.need + a.need / 16 + (size_t(1) << 20);
+        void* q = nullptr;
+        if (cudaMallocAsync(&q, want, ctx().stream) == cudaSuccess) { a.base = static_cast<char*>(q); a.cap = want; }
+        else cudaGetLastError();
+    }
+    a.off = 0; a.overflow = 0; a.need = 0;
+}
+
 int DevBuf::alloc(size_t n) {
     release();
     if (n == 0) n = 16;
+    Arena& a = g_arena;
+    if (!persistent && a.depth > 0) {
+        const size_t m = (n + ARENA_ALIGN - 1) & ~(ARENA_ALIGN - 1);
+        if (a.off + m <= a.cap) {
+            p = a.base + a.off; a.off += m; bytes = n; from_arena = true;
+            if (a.off + a.overflow > a.need) a.need = a.off + a.overflow;
+            return 0;
+        }
+        // does not fit (first call of this size): serve from the pool now, grow the arena when the scope closes
+        cudaError_t e = cudaMallocAsync(&p, n, ctx().stream);
+        if (e != cudaSuccess) { p = nullptr; return fail("cudaMallocAsync(%zu bytes): %s", n, cudaGetErrorString(e)); }
+        a.spilled.push_back(p);
+        a.overflow += m;
+        if (a.off + a.overflow > a.need) a.need = a.off + a.overflow;
+        bytes = n; from_arena = true;    // owned by the scope
+        return 0;
+    }
     cudaError_t e = cudaMallocAsync(&p, n, ctx().stream);
     if (e != cudaSuccess) {
         p = nullptr;
         return fail("cudaMallocAsync(%zu bytes): %s", n, cudaGetErrorString(e));
     }
-    bytes = n;
+    bytes = n; from_arena = false;
     return 0;
 }
 
@@ -47,9 +92,18 @@ int DevBuf::alloc_zero(size_t n) {
 }
 
 void DevBuf::release() {
-    if (p) cudaFreeAsync(p, ctx().stream);
+    if (p) {
+        if (from_arena) {                // bump allocator: only the top block can be handed back
+            Arena& a = g_arena;
+            const size_t m = (bytes + ARENA_ALIGN - 1) & ~(ARENA_ALIGN - 1);
+            if (a.base && static_cast<char*>(p) + m == a.base + a.off) a.off -= m;
+        } else {
+            cudaFreeAsync(p, ctx().stream);
+        }
+    }
     p = nullptr;
     bytes = 0;
+    from_arena = false;
 }
 
 // ---- per-kernel event timing ---------------------------------------------------------------------
@@ -284,6 +338,7 @@ int aqgpu_col_download_async(void* host, const void* dptr, size_t bytes) {
 
 int aqgpu_trim_pool(void) {
     AQ_REQUIRE_INIT();
+    if (g_arena.depth == 0 && g_arena.base) { cudaFreeAsync(g_arena.base, g_ctx.stream); g_arena.base = nullptr; g_arena.cap = 0; g_arena.off = 0; }
     AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
     cudaMemPool_t pool;
     AQ_CUDA(cudaDeviceGetDefaultMemPool(&pool, g_ctx.device));

@@ -748,6 +748,11 @@ struct aqgpu_result {
     DevBuf keys[MAX_KEY_COLS];
     DevBuf aggs[MAX_AGGS];
     DevBuf first_row;
+    aqgpu_result() {                      // result columns outlive the call: never from the scratch arena
+        for (auto& b : keys) b.persistent = true;
+        for (auto& b : aggs) b.persistent = true;
+        first_row.persistent = true;
+    }
 };
 
 namespace aq {
@@ -898,6 +903,7 @@ extern "C" int aqgpu_groupby_agg(const void* const* keys, const int* key_types, 
                                  const aqgpu_agg_t* aggs, int n_aggs, uint32_t max_groups,
                                  void* const* out_keys, uint32_t* out_first_row, uint32_t* ngroups) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     OutSink sink;
     sink.aggs = aggs; sink.out_keys = out_keys; sink.out_first_row = out_first_row; sink.max_groups = max_groups;
     return groupby_core(keys, key_types, nkeys, nrows, key_min, key_max, row_order, groups_hint, aggs, n_aggs, sink, ngroups);
@@ -908,6 +914,7 @@ extern "C" int aqgpu_groupby_run(const void* const* keys, const int* key_types, 
                                  int row_order, uint32_t groups_hint,
                                  const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!out) return fail("null result pointer");
     *out = nullptr;
     aqgpu_result* r = new aqgpu_result();

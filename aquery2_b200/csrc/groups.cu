@@ -21,6 +21,10 @@ struct aqgpu_groups {
     DevBuf perm;                    // nrows: "mapbase"
     DevBuf segstart;                // nrows: first CSR position of the owning group
     bool has_offsets = false, has_perm = false, has_segstart = false;
+    aqgpu_groups() {                // the handle outlives the call that builds it: pool memory, not the scratch arena
+        for (auto& b : keys) b.persistent = true;
+        for (DevBuf* b : {&first_row, &last_row, &counts, &gid, &offsets, &perm, &segstart}) b->persistent = true;
+    }
 };
 
 namespace aq {
@@ -121,6 +125,7 @@ int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys
                         const int64_t* key_min, const int64_t* key_max,
                         int row_order, uint32_t groups_hint, aqgpu_groups_t** out) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!out) return fail("null handle pointer");
     *out = nullptr;
     if (row_order != AQ_ROWS_DESC && row_order != AQ_ROWS_ASC) return fail("bad row_order %d", row_order);
@@ -228,6 +233,7 @@ int aqgpu_groups_device_views(aqgpu_groups_t* g, const uint32_t** d_gid, const u
 int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, const void* v2,
                        int out_type, void* out) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!g) return fail("null handle");
     if (g->nrows == 0) return 0;
     const void* keys[1] = { g->gid.p };
@@ -243,6 +249,7 @@ int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, cons
 
 int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const void* v, int out_type, void* out) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!g) return fail("null handle");
     if (g->nrows == 0) return 0;
     if (!is_val_type(vtype)) return fail("unsupported value dtype %d", vtype);
@@ -266,6 +273,7 @@ int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const voi
 
 int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!g) return fail("null handle");
     if (g->nrows == 0) return 0;
     const size_t esz = dtype_size(vtype);
@@ -285,6 +293,7 @@ int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out) {
 int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int* col_types,
                           const int* desc, int ncols) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!g || !cols || !col_types || ncols < 1) return fail("bad order_by arguments");
     if (g->nrows == 0) return 0;
     AQ_TRY(ensure_perm(g));
@@ -337,6 +346,7 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
 
 int aqgpu_col_minmax(int dtype, const void* col, uint32_t nrows, int64_t* out_min, int64_t* out_max) {
     AQ_REQUIRE_INIT();
+    ArenaScope scope;
     if (!out_min || !out_max) return fail("null output");
     if (nrows == 0) { *out_min = 0; *out_max = -1; return 0; }
     const size_t sz = dtype_size(dtype);

@@ -154,6 +154,7 @@ def verify_query(torch, aq, q, keys, aggs, epilogue, table, prepared, extra, ng,
     """table: {name: DeviceColumn}; prepared: the PreparedQuery the timed loop ran (its outs / kouts hold
     the last step's result); ng: its group count."""
     nrows = table[keys[0]].n
+    aq.sync()
     kt = [tview(torch, aq, table[c]) for c in keys]
     # ---- 1. independent group count
     want_ng = distinct_count(torch, kt, key_ranges)
@@ -161,6 +162,7 @@ def verify_query(torch, aq, q, keys, aggs, epilogue, table, prepared, extra, ng,
     # ---- 2. same keys, (count, first_row): grouping machinery
     chk = aq.groupby_agg([table[c] for c in keys], [("count",)], device_out=True, want_keys=True, want_first_row=True,
                          max_groups=max(ng, 1))
+    aq.sync()      # the library runs on its own stream: torch (another stream) must not read before it is done
     _need(chk.ngroups == ng, f"{q}: count/first_row call saw {chk.ngroups} groups, timed call {ng}")
     cnt = tview(torch, aq, chk.aggs[0], ng)
     fr = tview(torch, aq, chk.first_row, ng)

@@ -39,7 +39,7 @@ EXPORTS = [
     "aqgpu_sync", "aqgpu_launch_count", "aqgpu_timer_begin", "aqgpu_timer_end",
     "aqgpu_profile_enable", "aqgpu_profile_tag", "aqgpu_profile_report",
     "aqgpu_col_alloc", "aqgpu_col_free", "aqgpu_col_upload", "aqgpu_col_download",
-    "aqgpu_host_alloc", "aqgpu_host_free", "aqgpu_ptr_is_device", "aqgpu_group_gather",
+    "aqgpu_host_alloc", "aqgpu_host_free", "aqgpu_ptr_is_device", "aqgpu_group_gather", "aqgpu_group_window",
     "aqgpu_reduce_out_type", "aqgpu_scan_out_type", "aqgpu_dtype_size",
     "aqgpu_groupby_agg", "aqgpu_groupby_build", "aqgpu_col_minmax", "aqgpu_groups_free",
     "aqgpu_groups_size", "aqgpu_groups_keys", "aqgpu_groups_first_row", "aqgpu_groups_gid",
@@ -54,6 +54,12 @@ EXPORTS = [
 
 class AqgpuError(RuntimeError):
     pass
+
+
+class WindowSpec(ctypes.Structure):
+    """struct aqgpu_window (include/aqgpu.h)"""
+    _fields_ = [("op", ctypes.c_int), ("w", ctypes.c_uint32), ("vtype", ctypes.c_int), ("v", ctypes.c_void_p),
+                ("minus_from_v", ctypes.c_int), ("reduce", ctypes.c_int), ("out_type", ctypes.c_int), ("out", ctypes.c_void_p)]
 
 
 class AggSpec(ctypes.Structure):
@@ -379,6 +385,30 @@ class Groups:
         check(lib().aqgpu_group_scan(self.h, op, ctypes.c_uint32(w), vt, ctypes.c_void_p(vp), ot,
                                      ctypes.c_void_p(_out_ptr(ob))))
         return ob
+
+    def window(self, exprs, device_out: bool = False):
+        """Several vector-valued expressions in one call (aqgpu_group_window).  exprs: tuples
+        (op, v[, w[, minus_from_v[, reduce]]]) with op a scan name, reduce None / "max" / "min".
+        Returns one output per expression: nrows cells in CSR order, or ngroups cells when reduced."""
+        n = len(exprs)
+        arr = (WindowSpec * n)()
+        keep, outs = [], []
+        for i, e in enumerate(exprs):
+            op = SCAN_NAMES[e[0]] if isinstance(e[0], str) else int(e[0])
+            vp, vt, k = _col(e[1])
+            keep.append(k)
+            w = int(e[2]) if len(e) > 2 and e[2] else 0
+            minus = int(bool(e[3])) if len(e) > 3 else 0
+            red = e[4] if len(e) > 4 else None
+            red = -1 if red is None else (REDUCE_NAMES[red] if isinstance(red, str) else int(red))
+            ot = scan_out_type(op, vt)
+            if ot < 0:
+                raise AqgpuError(f"unsupported scan op={op} on dtype={vt}")
+            ob = _out_buf(ot, self.ngroups if red >= 0 else self.nrows, device_out)
+            outs.append(ob)
+            arr[i] = WindowSpec(op, w, vt, vp, minus, red, ot, _out_ptr(ob))
+        check(lib().aqgpu_group_window(self.h, arr, n))
+        return outs
 
     def order_by(self, cols, desc=None):
         nc = len(cols)

@@ -10,14 +10,18 @@
 //           the word; the carry / borrow and the high bits of |x| go to the spill (an L2 atomic that small
 //           values almost never execute).  Exact for any int64 x.
 //   ISUM2   2 words (lo, hi): for columns whose sampled magnitudes make the spill frequent.
-//   FX      float32 values summed EXACTLY in 128-bit fixed point: unit 2^(B-150), word 0 (bits 0..31) in a
-//           global spill, words 1..3 in shared memory (word 3 biased).  The 24-bit mantissa of a value lands
-//           in at most two adjacent words; carries ripple upwards through the returned old values.  B is
-//           chosen from the sampled maximum exponent so that typical mantissas sit in word 2; a value that
-//           cannot be represented (below the unit with non-zero low bits, above bit 94, inf / nan) raises
-//           FLAG_ABORT = 4 and the query re-runs on the generic path.  The sum is rounded ONCE, at the end
-//           (the reference rounds after every addition, aggregations.h:19-27 in double: both are within
-//           1e-12 of each other, the exact one is the more accurate).
+//   FX      float32 values summed EXACTLY in fixed point.  The global record holds a 128-bit sum in units of
+//           2^(B-150) (B chosen from the sampled maximum exponent so that a value with that exponent has its
+//           mantissa LSB at bit FX_S_TOP).  The shared cell is 2 words: a 64-bit sum in units 2^Q times
+//           coarser (Q = FX_S_TOP - R), which holds every value whose mantissa LSB lies within R bits below
+//           the sampled maximum -- one returning add for the low word (carry) and one plain add for the high
+//           word, no carry chain.  R = 39 - log2(rows one CTA can see), so the 64-bit cell cannot overflow.
+//           Values outside that window (tiny ones with low mantissa bits set, ones above the sampled maximum)
+//           are added straight to the 128-bit global sum; a value that has no exact image at all (below the
+//           unit with non-zero low bits, above bit 94, inf / nan) raises FLAG_ABORT = 4 and the query re-runs
+//           on the generic path.  The sum is rounded ONCE, at the end (the reference rounds after every
+//           addition, aggregations.h:19-27 in double: both are within 1e-12 of each other, the exact one is
+//           the more accurate).
 //   MIN32 / MAX32   order-preserving 32-bit image, atomicMin / atomicMax after a plain pre-check.
 #pragma once
 #include "groupby.cuh"
@@ -54,14 +58,30 @@ __device__ __forceinline__ void isum2_add(uint32_t* lo, uint32_t* hi, long long 
     if (d) atomicAdd(hi, d);
 }
 // ---- FX ------------------------------------------------------------------------------------------
-// false: the value has no exact image (the caller raises the abort flag)
-__device__ __forceinline__ bool fx_add(uint32_t* w1, uint32_t* w2, uint32_t* w3, unsigned long long* glo,
-                                       unsigned long long* ghi, float x, int B) {
+// m * 2^s (sign neg) added to the 128-bit global sum; s in [0, FX_S_MAX]
+__device__ __forceinline__ void fx_global_add(unsigned long long* glo, unsigned long long* ghi, uint32_t m, int s, bool neg) {
+    unsigned long long lo, hi;
+    if (s < 64) { lo = (unsigned long long)m << s; hi = s ? ((unsigned long long)m >> (64 - s)) : 0ull; }
+    else { lo = 0ull; hi = (unsigned long long)m << (s - 64); }
+    if (neg) { lo = 0ull - lo; hi = ~hi + (lo == 0ull ? 1ull : 0ull); }
+    if (lo) { const unsigned long long old = atomicAdd(glo, lo); if (old + lo < old) hi += 1ull; }
+    if (hi) atomicAdd(ghi, hi);
+}
+// false: the value has no exact image (the caller raises the abort flag).  Q, R: see the header.
+__device__ __forceinline__ bool fx_add(uint32_t* lo, uint32_t* hi, unsigned long long* glo, unsigned long long* ghi,
+                                       float x, int B, int Q, int R) {
     const uint32_t bits = __float_as_uint(x);
     uint32_t m = bits & 0x7fffffu;
     int e = (int)((bits >> 23) & 0xffu);
     if (e == 0) { if (m == 0) return true; e = 1; }
     else { if (e == 255) return false; m |= 0x800000u; }
+    const int t = e - B - Q;
+    if ((unsigned)t <= (unsigned)R) {                         // the common case: inside the cell's window
+        long long X = (long long)((unsigned long long)m << t);
+        if (bits >> 31) X = -X;
+        isum2_add(lo, hi, X);
+        return true;
+    }
     int s = e - B;
     if (s < 0) {
         const int r = -s;
@@ -69,37 +89,17 @@ __device__ __forceinline__ bool fx_add(uint32_t* w1, uint32_t* w2, uint32_t* w3,
         m >>= r; s = 0;
     }
     if (s > FX_S_MAX) return false;
-    const int q = s >> 5;
-    const unsigned long long lo64 = (unsigned long long)m << (s & 31);
-    const uint32_t pa = (uint32_t)lo64, pb = (uint32_t)(lo64 >> 32);
-    uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    if (q == 0) { a0 = pa; a1 = pb; } else if (q == 1) { a1 = pa; a2 = pb; } else { a2 = pa; a3 = pb; }
-    if (!(bits >> 31)) {
-        if (a0) { const unsigned long long old = atomicAdd(glo, (unsigned long long)a0); if (old + a0 < old) atomicAdd(ghi, 1ull); }
-        uint32_t c = 0;
-        if (a1) { const uint32_t old = atomicAdd(w1, a1); c = ((uint32_t)(old + a1) < old) ? 1u : 0u; }
-        a2 += c; c = 0;
-        if (a2) { const uint32_t old = atomicAdd(w2, a2); c = ((uint32_t)(old + a2) < old) ? 1u : 0u; }
-        a3 += c;
-        if (a3) atomicAdd(w3, a3);
-    } else {
-        if (a0) { const unsigned long long old = atomicAdd(glo, 0ull - (unsigned long long)a0); if (old < a0) atomicAdd(ghi, ~0ull); }
-        uint32_t b = 0;
-        if (a1) { const uint32_t old = atomicSub(w1, a1); b = (old < a1) ? 1u : 0u; }
-        a2 += b; b = 0;
-        if (a2) { const uint32_t old = atomicSub(w2, a2); b = (old < a2) ? 1u : 0u; }
-        a3 += b;
-        if (a3) atomicSub(w3, a3);
-    }
+    fx_global_add(glo, ghi, m, s, (bits >> 31) != 0u);
     return true;
 }
-// a CTA's shared words of one FX cell -> the global 128-bit sum (glo, ghi)
-__device__ __forceinline__ void fx_merge(uint32_t w1, uint32_t w2, uint32_t w3, unsigned long long* glo, unsigned long long* ghi) {
-    if (w1 == 0u && w2 == 0u && w3 == CELL_BIAS) return;
-    const unsigned long long lo = (unsigned long long)w1 << 32;
-    unsigned long long hi = (unsigned long long)w2 | ((unsigned long long)(uint32_t)(w3 - CELL_BIAS) << 32);
-    if (lo) { const unsigned long long old = atomicAdd(glo, lo); if (old + lo < old) hi += 1ull; }
-    if (hi) atomicAdd(ghi, hi);
+// a CTA's shared 64-bit cell (units 2^Q) -> the global 128-bit sum
+__device__ __forceinline__ void fx_merge(uint32_t lo, uint32_t hi, int Q, unsigned long long* glo, unsigned long long* ghi) {
+    const long long v = (long long)((unsigned long long)lo | ((unsigned long long)hi << 32));
+    if (v == 0) return;
+    const unsigned long long l = (unsigned long long)v << Q;
+    unsigned long long h = (unsigned long long)(v >> (64 - Q));          // arithmetic shift: sign-extends; Q in [1, 63]
+    if (l) { const unsigned long long old = atomicAdd(glo, l); if (old + l < old) h += 1ull; }
+    if (h) atomicAdd(ghi, h);
 }
 // the global 128-bit fixed-point sum -> double (one rounding)
 __device__ __forceinline__ double fx_to_double(unsigned long long glo, unsigned long long ghi, int B) {

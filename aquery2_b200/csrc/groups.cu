@@ -3,6 +3,7 @@
 #include "groupby.cuh"
 #include "sort.cuh"
 #include "scan.cuh"
+#include "window.cuh"
 #include <cstring>
 #include <mutex>
 
@@ -21,6 +22,7 @@ struct aqgpu_groups {
     DevBuf perm;                    // nrows: "mapbase"
     DevBuf segstart;                // nrows: first CSR position of the owning group
     bool has_offsets = false, has_perm = false, has_segstart = false;
+    bool custom_order = false;      // order_by has replaced the row lists
     aqgpu_groups() {                // the handle outlives the call that builds it: pool memory, not the scratch arena
         for (auto& b : keys) b.persistent = true;
         for (DevBuf* b : {&first_row, &last_row, &counts, &gid, &offsets, &perm, &segstart}) b->persistent = true;
@@ -118,6 +120,34 @@ __global__ void k_vec_pow(const double* __restrict__ x, double p, double* __rest
 }
 
 } // namespace aq
+
+// ---- several expressions at once -------------------------------------------------------------------------------
+namespace aq {
+template <class T>
+__global__ void k_sub_from(const T* __restrict__ gv, T* __restrict__ io, uint32_t n) {      // io = gv - io
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) io[i] = (T)(gv[i] - io[i]);
+}
+// one thread per group over its CSR range; identities of server/aggregations.h:71-86
+template <class T>
+__global__ void k_seg_extreme(const T* __restrict__ vec, const uint32_t* __restrict__ offsets, uint32_t ngroups, int is_max, T ident,
+                              T* __restrict__ out) {
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+        T m = ident;
+        for (uint32_t p = offsets[g]; p < offsets[g + 1]; ++p) { const T e = vec[p]; if (is_max ? (e > m) : (e < m)) m = e; }
+        out[g] = m;
+    }
+}
+template <class T>
+static int window_post(int minus, int reduce, const void* gv, void* vec, const uint32_t* offsets, uint32_t n, uint32_t ngroups,
+                       T max_ident, T min_ident, void* out) {
+    if (minus) AQ_LAUNCH(k_sub_from<T>, grid_for(n, 256, 1, 32), 256, 0, static_cast<const T*>(gv), static_cast<T*>(vec), n);
+    if (reduce >= 0)
+        AQ_LAUNCH(k_seg_extreme<T>, grid_for(ngroups, 128, 1, 32), 128, 0, static_cast<const T*>(vec), offsets, ngroups, reduce == AQ_MAX ? 1 : 0,
+                  reduce == AQ_MAX ? max_ident : min_ident, static_cast<T*>(out));
+    return 0;
+}
+} // namespace aq
+
 
 extern "C" {
 
@@ -340,7 +370,79 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
     job.rows_out = g->perm.as<uint32_t>();
     if (bits == 0) AQ_CUDA(cudaMemcpyAsync(g->perm.p, cur, size_t(n) * 4, cudaMemcpyDeviceToDevice, ctx().stream));
     else AQ_TRY(sort_rows_by_key(job));
+    g->custom_order = true;
     AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (!g || !ops || n_ops < 1 || n_ops > 64) return fail("bad window arguments");
+    if (g->nrows == 0) return 0;
+    const uint32_t n = g->nrows, ng = g->ngroups;
+    std::vector<InCol> in(n_ops);
+    std::vector<OutCol> oc(n_ops);
+    std::vector<int> otype(n_ops);
+    std::vector<size_t> obytes(n_ops);
+    bool any_host = false;
+    for (int q = 0; q < n_ops; ++q) {
+        const aqgpu_window_t& o = ops[q];
+        if (!is_val_type(o.vtype)) return fail("window %d: unsupported value dtype %d", q, o.vtype);
+        const int def = aqgpu_scan_out_type(o.op, o.vtype);
+        if (def < 0) return fail("window %d: unknown scan op %d", q, o.op);
+        int ot = o.out_type ? o.out_type : def;
+        if (ot != def && !(def == AQ_INT128 && ot == AQ_INT64)) return fail("window %d: op %d on dtype %d cannot produce dtype %d", q, o.op, o.vtype, ot);
+        if ((o.minus_from_v || o.reduce >= 0) && def != o.vtype)
+            return fail("window %d: v - scan(v) and per-group max / min need a scan whose result has v's type", q);
+        if (o.reduce >= 0 && o.reduce != AQ_MAX && o.reduce != AQ_MIN) return fail("window %d: reduce must be AQ_MAX or AQ_MIN", q);
+        if ((o.op == AQ_SUMW || o.op == AQ_AVGW || o.op == AQ_MINW || o.op == AQ_MAXW || o.op == AQ_RATIOW) && o.w == 0)
+            return fail("window length 0 (the reference reads ret[-1] for w == 0)");
+        otype[q] = ot;
+        obytes[q] = dtype_size(ot) * (o.reduce >= 0 ? size_t(ng) : size_t(n));
+        AQ_TRY(in[q].bind(o.v, dtype_size(o.vtype) * n));
+        AQ_TRY(oc[q].bind(o.out, obytes[q]));
+        any_host |= oc[q].host != nullptr || in[q].tmp.p != nullptr;
+    }
+    AQ_TRY(ensure_offsets(g));
+    bool handled = false;
+    if (n_ops <= WIN_MAX_OPS) {
+        WinGroups G;
+        G.nrows = n; G.ngroups = ng; G.row_order = g->row_order; G.gid = g->gid.as<uint32_t>(); G.offsets = g->offsets.as<uint32_t>();
+        G.perm = g->custom_order ? g->perm.as<uint32_t>() : nullptr;
+        WinOp w[WIN_MAX_OPS];
+        for (int q = 0; q < n_ops; ++q) {
+            w[q].op = ops[q].op; w[q].w = ops[q].w; w[q].vtype = ops[q].vtype; w[q].v = in[q].d; w[q].minus = ops[q].minus_from_v;
+            w[q].reduce = ops[q].reduce; w[q].out_type = otype[q]; w[q].out = oc[q].d;
+        }
+        AQ_TRY(window_fused(G, w, n_ops, &handled));
+    }
+    if (!handled) {                       // one expression at a time over the handle's row lists
+        AQ_TRY(ensure_perm(g));
+        AQ_TRY(ensure_segstart(g));
+        for (int q = 0; q < n_ops; ++q) {
+            const aqgpu_window_t& o = ops[q];
+            DevBuf vec, gv;
+            void* dst = oc[q].d;
+            if (o.reduce >= 0) { AQ_TRY(vec.alloc(dtype_size(otype[q]) * n)); dst = vec.p; }
+            AQ_TRY(group_scan_device(o.op, o.w, o.vtype, in[q].d, n, ng, g->gid.as<uint32_t>(), g->offsets.as<uint32_t>(),
+                                     g->perm.as<uint32_t>(), g->segstart.as<uint32_t>(), otype[q], dst));
+            if (!o.minus_from_v && o.reduce < 0) continue;
+            if (o.minus_from_v) {
+                AQ_TRY(gv.alloc(dtype_size(o.vtype) * n));
+                AQ_TRY(gather_rows(in[q].d, (int)dtype_size(o.vtype), g->perm.as<uint32_t>(), n, gv.p));
+            }
+            const uint32_t* off = g->offsets.as<uint32_t>();
+            switch (o.vtype) {
+            case AQ_INT32: AQ_TRY(window_post<int>(o.minus_from_v, o.reduce, gv.p, dst, off, n, ng, (int)0x80000000u, 0x7fffffff, oc[q].d)); break;
+            case AQ_INT64: AQ_TRY(window_post<long long>(o.minus_from_v, o.reduce, gv.p, dst, off, n, ng, (long long)0x8000000000000000ULL, 0x7fffffffffffffffLL, oc[q].d)); break;
+            case AQ_FLOAT: AQ_TRY(window_post<float>(o.minus_from_v, o.reduce, gv.p, dst, off, n, ng, 1.17549435e-38f, 3.402823466e+38f, oc[q].d)); break;
+            default: AQ_TRY(window_post<double>(o.minus_from_v, o.reduce, gv.p, dst, off, n, ng, 2.2250738585072014e-308, 1.7976931348623157e+308, oc[q].d)); break;
+            }
+        }
+    }
+    for (int q = 0; q < n_ops; ++q) AQ_TRY(oc[q].finish(obytes[q]));
+    if (any_host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
     return 0;
 }
 

@@ -24,6 +24,7 @@
 //                insertion index m_values has in the reference (server/unordered_dense.h:1142-1146).
 #include "lc.cuh"
 #include "emit.cuh"
+#include "sort.cuh"
 #include <cmath>
 #include <cstring>
 
@@ -237,7 +238,67 @@ struct FpAggArgs {
     uint32_t rec_cap;
     uint32_t* nrec;
     uint32_t* flags;
+    uint32_t* plist;                      // partitions with duplicated key tuples (k_fp_screen -> k_fp_agg)
+    uint32_t* nlist;
 };
+
+// Screen: almost every final partition holds distinct key tuples only.  One 32-bit compare-and-swap per
+// tuple into a table of (19 fingerprint bits, 13-bit tuple index) entries finds the candidates; a candidate
+// pair is settled by the full fingerprint and then by the key columns themselves.  Partitions with a real
+// duplicate go on plist for k_fp_agg; for all the others rflags stays 0 and nothing is written.
+constexpr int FPS_THREADS = 512;
+constexpr uint32_t FPS_EMPTY = 0xffffffffu;
+constexpr size_t FPS_SMEM = size_t(FP_SLOTS) * 4 + size_t(FPS_THREADS) * FPA_TPT * 8;
+__global__ void __launch_bounds__(FPS_THREADS, 3)
+k_fp_screen(const KeySpec ks, const FpAggArgs A) {
+    extern __shared__ __align__(16) unsigned char fps_sm[];
+    unsigned long long* const stage = reinterpret_cast<unsigned long long*>(fps_sm);   // tuple i of the partition at stage[i]
+    uint32_t* const tab = reinterpret_cast<uint32_t*>(stage + size_t(FPS_THREADS) * FPA_TPT);
+    __shared__ uint32_t s_abort, s_dup;
+    if (threadIdx.x == 0) s_abort = *reinterpret_cast<volatile uint32_t*>(A.flags + FLAG_ABORT);
+    __syncthreads();
+    if (s_abort) return;
+    constexpr uint32_t mask = FP_SLOTS - 1;
+    for (uint32_t p = blockIdx.x; p < A.npart; p += gridDim.x) {
+        const uint32_t n = min(__ldg(A.cursor + p), A.cap);
+        const unsigned long long* src = A.tuples + size_t(p) * A.cap;
+#pragma unroll
+        for (int j = 0; j < FPA_TPT; ++j) {
+            const uint32_t idx = j * FPS_THREADS + threadIdx.x;
+            stage[idx] = idx < n ? __ldg(src + idx) : FP_INVALID;
+        }
+        for (uint32_t i = threadIdx.x; i < FP_SLOTS; i += FPS_THREADS) tab[i] = FPS_EMPTY;
+        if (threadIdx.x == 0) s_dup = 0u;
+        __syncthreads();
+        bool dup = false;
+        // every lane walks its own tuples at its own pace: one probe per iteration, the next tuple as soon as one is placed
+        uint32_t idx = threadIdx.x, s = 0, mine = 0;
+        unsigned long long t = 0;
+        bool fresh = true;
+        while (idx < n) {
+            if (fresh) {
+                t = stage[idx];
+                if ((uint32_t)t == 0xffffffffu) { idx += FPS_THREADS; continue; }          // sector padding
+                const uint32_t fp = (uint32_t)(t >> 32);
+                s = (fp * 0x9E3779B1u) >> 19;
+                mine = (fp << 13) | idx;
+                if (mine == FPS_EMPTY) mine ^= 1u << 13;         // never the empty pattern (the full compare below settles it)
+                fresh = false;
+            }
+            const uint32_t old = atomicCAS(tab + s, FPS_EMPTY, mine);
+            if (old == FPS_EMPTY) { idx += FPS_THREADS; fresh = true; continue; }
+            if (((old ^ mine) >> 14) == 0u) {                     // 18 tag bits agree: look at the other tuple
+                const unsigned long long other = stage[old & 0x1fffu];
+                if ((uint32_t)(other >> 32) == (uint32_t)(t >> 32) && keys_equal(ks, (uint32_t)t, (uint32_t)other)) dup = true;
+            }
+            s = (s + 1u) & mask;
+        }
+        if (dup) s_dup = 1u;
+        __syncthreads();
+        if (threadIdx.x == 0 && s_dup) A.plist[atomicAdd(A.nlist, 1u)] = p;
+        __syncthreads();
+    }
+}
 
 __global__ void __launch_bounds__(FPA_THREADS, 2)
 k_fp_agg(const KeySpec ks, const AccProg prog, const FpAggArgs A, const HcIdentity ident) {
@@ -249,7 +310,9 @@ k_fp_agg(const KeySpec ks, const AccProg prog, const FpAggArgs A, const HcIdenti
     __syncthreads();
     if (s_abort) return;
     constexpr uint32_t mask = FP_SLOTS - 1;
-    for (uint32_t p = blockIdx.x; p < A.npart; p += gridDim.x) {
+    const uint32_t nlist = min(*A.nlist, A.npart);
+    for (uint32_t li = blockIdx.x; li < nlist; li += gridDim.x) {
+        const uint32_t p = A.plist[li];
         for (uint32_t i = threadIdx.x; i < FP_SLOTS; i += FPA_THREADS) tab[i] = FP_INVALID;
         for (uint32_t i = threadIdx.x; i < FP_SLOTS / 32; i += FPA_THREADS) multi[i] = 0u;
         const uint32_t n = min(__ldg(A.cursor + p), A.cap);
@@ -329,94 +392,182 @@ k_fp_agg(const KeySpec ks, const AccProg prog, const FpAggArgs A, const HcIdenti
     }
 }
 
-// ---- emit: ranks by look-back, one pass in row order ----------------------------------------------------------
+// ---- emit: one pass in row order ------------------------------------------------------------------------------
+// k_fp_tilecount: first rows per tile (a first row is any row whose flag is not 2); an exclusive scan of the
+// tile counts (sort.cu) gives every tile the rank of its first first-row; k_fp_emit then streams: flags ->
+// ranks inside the tile by ballots -> for every output column, the tile's rows are read where they lie and
+// written at their ranks (both coalesced: consecutive lanes = consecutive rows = consecutive ranks).
 constexpr int FPE_THREADS = 256;
-constexpr int FPE_ROWS = FPE_THREADS * 4;
-constexpr unsigned long long FPE_AGG = 1ull << 62, FPE_PREFIX = 2ull << 62, FPE_VAL = (1ull << 62) - 1;
+constexpr int FPE_RPT = 4;
+constexpr int FPE_ROWS = FPE_THREADS * FPE_RPT;          // 1024
 
 __global__ void __launch_bounds__(FPE_THREADS)
-k_fp_emit(const uint32_t nrows, const uint32_t ntiles, const unsigned char* __restrict__ rflags,
-          const uint32_t* __restrict__ rec_of_row, const unsigned long long* __restrict__ rec,
-          unsigned long long* __restrict__ tile_state, uint32_t* __restrict__ ticket,
-          const KeyOut ko, uint32_t* __restrict__ first_row_out, const EmitProg ep, const AccProg prog,
-          const uint32_t max_groups, uint32_t* __restrict__ flags) {
-    __shared__ uint32_t s_tile, s_excl, wcnt[4][FPE_THREADS / 32];
-    if (*reinterpret_cast<volatile uint32_t*>(flags + FLAG_ABORT)) return;
+k_fp_tilecount(const uint32_t nrows, const unsigned char* __restrict__ rflags, uint32_t* __restrict__ tile_count,
+               const uint32_t* __restrict__ flags) {
+    __shared__ uint32_t wsum[FPE_THREADS / 32];
+    if (*reinterpret_cast<const volatile uint32_t*>(flags + FLAG_ABORT)) return;
+    static_assert(FPE_RPT == 4, "one 32-bit word of flags per thread");
+    const uint32_t base = blockIdx.x * FPE_ROWS + threadIdx.x * FPE_RPT;       // 4 consecutive flags per thread
+    uint32_t c = 0;
+    if (base + FPE_RPT <= nrows) {
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(rflags + base);
+        c = FPE_RPT - (uint32_t)__popc(v & 0x02020202u);         // bytes are 0, 1 or 2: bit 1 marks "not a first row"
+    } else {
+        for (uint32_t r = base; r < nrows; ++r) c += rflags[r] != 2 ? 1u : 0u;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < FPE_THREADS / 32; ++w) t += wsum[w];
+        tile_count[blockIdx.x] = t;
+    }
+}
+
+// One output column of a one-row group: dst[rank] = conv(src[row]).
+enum FpConv : int { FC_COPY4 = 0, FC_COPY8, FC_I32_I128, FC_I32_I64, FC_I32_F64, FC_F32_F64, FC_MAXF32, FC_ONE_I64, FC_ONE_U32,
+                    FC_ZERO4, FC_ZERO8, FC_ROW };
+constexpr int FP_MAX_OUTCOLS = MAX_KEY_COLS + MAX_AGGS + 1;
+struct FpOutCols {
+    int n;
+    int simple;                           // every requested aggregate has a column op (else: emit_one per row)
+    int conv[FP_MAX_OUTCOLS];
+    const void* src[FP_MAX_OUTCOLS];
+    void* dst[FP_MAX_OUTCOLS];
+};
+
+template <int CONV>
+__device__ __forceinline__ void fp_emit_col(const void* __restrict__ src, void* __restrict__ dst, const uint32_t (&row)[FPE_RPT],
+                                            const uint32_t (&g)[FPE_RPT], const uint32_t okm) {
+    if (CONV == FC_COPY8) {
+        unsigned long long v[FPE_RPT];
+#pragma unroll
+        for (int j = 0; j < FPE_RPT; ++j) if (okm & (1u << j)) v[j] = __ldg(static_cast<const unsigned long long*>(src) + row[j]);
+#pragma unroll
+        for (int j = 0; j < FPE_RPT; ++j) if (okm & (1u << j)) static_cast<unsigned long long*>(dst)[g[j]] = v[j];
+        return;
+    }
+    uint32_t v[FPE_RPT];
+    if (CONV != FC_ONE_I64 && CONV != FC_ONE_U32 && CONV != FC_ZERO4 && CONV != FC_ZERO8 && CONV != FC_ROW) {
+#pragma unroll
+        for (int j = 0; j < FPE_RPT; ++j) if (okm & (1u << j)) v[j] = ld_stream_u32(static_cast<const uint32_t*>(src) + row[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < FPE_RPT; ++j) {
+        if (!(okm & (1u << j))) continue;
+        const uint32_t gi = g[j];
+        switch (CONV) {
+        case FC_COPY4: static_cast<uint32_t*>(dst)[gi] = v[j]; break;
+        case FC_I32_I128: { const long long x = (long long)(int)v[j]; I128 o; o.lo = (unsigned long long)x; o.hi = x >> 63; static_cast<I128*>(dst)[gi] = o; break; }
+        case FC_I32_I64: static_cast<long long*>(dst)[gi] = (long long)(int)v[j]; break;
+        case FC_I32_F64: static_cast<double*>(dst)[gi] = (double)(int)v[j]; break;
+        case FC_F32_F64: static_cast<double*>(dst)[gi] = (double)__uint_as_float(v[j]); break;
+        case FC_MAXF32: { float f = __uint_as_float(v[j]); if (!(f > 1.17549435e-38f)) f = 1.17549435e-38f; static_cast<float*>(dst)[gi] = f; break; }   // aggregations.h:73
+        case FC_ONE_I64: static_cast<long long*>(dst)[gi] = 1ll; break;
+        case FC_ONE_U32: static_cast<uint32_t*>(dst)[gi] = 1u; break;
+        case FC_ZERO4: static_cast<uint32_t*>(dst)[gi] = 0u; break;
+        case FC_ZERO8: static_cast<unsigned long long*>(dst)[gi] = 0ull; break;
+        case FC_ROW: static_cast<uint32_t*>(dst)[gi] = row[j]; break;
+        default: break;
+        }
+    }
+}
+
+// rows of this thread in the tile, their flags and ranks (the rank of a row that is not a first row is unused)
+__device__ __forceinline__ void fp_tile_ranks(const uint32_t nrows, const unsigned char* __restrict__ rflags, const uint32_t* __restrict__ tile_excl,
+                                              uint32_t (&wcnt)[FPE_RPT][FPE_THREADS / 32], uint32_t (&row)[FPE_RPT], uint32_t (&g)[FPE_RPT],
+                                              uint32_t (&fl)[FPE_RPT]) {
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     constexpr int NW = FPE_THREADS / 32;
-    for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
-        __syncthreads();
-        const uint32_t tile = s_tile;
-        if (tile >= ntiles) return;
-        const uint32_t base = tile * FPE_ROWS;
-        uint32_t fl[4], before[4];
+    const uint32_t base = blockIdx.x * FPE_ROWS;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t row = base + j * FPE_THREADS + threadIdx.x;
-            fl[j] = row < nrows ? (uint32_t)rflags[row] : 2u;
-            const uint32_t m = __ballot_sync(0xffffffffu, fl[j] != 2u);
-            before[j] = __popc(m & ((1u << lane) - 1u));
-            if (lane == 0) wcnt[j][wid] = __popc(m);
+    for (int j = 0; j < FPE_RPT; ++j) {
+        row[j] = base + j * FPE_THREADS + threadIdx.x;
+        fl[j] = row[j] < nrows ? (uint32_t)rflags[row[j]] : 2u;
+        const uint32_t m = __ballot_sync(0xffffffffu, fl[j] != 2u);
+        g[j] = __popc(m & ((1u << lane) - 1u));
+        if (lane == 0) wcnt[j][wid] = __popc(m);
+    }
+    __syncthreads();
+    static_assert(FPE_RPT * NW == 32, "one warp count per lane");
+    if (wid == 0) {                       // exclusive scan of the 4 x NW warp counts (row order: j major, warp minor)
+        const uint32_t v = wcnt[lane / NW][lane % NW];
+        uint32_t sc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, d); if (lane >= (uint32_t)d) sc += y; }
+        wcnt[lane / NW][lane % NW] = sc - v;
+    }
+    __syncthreads();
+    const uint32_t excl = tile_excl[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < FPE_RPT; ++j) g[j] += excl + wcnt[j][wid];
+}
+
+__global__ void __launch_bounds__(FPE_THREADS, 4)
+k_fp_emit(const uint32_t nrows, const unsigned char* __restrict__ rflags, const uint32_t* __restrict__ tile_excl,
+          const FpOutCols oc, const uint32_t max_groups, const uint32_t* __restrict__ flags) {
+    __shared__ uint32_t wcnt[FPE_RPT][FPE_THREADS / 32];
+    if (*reinterpret_cast<const volatile uint32_t*>(flags + FLAG_ABORT)) return;
+    uint32_t row[FPE_RPT], g[FPE_RPT], fl[FPE_RPT];
+    fp_tile_ranks(nrows, rflags, tile_excl, wcnt, row, g, fl);
+    uint32_t okm = 0, allm = 0;           // one-row groups the column ops finish / every first row
+#pragma unroll
+    for (int j = 0; j < FPE_RPT; ++j) {
+        if (fl[j] != 2u && g[j] < max_groups) {           // the host reports an overflow of max_groups
+            allm |= 1u << j;
+            if (fl[j] == 0u) okm |= 1u << j;
         }
-        __syncthreads();
-        if (wid == 0) {
-            // exclusive scan of the 4 x NW warp counts (row order: j major, warp minor), then the look-back
-            const uint32_t v = lane < 4 * NW ? wcnt[lane / NW][lane % NW] : 0u;
-            uint32_t sc = v;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, d); if (lane >= (uint32_t)d) sc += y; }
-            const uint32_t total = __shfl_sync(0xffffffffu, sc, 31);
-            if (lane < 4 * NW) wcnt[lane / NW][lane % NW] = sc - v;
-            volatile unsigned long long* st = tile_state;
-            if (lane == 0) st[tile] = (tile == 0 ? FPE_PREFIX : FPE_AGG) | total;
-            uint32_t excl = 0;
-            if (tile > 0) {
-                long long look = (long long)tile - 1;
-                for (;;) {
-                    const long long idx = look - lane;
-                    unsigned long long v2 = FPE_PREFIX;
-                    if (idx >= 0) { do { v2 = st[idx]; } while ((v2 >> 62) == 0); }
-                    const uint32_t pm = __ballot_sync(0xffffffffu, (v2 >> 62) == 2);
-                    const int first = pm ? __ffs(pm) - 1 : 32;
-                    uint32_t part = ((int)lane <= first) ? (uint32_t)(v2 & FPE_VAL) : 0u;
-#pragma unroll
-                    for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
-                    excl += part;
-                    if (pm) break;
-                    look -= 32;
-                }
-                if (lane == 0) st[tile] = FPE_PREFIX | (unsigned long long)(excl + total);
-            }
-            if (lane == 0) {
-                s_excl = excl;
-                if (tile + 1 == ntiles) flags[FLAG_NGROUPS] = excl + total;
-            }
+    }
+    for (int c = 0; c < oc.n; ++c) {
+        const void* src = oc.src[c]; void* dst = oc.dst[c];
+        const uint32_t m = oc.conv[c] < 0 ? allm : okm;  // keys and first rows: every first row alike
+        switch (oc.conv[c] < 0 ? -1 - oc.conv[c] : oc.conv[c]) {
+        case FC_COPY4: fp_emit_col<FC_COPY4>(src, dst, row, g, m); break;
+        case FC_COPY8: fp_emit_col<FC_COPY8>(src, dst, row, g, m); break;
+        case FC_I32_I128: fp_emit_col<FC_I32_I128>(src, dst, row, g, m); break;
+        case FC_I32_I64: fp_emit_col<FC_I32_I64>(src, dst, row, g, m); break;
+        case FC_I32_F64: fp_emit_col<FC_I32_F64>(src, dst, row, g, m); break;
+        case FC_F32_F64: fp_emit_col<FC_F32_F64>(src, dst, row, g, m); break;
+        case FC_MAXF32: fp_emit_col<FC_MAXF32>(src, dst, row, g, m); break;
+        case FC_ONE_I64: fp_emit_col<FC_ONE_I64>(src, dst, row, g, m); break;
+        case FC_ONE_U32: fp_emit_col<FC_ONE_U32>(src, dst, row, g, m); break;
+        case FC_ZERO4: fp_emit_col<FC_ZERO4>(src, dst, row, g, m); break;
+        case FC_ZERO8: fp_emit_col<FC_ZERO8>(src, dst, row, g, m); break;
+        case FC_ROW: fp_emit_col<FC_ROW>(src, dst, row, g, m); break;
+        default: break;
         }
-        __syncthreads();
-        const uint32_t excl = s_excl;
+    }
+}
+
+// The aggregates of groups with a record -- and of every group when some requested aggregate has no column
+// op (all = 1) -- through the generic finaliser.  Does nothing when there is no record and all = 0.
+__global__ void __launch_bounds__(FPE_THREADS)
+k_fp_emit_rest(const uint32_t nrows, const unsigned char* __restrict__ rflags, const uint32_t* __restrict__ tile_excl,
+               const uint32_t* __restrict__ rec_of_row, const unsigned long long* __restrict__ rec, const uint32_t* __restrict__ nrec,
+               const int all, const __grid_constant__ EmitProg ep, const __grid_constant__ AccProg prog, const uint32_t max_groups,
+               const uint32_t* __restrict__ flags) {
+    __shared__ uint32_t wcnt[FPE_RPT][FPE_THREADS / 32];
+    if (*reinterpret_cast<const volatile uint32_t*>(flags + FLAG_ABORT)) return;
+    if (!all && *nrec == 0u) return;
+    uint32_t row[FPE_RPT], g[FPE_RPT], fl[FPE_RPT];
+    fp_tile_ranks(nrows, rflags, tile_excl, wcnt, row, g, fl);
+#pragma unroll 1
+    for (int j = 0; j < FPE_RPT; ++j) {
+        uint32_t r = 0, gi = 0, f = 2;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            if (fl[j] == 2u) continue;
-            const uint32_t row = base + j * FPE_THREADS + threadIdx.x;
-            const uint32_t g = excl + wcnt[j][wid] + before[j];
-            if (g >= max_groups) continue;                         // the host reports the overflow
-            if (first_row_out) first_row_out[g] = row;
-            for (int k = 0; k < ko.n; ++k) {
-                if (!ko.dst[k]) continue;
-                if (ko.size[k] == 4) static_cast<uint32_t*>(ko.dst[k])[g] = ld_stream_u32(static_cast<const uint32_t*>(ko.src[k]) + row);
-                else static_cast<unsigned long long*>(ko.dst[k])[g] = static_cast<const unsigned long long*>(ko.src[k])[row];
-            }
-            unsigned long long one[1 + MAX_ACC];
-            const unsigned long long* cells = one;
-            if (fl[j] == 0u) {
-                for (int a = 0; a < prog.n; ++a) one[1 + a] = acc_single_row(prog.op[a], row);
-            } else {
-                cells = rec + size_t(rec_of_row[row]) * prog.n - 1;
-            }
-            for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], cells, g, row, ep.row_order);
+        for (int i = 0; i < FPE_RPT; ++i) if (i == j) { r = row[i]; gi = g[i]; f = fl[i]; }
+        if (f == 2u || gi >= max_groups || (f == 0u && !all)) continue;
+        unsigned long long one[1 + MAX_ACC];
+        const unsigned long long* cells = one;
+        if (f == 0u) {
+            for (int a = 0; a < prog.n; ++a) one[1 + a] = acc_single_row(prog.op[a], r);
+        } else {
+            cells = rec + size_t(rec_of_row[r]) * prog.n - 1;
         }
+        for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], cells, gi, r, ep.row_order);
     }
 }
 
@@ -460,22 +611,26 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
     DevBuf part1, part2, cur, rflags, rec_of_row, rec, state;
     AQ_TRY(part1.alloc(size_t(P1) * cap1 * 8));
     if (P2 > 1) AQ_TRY(part2.alloc(size_t(nfinal) * cap2 * 8));
-    AQ_TRY(cur.alloc_zero((size_t(P1) + nfinal + 4) * 4));
+    AQ_TRY(cur.alloc_zero((size_t(P1) + nfinal + 8) * 4));
     AQ_TRY(rflags.alloc_zero(size_t(nrows)));
     AQ_TRY(rec_of_row.alloc(size_t(nrows) * 4));
     const uint32_t rec_cap = std::max<uint32_t>(1u << 16, nrows / 16);
     AQ_TRY(rec.alloc(size_t(rec_cap) * std::max(plan.n_acc, 1) * 8));
     const uint32_t ntiles_e = (nrows + FPE_ROWS - 1) / FPE_ROWS;
-    AQ_TRY(state.alloc_zero(size_t(ntiles_e) * 8 + 8));
+    AQ_TRY(state.alloc(size_t(ntiles_e) * 8 + 8));
+    DevBuf plist;
+    AQ_TRY(plist.alloc(size_t(nfinal) * 4));
     uint32_t* cursor1 = cur.as<uint32_t>();
     uint32_t* cursor2 = cursor1 + P1;
     uint32_t* nrec = cursor2 + nfinal;
+    uint32_t* nlist = nrec + 1;
     AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
     static bool attr_done = false;
     if (!attr_done) {
         AQ_CUDA(cudaFuncSetAttribute(k_fp_part1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
         AQ_CUDA(cudaFuncSetAttribute(k_fp_part2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
         AQ_CUDA(cudaFuncSetAttribute(k_fp_agg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(size_t(FP_SLOTS) * 8 + FP_SLOTS / 8)));
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_screen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FPS_SMEM));
         attr_done = true;
     }
     AQ_LAUNCH(k_fp_part1, c.sm_count, FP_THREADS, sizeof(FpSmem), ks, nrows, P1, cursor1, part1.as<unsigned long long>(), cap1, c.d_flags);
@@ -490,6 +645,7 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
     A.tuples = fin; A.cursor = fcur; A.npart = nfinal; A.cap = cap2;
     A.rflags = rflags.as<unsigned char>(); A.rec_of_row = rec_of_row.as<uint32_t>();
     A.rec = rec.as<unsigned long long>(); A.rec_cap = rec_cap; A.nrec = nrec; A.flags = c.d_flags;
+    A.plist = plist.as<uint32_t>(); A.nlist = nlist;
     HcIdentity ident;
     for (int a = 0; a < MAX_ACC; ++a) ident.w[a] = 0ull;
     for (int a = 0; a < plan.n_acc; ++a) {
@@ -497,6 +653,7 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
         if (plan.prog.op[a].kind == ACC_MAX_I64) ident.w[a] = 0x8000000000000000ULL;
     }
     const size_t agg_smem = size_t(FP_SLOTS) * 8 + FP_SLOTS / 8;
+    AQ_LAUNCH(k_fp_screen, (int)std::min<uint32_t>(nfinal, (uint32_t)c.sm_count * 3), FPS_THREADS, FPS_SMEM, ks, A);
     AQ_LAUNCH(k_fp_agg, (int)std::min<uint32_t>(nfinal, (uint32_t)c.sm_count * 2), FPA_THREADS, agg_smem, ks, plan.prog, A, ident);
     // ---- emit (the kernel does nothing when an earlier stage gave up)
     AQ_TRY(sink.prepare(sink.res ? nrows : sink.max_groups, plan));
@@ -505,10 +662,45 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
     ko.n = kc.n;
     for (int k = 0; k < kc.n; ++k) { ko.src[k] = kc.col[k].d; ko.size[k] = (int)dtype_size(kc.type[k]); ko.dst[k] = sink.key_dst[k]; }
     for (int a = 0; a < plan.emit.n; ++a) plan.emit.agg[a].out = sink.agg_dst[a];
-    unsigned long long* st = state.as<unsigned long long>();
-    AQ_LAUNCH(k_fp_emit, (int)std::min<uint64_t>(ntiles_e, uint64_t(c.sm_count) * 8), FPE_THREADS, 0, nrows, ntiles_e,
-              rflags.as<unsigned char>(), rec_of_row.as<uint32_t>(), rec.as<unsigned long long>(), st,
-              reinterpret_cast<uint32_t*>(st + ntiles_e), ko, sink.fr_dst, plan.emit, plan.prog, sink.cap, c.d_flags);
+    FpOutCols oc;
+    memset(&oc, 0, sizeof(oc));
+    oc.simple = 1;
+    auto add_col = [&](int conv, const void* src, void* dst) { oc.conv[oc.n] = conv; oc.src[oc.n] = src; oc.dst[oc.n] = dst; ++oc.n; };
+    for (int k = 0; k < kc.n; ++k)
+        if (ko.dst[k]) add_col(-1 - (ko.size[k] == 4 ? FC_COPY4 : FC_COPY8), ko.src[k], ko.dst[k]);
+    if (sink.fr_dst) add_col(-1 - FC_ROW, nullptr, sink.fr_dst);
+    const int nfixed = oc.n;
+    for (int a = 0; a < plan.emit.n && oc.simple; ++a) {
+        const EmitAgg& e = plan.emit.agg[a];
+        const AccOp* o = (e.a[0] >= 0 && e.a[0] < plan.n_acc) ? &plan.prog.op[e.a[0]] : nullptr;
+        const bool v4 = e.vtype == AQ_INT32 || e.vtype == AQ_FLOAT;
+        int conv = -1; const void* src = nullptr;
+        switch (e.op) {
+        case AQ_SUM:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = e.vtype == AQ_FLOAT ? FC_F32_F64 : (e.out_type == AQ_INT128 ? FC_I32_I128 : FC_I32_I64); }
+            break;
+        case AQ_AVG:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = e.vtype == AQ_FLOAT ? FC_F32_F64 : FC_I32_F64; }
+            break;
+        case AQ_MIN: case AQ_MAX:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = (e.op == AQ_MAX && e.vtype == AQ_FLOAT) ? FC_MAXF32 : FC_COPY4; }
+            break;
+        case AQ_COUNT: conv = e.out_type == AQ_INT64 ? FC_ONE_I64 : FC_ONE_U32; break;
+        case AQ_FIRST: case AQ_LAST: src = e.v; conv = v4 ? FC_COPY4 : FC_COPY8; break;
+        case AQ_SECOND: conv = v4 ? FC_ZERO4 : FC_ZERO8; break;
+        default: break;
+        }
+        if (conv < 0) { oc.simple = 0; break; }
+        add_col(conv, src, e.out);
+    }
+    if (!oc.simple) oc.n = nfixed;
+    uint32_t* tile_count = state.as<uint32_t>();
+    uint32_t* tile_excl = tile_count + ntiles_e + 1;
+    AQ_LAUNCH(k_fp_tilecount, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_count, c.d_flags);
+    AQ_TRY(exclusive_scan_u32(tile_count, tile_excl, ntiles_e, c.d_flags + FLAG_NGROUPS));
+    AQ_LAUNCH(k_fp_emit, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_excl, oc, sink.cap, c.d_flags);
+    AQ_LAUNCH(k_fp_emit_rest, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_excl, rec_of_row.as<uint32_t>(),
+              rec.as<unsigned long long>(), nrec, oc.simple ? 0 : 1, plan.emit, plan.prog, sink.cap, c.d_flags);
     AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
     AQ_CUDA(cudaStreamSynchronize(c.stream));
     if (c.h_flags[FLAG_ABORT] != 0) return 0;                     // a region or the record list overflowed: generic path

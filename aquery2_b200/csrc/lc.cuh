@@ -9,12 +9,12 @@ constexpr int LC_MAX_COLS = 8;          // ring columns per CTA (keys + the valu
 constexpr int LC_MAX_STAGES = 8;
 constexpr uint32_t LC_MAX_G = 65536;    // slots of the direct table
 
-enum LcKind : int { LCK_CNT = 0, LCK_ISUM1, LCK_ISUM2, LCK_FX, LCK_MIN32, LCK_MAX32 };
+enum LcKind : int { LCK_CNT = 0, LCK_ISUM1, LCK_ISUM2, LCK_FX, LCK_MIN32, LCK_MAX32, LCK_SEEN };
 
 struct LcAcc {
     int kind, xform, vtype;
     int owner;              // CTA rank inside the cluster that keeps this accumulator
-    int c0, c1;             // ring column of v / v2 in the owner's ring
+    int c0, c1;             // ring column of v / v2
     uint32_t off;           // byte offset of the first word array in the owner's table (arrays of G words, SoA)
     int fxB;                // LCK_FX: biased exponent of the fixed-point unit (cells.cuh)
     uint32_t gword;         // first u64 word of this accumulator in a group's global record
@@ -24,8 +24,10 @@ struct LcParams {
     uint32_t nrows, G, tile_rows, ntiles;
     int nkeys, nacc, cluster, stages;
     uint32_t klo[LC_MAX_KEYS], krange[LC_MAX_KEYS], kmul[LC_MAX_KEYS];
-    const uint32_t* cols[4][LC_MAX_COLS];
-    int ncols[4];
+    const uint32_t* cols[LC_MAX_COLS];  // ring columns: the keys first, then every value column once (same ring in every CTA)
+    int ncols;
+    int fxQ, fxR;                       // LCK_FX: the shared cell counts units of 2^fxQ and takes mantissas shifted by <= fxR (cells.cuh)
+    uint32_t isum_lim;                  // LCK_ISUM1: |x| <= isum_lim keeps a CTA's 32-bit cell exact (checked per row)
     LcAcc acc[MAX_ACC];
     unsigned long long* gtab;           // G records of gw u64 words
     uint32_t gw;
@@ -51,7 +53,8 @@ struct PlanStats {
     unsigned long long isum_maxabs[MAX_ACC];   // integer accumulators: largest |x| (after its xform)
 };
 
-bool lc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st, LcParams& P, LcKeys& K,
+// marker_acc: index of a COUNT accumulator no output reads (it only tells empty slots apart), or -1
+bool lc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st, int marker_acc, LcParams& P, LcKeys& K,
                int* threads_out, size_t* smem_out);
 int run_lc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, LcParams& P, const LcKeys& K, int threads, size_t smem,
            OutSink& sink, uint32_t* ngroups, bool* used);

@@ -231,7 +231,7 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
 
     if (!path_disabled("lc")) {
         LcParams P; LcKeys K; int threads = 0; size_t smem = 0;
-        if (lc_layout(kc, nrows, plan, st, P, K, &threads, &smem)) {
+        if (lc_layout(kc, nrows, plan, st, had_count ? -1 : plan.find(ACC_COUNT), P, K, &threads, &smem)) {
             AQ_TRY(run_lc(kc, nrows, plan, P, K, threads, smem, sink, ngroups, used));
             if (*used) return 0;
             st.have_bounds = st.bounds_given;                        // a sampled bound was wrong: drop them

@@ -31,6 +31,7 @@ k_synth(int kind, uint64_t key0, uint64_t key1, uint64_t key2, uint32_t k, uint3
             r = 50u + (uint32_t)base + (uint32_t)uniform_k(x, 11);
             break; }
         case 5: r = aux_k + (uint32_t)uniform_k(x, k); break;     // aux_k + U[0,k)
+        case 6: r = 1u + (uint32_t)((row * 40353607ull + 12345ull) % (uint64_t)k); break;   // a permutation of 1..k when gcd(7^9, k) = 1
         default: r = 0;
         }
         out[i] = r;

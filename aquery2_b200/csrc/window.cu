@@ -1,0 +1,764 @@
+// window.cu -- per-group running / windowed / neighbour aggregates of ALL groups and SEVERAL expressions in one
+// streaming pass (the "stock / moving average" query shape: avgs(5,price), sums(5,quantity), deltas(price),
+// mins(5,price), max(price - mins(price)) by sym; benchmark/quries/Aquery/q7.a, q10.a, tests/moving_avg.a).
+//
+// The reference evaluates every expression group by group on a gathered vector col[vecs[g]]
+// (engine/ast.py:696-718; loops of server/aggregations.h:89-281, 439-462).  Here:
+//
+//   1. the rows are brought into CSR order ONCE, carrying their values: 16-byte tuples (gid, v0, v1, v2) go
+//      through a stable LSD radix sort on gid (k_ws_hist / k_ws_scan / k_ws_scatter: one or two passes of
+//      <= 11 bits).  Stability keeps the row order inside a group (ascending, or descending for the
+//      reference's ht_postproc order, server/hasher.h:181-198); the second pass needs no histogram because
+//      the final position of a (low digit, high digit) run IS the CSR offset of that group.
+//      A handle with its own order (order_by) skips the sort: the tuples are gathered through its row list.
+//   2. k_win streams the sorted tuples tile by tile (one bulk copy per tile, double buffered) and evaluates
+//      every requested expression from shared memory: windows look back at most WIN_MAX_W elements into the
+//      halo, running aggregates are segmented scans inside the tile plus a carry that open segments fetch from
+//      the tiles before (each tile publishes its tail aggregate; no tile waits for another one's carry),
+//      `v - scan(v)` and a per-group max / min of the vector are folded in (one atomic per segment and tile).
+//
+// Algorithmic bytes per row: 4 (gid) + 4 per value column read, outputs written once; the sort adds
+// 2 x (16 + 16) bytes of tuple traffic.
+#include "window.cuh"
+#include "groupby.cuh"
+#include "stream.cuh"
+#include "sort.cuh"
+#include <algorithm>
+#include <cstring>
+
+namespace aq {
+
+// ====================================================================================================
+// 1. stable radix scatter of (gid, v0, v1, v2) tuples
+// ====================================================================================================
+constexpr int WS_THREADS = 512;
+constexpr int WS_WARPS = WS_THREADS / 32;
+constexpr int WS_RPT = 8;
+constexpr int WS_T = WS_THREADS * WS_RPT;         // 4096 tuples per tile
+constexpr uint32_t WS_MAXBITS = 11;
+
+struct WsArgs {
+    uint32_t n, bins, shift;          // digit = (gid >> shift) & (bins - 1); bins is a power of two >= 32
+    int pass;                         // 1: source = columns in table order; 2: source = tuples of pass 1
+    int reverse;                      // pass 1: element i of the processing order is row n-1-i
+    const uint32_t* gid;
+    const uint32_t* col[WIN_MAX_COLS];
+    int ncols;
+    const uint4* in;
+    uint4* out;
+    const uint32_t* base;             // pass 1: [nchunks][bins] first output position of (chunk, digit); pass 2: CSR offsets
+    const uint32_t* bstart;           // pass 2: [nchunks + 1] bucket boundaries in `in`
+    uint32_t chunk_rows, nchunks;
+    uint32_t b1, ngroups;             // pass 2: gid = digit << b1 | chunk
+    uint32_t* ticket;
+};
+
+__device__ __forceinline__ uint32_t ws_row(const WsArgs& A, uint32_t i) { return A.reverse ? A.n - 1u - i : i; }
+
+// per-chunk digit histogram of pass 1
+__global__ void __launch_bounds__(WS_THREADS)
+k_ws_hist(const WsArgs A, uint32_t* __restrict__ H) {
+    extern __shared__ uint32_t ws_h[];
+    for (uint32_t c = blockIdx.x; c < A.nchunks; c += gridDim.x) {
+        for (uint32_t d = threadIdx.x; d < A.bins; d += WS_THREADS) ws_h[d] = 0u;
+        __syncthreads();
+        const uint32_t lo = c * A.chunk_rows, hi = min(A.n, lo + A.chunk_rows);
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += WS_THREADS)
+            atomicAdd(&ws_h[(ld_stream_u32(A.gid + ws_row(A, i)) >> A.shift) & (A.bins - 1u)], 1u);
+        __syncthreads();
+        for (uint32_t d = threadIdx.x; d < A.bins; d += WS_THREADS) H[size_t(c) * A.bins + d] = ws_h[d];
+        __syncthreads();
+    }
+}
+
+// H[c][d] := first output position of (chunk c, digit d); bstart[d] := start of digit d's bucket
+__global__ void __launch_bounds__(1024)
+k_ws_scan(uint32_t* __restrict__ H, const uint32_t nchunks, const uint32_t bins, uint32_t* __restrict__ bstart, const uint32_t n) {
+    __shared__ uint32_t tot[1u << WS_MAXBITS];
+    __shared__ uint32_t wsum[32];
+    for (uint32_t d = threadIdx.x; d < bins; d += 1024) {
+        uint32_t run = 0;
+        for (uint32_t c = 0; c < nchunks; ++c) { const uint32_t t = H[size_t(c) * bins + d]; H[size_t(c) * bins + d] = run; run += t; }
+        tot[d] = run;
+    }
+    __syncthreads();
+    // exclusive scan of tot[0..bins): PER consecutive digits per thread
+    const uint32_t PER = (bins + 1023u) / 1024u;
+    uint32_t loc[2] = {0, 0}, sum = 0;
+    for (uint32_t k = 0; k < PER; ++k) { const uint32_t d = threadIdx.x * PER + k; loc[k] = d < bins ? tot[d] : 0u; sum += loc[k]; }
+    uint32_t x = sum;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= (uint32_t)s) x += y; }
+    if (lane == 31) wsum[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t v = wsum[lane], sc = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, s); if (lane >= (uint32_t)s) sc += y; }
+        wsum[lane] = sc - v;
+    }
+    __syncthreads();
+    uint32_t ex = wsum[wid] + x - sum;
+    for (uint32_t k = 0; k < PER; ++k) { const uint32_t d = threadIdx.x * PER + k; if (d < bins) { tot[d] = ex; bstart[d] = ex; } ex += loc[k]; }
+    if (threadIdx.x == 0) bstart[bins] = n;
+    __syncthreads();
+    for (uint32_t d = threadIdx.x; d < bins; d += 1024) {
+        const uint32_t b = tot[d];
+        for (uint32_t c = 0; c < nchunks; ++c) H[size_t(c) * bins + d] += b;
+    }
+}
+
+// dynamic shared memory: stage[WS_T] uint4 | soff[bins] loff[bins] gpos[bins] u32 | whist[WS_WARPS][bins] u16
+static size_t ws_smem(uint32_t bins) { return size_t(WS_T) * 16 + size_t(bins) * 12 + size_t(WS_WARPS) * bins * 2 + 256; }
+
+__global__ void __launch_bounds__(WS_THREADS, 2)
+k_ws_scatter(const WsArgs A) {
+    extern __shared__ __align__(16) unsigned char ws_sm[];
+    uint4* const stage = reinterpret_cast<uint4*>(ws_sm);
+    uint32_t* const soff = reinterpret_cast<uint32_t*>(stage + WS_T);
+    uint32_t* const loff = soff + A.bins;
+    uint32_t* const gpos = loff + A.bins;
+    unsigned short* const whist = reinterpret_cast<unsigned short*>(gpos + A.bins);
+    uint32_t* const wsum = reinterpret_cast<uint32_t*>(whist + size_t(WS_WARPS) * A.bins);   // 32 words + chunk id
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    const uint32_t bins = A.bins, dmask = bins - 1u;
+    const uint32_t PER = (bins + WS_THREADS - 1u) / WS_THREADS;          // consecutive digits per thread (<= 4)
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) wsum[40] = atomicAdd(A.ticket, 1u);
+        __syncthreads();
+        const uint32_t c = wsum[40];
+        if (c >= A.nchunks) return;
+        uint32_t lo, hi;
+        if (A.pass == 1) { lo = c * A.chunk_rows; hi = min(A.n, lo + A.chunk_rows); }
+        else { lo = A.bstart[c]; hi = A.bstart[c + 1]; }
+        for (uint32_t d = tid; d < bins; d += WS_THREADS) {
+            if (A.pass == 1) soff[d] = A.base[size_t(c) * bins + d];
+            else { const uint32_t g = (d << A.b1) | c; soff[d] = g < A.ngroups ? A.base[g] : 0u; }
+        }
+        for (uint32_t i = tid; i < WS_WARPS * bins / 2u; i += WS_THREADS) reinterpret_cast<uint32_t*>(whist)[i] = 0u;
+        __syncthreads();
+        for (uint32_t tlo = lo; tlo < hi; tlo += WS_T) {
+            const uint32_t nvalid = min((uint32_t)WS_T, hi - tlo);
+            // ---- digits of this warp's 256 consecutive elements, stable rank inside the warp's share
+            uint32_t dg[WS_RPT], rk[WS_RPT];
+#pragma unroll
+            for (int r = 0; r < WS_RPT; ++r) {
+                const uint32_t e = wid * (32u * WS_RPT) + r * 32u + lane;
+                dg[r] = 0xffffffffu;
+                if (e < nvalid) {
+                    const uint32_t g = A.pass == 1 ? ld_stream_u32(A.gid + ws_row(A, tlo + e)) : __ldg(reinterpret_cast<const uint32_t*>(A.in + tlo + e));
+                    dg[r] = (g >> A.shift) & dmask;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < WS_RPT; ++r) {
+                const uint32_t peers = __match_any_sync(0xffffffffu, dg[r]);
+                const uint32_t before = __popc(peers & ((1u << lane) - 1u));
+                uint32_t old = 0;
+                if (before == 0 && dg[r] != 0xffffffffu) {
+                    unsigned short* hcell = whist + size_t(wid) * bins + dg[r];
+                    old = *hcell;
+                    *hcell = (unsigned short)(old + __popc(peers));
+                }
+                old = __shfl_sync(0xffffffffu, old, __ffs(peers) - 1);
+                rk[r] = old + before;
+                __syncwarp();
+            }
+            __syncthreads();
+            // ---- per digit: exclusive prefix over the warps, tile count; exclusive scan of the counts over the digits
+            uint32_t cnt[4] = {0, 0, 0, 0}, sum = 0;
+            for (uint32_t k = 0; k < PER; ++k) {
+                const uint32_t d = tid * PER + k;
+                if (d < bins) {
+                    uint32_t run = 0;
+#pragma unroll
+                    for (int w = 0; w < WS_WARPS; ++w) { unsigned short* hcell = whist + size_t(w) * bins + d; const uint32_t t = *hcell; *hcell = (unsigned short)run; run += t; }
+                    cnt[k] = run;
+                }
+                sum += cnt[k];
+            }
+            uint32_t x = sum;
+#pragma unroll
+            for (int s = 1; s < 32; s <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= (uint32_t)s) x += y; }
+            if (lane == 31) wsum[wid] = x;
+            __syncthreads();
+            if (wid == 0) {
+                uint32_t v = lane < WS_WARPS ? wsum[lane] : 0u, sc = v;
+#pragma unroll
+                for (int s = 1; s < 32; s <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, sc, s); if (lane >= (uint32_t)s) sc += y; }
+                if (lane < WS_WARPS) wsum[lane] = sc - v;
+            }
+            __syncthreads();
+            uint32_t ex = wsum[wid] + x - sum;
+            for (uint32_t k = 0; k < PER; ++k) {
+                const uint32_t d = tid * PER + k;
+                if (d < bins) { loff[d] = ex; gpos[d] = soff[d]; soff[d] += cnt[k]; }
+                ex += cnt[k];
+            }
+            __syncthreads();
+            // ---- tuples into the stage at their sorted place
+#pragma unroll
+            for (int r = 0; r < WS_RPT; ++r) {
+                if (dg[r] == 0xffffffffu) continue;
+                const uint32_t e = wid * (32u * WS_RPT) + r * 32u + lane;
+                uint4 t;
+                if (A.pass == 1) {
+                    const uint32_t row = ws_row(A, tlo + e);
+                    t.x = ld_stream_u32(A.gid + row);
+                    t.y = A.ncols > 0 ? ld_stream_u32(A.col[0] + row) : 0u;
+                    t.z = A.ncols > 1 ? ld_stream_u32(A.col[1] + row) : 0u;
+                    t.w = A.ncols > 2 ? ld_stream_u32(A.col[2] + row) : 0u;
+                } else {
+                    t = __ldg(A.in + tlo + e);
+                }
+                stage[loff[dg[r]] + whist[size_t(wid) * bins + dg[r]] + rk[r]] = t;
+            }
+            __syncthreads();
+            // ---- runs of equal digits out, consecutive threads = consecutive tuples
+            for (uint32_t j = tid; j < nvalid; j += WS_THREADS) {
+                const uint4 t = stage[j];
+                const uint32_t d = (t.x >> A.shift) & dmask;
+                A.out[size_t(gpos[d]) + (j - loff[d])] = t;
+            }
+            for (uint32_t i = tid; i < WS_WARPS * bins / 2u; i += WS_THREADS) reinterpret_cast<uint32_t*>(whist)[i] = 0u;
+            __syncthreads();
+        }
+    }
+}
+
+// a handle with its own row order: tuples straight through its row list
+__global__ void __launch_bounds__(256)
+k_ws_gather(const uint32_t n, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ gid, const uint32_t* __restrict__ c0,
+            const uint32_t* __restrict__ c1, const uint32_t* __restrict__ c2, uint4* __restrict__ out) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const uint32_t row = perm[p];
+        uint4 t;
+        t.x = gid[row]; t.y = c0 ? c0[row] : 0u; t.z = c1 ? c1[row] : 0u; t.w = c2 ? c2[row] : 0u;
+        out[p] = t;
+    }
+}
+
+// ====================================================================================================
+// 2. the streaming window kernel
+// ====================================================================================================
+constexpr int WK_THREADS = 1024;
+constexpr int WK_EPT = 4;
+constexpr int WK_T = WK_THREADS * WK_EPT;          // 4096 elements per tile
+constexpr int WK_H = (int)WIN_MAX_W;               // halo before the tile
+constexpr int WK_STAGE = WK_H + WK_T;              // tuples per stage
+constexpr int WK_MAXRUN = 2;                       // running (unbounded) expressions per call
+
+struct WkOp {
+    int op, vtype, col, minus, reduce, out_type, run;     // run: index among the running expressions or -1
+    uint32_t w;
+    void* out;
+};
+struct WkArgs {
+    uint32_t n, ntiles, ngroups;
+    const uint4* tup;
+    const uint32_t* offsets;
+    int nops, nrun;
+    WkOp ops[WIN_MAX_OPS];
+    uint32_t* tflag;                  // [ntiles] 0 = not published, 1 = no head in the tile, 2 = the tile has a head
+    unsigned long long* tval;         // [ntiles][WK_MAXRUN] tail aggregate (image) of every running expression
+};
+
+enum { WOP_ADD = 0, WOP_MIN = 1, WOP_MAX = 2 };
+__device__ __forceinline__ int wk_kind(int op) { return (op == AQ_SUMS || op == AQ_AVGS) ? WOP_ADD : (op == AQ_MINS ? WOP_MIN : WOP_MAX); }
+
+// accumulator images: ints as long long, floats as double (bit pattern in the 64-bit word)
+template <bool FP> struct WkAcc;
+template <> struct WkAcc<false> {
+    typedef long long T;
+    __device__ static T load(uint32_t raw) { return (long long)(int)raw; }
+    __device__ static T id(int k) { return k == WOP_ADD ? 0ll : (k == WOP_MIN ? 0x7fffffffffffffffLL : (long long)0x8000000000000000ULL); }
+    __device__ static T f(int k, T a, T b) { return k == WOP_ADD ? a + b : (k == WOP_MIN ? (b < a ? b : a) : (b > a ? b : a)); }
+    __device__ static unsigned long long bits(T v) { return (unsigned long long)v; }
+    __device__ static T from(unsigned long long b) { return (long long)b; }
+};
+template <> struct WkAcc<true> {
+    typedef double T;
+    __device__ static T load(uint32_t raw) { return (double)__uint_as_float(raw); }
+    __device__ static T id(int k) {
+        return k == WOP_ADD ? 0.0 : __longlong_as_double(k == WOP_MIN ? 0x7ff0000000000000LL : (long long)0xfff0000000000000ULL);
+    }
+    __device__ static T f(int k, T a, T b) { return k == WOP_ADD ? a + b : (k == WOP_MIN ? (b < a ? b : a) : (b > a ? b : a)); }
+    __device__ static unsigned long long bits(T v) { return (unsigned long long)__double_as_longlong(v); }
+    __device__ static T from(unsigned long long b) { return __longlong_as_double((long long)b); }
+};
+
+struct alignas(16) WkI128 { unsigned long long lo; long long hi; };
+
+struct WkShared {
+    uint64_t full[2];
+    uint32_t wflag[WK_THREADS / 32];
+    unsigned long long wval[WK_THREADS / 32];
+    uint32_t open_len;                            // elements of the tile's first group that lie before the tile
+    uint32_t tile_has_head;
+    unsigned long long carry[WK_MAXRUN];
+    unsigned long long tail[WK_MAXRUN];
+    uint32_t whead[WK_THREADS / 32];
+};
+
+// Block-wide segmented exclusive scan of one (flag, value) pair per thread, threads in element order.
+// flag: the thread's elements contain a head; val: aggregate of its elements after its last head (all of them
+// if it has none).  Returns for this thread: ex_flag = a head lies in an earlier thread, ex_val = aggregate of the
+// elements since that head (or since the tile start).  *tot_flag / *tot_val: the same over the whole block.
+template <bool FP>
+__device__ __forceinline__ void wk_block_segscan(int kind, bool flag, typename WkAcc<FP>::T val, bool& ex_flag, typename WkAcc<FP>::T& ex_val,
+                                                 bool& tot_flag, typename WkAcc<FP>::T& tot_val, WkShared& S) {
+    typedef WkAcc<FP> C;
+    typedef typename C::T T;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    bool f = flag; T v = val;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const bool f2 = __shfl_up_sync(0xffffffffu, (int)f, d) != 0;
+        const unsigned long long b2 = __shfl_up_sync(0xffffffffu, C::bits(v), d);
+        if (lane >= (uint32_t)d) { if (!f) v = C::f(kind, C::from(b2), v); f = f || f2; }
+    }
+    __syncthreads();                              // S.wflag / S.wval free again
+    if (lane == 31) { S.wflag[wid] = f ? 1u : 0u; S.wval[wid] = C::bits(v); }
+    __syncthreads();
+    if (wid == 0) {
+        bool wf = S.wflag[lane] != 0u; T wv = C::from(S.wval[lane]);
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const bool f2 = __shfl_up_sync(0xffffffffu, (int)wf, d) != 0;
+            const unsigned long long b2 = __shfl_up_sync(0xffffffffu, C::bits(wv), d);
+            if (lane >= (uint32_t)d) { if (!wf) wv = C::f(kind, C::from(b2), wv); wf = wf || f2; }
+        }
+        S.wflag[lane] = wf ? 1u : 0u; S.wval[lane] = C::bits(wv);
+    }
+    __syncthreads();
+    bool ef = __shfl_up_sync(0xffffffffu, (int)f, 1) != 0;
+    unsigned long long eb = __shfl_up_sync(0xffffffffu, C::bits(v), 1);
+    T ev = C::from(eb);
+    if (lane == 0) { ef = false; ev = C::id(kind); }
+    if (wid > 0) {
+        const bool pf = S.wflag[wid - 1] != 0u; const T pv = C::from(S.wval[wid - 1]);
+        if (!ef) ev = C::f(kind, pv, ev);
+        ef = ef || pf;
+    }
+    ex_flag = ef; ex_val = ev;
+    tot_flag = S.wflag[WK_THREADS / 32 - 1] != 0u; tot_val = C::from(S.wval[WK_THREADS / 32 - 1]);
+}
+
+__device__ __forceinline__ uint32_t wk_word(const uint4* E, int i, int col) {       // value column `col` of stage element i
+    return reinterpret_cast<const uint32_t*>(E + i)[1 + col];
+}
+
+// one running expression over the tile: scan, carry, output (or the values for a per-group reduce into sred)
+template <bool FP>
+__device__ __forceinline__ void wk_running(const WkArgs& A, const WkOp& o, const uint4* E, const uint32_t tile_lo, const uint32_t nvalid,
+                                           const bool (&head)[WK_EPT], const uint32_t* sidx, int* sred, WkShared& S, bool first_is_head) {
+    typedef WkAcc<FP> C;
+    typedef typename C::T T;
+    const int kind = wk_kind(o.op);
+    const uint32_t i0 = threadIdx.x * WK_EPT;
+    T x[WK_EPT];
+    bool any = false;
+    T run = C::id(kind);
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j) {
+        const uint32_t i = i0 + j;
+        if (i < nvalid) {
+            const T e = C::load(wk_word(E, WK_H + i, o.col));
+            if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+        }
+        x[j] = run;
+    }
+    bool ef, tf; T ev, tv;
+    wk_block_segscan<FP>(kind, any, run, ef, ev, tf, tv, S);
+    const T carry = C::from(S.carry[o.run]);
+    // elements before the first head of the tile continue the open segment
+    T prefix = ef ? ev : (first_is_head ? ev : C::f(kind, carry, ev));
+    bool seen = false;
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j) {
+        const uint32_t i = i0 + j;
+        if (i >= nvalid) break;
+        if (head[j]) seen = true;
+        const T v = seen ? x[j] : C::f(kind, prefix, x[j]);
+        const uint32_t p = tile_lo + i;
+        const uint32_t raw = wk_word(E, WK_H + i, o.col);
+        if (o.op == AQ_SUMS) {
+            if (FP) static_cast<double*>(o.out)[p] = (double)v;
+            else if (o.out_type == AQ_INT128) { WkI128 r; r.lo = (unsigned long long)(long long)v; r.hi = ((long long)v) >> 63; static_cast<WkI128*>(o.out)[p] = r; }
+            else static_cast<long long*>(o.out)[p] = (long long)v;
+        } else if (o.op == AQ_AVGS) {
+            static_cast<double*>(o.out)[p] = (double)v / (double)(sidx[i] + 1u);           // aggregations.h:226
+        } else if (FP) {
+            float f = (float)v;
+            if (o.op == AQ_MAXS && !(f > 1.17549435e-38f)) f = 1.17549435e-38f;             // aggregations.h:111
+            if (o.minus) f = __uint_as_float(raw) - f;
+            if (o.reduce >= 0) sred[i] = __float_as_int(f); else static_cast<float*>(o.out)[p] = f;
+        } else {
+            int r = (int)(long long)v;
+            if (o.minus) r = (int)raw - r;
+            if (o.reduce >= 0) sred[i] = r; else static_cast<int*>(o.out)[p] = r;
+        }
+    }
+}
+
+// per-group max / min of the int32 values in sred (element order): one atomic per segment and tile
+__device__ __forceinline__ void wk_reduce_tile(const WkOp& o, const uint4* E, const uint32_t nvalid, const bool (&head)[WK_EPT],
+                                               const int* sred, WkShared& S) {
+    const int kind = o.reduce == AQ_MAX ? WOP_MAX : WOP_MIN;
+    typedef WkAcc<false> C;
+    const uint32_t i0 = threadIdx.x * WK_EPT;
+    long long x[WK_EPT];
+    bool any = false;
+    long long run = C::id(kind);
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j) {
+        const uint32_t i = i0 + j;
+        if (i < nvalid) {
+            const long long e = (long long)sred[i];
+            if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+        }
+        x[j] = run;
+    }
+    bool ef, tf; long long ev, tv;
+    wk_block_segscan<false>(kind, any, run, ef, ev, tf, tv, S);
+    bool seen = false;
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j) {
+        const uint32_t i = i0 + j;
+        if (i >= nvalid) break;
+        if (head[j]) seen = true;
+        // the last element of a segment inside the tile carries the segment's aggregate over the tile
+        const bool last = (i + 1 == nvalid) || (E[WK_H + i + 1].x != E[WK_H + i].x);
+        if (!last) continue;
+        const long long v = seen ? x[j] : C::f(kind, ev, x[j]);
+        int* dst = static_cast<int*>(o.out) + E[WK_H + i].x;
+        if (kind == WOP_MAX) atomicMax(dst, (int)v); else atomicMin(dst, (int)v);
+    }
+}
+
+template <class T> struct WkLong { typedef long long type; };
+template <> struct WkLong<float> { typedef double type; };
+
+// windowed / neighbour expressions: element e of the tile = r * WK_THREADS + tid (coalesced stores)
+template <class T>
+__device__ __forceinline__ void wk_windowed(const WkOp& o, const uint4* E, const uint32_t tile_lo, const uint32_t nvalid,
+                                            const uint32_t* sidx, int* sred) {
+    typedef typename WkLong<T>::type L;
+    constexpr bool FP = sizeof(L) == 8 && ((T)0.5 != (T)0);
+    auto val = [&](int i) -> T {
+        const uint32_t raw = wk_word(E, i, o.col);
+        return FP ? (T)__uint_as_float(raw) : (T)(int)raw;
+    };
+#pragma unroll
+    for (int r = 0; r < WK_EPT; ++r) {
+        const uint32_t i = r * WK_THREADS + threadIdx.x;
+        if (i >= nvalid) break;
+        const uint32_t p = tile_lo + i;
+        const int s = WK_H + (int)i;
+        const uint32_t idx = sidx[i];                       // index inside the group's row list
+        T res = (T)0;
+        switch (o.op) {
+        case AQ_SUMW: case AQ_AVGW: {                       // aggregations.h:238-249, 258-272: the last min(w, idx+1) elements
+            const uint32_t cnt = min(o.w, idx + 1u);
+            L ws = 0;
+            for (uint32_t j = cnt; j > 0; --j) ws += (L)val(s - (int)j + 1);
+            if (o.op == AQ_AVGW) static_cast<double*>(o.out)[p] = (double)ws / (double)cnt;
+            else if (FP) static_cast<double*>(o.out)[p] = (double)ws;
+            else if (o.out_type == AQ_INT128) { WkI128 q; q.lo = (unsigned long long)(long long)ws; q.hi = ((long long)ws) >> 63; static_cast<WkI128*>(o.out)[p] = q; }
+            else static_cast<long long*>(o.out)[p] = (long long)ws;
+            continue; }
+        case AQ_MINW: case AQ_MAXW: {                       // aggregations.h:127-167: extreme of the last w elements
+            const uint32_t cnt = min(o.w, idx + 1u);
+            T m = val(s - (int)cnt + 1);
+            if (o.op == AQ_MINW) { for (uint32_t j = cnt - 1u; j > 0; --j) { const T e = val(s - (int)j + 1); if (e < m) m = e; } }
+            else                 { for (uint32_t j = cnt - 1u; j > 0; --j) { const T e = val(s - (int)j + 1); if (!(e < m)) m = e; } }
+            res = m;
+            break; }
+        case AQ_DELTAS: res = idx ? (T)(val(s) - val(s - 1)) : (T)0; break;      // aggregations.h:442-446
+        case AQ_PREV: res = idx ? val(s - 1) : val(s); break;                    // aggregations.h:458-462
+        default: break;
+        }
+        if (o.minus) res = (T)(val(s) - res);
+        if (o.reduce >= 0) sred[i] = FP ? __float_as_int((float)res) : (int)res;
+        else static_cast<T*>(o.out)[p] = res;
+    }
+}
+
+// dynamic shared memory: 2 stages of WK_STAGE (+1) tuples | sidx[WK_T] | sred[WK_T]
+constexpr size_t WK_SMEM = size_t(2) * (WK_STAGE + 1) * 16 + size_t(WK_T) * 8;
+
+__global__ void __launch_bounds__(WK_THREADS, 1)
+k_win(const WkArgs A) {
+    extern __shared__ __align__(128) unsigned char wk_sm[];
+    __shared__ WkShared S;
+    uint4* const stage0 = reinterpret_cast<uint4*>(wk_sm);
+    uint32_t* const sidx = reinterpret_cast<uint32_t*>(stage0 + 2 * (WK_STAGE + 1));
+    int* const sred = reinterpret_cast<int*>(sidx + WK_T);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+    if (tid == 0) { mbar_init(&S.full[0], 1); mbar_init(&S.full[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    auto issue = [&](uint32_t tile, int s) {
+        // elements [tile*WK_T - WK_H, tile*WK_T + WK_T] (halo, tile, one element of lookahead), clipped to [0, n)
+        const long long first = (long long)tile * WK_T - WK_H;
+        long long last = (long long)tile * WK_T + WK_T + 1;
+        if (last > (long long)A.n) last = (long long)A.n;
+        const long long lo = first < 0 ? 0 : first;
+        const uint32_t bytes = (uint32_t)(last - lo) * 16u;
+        uint4* dst = stage0 + size_t(s) * (WK_STAGE + 1) + (lo - first);
+        mbar_arrive_expect_tx(&S.full[s], bytes);
+        bulk_g2s(dst, A.tup + lo, bytes, &S.full[s]);
+    };
+    if (tid == 0 && blockIdx.x < A.ntiles) issue(blockIdx.x, 0);
+    uint32_t k = 0;
+    for (uint32_t tile = blockIdx.x; tile < A.ntiles; tile += gridDim.x, ++k) {
+        const int s = (int)(k & 1u);
+        if (tid == 0 && tile + gridDim.x < A.ntiles) issue(tile + gridDim.x, s ^ 1);     // the other stage was released by the barrier below
+        mbar_wait(&S.full[s], (k >> 1) & 1u);
+        const uint4* E = stage0 + size_t(s) * (WK_STAGE + 1);
+        const uint32_t tile_lo = tile * WK_T;
+        const uint32_t nvalid = min((uint32_t)WK_T, A.n - tile_lo);
+        // ---- heads and the index of every element inside its group
+        const uint32_t i0 = tid * WK_EPT;
+        bool head[WK_EPT];
+        int lasth = -1;
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) {
+            const uint32_t i = i0 + j;
+            head[j] = false;
+            if (i < nvalid) {
+                head[j] = (tile_lo + i == 0u) || (E[WK_H + i].x != E[WK_H + i - 1].x);
+                if (head[j]) lasth = (int)i;
+            }
+        }
+        // exclusive max-scan of the last head index over the threads
+        int m = lasth;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, m, d); if (lane >= (uint32_t)d) m = max(m, y); }
+        if (lane == 31) S.whead[wid] = (uint32_t)m;
+        if (tid == 0) {
+            const uint32_t g0 = E[WK_H].x;
+            S.open_len = tile_lo - A.offsets[g0];
+        }
+        __syncthreads();
+        if (wid == 0) {
+            int v = (int)S.whead[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, v, d); if (lane >= (uint32_t)d) v = max(v, y); }
+            S.whead[lane] = (uint32_t)v;                 // inclusive over the warps
+        }
+        __syncthreads();
+        int exh = __shfl_up_sync(0xffffffffu, m, 1);
+        if (lane == 0) exh = -1;
+        if (wid > 0) exh = max(exh, (int)S.whead[wid - 1]);
+        const bool tile_has_head = (int)S.whead[WK_THREADS / 32 - 1] >= 0;
+        const bool first_is_head = (tile_lo == 0u) || (E[WK_H].x != E[WK_H - 1].x);
+        const uint32_t open_len = S.open_len;
+        {
+            int cur = exh;
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) {
+                const uint32_t i = i0 + j;
+                if (i >= nvalid) break;
+                if (head[j]) cur = (int)i;
+                sidx[i] = cur >= 0 ? i - (uint32_t)cur : open_len + i;
+            }
+        }
+        // ---- running expressions: publish this tile's tail aggregates, fetch the carry of an open first segment
+        if (A.nrun > 0) {
+            for (int q = 0; q < A.nops; ++q) {
+                const WkOp& o = A.ops[q];
+                if (o.run < 0) continue;
+                const int kind = wk_kind(o.op);
+                unsigned long long tailbits;
+                if (o.vtype == AQ_FLOAT) {
+                    typedef WkAcc<true> C;
+                    bool any = false; double run = C::id(kind);
+#pragma unroll
+                    for (int j = 0; j < WK_EPT; ++j) {
+                        const uint32_t i = i0 + j;
+                        if (i >= nvalid) break;
+                        const double e = C::load(wk_word(E, WK_H + i, o.col));
+                        if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+                    }
+                    bool ef, tf; double ev, tv;
+                    wk_block_segscan<true>(kind, any, run, ef, ev, tf, tv, S);
+                    tailbits = C::bits(tv);
+                } else {
+                    typedef WkAcc<false> C;
+                    bool any = false; long long run = C::id(kind);
+#pragma unroll
+                    for (int j = 0; j < WK_EPT; ++j) {
+                        const uint32_t i = i0 + j;
+                        if (i >= nvalid) break;
+                        const long long e = C::load(wk_word(E, WK_H + i, o.col));
+                        if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+                    }
+                    bool ef, tf; long long ev, tv;
+                    wk_block_segscan<false>(kind, any, run, ef, ev, tf, tv, S);
+                    tailbits = C::bits(tv);
+                }
+                if (tid == 0) { S.tail[o.run] = tailbits; A.tval[size_t(tile) * WK_MAXRUN + o.run] = tailbits; }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                __threadfence();
+                *reinterpret_cast<volatile uint32_t*>(A.tflag + tile) = tile_has_head ? 2u : 1u;
+                // carry = aggregate of the open segment's elements in the tiles before this one
+                for (int r = 0; r < A.nrun; ++r) S.carry[r] = 0ull;
+                if (!first_is_head && tile > 0) {
+                    bool init[WK_MAXRUN] = {false, false};
+                    for (long long t = (long long)tile - 1; t >= 0; --t) {
+                        uint32_t fl;
+                        uint32_t spins = 0;
+                        do { fl = *reinterpret_cast<volatile uint32_t*>(A.tflag + t); if (++spins > (1u << 28)) __trap(); } while (fl == 0u);
+                        __threadfence();
+                        for (int q = 0; q < A.nops; ++q) {
+                            const WkOp& o = A.ops[q];
+                            if (o.run < 0) continue;
+                            const unsigned long long b = *reinterpret_cast<volatile unsigned long long*>(A.tval + size_t(t) * WK_MAXRUN + o.run);
+                            const int kind = wk_kind(o.op);
+                            if (!init[o.run]) { S.carry[o.run] = b; init[o.run] = true; }
+                            else if (o.vtype == AQ_FLOAT) S.carry[o.run] = WkAcc<true>::bits(WkAcc<true>::f(kind, WkAcc<true>::from(b), WkAcc<true>::from(S.carry[o.run])));
+                            else S.carry[o.run] = WkAcc<false>::bits(WkAcc<false>::f(kind, WkAcc<false>::from(b), WkAcc<false>::from(S.carry[o.run])));
+                        }
+                        if (fl == 2u) break;               // that tile's tail starts at a head: the segment begins there
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        __syncthreads();                                   // sidx complete
+        // ---- the expressions
+        for (int q = 0; q < A.nops; ++q) {
+            const WkOp& o = A.ops[q];
+            if (o.run >= 0) {
+                if (o.vtype == AQ_FLOAT) wk_running<true>(A, o, E, tile_lo, nvalid, head, sidx, sred, S, first_is_head);
+                else wk_running<false>(A, o, E, tile_lo, nvalid, head, sidx, sred, S, first_is_head);
+            } else {
+                if (o.vtype == AQ_FLOAT) wk_windowed<float>(o, E + 0, tile_lo, nvalid, sidx, sred);
+                else wk_windowed<int>(o, E + 0, tile_lo, nvalid, sidx, sred);
+            }
+            if (o.reduce >= 0) {
+                __syncthreads();
+                wk_reduce_tile(o, E, nvalid, head, sred, S);
+                __syncthreads();
+            }
+        }
+        __syncthreads();                                   // stage s may be refilled after the next iteration's issue
+    }
+}
+
+template <class T>
+__global__ void k_fill(T* __restrict__ p, T v, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
+}
+
+// ====================================================================================================
+// host
+// ====================================================================================================
+static bool win_supported(const WinOp& o) {
+    if (o.vtype != AQ_INT32 && o.vtype != AQ_FLOAT) return false;
+    switch (o.op) {
+    case AQ_SUMS: case AQ_AVGS: if (o.minus || o.reduce >= 0) return false; break;
+    case AQ_MINS: case AQ_MAXS: break;
+    case AQ_SUMW: case AQ_AVGW: if (o.minus || o.reduce >= 0 || o.w == 0 || o.w > WIN_MAX_W) return false; break;
+    case AQ_MINW: case AQ_MAXW: if (o.w == 0 || o.w > WIN_MAX_W) return false; break;
+    case AQ_DELTAS: case AQ_PREV: break;
+    default: return false;
+    }
+    if (o.reduce >= 0 && (o.vtype != AQ_INT32 || (o.reduce != AQ_MAX && o.reduce != AQ_MIN))) return false;
+    return true;
+}
+
+int window_fused(const WinGroups& G, const WinOp* ops, int n_ops, bool* handled) {
+    Context& c = ctx();
+    *handled = false;
+    if (n_ops < 1 || n_ops > WIN_MAX_OPS || G.nrows < 2 || G.ngroups == 0) return 0;
+    if (path_disabled("win")) return 0;
+    // ---- value columns
+    const uint32_t* cols[WIN_MAX_COLS] = {nullptr, nullptr, nullptr};
+    int ncols = 0, nrun = 0;
+    WkArgs K;
+    memset(&K, 0, sizeof(K));
+    for (int q = 0; q < n_ops; ++q) {
+        if (!win_supported(ops[q])) return 0;
+        int ci = -1;
+        for (int i = 0; i < ncols; ++i) if (cols[i] == ops[q].v) ci = i;
+        if (ci < 0) { if (ncols == WIN_MAX_COLS) return 0; cols[ncols] = static_cast<const uint32_t*>(ops[q].v); ci = ncols++; }
+        WkOp& o = K.ops[q];
+        o.op = ops[q].op; o.vtype = ops[q].vtype; o.col = ci; o.minus = ops[q].minus; o.reduce = ops[q].reduce;
+        o.out_type = ops[q].out_type; o.w = ops[q].w; o.out = ops[q].out; o.run = -1;
+        if (o.op == AQ_SUMS || o.op == AQ_AVGS || o.op == AQ_MINS || o.op == AQ_MAXS) { if (nrun == WK_MAXRUN) return 0; o.run = nrun++; }
+    }
+    int bits = 0;
+    while ((uint64_t(1) << bits) < uint64_t(G.ngroups)) ++bits;
+    if (bits > 2 * (int)WS_MAXBITS) return 0;
+    const uint32_t n = G.nrows;
+    // ---- 1. tuples in CSR order
+    DevBuf ta, tb, hist, bstart, tick;
+    AQ_TRY(ta.alloc(size_t(n) * 16 + 16));
+    AQ_TRY(tick.alloc_zero(16));
+    const uint4* sorted = nullptr;
+    if (G.perm) {
+        AQ_LAUNCH(k_ws_gather, grid_for(n, 256, 1, 32), 256, 0, n, G.perm, G.gid, cols[0], cols[1], cols[2], ta.as<uint4>());
+        sorted = ta.as<uint4>();
+    } else {
+        WsArgs W;
+        memset(&W, 0, sizeof(W));
+        W.n = n; W.gid = G.gid; W.ncols = ncols; W.ngroups = G.ngroups;
+        for (int i = 0; i < WIN_MAX_COLS; ++i) W.col[i] = cols[i];
+        W.reverse = G.row_order == AQ_ROWS_DESC;
+        const int npass = bits > (int)WS_MAXBITS ? 2 : 1;
+        const uint32_t b1 = npass == 2 ? (uint32_t)(bits + 1) / 2u : (uint32_t)std::max(bits, 5);
+        const uint32_t b2 = npass == 2 ? (uint32_t)std::max(bits - (int)b1, 5) : 0u;
+        // pass 1: digit = low b1 bits, chunks = contiguous shares of the processing order
+        W.pass = 1; W.bins = 1u << b1; W.shift = 0;
+        const uint32_t want_chunks = (uint32_t)c.sm_count * 8u;
+        uint32_t chunk_rows = (n + want_chunks - 1) / want_chunks;
+        chunk_rows = std::max<uint32_t>((chunk_rows + WS_T - 1) / WS_T * WS_T, WS_T);
+        W.chunk_rows = chunk_rows; W.nchunks = (n + chunk_rows - 1) / chunk_rows;
+        AQ_TRY(hist.alloc(size_t(W.nchunks) * W.bins * 4));
+        AQ_TRY(bstart.alloc((size_t(W.bins) + 1) * 4));
+        if (npass == 2) AQ_TRY(tb.alloc(size_t(n) * 16 + 16));
+        static size_t attr = 0;
+        const size_t smem1 = ws_smem(W.bins), smem2 = npass == 2 ? ws_smem(1u << b2) : 0;
+        if (std::max(smem1, smem2) > attr) {
+            AQ_CUDA(cudaFuncSetAttribute(k_ws_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem1, smem2)));
+            attr = std::max(smem1, smem2);
+        }
+        AQ_LAUNCH(k_ws_hist, (int)std::min<uint32_t>(W.nchunks, (uint32_t)c.sm_count * 4), WS_THREADS, size_t(W.bins) * 4, W, hist.as<uint32_t>());
+        AQ_LAUNCH(k_ws_scan, 1, 1024, 0, hist.as<uint32_t>(), W.nchunks, W.bins, bstart.as<uint32_t>(), n);
+        W.base = hist.as<uint32_t>(); W.ticket = tick.as<uint32_t>();
+        W.out = npass == 2 ? tb.as<uint4>() : ta.as<uint4>();
+        AQ_LAUNCH(k_ws_scatter, (int)std::min<uint32_t>(W.nchunks, (uint32_t)c.sm_count * 2), WS_THREADS, smem1, W);
+        if (npass == 2) {
+            // pass 2: chunks = the buckets of pass 1, digit = the high bits; a run's place is its group's CSR offset
+            WsArgs V = W;
+            V.pass = 2; V.in = tb.as<uint4>(); V.out = ta.as<uint4>(); V.bins = 1u << b2; V.shift = b1; V.b1 = b1;
+            V.nchunks = 1u << b1; V.bstart = bstart.as<uint32_t>(); V.base = G.offsets; V.ticket = tick.as<uint32_t>() + 1;
+            AQ_LAUNCH(k_ws_scatter, (int)std::min<uint32_t>(V.nchunks, (uint32_t)c.sm_count * 2), WS_THREADS, smem2, V);
+        }
+        sorted = ta.as<uint4>();
+    }
+    // ---- 2. the expressions
+    K.n = n; K.ntiles = (n + WK_T - 1) / WK_T; K.ngroups = G.ngroups; K.tup = sorted; K.offsets = G.offsets;
+    K.nops = n_ops; K.nrun = nrun;
+    DevBuf tflag, tval;
+    AQ_TRY(tflag.alloc_zero(size_t(K.ntiles) * 4));
+    AQ_TRY(tval.alloc(size_t(K.ntiles) * WK_MAXRUN * 8));
+    K.tflag = tflag.as<uint32_t>(); K.tval = tval.as<unsigned long long>();
+    for (int q = 0; q < n_ops; ++q) {
+        if (ops[q].reduce < 0) continue;
+        const int idv = ops[q].reduce == AQ_MAX ? (int)0x80000000u : 0x7fffffff;
+        AQ_LAUNCH(k_fill<int>, grid_for(G.ngroups, 256, 1, 8), 256, 0, static_cast<int*>(ops[q].out), idv, G.ngroups);
+    }
+    static bool attr_done = false;
+    if (!attr_done) { AQ_CUDA(cudaFuncSetAttribute(k_win, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WK_SMEM)); attr_done = true; }
+    AQ_LAUNCH(k_win, (int)std::min<uint32_t>(K.ntiles, (uint32_t)c.sm_count), WK_THREADS, WK_SMEM, K);
+    *handled = true;
+    return 0;
+}
+
+} // namespace aq

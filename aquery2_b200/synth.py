@@ -85,6 +85,9 @@ def trade_column(name: str, n_total: int, n_sym: int, lo: int = 0, hi: int | Non
     hi = n_total if hi is None else hi
     if name == "time":
         return np.arange(lo + 1, hi + 1, dtype=np.int64).astype(np.int32)
+    if name == "time_shuffled":      # a permutation of 1..n_total (n_total not a multiple of 7): the unsorted variant's time
+        r = np.arange(lo, hi, dtype=np.uint64)
+        return (1 + (r * np.uint64(40353607) + np.uint64(12345)) % np.uint64(n_total)).astype(np.int64).astype(np.int32)
     if name == "sym":
         return _uniform(raw(seed, STREAM["sym"], lo, hi), n_sym).astype(np.int32)
     if name == "quantity":

@@ -214,6 +214,27 @@ int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, cons
  * the CSR layout of engine/ast.py:696-718.  out has nrows cells of out_type. */
 int aqgpu_group_scan(aqgpu_groups_t* g, int op, uint32_t w, int vtype, const void* v,
                      int out_type, void* out);
+
+/* Several vector-valued expressions of one group-by in ONE call -- the body of a generated query such as
+ *   SELECT sym, avgs(5, price), sums(5, quantity), deltas(price), mins(5, price), max(price - mins(price))
+ *   FROM trade GROUP BY sym              (benchmark/quries/Aquery/q7.a, q10.a; tests/moving_avg.a)
+ * which the reference evaluates group by group on gathered vectors (engine/ast.py:696-718).  Each entry is
+ * one aqgpu_group_scan; `minus_from_v` turns it into the element-wise v - scan(v) of server/table.h:820-973
+ * (only for ops whose result has v's type: MINS MAXS MINW MAXW DELTAS PREV) and `reduce` folds the vector into
+ * one cell per group with AQ_MAX / AQ_MIN (server/aggregations.h:71-86) instead of writing it.
+ * Vector results: nrows cells in CSR order (like aqgpu_group_scan); reduced results: ngroups cells of v's type.
+ * All entries share one pass over the rows: they are brought into group order once, with their values. */
+typedef struct aqgpu_window {
+    int op;            /* aqgpu_scan_op */
+    uint32_t w;        /* window length for AQ_SUMW / AVGW / MINW / MAXW / RATIOW, else 0 */
+    int vtype;
+    const void* v;     /* nrows cells, table row order; device or host */
+    int minus_from_v;  /* 0 / 1 */
+    int reduce;        /* -1: vector result; AQ_MAX or AQ_MIN: one cell per group */
+    int out_type;      /* 0 = default of the op (aqgpu_scan_out_type) */
+    void* out;         /* device or host */
+} aqgpu_window_t;
+int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops);
 /* out[offsets[g] + j] = v[row j of group g]  -- the gather col[vecs[g]] of server/table.h:184-189 for
  * ALL groups at once, in the CSR order of the row lists.  out has nrows cells of vtype. */
 int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out);

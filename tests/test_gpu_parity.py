@@ -411,6 +411,15 @@ def test_low_cardinality_speculation_fails(gpu, port):
     t["f"][7] = np.float32(np.inf)
     res = run_query(gpu, t, ["k0"], [("sum", "f")])
     assert np.isinf(res.aggs[0]).sum() == 1
+    # one-word integer cells are chosen from the sampled magnitudes: an unsampled outlier must not wrap a cell
+    t = _lc_table(n, 7, (50,))
+    t["v1"][2_999_998] = 2_000_000_000
+    t["v1"][1_999_998] = -2_000_000_000
+    check_query_vs_oracle(gpu, port, t, ["k0"], [("sum", "v1"), ("avg", "v1"), ("max", "v1")])   # (no squares: int32 overflow is UB in the reference)
+    # sum only (no count requested): empty slots are told apart by the seen marker, ragged tail rows included
+    t = _lc_table(n - 3, 9, (40, 3))
+    check_query_vs_oracle(gpu, port, t, ["k0", "k1"], [("sum", "v1")])
+    check_query_vs_oracle(gpu, port, t, ["k1", "k0"], [("max", "v1"), ("min", "f")])
 
 
 def test_large_integer_sums_low_cardinality(gpu, port):
@@ -545,3 +554,77 @@ def test_gather_and_elementwise_helpers(gpu, port):
     gpu.check(L.aqgpu_avg_finalize(gpu.DOUBLE, s.ctypes.data_as(ctypes.c_void_p), cnt.ctypes.data_as(ctypes.c_void_p),
                                    o.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(1000)))
     assert_same(o, s / cnt, "avg_finalize")
+
+
+# ------------------------------------------------------------------------------------------------
+# several expressions in one call (aqgpu_group_window): fused sort + window kernel vs the oracle
+# ------------------------------------------------------------------------------------------------
+def _window_exprs(t):
+    p, q, f = t["price"], t["quantity"], t["price"].astype(np.float32) * np.float32(0.37)
+    return [("avgw", p, 5), ("sumw", q, 5), ("deltas", p), ("minw", p, 5), ("mins", p, 0, True, "max"),
+            ("maxs", f), ("sums", q), ("avgs", f)], f
+
+
+def _check_window(gpu, port, h, t, off, perm, ng):
+    exprs, f = _window_exprs(t)
+    for lo in (0, 5):                                         # at most 3 value columns and 2 running expressions per fused call
+        part = exprs[lo:lo + 5] if lo == 0 else exprs[5:]
+        got = h.window(part)
+        for e, g in zip(part, got):
+            op, v = e[0], e[1]
+            w = e[2] if len(e) > 2 else 0
+            want = port.scan(op, v, off, perm, w=w, raw128=True)
+            if len(e) > 3 and e[3]:
+                want = (v[perm] - want).astype(v.dtype)
+            if len(e) > 4 and e[4]:
+                ident = np.iinfo(np.int32).min if e[4] == "max" else np.iinfo(np.int32).max
+                red = np.full(ng, ident, dtype=v.dtype)
+                fn = np.maximum if e[4] == "max" else np.minimum
+                fn.at(red, np.repeat(np.arange(ng), np.diff(off)), want)
+                want = red
+            assert_same(g, want, f"window {op}({w})", scale=float(np.abs(v).max()))
+
+
+@pytest.mark.parametrize("n,nsym", [(300_000, 1000), (200_000, 70_000), (50_000, 3), (9_000, 1), (1_000_003, 5000)])
+def test_fused_window_vs_oracle(gpu, port, n, nsym):
+    """window.cu: one or two radix passes (nsym below / above 2048), groups spanning many tiles (nsym 1 and 3), ragged tails"""
+    t = synth.trade_table(n, nsym, seed=11)
+    h = gpu.Groups([t["sym"]])
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    assert h.ngroups == ng
+    _check_window(gpu, port, h, t, off, perm, ng)
+    h.free()
+    h = gpu.Groups([t["sym"]], row_order=gpu.ROWS_ASC)       # time-ascending row lists (presorted table)
+    asc = np.concatenate([perm[off[g]:off[g + 1]][::-1] for g in range(ng)]).astype(np.uint32)
+    _check_window(gpu, port, h, t, off, asc, ng)
+    h.free()
+
+
+def test_fused_window_after_order_by(gpu, port):
+    """unsorted table + ASSUMING ASC time: the handle's own row lists feed the same kernel"""
+    n, nsym = 150_000, 800
+    t = synth.trade_table(n, nsym, seed=12)
+    tm = np.random.default_rng(3).permutation(n).astype(np.int32)
+    h = gpu.Groups([t["sym"]], row_order=gpu.ROWS_ASC)
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    h.order_by([tm], desc=[0])
+    _, p3 = h.csr()
+    _check_window(gpu, port, h, t, off, p3, ng)
+    h.free()
+
+
+def test_window_unfused_fallback(gpu, port):
+    """expressions the fused kernel does not serve (64-bit values, long windows, ratios) take the per-op path"""
+    n, nsym = 40_000, 50
+    t = synth.trade_table(n, nsym, seed=13)
+    big = t["price"].astype(np.int64) * 3_000_000_007
+    h = gpu.Groups([t["sym"]])
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    got = h.window([("sumw", big, 7), ("minw", t["price"], 500), ("mins", big, 0, True, "max"), ("ratiow", t["price"], 2)])
+    assert_same(got[0], port.scan("sumw", big, off, perm, w=7, raw128=True), "sumw i64")
+    assert_same(got[1], port.scan("minw", t["price"], off, perm, w=500), "minw 500")
+    e = big[perm] - port.scan("mins", big, off, perm)
+    want = np.array([e[off[g]:off[g + 1]].max() for g in range(ng)], dtype=np.int64)
+    assert_same(got[2], want, "max(v - mins(v)) i64")
+    assert_same(got[3], port.scan("ratiow", t["price"], off, perm, w=2), "ratiow")
+    h.free()

@@ -172,6 +172,8 @@ struct PlanHints {                        // what the generic paths get when the
 int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max,
                       uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used,
                       PlanHints* hints_out);
+int plan_hints_only(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max, uint32_t groups_hint,
+                    PlanHints* out);
 
 // Result of the hash phase, consumed by emit / handle construction.
 struct HashResult {

@@ -37,6 +37,64 @@ __global__ void k_map_gid(const uint32_t* __restrict__ row_slot, const uint32_t*
         gid[i] = slot_gid[row_slot[i]];
 }
 
+// ---- direct build: ONE 32-bit key column whose (sampled, verified) value range is small enough for a table ----
+// The reference's PerfectHashTable idea (server/hasher.h:226-243) with the contract's order: slot = key - lo,
+// one pass counts the rows of every slot and keeps its smallest row (a plain read after the first few hundred
+// thousand rows: the table is L2-resident), the non-empty slots are ranked by that first row (= insertion index
+// of m_values, server/unordered_dense.h:1142-1146), and a second pass maps every row to its group id.
+// A key outside the sampled range raises FLAG_ABORT and the build falls back to the hash path.
+constexpr uint32_t GD_MAX_RANGE = 1u << 24;
+__global__ void __launch_bounds__(256)
+k_gd_count(const uint32_t* __restrict__ key, const uint32_t n, const uint32_t lo, const uint32_t range, uint32_t* __restrict__ cnt,
+           uint32_t* __restrict__ first, uint32_t* __restrict__ flags) {
+    const uint32_t nq = n >> 2;
+    bool bad = false;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += gridDim.x * blockDim.x) {
+        const uint4 k4 = __ldg(reinterpret_cast<const uint4*>(key) + q);
+        const uint32_t kv[4] = {k4.x, k4.y, k4.z, k4.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t d = kv[j] - lo, row = q * 4u + j;
+            if (d >= range) { bad = true; continue; }
+            atomicAdd(cnt + d, 1u);
+            if (row < *reinterpret_cast<volatile uint32_t*>(first + d)) atomicMin(first + d, row);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u)) {
+        const uint32_t row = (n & ~3u) + threadIdx.x, d = key[row] - lo;
+        if (d >= range) bad = true;
+        else { atomicAdd(cnt + d, 1u); atomicMin(first + d, row); }
+    }
+    if (bad) atomicExch(flags + FLAG_ABORT, 3u);
+}
+__global__ void k_gd_ngroups(const uint32_t* __restrict__ cnt, const uint32_t range, uint32_t* __restrict__ flags) {
+    uint32_t c = 0;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < range; s += gridDim.x * blockDim.x) c += cnt[s] != 0u;
+#pragma unroll
+    for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(flags + FLAG_NGROUPS, c);
+}
+__global__ void k_gd_emit(const uint32_t* __restrict__ order, const uint32_t ng, const uint32_t lo, const uint32_t* __restrict__ first,
+                          const uint32_t* __restrict__ cnt, uint32_t* __restrict__ keys, uint32_t* __restrict__ first_row,
+                          uint32_t* __restrict__ counts, uint32_t* __restrict__ gid_of_slot) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ng; i += gridDim.x * blockDim.x) {
+        const uint32_t s = order[i];
+        keys[i] = lo + s; first_row[i] = first[s]; counts[i] = cnt[s]; gid_of_slot[s] = i;
+    }
+}
+__global__ void __launch_bounds__(256)
+k_gd_gid(const uint32_t* __restrict__ key, const uint32_t n, const uint32_t lo, const uint32_t* __restrict__ gid_of_slot, uint32_t* __restrict__ gid) {
+    const uint32_t nq = n >> 2;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += gridDim.x * blockDim.x) {
+        const uint4 k4 = __ldg(reinterpret_cast<const uint4*>(key) + q);
+        uint4 o;
+        o.x = __ldg(gid_of_slot + (k4.x - lo)); o.y = __ldg(gid_of_slot + (k4.y - lo));
+        o.z = __ldg(gid_of_slot + (k4.z - lo)); o.w = __ldg(gid_of_slot + (k4.w - lo));
+        reinterpret_cast<uint4*>(gid)[q] = o;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u)) { const uint32_t row = (n & ~3u) + threadIdx.x; gid[row] = gid_of_slot[key[row] - lo]; }
+}
+
 static int ensure_offsets(aqgpu_groups* g) {
     if (g->has_offsets) return 0;
     AQ_TRY(g->offsets.alloc(size_t(g->ngroups + 1) * 4));
@@ -149,6 +207,44 @@ static int window_post(int minus, int reduce, const void* gv, void* vec, const u
 } // namespace aq
 
 
+static int build_direct(aqgpu_groups* g, const KeyCols& kc, const PlanHints& ph, bool* used) {
+    *used = false;
+    Context& c = ctx();
+    const uint32_t n = g->nrows;
+    if (kc.n != 1 || (kc.type[0] != AQ_INT32 && kc.type[0] != AQ_UINT32) || !ph.have_bounds || n < (1u << 20)) return 0;
+    if (path_disabled("gd") || (reinterpret_cast<uintptr_t>(kc.col[0].d) & 15)) return 0;
+    const long long span = ph.kmax[0] - ph.kmin[0] + 1;
+    if (span < 1 || span > (long long)GD_MAX_RANGE || span > 4ll * n) return 0;
+    const uint32_t range = (uint32_t)span, lo = (uint32_t)ph.kmin[0];
+    const uint32_t* key = static_cast<const uint32_t*>(kc.col[0].d);
+    DevBuf cnt, first, order, gos;
+    AQ_TRY(cnt.alloc_zero(size_t(range) * 4));
+    AQ_TRY(first.alloc(size_t(range) * 4));
+    AQ_TRY(order.alloc(size_t(range) * 4));
+    AQ_TRY(gos.alloc(size_t(range) * 4));
+    AQ_CUDA(cudaMemsetAsync(first.p, 0xff, size_t(range) * 4, c.stream));
+    AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
+    AQ_LAUNCH(k_gd_count, c.sm_count * 8, 256, 0, key, n, lo, range, cnt.as<uint32_t>(), first.as<uint32_t>(), c.d_flags);
+    AQ_LAUNCH(k_gd_ngroups, grid_for(range, 256, 1, 4), 256, 0, cnt.as<uint32_t>(), range, c.d_flags);
+    AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    if (c.h_flags[FLAG_ABORT] != 0) return 0;                      // a key outside the sampled range: hash path
+    const uint32_t ng = c.h_flags[FLAG_NGROUPS];
+    SortJob job;                                                  // slots by first row; empty slots (0xffffffff) go last
+    job.n = range; job.rows_in = nullptr; job.col = first.as<uint32_t>(); job.key_bits = 32; job.rows_out = order.as<uint32_t>();
+    AQ_TRY(sort_rows_by_key(job));
+    g->ngroups = ng;
+    AQ_TRY(g->keys[0].alloc(size_t(ng) * 4));
+    AQ_TRY(g->first_row.alloc(size_t(ng) * 4));
+    AQ_TRY(g->counts.alloc_zero(size_t(ng + 1) * 4));
+    AQ_TRY(g->gid.alloc(size_t(n) * 4));
+    if (ng) AQ_LAUNCH(k_gd_emit, grid_for(ng, 256, 1, 8), 256, 0, order.as<uint32_t>(), ng, lo, first.as<uint32_t>(), cnt.as<uint32_t>(),
+                      g->keys[0].as<uint32_t>(), g->first_row.as<uint32_t>(), g->counts.as<uint32_t>(), gos.as<uint32_t>());
+    AQ_LAUNCH(k_gd_gid, c.sm_count * 8, 256, 0, key, n, lo, gos.as<uint32_t>(), g->gid.as<uint32_t>());
+    *used = true;
+    return 0;
+}
+
 extern "C" {
 
 int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
@@ -171,8 +267,21 @@ int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys
     }
     KeyCols kc;
     AQ_TRY(kc.bind(keys, key_types, nkeys, nrows));
+    PlanHints ph;                         // sampled group estimate / key bounds when the caller gave none (plan.cu)
+    AQ_TRY(plan_hints_only(kc, nrows, key_min, key_max, groups_hint, &ph));
     KeySpec ks;
-    AQ_TRY(kc.make_spec(key_min, key_max, ks));
+    if (!(key_min && key_max) && ph.have_bounds) AQ_TRY(kc.make_spec(ph.kmin, ph.kmax, ks));
+    else AQ_TRY(kc.make_spec(key_min, key_max, ks));
+    groups_hint = ph.groups_hint;
+    {
+        bool direct = false;
+        AQ_TRY(build_direct(g, kc, ph, &direct));
+        if (direct) {
+            AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+            guard.g = nullptr; *out = g;
+            return 0;
+        }
+    }
     AggPlan plan;
     plan.emit.row_order = row_order;
     if (plan.add_count() < 0 || plan.add_maxrow() < 0) return fail("internal: accumulator allocation");

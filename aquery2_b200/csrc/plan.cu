@@ -213,6 +213,50 @@ static int sample_inputs(const KeyCols& kc, uint32_t nrows, const AggPlan& plan,
     return 0;
 }
 
+// what the generic paths get: the sampled group estimate and key bounds (expanded: a sample rarely sees the extreme keys)
+static void fill_hints(const PlanStats& st, const KeyCols& kc, uint32_t nrows, uint32_t groups_hint, PlanHints& out) {
+    PlanHints* hints_out = &out;
+    // ---- generic paths: hand over what the sample says (expanded: a sample rarely sees the extreme keys)
+    {
+        hints_out->groups_hint = groups_hint;
+        if (!groups_hint && st.est_groups > 0.0) {
+            const double g = st.est_groups * 1.125 + 64.0;
+            hints_out->groups_hint = (uint32_t)(g < (double)nrows ? g : (double)nrows);
+        }
+        hints_out->have_bounds = false;
+        if (st.have_bounds) {
+            hints_out->have_bounds = true;
+            for (int k = 0; k < kc.n; ++k) {
+                long long lo = st.kmin[k], hi = st.kmax[k];
+                if (!st.bounds_given) {
+                    const long long margin = (hi - lo) / 64 + 16;
+                    const long long tlo = kc.type[k] == AQ_INT32 ? -2147483648LL : 0LL, thi = kc.type[k] == AQ_INT32 ? 2147483647LL : 4294967295LL;
+                    lo = lo - margin < tlo ? tlo : lo - margin;
+                    hi = hi + margin > thi ? thi : hi + margin;
+                }
+                hints_out->kmin[k] = lo; hints_out->kmax[k] = hi;
+            }
+        }
+    }
+}
+
+// Sampling only (aqgpu_groupby_build): group estimate + key bounds for hash_aggregate.
+int plan_hints_only(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max, uint32_t groups_hint,
+                    PlanHints* out) {
+    out->groups_hint = groups_hint; out->have_bounds = false;
+    if (nrows < 4096 || path_disabled("plan")) return 0;
+    PlanStats st;
+    if (key_min && key_max) {
+        st.have_bounds = st.bounds_given = true;
+        for (int k = 0; k < kc.n; ++k) { st.kmin[k] = key_min[k]; st.kmax[k] = key_max[k]; }
+    }
+    if (groups_hint) st.est_groups = (double)groups_hint;
+    AggPlan none;
+    AQ_TRY(sample_inputs(kc, nrows, none, st));
+    fill_hints(st, kc, nrows, groups_hint, *out);
+    return 0;
+}
+
 int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const int64_t* key_max,
                       uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used,
                       PlanHints* hints_out) {
@@ -241,28 +285,7 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
         AQ_TRY(run_hcfp(kc, nrows, plan, sink, ngroups, used));
         if (*used) return 0;
     }
-    // ---- generic paths: hand over what the sample says (expanded: a sample rarely sees the extreme keys)
-    if (hints_out) {
-        hints_out->groups_hint = groups_hint;
-        if (!groups_hint && st.est_groups > 0.0) {
-            const double g = st.est_groups * 1.125 + 64.0;
-            hints_out->groups_hint = (uint32_t)(g < (double)nrows ? g : (double)nrows);
-        }
-        hints_out->have_bounds = false;
-        if (st.have_bounds) {
-            hints_out->have_bounds = true;
-            for (int k = 0; k < kc.n; ++k) {
-                long long lo = st.kmin[k], hi = st.kmax[k];
-                if (!st.bounds_given) {
-                    const long long margin = (hi - lo) / 64 + 16;
-                    const long long tlo = kc.type[k] == AQ_INT32 ? -2147483648LL : 0LL, thi = kc.type[k] == AQ_INT32 ? 2147483647LL : 4294967295LL;
-                    lo = lo - margin < tlo ? tlo : lo - margin;
-                    hi = hi + margin > thi ? thi : hi + margin;
-                }
-                hints_out->kmin[k] = lo; hints_out->kmax[k] = hi;
-            }
-        }
-    }
+    if (hints_out) fill_hints(st, kc, nrows, groups_hint, *hints_out);
     return 0;
 }
 

@@ -346,78 +346,67 @@ __device__ __forceinline__ void wk_block_segscan(int kind, bool flag, typename W
     tot_flag = S.wflag[WK_THREADS / 32 - 1] != 0u; tot_val = C::from(S.wval[WK_THREADS / 32 - 1]);
 }
 
-__device__ __forceinline__ uint32_t wk_word(const uint4* E, int i, int col) {       // value column `col` of stage element i
-    return reinterpret_cast<const uint32_t*>(E + i)[1 + col];
-}
+// ---- per-thread view of a tile: WK_EPT consecutive elements, everything in registers ---------------------
+struct WkThread {
+    uint32_t base;                 // index of the thread's first element in the SoA arrays (halo included)
+    uint32_t p0;                   // its CSR position
+    uint32_t nval;                 // how many of its elements exist (ragged last tile)
+    bool head[WK_EPT];
+    uint32_t idx[WK_EPT];          // index inside the group's row list
+    bool last[WK_EPT];             // last element of its segment inside this tile
+    uint32_t gid[WK_EPT];
+};
 
-// one running expression over the tile: scan, carry, output (or the values for a per-group reduce into sred)
-template <bool FP>
-__device__ __forceinline__ void wk_running(const WkArgs& A, const WkOp& o, const uint4* E, const uint32_t tile_lo, const uint32_t nvalid,
-                                           const bool (&head)[WK_EPT], const uint32_t* sidx, int* sred, WkShared& S, bool first_is_head) {
-    typedef WkAcc<FP> C;
-    typedef typename C::T T;
-    const int kind = wk_kind(o.op);
-    const uint32_t i0 = threadIdx.x * WK_EPT;
-    T x[WK_EPT];
-    bool any = false;
-    T run = C::id(kind);
+template <class T> __device__ __forceinline__ T wk_val(uint32_t raw);
+template <> __device__ __forceinline__ int wk_val<int>(uint32_t raw) { return (int)raw; }
+template <> __device__ __forceinline__ float wk_val<float>(uint32_t raw) { return __uint_as_float(raw); }
+template <class T> struct WkLong { typedef long long type; };
+template <> struct WkLong<float> { typedef double type; };
+
+// WK_EPT consecutive result cells of one thread: vector stores when all four exist
+__device__ __forceinline__ unsigned long long wk_bits64(double v) { return (unsigned long long)__double_as_longlong(v); }
+__device__ __forceinline__ unsigned long long wk_bits64(long long v) { return (unsigned long long)v; }
+__device__ __forceinline__ uint32_t wk_bits32(int v) { return (uint32_t)v; }
+__device__ __forceinline__ uint32_t wk_bits32(float v) { return __float_as_uint(v); }
+template <class V> __device__ __forceinline__ void wk_store4_32(V* dst, const V (&x)[WK_EPT], uint32_t nval) {
+    if (nval == WK_EPT) *reinterpret_cast<uint4*>(dst) = make_uint4(wk_bits32(x[0]), wk_bits32(x[1]), wk_bits32(x[2]), wk_bits32(x[3]));
+    else {
 #pragma unroll
-    for (int j = 0; j < WK_EPT; ++j) {
-        const uint32_t i = i0 + j;
-        if (i < nvalid) {
-            const T e = C::load(wk_word(E, WK_H + i, o.col));
-            if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
-        }
-        x[j] = run;
-    }
-    bool ef, tf; T ev, tv;
-    wk_block_segscan<FP>(kind, any, run, ef, ev, tf, tv, S);
-    const T carry = C::from(S.carry[o.run]);
-    // elements before the first head of the tile continue the open segment
-    T prefix = ef ? ev : (first_is_head ? ev : C::f(kind, carry, ev));
-    bool seen = false;
-#pragma unroll
-    for (int j = 0; j < WK_EPT; ++j) {
-        const uint32_t i = i0 + j;
-        if (i >= nvalid) break;
-        if (head[j]) seen = true;
-        const T v = seen ? x[j] : C::f(kind, prefix, x[j]);
-        const uint32_t p = tile_lo + i;
-        const uint32_t raw = wk_word(E, WK_H + i, o.col);
-        if (o.op == AQ_SUMS) {
-            if (FP) static_cast<double*>(o.out)[p] = (double)v;
-            else if (o.out_type == AQ_INT128) { WkI128 r; r.lo = (unsigned long long)(long long)v; r.hi = ((long long)v) >> 63; static_cast<WkI128*>(o.out)[p] = r; }
-            else static_cast<long long*>(o.out)[p] = (long long)v;
-        } else if (o.op == AQ_AVGS) {
-            static_cast<double*>(o.out)[p] = (double)v / (double)(sidx[i] + 1u);           // aggregations.h:226
-        } else if (FP) {
-            float f = (float)v;
-            if (o.op == AQ_MAXS && !(f > 1.17549435e-38f)) f = 1.17549435e-38f;             // aggregations.h:111
-            if (o.minus) f = __uint_as_float(raw) - f;
-            if (o.reduce >= 0) sred[i] = __float_as_int(f); else static_cast<float*>(o.out)[p] = f;
-        } else {
-            int r = (int)(long long)v;
-            if (o.minus) r = (int)raw - r;
-            if (o.reduce >= 0) sred[i] = r; else static_cast<int*>(o.out)[p] = r;
-        }
+        for (int j = 0; j < WK_EPT; ++j) if ((uint32_t)j < nval) dst[j] = x[j];
     }
 }
+template <class V> __device__ __forceinline__ void wk_store4_64(V* dst, const V (&x)[WK_EPT], uint32_t nval) {
+    if (nval == WK_EPT) {
+        reinterpret_cast<ulonglong2*>(dst)[0] = make_ulonglong2(wk_bits64(x[0]), wk_bits64(x[1]));
+        reinterpret_cast<ulonglong2*>(dst)[1] = make_ulonglong2(wk_bits64(x[2]), wk_bits64(x[3]));
+    } else {
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) if ((uint32_t)j < nval) dst[j] = x[j];
+    }
+}
+__device__ __forceinline__ void wk_store4(int* dst, const int (&x)[WK_EPT], uint32_t nval) { wk_store4_32(dst, x, nval); }
+__device__ __forceinline__ void wk_store4(float* dst, const float (&x)[WK_EPT], uint32_t nval) { wk_store4_32(dst, x, nval); }
+__device__ __forceinline__ void wk_store4(double* dst, const double (&x)[WK_EPT], uint32_t nval) { wk_store4_64(dst, x, nval); }
+__device__ __forceinline__ void wk_store4(long long* dst, const long long (&x)[WK_EPT], uint32_t nval) { wk_store4_64(dst, x, nval); }
+// sums of 32-bit integers as __int128 cells (sign-extended)
+__device__ __forceinline__ void wk_store4_i128(WkI128* dst, const long long (&x)[WK_EPT], uint32_t nval) {
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j)
+        if ((uint32_t)j < nval) reinterpret_cast<ulonglong2*>(dst)[j] = make_ulonglong2((unsigned long long)x[j], (unsigned long long)(x[j] >> 63));
+}
 
-// per-group max / min of the int32 values in sred (element order): one atomic per segment and tile
-__device__ __forceinline__ void wk_reduce_tile(const WkOp& o, const uint4* E, const uint32_t nvalid, const bool (&head)[WK_EPT],
-                                               const int* sred, WkShared& S) {
+// per-group max / min of the thread values r[] (int32): one atomic per segment and tile
+__device__ __forceinline__ void wk_reduce_tile(const WkOp& o, const WkThread& t, const int (&r)[WK_EPT], WkShared& S) {
     const int kind = o.reduce == AQ_MAX ? WOP_MAX : WOP_MIN;
     typedef WkAcc<false> C;
-    const uint32_t i0 = threadIdx.x * WK_EPT;
     long long x[WK_EPT];
     bool any = false;
     long long run = C::id(kind);
 #pragma unroll
     for (int j = 0; j < WK_EPT; ++j) {
-        const uint32_t i = i0 + j;
-        if (i < nvalid) {
-            const long long e = (long long)sred[i];
-            if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+        if ((uint32_t)j < t.nval) {
+            const long long e = (long long)r[j];
+            if (t.head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
         }
         x[j] = run;
     }
@@ -426,161 +415,265 @@ __device__ __forceinline__ void wk_reduce_tile(const WkOp& o, const uint4* E, co
     bool seen = false;
 #pragma unroll
     for (int j = 0; j < WK_EPT; ++j) {
-        const uint32_t i = i0 + j;
-        if (i >= nvalid) break;
-        if (head[j]) seen = true;
-        // the last element of a segment inside the tile carries the segment's aggregate over the tile
-        const bool last = (i + 1 == nvalid) || (E[WK_H + i + 1].x != E[WK_H + i].x);
-        if (!last) continue;
+        if ((uint32_t)j >= t.nval) break;
+        if (t.head[j]) seen = true;
+        if (!t.last[j]) continue;
         const long long v = seen ? x[j] : C::f(kind, ev, x[j]);
-        int* dst = static_cast<int*>(o.out) + E[WK_H + i].x;
+        int* dst = static_cast<int*>(o.out) + t.gid[j];
         if (kind == WOP_MAX) atomicMax(dst, (int)v); else atomicMin(dst, (int)v);
     }
 }
 
-template <class T> struct WkLong { typedef long long type; };
-template <> struct WkLong<float> { typedef double type; };
-
-// windowed / neighbour expressions: element e of the tile = r * WK_THREADS + tid (coalesced stores)
-template <class T>
-__device__ __forceinline__ void wk_windowed(const WkOp& o, const uint4* E, const uint32_t tile_lo, const uint32_t nvalid,
-                                            const uint32_t* sidx, int* sred) {
-    typedef typename WkLong<T>::type L;
-    constexpr bool FP = sizeof(L) == 8 && ((T)0.5 != (T)0);
-    auto val = [&](int i) -> T {
-        const uint32_t raw = wk_word(E, i, o.col);
-        return FP ? (T)__uint_as_float(raw) : (T)(int)raw;
-    };
+// one running expression over the tile: scan, carry, output (or a per-group reduce)
+template <bool FP>
+__device__ __forceinline__ void wk_running(const WkOp& o, const WkThread& t, const uint32_t (&cur)[WK_EPT], WkShared& S, bool first_is_head) {
+    typedef WkAcc<FP> C;
+    typedef typename C::T T;
+    const int kind = wk_kind(o.op);
+    T x[WK_EPT];
+    bool any = false;
+    T run = C::id(kind);
 #pragma unroll
-    for (int r = 0; r < WK_EPT; ++r) {
-        const uint32_t i = r * WK_THREADS + threadIdx.x;
-        if (i >= nvalid) break;
-        const uint32_t p = tile_lo + i;
-        const int s = WK_H + (int)i;
-        const uint32_t idx = sidx[i];                       // index inside the group's row list
-        T res = (T)0;
-        switch (o.op) {
-        case AQ_SUMW: case AQ_AVGW: {                       // aggregations.h:238-249, 258-272: the last min(w, idx+1) elements
-            const uint32_t cnt = min(o.w, idx + 1u);
-            L ws = 0;
-            for (uint32_t j = cnt; j > 0; --j) ws += (L)val(s - (int)j + 1);
-            if (o.op == AQ_AVGW) static_cast<double*>(o.out)[p] = (double)ws / (double)cnt;
-            else if (FP) static_cast<double*>(o.out)[p] = (double)ws;
-            else if (o.out_type == AQ_INT128) { WkI128 q; q.lo = (unsigned long long)(long long)ws; q.hi = ((long long)ws) >> 63; static_cast<WkI128*>(o.out)[p] = q; }
-            else static_cast<long long*>(o.out)[p] = (long long)ws;
-            continue; }
-        case AQ_MINW: case AQ_MAXW: {                       // aggregations.h:127-167: extreme of the last w elements
-            const uint32_t cnt = min(o.w, idx + 1u);
-            T m = val(s - (int)cnt + 1);
-            if (o.op == AQ_MINW) { for (uint32_t j = cnt - 1u; j > 0; --j) { const T e = val(s - (int)j + 1); if (e < m) m = e; } }
-            else                 { for (uint32_t j = cnt - 1u; j > 0; --j) { const T e = val(s - (int)j + 1); if (!(e < m)) m = e; } }
-            res = m;
-            break; }
-        case AQ_DELTAS: res = idx ? (T)(val(s) - val(s - 1)) : (T)0; break;      // aggregations.h:442-446
-        case AQ_PREV: res = idx ? val(s - 1) : val(s); break;                    // aggregations.h:458-462
-        default: break;
+    for (int j = 0; j < WK_EPT; ++j) {
+        if ((uint32_t)j < t.nval) {
+            const T e = C::load(cur[j]);
+            if (t.head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
         }
-        if (o.minus) res = (T)(val(s) - res);
-        if (o.reduce >= 0) sred[i] = FP ? __float_as_int((float)res) : (int)res;
-        else static_cast<T*>(o.out)[p] = res;
+        x[j] = run;
+    }
+    bool ef, tf; T ev, tv;
+    wk_block_segscan<FP>(kind, any, run, ef, ev, tf, tv, S);
+    const T carry = C::from(S.carry[o.run]);
+    const T prefix = ef ? ev : (first_is_head ? ev : C::f(kind, carry, ev));   // elements before the tile's first head continue the open segment
+    bool seen = false;
+#pragma unroll
+    for (int j = 0; j < WK_EPT; ++j) { if (t.head[j]) seen = true; if (!seen) x[j] = C::f(kind, prefix, x[j]); }
+    if (o.op == AQ_SUMS) {
+        if (FP) {
+            double r[WK_EPT];
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) r[j] = (double)x[j];
+            wk_store4(static_cast<double*>(o.out) + t.p0, r, t.nval);
+        }
+        else {
+            long long r[WK_EPT];
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) r[j] = (long long)x[j];
+            if (o.out_type == AQ_INT128) wk_store4_i128(static_cast<WkI128*>(o.out) + t.p0, r, t.nval);
+            else wk_store4(static_cast<long long*>(o.out) + t.p0, r, t.nval);
+        }
+    } else if (o.op == AQ_AVGS) {
+        double r[WK_EPT];
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) r[j] = (double)x[j] / (double)(t.idx[j] + 1u);     // aggregations.h:226
+        wk_store4(static_cast<double*>(o.out) + t.p0, r, t.nval);
+    } else if (FP) {
+        float r[WK_EPT];
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) {
+            float f = (float)x[j];
+            if (o.op == AQ_MAXS && !(f > 1.17549435e-38f)) f = 1.17549435e-38f;             // aggregations.h:111
+            r[j] = o.minus ? __uint_as_float(cur[j]) - f : f;
+        }
+        wk_store4(static_cast<float*>(o.out) + t.p0, r, t.nval);
+    } else {
+        int r[WK_EPT];
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) { const int m = (int)(long long)x[j]; r[j] = o.minus ? (int)cur[j] - m : m; }
+        if (o.reduce >= 0) wk_reduce_tile(o, t, r, S);
+        else wk_store4(static_cast<int*>(o.out) + t.p0, r, t.nval);
     }
 }
 
-// dynamic shared memory: 2 stages of WK_STAGE (+1) tuples | sidx[WK_T] | sred[WK_T]
-constexpr size_t WK_SMEM = size_t(2) * (WK_STAGE + 1) * 16 + size_t(WK_T) * 8;
+// windowed / neighbour expressions over the thread's elements.  v[]: the column's values at base-8 .. base+3
+// (own elements at 8..11); longer windows read shared memory (colp = the column's SoA array).
+constexpr int WK_REGW = 9;            // windows up to this length are served from registers
+template <class T>
+__device__ __forceinline__ void wk_windowed(const WkOp& o, const WkThread& t, const uint32_t (&v)[12], const uint32_t* colp, WkShared& S) {
+    typedef typename WkLong<T>::type L;
+    constexpr bool FP = sizeof(T) == 4 && ((T)0.5 != (T)0);
+    T res[WK_EPT];
+    switch (o.op) {
+    case AQ_SUMW: case AQ_AVGW: {          // aggregations.h:238-249, 258-272: the last min(w, idx+1) elements
+        L ws[WK_EPT]; uint32_t cnt[WK_EPT];
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) {
+            cnt[j] = min(o.w, t.idx[j] + 1u);
+            ws[j] = 0;
+            if (o.w <= (uint32_t)WK_REGW) {
+#pragma unroll
+                for (int k = WK_REGW - 1; k >= 0; --k) if ((uint32_t)k < cnt[j]) ws[j] += (L)wk_val<T>(v[8 + j - k]);     // oldest first
+            } else {
+                for (uint32_t k = cnt[j]; k > 0; --k) ws[j] += (L)wk_val<T>(colp[t.base + j + 1 - k]);
+            }
+        }
+        if (o.op == AQ_AVGW) {
+            double r[WK_EPT];
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) r[j] = (double)ws[j] / (double)cnt[j];
+            wk_store4(static_cast<double*>(o.out) + t.p0, r, t.nval);
+        } else if (FP) {
+            double r[WK_EPT];
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) r[j] = (double)ws[j];
+            wk_store4(static_cast<double*>(o.out) + t.p0, r, t.nval);
+        } else {
+            long long r[WK_EPT];
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) r[j] = (long long)ws[j];
+            if (o.out_type == AQ_INT128) wk_store4_i128(static_cast<WkI128*>(o.out) + t.p0, r, t.nval);
+            else wk_store4(static_cast<long long*>(o.out) + t.p0, r, t.nval);
+        }
+        return; }
+    case AQ_MINW: case AQ_MAXW: {          // aggregations.h:127-167: extreme of the last w elements
+        const bool is_min = o.op == AQ_MINW;
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) {
+            const uint32_t cnt = min(o.w, t.idx[j] + 1u);
+            T m;
+            if (o.w <= (uint32_t)WK_REGW) {
+                m = wk_val<T>(v[8 + j]);
+                // oldest to newest like the reference's deque: ties keep the newer element, nan never wins a `<`
+                bool have = false;
+#pragma unroll
+                for (int k = WK_REGW - 1; k >= 0; --k) {
+                    if ((uint32_t)k >= cnt) continue;
+                    const T e = wk_val<T>(v[8 + j - k]);
+                    if (!have) { m = e; have = true; }
+                    else if (is_min ? (e < m) : !(e < m)) m = e;
+                }
+            } else {
+                m = wk_val<T>(colp[t.base + j + 1 - cnt]);
+                for (uint32_t k = cnt - 1u; k > 0; --k) { const T e = wk_val<T>(colp[t.base + j + 1 - k]); if (is_min ? (e < m) : !(e < m)) m = e; }
+            }
+            res[j] = m;
+        }
+        break; }
+    case AQ_DELTAS:
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) res[j] = t.idx[j] ? (T)(wk_val<T>(v[8 + j]) - wk_val<T>(v[7 + j])) : (T)0;       // aggregations.h:442-446
+        break;
+    case AQ_PREV:
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) res[j] = t.idx[j] ? wk_val<T>(v[7 + j]) : wk_val<T>(v[8 + j]);                    // aggregations.h:458-462
+        break;
+    default: return;
+    }
+    if (o.minus) {
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) res[j] = (T)(wk_val<T>(v[8 + j]) - res[j]);
+    }
+    if (o.reduce >= 0) {
+        int r[WK_EPT];
+#pragma unroll
+        for (int j = 0; j < WK_EPT; ++j) r[j] = (int)res[j];
+        wk_reduce_tile(o, t, r, S);
+    } else wk_store4(static_cast<T*>(o.out) + t.p0, res, t.nval);
+}
+
+// dynamic shared memory: the tile as it arrives (16-byte tuples) | the same as four word arrays (gid, v0, v1, v2)
+constexpr int WK_SOA = WK_STAGE + 4;               // words per array (16-byte aligned rows, one element of lookahead)
+constexpr size_t WK_SMEM = size_t(WK_STAGE + 1) * 16 + size_t(4) * WK_SOA * 4;
 
 __global__ void __launch_bounds__(WK_THREADS, 1)
 k_win(const WkArgs A) {
     extern __shared__ __align__(128) unsigned char wk_sm[];
     __shared__ WkShared S;
-    uint4* const stage0 = reinterpret_cast<uint4*>(wk_sm);
-    uint32_t* const sidx = reinterpret_cast<uint32_t*>(stage0 + 2 * (WK_STAGE + 1));
-    int* const sred = reinterpret_cast<int*>(sidx + WK_T);
+    uint4* const aos = reinterpret_cast<uint4*>(wk_sm);
+    uint32_t* const soa = reinterpret_cast<uint32_t*>(aos + (WK_STAGE + 1));
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
-    if (tid == 0) { mbar_init(&S.full[0], 1); mbar_init(&S.full[1], 1); mbar_fence_init(); }
+    if (tid == 0) { mbar_init(&S.full[0], 1); mbar_fence_init(); }
     __syncthreads();
-    auto issue = [&](uint32_t tile, int s) {
+    auto issue = [&](uint32_t tile) {
         // elements [tile*WK_T - WK_H, tile*WK_T + WK_T] (halo, tile, one element of lookahead), clipped to [0, n)
         const long long first = (long long)tile * WK_T - WK_H;
         long long last = (long long)tile * WK_T + WK_T + 1;
         if (last > (long long)A.n) last = (long long)A.n;
         const long long lo = first < 0 ? 0 : first;
         const uint32_t bytes = (uint32_t)(last - lo) * 16u;
-        uint4* dst = stage0 + size_t(s) * (WK_STAGE + 1) + (lo - first);
-        mbar_arrive_expect_tx(&S.full[s], bytes);
-        bulk_g2s(dst, A.tup + lo, bytes, &S.full[s]);
+        mbar_arrive_expect_tx(&S.full[0], bytes);
+        bulk_g2s(aos + (lo - first), A.tup + lo, bytes, &S.full[0]);
     };
-    if (tid == 0 && blockIdx.x < A.ntiles) issue(blockIdx.x, 0);
+    if (tid == 0 && blockIdx.x < A.ntiles) issue(blockIdx.x);
     uint32_t k = 0;
     for (uint32_t tile = blockIdx.x; tile < A.ntiles; tile += gridDim.x, ++k) {
-        const int s = (int)(k & 1u);
-        if (tid == 0 && tile + gridDim.x < A.ntiles) issue(tile + gridDim.x, s ^ 1);     // the other stage was released by the barrier below
-        mbar_wait(&S.full[s], (k >> 1) & 1u);
-        const uint4* E = stage0 + size_t(s) * (WK_STAGE + 1);
+        mbar_wait(&S.full[0], k & 1u);
         const uint32_t tile_lo = tile * WK_T;
         const uint32_t nvalid = min((uint32_t)WK_T, A.n - tile_lo);
-        // ---- heads and the index of every element inside its group
-        const uint32_t i0 = tid * WK_EPT;
-        bool head[WK_EPT];
-        int lasth = -1;
-#pragma unroll
-        for (int j = 0; j < WK_EPT; ++j) {
-            const uint32_t i = i0 + j;
-            head[j] = false;
-            if (i < nvalid) {
-                head[j] = (tile_lo + i == 0u) || (E[WK_H + i].x != E[WK_H + i - 1].x);
-                if (head[j]) lasth = (int)i;
+        // ---- tuples -> word arrays (conflict-free on both sides); then the arrival buffer is free for the next tile
+        {
+            const uint32_t e_lo = tile_lo == 0u ? (uint32_t)WK_H : 0u;
+            const uint32_t e_hi = WK_H + nvalid + ((tile_lo + nvalid < A.n) ? 1u : 0u);
+            for (uint32_t e = e_lo + tid; e < e_hi; e += WK_THREADS) {
+                const uint4 t4 = aos[e];
+                soa[e] = t4.x; soa[WK_SOA + e] = t4.y; soa[2 * WK_SOA + e] = t4.z; soa[3 * WK_SOA + e] = t4.w;
             }
         }
-        // exclusive max-scan of the last head index over the threads
-        int m = lasth;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, m, d); if (lane >= (uint32_t)d) m = max(m, y); }
-        if (lane == 31) S.whead[wid] = (uint32_t)m;
-        if (tid == 0) {
-            const uint32_t g0 = E[WK_H].x;
-            S.open_len = tile_lo - A.offsets[g0];
-        }
         __syncthreads();
-        if (wid == 0) {
-            int v = (int)S.whead[lane];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, v, d); if (lane >= (uint32_t)d) v = max(v, y); }
-            S.whead[lane] = (uint32_t)v;                 // inclusive over the warps
-        }
-        __syncthreads();
-        int exh = __shfl_up_sync(0xffffffffu, m, 1);
-        if (lane == 0) exh = -1;
-        if (wid > 0) exh = max(exh, (int)S.whead[wid - 1]);
-        const bool tile_has_head = (int)S.whead[WK_THREADS / 32 - 1] >= 0;
-        const bool first_is_head = (tile_lo == 0u) || (E[WK_H].x != E[WK_H - 1].x);
-        const uint32_t open_len = S.open_len;
+        if (tid == 0 && tile + gridDim.x < A.ntiles) issue(tile + gridDim.x);
+        // ---- heads and the index of every element inside its group
+        WkThread t;
+        t.base = WK_H + tid * WK_EPT;
+        t.p0 = tile_lo + tid * WK_EPT;
+        t.nval = tid * WK_EPT < nvalid ? min((uint32_t)WK_EPT, nvalid - tid * WK_EPT) : 0u;
         {
-            int cur = exh;
+            const uint4 g4 = *reinterpret_cast<const uint4*>(soa + t.base);
+            t.gid[0] = g4.x; t.gid[1] = g4.y; t.gid[2] = g4.z; t.gid[3] = g4.w;
+            const uint32_t gprev = (t.p0 == 0u) ? ~g4.x : soa[t.base - 1];
+            const uint32_t gnext = soa[t.base + WK_EPT];
+            int lasth = -1;
 #pragma unroll
             for (int j = 0; j < WK_EPT; ++j) {
-                const uint32_t i = i0 + j;
-                if (i >= nvalid) break;
-                if (head[j]) cur = (int)i;
-                sidx[i] = cur >= 0 ? i - (uint32_t)cur : open_len + i;
+                const uint32_t pj = j ? t.gid[j - 1] : gprev;
+                t.head[j] = (uint32_t)j < t.nval && t.gid[j] != pj;
+                if (t.head[j]) lasth = (int)(tid * WK_EPT) + j;
+                const uint32_t nj = j + 1 < WK_EPT ? t.gid[j + 1] : gnext;
+                t.last[j] = (uint32_t)j < t.nval && ((tid * WK_EPT + j + 1 == nvalid) || nj != t.gid[j]);
+            }
+            // exclusive max-scan of the last head index over the threads
+            int m = lasth;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, m, d); if (lane >= (uint32_t)d) m = max(m, y); }
+            if (lane == 31) S.whead[wid] = (uint32_t)m;
+            if (tid == 0) S.open_len = tile_lo - A.offsets[soa[WK_H]];
+            __syncthreads();
+            if (wid == 0) {
+                int v = (int)S.whead[lane];
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, v, d); if (lane >= (uint32_t)d) v = max(v, y); }
+                S.whead[lane] = (uint32_t)v;             // inclusive over the warps
+            }
+            __syncthreads();
+            int cur = __shfl_up_sync(0xffffffffu, m, 1);
+            if (lane == 0) cur = -1;
+            if (wid > 0) cur = max(cur, (int)S.whead[wid - 1]);
+            const uint32_t open_len = S.open_len;
+#pragma unroll
+            for (int j = 0; j < WK_EPT; ++j) {
+                const uint32_t i = tid * WK_EPT + j;
+                if (t.head[j]) cur = (int)i;
+                t.idx[j] = cur >= 0 ? i - (uint32_t)cur : open_len + i;
             }
         }
+        const bool tile_has_head = (int)S.whead[WK_THREADS / 32 - 1] >= 0;
+        const bool first_is_head = (tile_lo == 0u) || (soa[WK_H] != soa[WK_H - 1]);
         // ---- running expressions: publish this tile's tail aggregates, fetch the carry of an open first segment
         if (A.nrun > 0) {
             for (int q = 0; q < A.nops; ++q) {
                 const WkOp& o = A.ops[q];
                 if (o.run < 0) continue;
                 const int kind = wk_kind(o.op);
+                const uint4 c4 = *reinterpret_cast<const uint4*>(soa + (1 + o.col) * WK_SOA + t.base);
+                const uint32_t cur[WK_EPT] = {c4.x, c4.y, c4.z, c4.w};
                 unsigned long long tailbits;
                 if (o.vtype == AQ_FLOAT) {
                     typedef WkAcc<true> C;
                     bool any = false; double run = C::id(kind);
 #pragma unroll
                     for (int j = 0; j < WK_EPT; ++j) {
-                        const uint32_t i = i0 + j;
-                        if (i >= nvalid) break;
-                        const double e = C::load(wk_word(E, WK_H + i, o.col));
-                        if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+                        if ((uint32_t)j >= t.nval) break;
+                        const double e = C::load(cur[j]);
+                        if (t.head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
                     }
                     bool ef, tf; double ev, tv;
                     wk_block_segscan<true>(kind, any, run, ef, ev, tf, tv, S);
@@ -590,16 +683,15 @@ k_win(const WkArgs A) {
                     bool any = false; long long run = C::id(kind);
 #pragma unroll
                     for (int j = 0; j < WK_EPT; ++j) {
-                        const uint32_t i = i0 + j;
-                        if (i >= nvalid) break;
-                        const long long e = C::load(wk_word(E, WK_H + i, o.col));
-                        if (head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
+                        if ((uint32_t)j >= t.nval) break;
+                        const long long e = C::load(cur[j]);
+                        if (t.head[j]) { run = e; any = true; } else run = C::f(kind, run, e);
                     }
                     bool ef, tf; long long ev, tv;
                     wk_block_segscan<false>(kind, any, run, ef, ev, tf, tv, S);
                     tailbits = C::bits(tv);
                 }
-                if (tid == 0) { S.tail[o.run] = tailbits; A.tval[size_t(tile) * WK_MAXRUN + o.run] = tailbits; }
+                if (tid == 0) A.tval[size_t(tile) * WK_MAXRUN + o.run] = tailbits;
             }
             __syncthreads();
             if (tid == 0) {
@@ -609,15 +701,15 @@ k_win(const WkArgs A) {
                 for (int r = 0; r < A.nrun; ++r) S.carry[r] = 0ull;
                 if (!first_is_head && tile > 0) {
                     bool init[WK_MAXRUN] = {false, false};
-                    for (long long t = (long long)tile - 1; t >= 0; --t) {
+                    for (long long pt = (long long)tile - 1; pt >= 0; --pt) {
                         uint32_t fl;
                         uint32_t spins = 0;
-                        do { fl = *reinterpret_cast<volatile uint32_t*>(A.tflag + t); if (++spins > (1u << 28)) __trap(); } while (fl == 0u);
+                        do { fl = *reinterpret_cast<volatile uint32_t*>(A.tflag + pt); if (++spins > (1u << 28)) __trap(); } while (fl == 0u);
                         __threadfence();
                         for (int q = 0; q < A.nops; ++q) {
                             const WkOp& o = A.ops[q];
                             if (o.run < 0) continue;
-                            const unsigned long long b = *reinterpret_cast<volatile unsigned long long*>(A.tval + size_t(t) * WK_MAXRUN + o.run);
+                            const unsigned long long b = *reinterpret_cast<volatile unsigned long long*>(A.tval + size_t(pt) * WK_MAXRUN + o.run);
                             const int kind = wk_kind(o.op);
                             if (!init[o.run]) { S.carry[o.run] = b; init[o.run] = true; }
                             else if (o.vtype == AQ_FLOAT) S.carry[o.run] = WkAcc<true>::bits(WkAcc<true>::f(kind, WkAcc<true>::from(b), WkAcc<true>::from(S.carry[o.run])));
@@ -629,24 +721,23 @@ k_win(const WkArgs A) {
             }
             __syncthreads();
         }
-        __syncthreads();                                   // sidx complete
         // ---- the expressions
         for (int q = 0; q < A.nops; ++q) {
             const WkOp& o = A.ops[q];
+            const uint32_t* colp = soa + (1 + o.col) * WK_SOA;
+            const uint4 c4 = *reinterpret_cast<const uint4*>(colp + t.base);
             if (o.run >= 0) {
-                if (o.vtype == AQ_FLOAT) wk_running<true>(A, o, E, tile_lo, nvalid, head, sidx, sred, S, first_is_head);
-                else wk_running<false>(A, o, E, tile_lo, nvalid, head, sidx, sred, S, first_is_head);
+                const uint32_t cur[WK_EPT] = {c4.x, c4.y, c4.z, c4.w};
+                if (o.vtype == AQ_FLOAT) wk_running<true>(o, t, cur, S, first_is_head);
+                else wk_running<false>(o, t, cur, S, first_is_head);
             } else {
-                if (o.vtype == AQ_FLOAT) wk_windowed<float>(o, E + 0, tile_lo, nvalid, sidx, sred);
-                else wk_windowed<int>(o, E + 0, tile_lo, nvalid, sidx, sred);
-            }
-            if (o.reduce >= 0) {
-                __syncthreads();
-                wk_reduce_tile(o, E, nvalid, head, sred, S);
-                __syncthreads();
+                const uint4 p1 = *reinterpret_cast<const uint4*>(colp + t.base - 4), p2 = *reinterpret_cast<const uint4*>(colp + t.base - 8);
+                const uint32_t v[12] = {p2.x, p2.y, p2.z, p2.w, p1.x, p1.y, p1.z, p1.w, c4.x, c4.y, c4.z, c4.w};
+                if (o.vtype == AQ_FLOAT) wk_windowed<float>(o, t, v, colp, S);
+                else wk_windowed<int>(o, t, v, colp, S);
             }
         }
-        __syncthreads();                                   // stage s may be refilled after the next iteration's issue
+        __syncthreads();                                   // the word arrays are rewritten by the next iteration
     }
 }
 

@@ -40,7 +40,11 @@
 #include <utility>
 #include <vector>
 #include <iostream>
+#if defined(__has_include) && !__has_include("../../include/aqgpu.h")
+#include <aqgpu.h>                      // headers copied next to a generated out.cpp: -I <repo>/include
+#else
 #include "../../include/aqgpu.h"
+#endif
 
 #ifndef __AQEXPORT__
 #define __AQEXPORT__(_Ty) extern "C" _Ty __attribute__((visibility("default")))      // server/libaquery.h:184
@@ -591,15 +595,181 @@ template <class T> aq::VecCol<types::GetFPType<T>> ratios(const aq::GroupedCol<T
 #undef AQ_WSCAN0
 #undef AQ_WSCANW
 
-// ---- Context / DataSource (server/libaquery.h:118-160, server/DataSource_conn.h:27-46): what c(cxt) touches ---------
-struct DataSource {
+// ---- expressions over result columns (server/table.h:820-973 vector arithmetic, aggregations.h:34-69,409-411) -----
+// Results of whole-column aggregates are columns of ngroups cells that live where their inputs live; the
+// operators the generated code applies to them run on the device for device-resident operands.
+template <class T> ColRef<T> operator-(const ColRef<T>& a, const ColRef<T>& b) {                    // q7: max(v1) - min(v2)
+    ColRef<T> out = aq::alloc_like_input<T>(a.container, a.size);
+    if (a.size) aq::check(aqgpu_vec_sub(aq::dtype_of<T>(), a.container, b.container, out.container, a.size));
+    return out;
+}
+inline ColRef<double> pow(const ColRef<double>& x, double p) {                                      // q9: pow(corr(v1, v2), 2)
+    ColRef<double> out = aq::alloc_like_input<double>(x.container, x.size);
+    if (x.size) aq::check(aqgpu_vec_pow(x.container, p, out.container, x.size));
+    return out;
+}
+template <class T> ColRef<T> second(const aq::GroupedCol<T>& c) { return aq::reduce_col<T, T>(c, AQ_SECOND); }   // subvec(v, 0, 2)[1], h2o q8
+
+namespace aq {
+// Several vector-valued expressions of one group-by evaluated by ONE library call (aqgpu_group_window): what the
+// whole-column emitter produces for `SELECT avgs(5, price), sums(5, quantity), ..., max(price - mins(price))`.
+// add() / add_reduced() allocate the result column and queue the expression; run() evaluates all of them.
+struct WindowBatch {
+    std::shared_ptr<GroupsHandle> handle;
+    std::vector<aqgpu_window_t> ops;
+    template <class G> explicit WindowBatch(const G& g) : handle(g.handle) {}
+    // scan op over col[g]; minus: the vector is col - scan(col)
+    template <class R, class T> VecCol<R> add(int op, uint32_t w, const ColRef<T>& col, bool minus = false) {
+        VecCol<R> out{alloc_like_input<R>(col.container, handle->nrows), handle};
+        ops.push_back(aqgpu_window_t{op, w, dtype_of<T>(), col.container, minus ? 1 : 0, -1, dtype_of<R>(), out.flat.container});
+        return out;
+    }
+    // max / min per group of the vector (aggregations.h:71-86 applied to the vector-valued expression)
+    template <class T> ColRef<T> add_reduced(int op, uint32_t w, const ColRef<T>& col, bool minus, int reduce) {
+        ColRef<T> out = alloc_like_input<T>(col.container, handle->ngroups);
+        ops.push_back(aqgpu_window_t{op, w, dtype_of<T>(), col.container, minus ? 1 : 0, reduce, dtype_of<T>(), out.container});
+        return out;
+    }
+    void run() { if (!ops.empty() && handle->nrows) check(aqgpu_group_window(handle->h, ops.data(), (int)ops.size())); ops.clear(); }
+};
+}  // namespace aq
+
+namespace aq {
+// row lists in ascending row order (a table the SQL side has sorted by time): AQ_ROWS_ASC
+template <class... Ts> Groups<Ts...> group_by_rows_ascending(const ColRef<Ts>&... cols) {
+    Groups<Ts...> g;
+    g.handle = build_groups<Ts...>(std::index_sequence_for<Ts...>(), AQ_ROWS_ASC, cols...);
+    g.size = g.handle->ngroups;
+    return g;
+}
+// Cells of a result TABLE are host-resident (print / monetdb_append_table read them): a scalar column comes back
+// as it is, a vector-valued one as vector_type cells over its flat CSR buffer (engine/ast.py:696-718).
+template <class T> ColRef<T> table_cells(const ColRef<T>& c) {
+    if (!c.on_device()) { ColRef<T> h; h.init_from(c.size, c.container); return h; }
+    const std::vector<T> v = c.to_host();
+    ColRef<T> h(c.size);
+    if (c.size) memcpy((void*)h.container, (const void*)v.data(), sizeof(T) * c.size);
+    return h;
+}
+template <class R> ColRef<vector_type<R>> table_cells(VecCol<R>& vc) {
+    if (vc.flat.on_device()) { ColRef<R>* h = new ColRef<R>(table_cells(vc.flat)); vc.flat.init_from(h->size, h->container); }
+    return vc.views();
+}
+// every column of a result table as raw cells in <prefix>_<i>.bin (vector cells: the flat buffer); test support
+template <class C> void dump_column(ColRef<C>& col, const char* prefix, size_t i) {
+    FILE* f = fopen((std::string(prefix) + "_" + std::to_string(i) + ".bin").c_str(), "wb");
+    if (!f) return;
+    if constexpr (is_vector_type_impl<C>::value) { for (uint32_t r = 0; r < col.size; ++r) fwrite(col.container[r].container, sizeof(*col.container[r].container), col.container[r].size, f); }
+    else fwrite(col.container, sizeof(C), col.size, f);
+    fclose(f);
+}
+template <class... Ts, size_t... I> void dump_table_impl(TableInfo<Ts...>& t, const char* prefix, std::index_sequence<I...>) {
+    (dump_column(t.template get_col<(int)I>(), prefix, I), ...);
+}
+template <class... Ts> void dump_table(TableInfo<Ts...>& t, const char* prefix) { dump_table_impl(t, prefix, std::index_sequence_for<Ts...>()); }
+}  // namespace aq
+
+// ---- Context / DataSource: the objects the real server hands to c(cxt) -------------------------------------
+// Layout-compatible restatements of server/libaquery.h:118-161 and server/DataSource_conn.h:27-54 for the
+// default build of the reference (THREADING=1 from aquery_config.py:29, no __AQ_USE_THREADEDGC__): same
+// member order, same virtual-function order, so a dll.so compiled against THESE headers can be loaded by the
+// reference's unmodified server.so (server/server.cpp:296-307).  The offsets are pinned by the static_asserts
+// below and compared with the reference's own headers in tests/test_host_layout.py.
+#ifndef AQGPU_HOST_NO_THREADING
+#define AQGPU_HOST_THREADING 1
+#endif
+enum Log_level : int { LOG_INFO, LOG_ERROR, LOG_SILENT };                                   // libaquery.h:60-64
+enum Backend_Type : int { BACKEND_AQuery, BACKEND_MonetDB, BACKEND_MariaDB, BACKEND_DuckDB, BACKEND_SQLite, BACKEND_TOTAL };
+struct QueryStats { long long monet_time, postproc_time; };                                 // libaquery.h:78-81
+struct Config {                                                                             // libaquery.h:82-88
+    int running, new_query, server_mode, backend_type, has_dll, n_buffers;
+    QueryStats stats;
+    int buffer_sizes[];
+};
+struct Session {                                                                            // libaquery.h:98-105
+    struct Statistic { size_t total_active, cnt_object, total_alloc; } stats;
+    void* memory_map;
+};
+struct StoredProcedure {                                                                    // libaquery.h:107-112
+    uint32_t cnt, postproc_modules;
+    char** queries;
+    const char* name;
+    void** __rt_loaded_modules;
+};
+struct Trigger;
+struct IntervalBasedTriggerHost;
+struct CallbackBasedTriggerHost;
+struct uColRef;
+
+struct Context;
+struct DataSource {                                                                         // DataSource_conn.h:27-54
+    void* server = nullptr;
+    Context* cxt = nullptr;
+    bool status = false;
+    char* query = nullptr;
+    Backend_Type DataSourceType = BACKEND_AQuery;
+    void* res = nullptr;
+    void* ret_col = nullptr;
     long long cnt = 0;
+    const char* last_error = nullptr;
+    void* handle = nullptr;
+    DataSource() = default;
+    // vtable order of the reference: connect, exec, getCol, getDSTable, close, haserror, print_results, destructor
+    virtual void connect(Context* cxt) = 0;
+    virtual void exec(const char* q) = 0;
     virtual void* getCol(int col_idx, int type) = 0;
-    virtual ~DataSource() = default;
+    virtual void getDSTable(const char* name, void* tbl) = 0;
+    virtual void close() = 0;
+    virtual bool haserror() = 0;
+    virtual void print_results(const char* = " ", const char* = "\n", uint32_t = 0xffffffffu) {}
+    virtual ~DataSource() {}
 };
-struct Context {
+
+struct Context {                                                                            // libaquery.h:118-161
+    typedef int (*printf_type)(const char* format, ...);
+    void* module_function_maps = nullptr;
+    Config* cfg = nullptr;
+    int n_buffers = 0, *sz_bufs = nullptr;
+    void** buffers = nullptr;
     void* curr_server = nullptr;
-    void* alt_server[8] = {nullptr};
+    void* alt_server[BACKEND_TOTAL] = {nullptr};
+    Log_level log_level = LOG_INFO;
+    Session current{};
+    const char* aquery_root_path = nullptr;
+#ifdef AQGPU_HOST_THREADING
+    void* thread_pool = nullptr;
+#endif
     void* gc = nullptr;
-    std::unordered_map<std::string, void*> tables;      // cached tables: TableInfo<...>* whose containers may live in HBM
+    printf_type print = &printf;
+    Context() {}
+    virtual ~Context() {}                              // the only virtual of the reference's Context
+    // maps of the reference (a libstdc++ unordered_map has one size whatever it maps to): tables, cols,
+    // stored_proc, triggers.  The generated code reads `tables` (cached TableInfo<...>*, server.cpp:552-583).
+    std::unordered_map<std::string, void*> tables;
+    std::unordered_map<std::string, uColRef*> cols;
+    std::unordered_map<std::string, StoredProcedure> stored_proc;
+    std::unordered_map<std::string, void*> triggers;   // reference: unordered_map<string, Trigger>
+    IntervalBasedTriggerHost* it_host = nullptr;
+    CallbackBasedTriggerHost* ct_host = nullptr;
 };
+#if defined(__x86_64__) && defined(__GLIBCXX__)
+#define AQ_OFFSET_IS(T, m, v) static_assert(__builtin_offsetof(T, m) == (v), "layout of " #T "::" #m " differs from the reference")
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Winvalid-offsetof"
+AQ_OFFSET_IS(DataSource, server, 8); AQ_OFFSET_IS(DataSource, cxt, 16); AQ_OFFSET_IS(DataSource, status, 24);
+AQ_OFFSET_IS(DataSource, query, 32); AQ_OFFSET_IS(DataSource, DataSourceType, 40); AQ_OFFSET_IS(DataSource, res, 48);
+AQ_OFFSET_IS(DataSource, ret_col, 56); AQ_OFFSET_IS(DataSource, cnt, 64); AQ_OFFSET_IS(DataSource, last_error, 72);
+AQ_OFFSET_IS(DataSource, handle, 80);
+static_assert(sizeof(DataSource) == 88, "DataSource size differs from the reference");
+AQ_OFFSET_IS(Context, module_function_maps, 8); AQ_OFFSET_IS(Context, cfg, 16); AQ_OFFSET_IS(Context, n_buffers, 24);
+AQ_OFFSET_IS(Context, sz_bufs, 32); AQ_OFFSET_IS(Context, buffers, 40); AQ_OFFSET_IS(Context, curr_server, 48);
+AQ_OFFSET_IS(Context, alt_server, 56); AQ_OFFSET_IS(Context, log_level, 96); AQ_OFFSET_IS(Context, current, 104);
+AQ_OFFSET_IS(Context, aquery_root_path, 136);
+#ifdef AQGPU_HOST_THREADING
+AQ_OFFSET_IS(Context, thread_pool, 144); AQ_OFFSET_IS(Context, gc, 152); AQ_OFFSET_IS(Context, print, 160);
+AQ_OFFSET_IS(Context, tables, 168); AQ_OFFSET_IS(Context, cols, 224); AQ_OFFSET_IS(Context, it_host, 392);
+static_assert(sizeof(Context) == 408, "Context size differs from the reference");
+#endif
+#pragma GCC diagnostic pop
+#undef AQ_OFFSET_IS
+#endif

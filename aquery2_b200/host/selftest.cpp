@@ -13,9 +13,14 @@
 #include <cassert>
 #include <map>
 
-struct VecSource : DataSource {
+struct VecSource : DataSource {                      // a data source in the reference's shape (DataSource_conn.h:27-54)
     std::vector<void*> cols;
+    void connect(Context* c) override { cxt = c; status = true; }
+    void exec(const char*) override {}
     void* getCol(int i, int) override { return cols[i]; }
+    void getDSTable(const char*, void*) override {}
+    void close() override { status = false; }
+    bool haserror() override { return last_error != nullptr; }
 };
 
 static int fails = 0;

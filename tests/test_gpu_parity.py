@@ -628,3 +628,26 @@ def test_window_unfused_fallback(gpu, port):
     assert_same(got[2], want, "max(v - mins(v)) i64")
     assert_same(got[3], port.scan("ratiow", t["price"], off, perm, w=2), "ratiow")
     h.free()
+
+
+def test_direct_group_build(gpu, port):
+    """groups.cu build_direct: one bounded 32-bit key, >= 2^20 rows; a key outside the sampled range falls back"""
+    n = 1_300_007
+    rng = np.random.default_rng(21)
+    k = (rng.integers(0, 50_000, n) - 20_000).astype(np.int32)            # negative keys, ~50k groups
+    v = rng.integers(-9, 9, n).astype(np.int32)
+    for outlier in (False, True):
+        if outlier:
+            k[n - 5] = 2_000_000_000
+        h = gpu.Groups([k])
+        ng, gid, off, perm = port.groupby([k])
+        assert h.ngroups == ng
+        assert_same(h.gid(), gid)
+        assert_same(h.keys(0), k[perm[off[:-1]]] if False else h.keys(0))   # keys checked through first rows below
+        assert_same(h.first_row(), np.array([perm[off[g + 1] - 1] for g in range(ng)], dtype=np.uint32))
+        o2, p2 = h.csr()
+        assert_same(o2, off); assert_same(p2, perm)
+        assert_same(h.keys(0), k[h.first_row()])
+        assert_same(h.reduce("sum", v), port.reduce("sum", v, off, perm, raw128=True))
+        assert_same(h.scan("sums", v), port.scan("sums", v, off, perm, raw128=True))
+        h.free()

@@ -374,6 +374,18 @@ k_rank_wordprefix(const uint32_t* __restrict__ bitmap, uint32_t nwords, const ui
     }
 }
 
+// Prefix popcount of a row bitmap (nwords words): wordprefix[w] = set bits before word w; the total goes to
+// flags[FLAG_NGROUPS].  Shared by hash_aggregate and the range-partitioned path (mc.cu).
+int bitmap_rank(const uint32_t* bitmap, uint32_t nwords, uint32_t* wordprefix) {
+    const uint32_t rank_blocks = (nwords + RANK_WORDS - 1) / RANK_WORDS;
+    DevBuf blocksum;
+    AQ_TRY(blocksum.alloc(size_t(rank_blocks) * 4));
+    AQ_LAUNCH(k_rank_blocksum, rank_blocks, RANK_THREADS, 0, bitmap, nwords, blocksum.as<uint32_t>());
+    AQ_LAUNCH(k_rank_scan_blocks, 1, RANK_THREADS, 0, blocksum.as<uint32_t>(), rank_blocks, ctx().d_flags);
+    AQ_LAUNCH(k_rank_wordprefix, rank_blocks, RANK_THREADS, 0, bitmap, nwords, blocksum.as<uint32_t>(), wordprefix);
+    return 0;
+}
+
 // Emit in ROW order: a warp walks 32 bitmap words (1024 rows) at a time; lane b of the warp owns row
 // 32*word + b.  A set bit = the first row of a group, whose gid is the rank of that bit.  The key
 // columns are read where they lie (coalesced for dense bitmaps), the group's slot is found again by

@@ -200,6 +200,9 @@ int hash_aggregate(KeySpec ks, uint32_t nrows, uint32_t groups_hint, AggPlan& pl
 int emit_fused(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
                const AggPlan& plan, uint32_t max_groups, uint32_t* ngroups);
 
+// wordprefix[w] = set bits of bitmap before word w; total -> flags[FLAG_NGROUPS] (groupby.cu)
+int bitmap_rank(const uint32_t* bitmap, uint32_t nwords, uint32_t* wordprefix);
+
 // Writes keys / first rows / aggregates in first-appearance order (gid = rank of the first row).
 int emit_groups(const KeySpec& ks, uint32_t nrows, const HashResult& hr, const KeyOut& ko, uint32_t* d_first_row,
                 uint32_t* d_counts, uint32_t* d_last_row, uint32_t* d_slot_gid, const AggPlan& plan, uint32_t max_groups);

@@ -59,6 +59,11 @@ bool lc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
 int run_lc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, LcParams& P, const LcKeys& K, int threads, size_t smem,
            OutSink& sink, uint32_t* ngroups, bool* used);
 
+// mid cardinality, bounded keys: range-partitioned direct tables (mc.cu).  *used = false: declined, or a per-row
+// check failed (*abort_code = the FLAG_ABORT value; 3 = a key outside the sampled bounds)
+int try_mc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, const PlanStats& st, OutSink& sink, uint32_t* ngroups, bool* used,
+           uint32_t* abort_code);
+
 // groups ~ rows: fingerprint-partitioned path (hcfp.cu)
 bool hcfp_qualifies(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st);
 int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used);

@@ -281,6 +281,12 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
             st.have_bounds = st.bounds_given;                        // a sampled bound was wrong: drop them
         }
     }
+    if (!path_disabled("mc")) {
+        uint32_t code = 0;
+        AQ_TRY(try_mc(kc, nrows, plan, st, sink, ngroups, used, &code));
+        if (*used) return 0;
+        if (code == 3) st.have_bounds = st.bounds_given;            // a sampled bound was wrong: drop them
+    }
     if (!path_disabled("hcfp") && hcfp_qualifies(kc, nrows, plan, st)) {
         AQ_TRY(run_hcfp(kc, nrows, plan, sink, ngroups, used));
         if (*used) return 0;

@@ -651,3 +651,78 @@ def test_direct_group_build(gpu, port):
         assert_same(h.reduce("sum", v), port.reduce("sum", v, off, perm, raw128=True))
         assert_same(h.scan("sums", v), port.scan("sums", v, off, perm, raw128=True))
         h.free()
+
+
+# ---- range-partitioned direct tables (mc.cu): groups beyond one SM, bounded keys ---------------------------
+def _took_mc(gpu, fn):
+    """runs fn() with per-kernel profiling on; returns (result, True if k_mc_agg ran)"""
+    gpu.profile_enable(True); gpu.profile_report()
+    try:
+        res = fn()
+    finally:
+        rep = gpu.profile_report(); gpu.profile_enable(False)
+    return res, any("k_mc_agg" in k for k in rep)
+
+
+MC_AGG_SETS = ([("sum", "v1"), ("avg", "v3")], [("sum", "v1"), ("sum", "v2"), ("sum", "v3")], [("max", "v1"), ("min", "v2")],
+               [("first", "v3"), ("second", "v3")], [("count",)], [("min", "v3"), ("max", "v3"), ("last", "v1")],
+               [("var", "v3"), ("stddev", "v1")], [("corr", "v1", "v2")])
+
+
+@pytest.mark.parametrize("n,k", [(1_000_000, 8), (777_777, 5)])
+def test_range_partitioned_one_key(gpu, port, monkeypatch, n, k):
+    """mc.cu on its own statistics (sampled bounds), every cell kind, ragged row counts; and with wrong bounds"""
+    monkeypatch.setenv("AQGPU_MC_MIN_ROWS", "4096")
+    t = synth.h2o_table(n, k, seed=3, columns=["id3", "v1", "v2", "v3"])
+    for aggs in MC_AGG_SETS:
+        _, took = _took_mc(gpu, lambda: check_query_vs_oracle(gpu, port, t, ["id3"], aggs))
+        assert took, f"mc path not taken for {aggs}"
+    check_query_vs_oracle(gpu, port, t, ["id3"], MC_AGG_SETS[0], key_bounds=[(1, n // k // 2)])       # wrong bounds: silent retry
+
+
+def test_range_partitioned_two_keys_skew_and_row_order(gpu, port, monkeypatch):
+    monkeypatch.setenv("AQGPU_MC_MIN_ROWS", "4096")
+    n = 1_500_000
+    rng = np.random.default_rng(17)
+    t = {"a": rng.integers(-200, 200, n).astype(np.int32), "b": rng.integers(1000, 1300, n).astype(np.int32),
+         "v1": rng.integers(-50, 50, n).astype(np.int32), "v2": rng.integers(1, 16, n).astype(np.int32),
+         "v3": np.round(rng.random(n) * 100, 6).astype(np.float32)}
+    for aggs in (MC_AGG_SETS[0], MC_AGG_SETS[2], MC_AGG_SETS[3], MC_AGG_SETS[7]):
+        _, took = _took_mc(gpu, lambda: check_query_vs_oracle(gpu, port, t, ["a", "b"], aggs))
+        assert took
+    # ascending row lists (PerfectHashTable / legacy order): first = value at the smallest row, second at the next one
+    res, took = _took_mc(gpu, lambda: run_query(gpu, t, ["b", "a"], MC_AGG_SETS[3], row_order=gpu.ROWS_ASC))
+    assert took
+    ng, gid, off, perm = port.groupby([t["b"], t["a"]])
+    assert res.ngroups == ng
+    r1 = perm[off[1:] - 1]
+    two = (off[1:] - off[:-1]) >= 2
+    r2 = perm[np.maximum(off[1:].astype(np.int64) - 2, 0)]
+    assert_same(res.aggs[0], t["v3"][r1], "asc first")
+    assert_same(res.aggs[1], np.where(two, t["v3"][r2], np.float32(0)).astype(np.float32), "asc second")
+    # a hot key: one partition holds a third of the rows (exact per-partition positions, no capacity speculation)
+    hot = rng.random(n) < 0.33
+    t["a"][hot] = 7; t["b"][hot] = 1111
+    _, took = _took_mc(gpu, lambda: check_query_vs_oracle(gpu, port, t, ["a", "b"], [("sum", "v1"), ("avg", "v3"), ("max", "v2")]))
+    assert took
+
+
+def test_range_partitioned_speculation_fails(gpu, port, monkeypatch):
+    """unsampled outliers: a key outside the sampled range, a float below the fixed-point unit, integers that would
+    wrap a 32-bit cell; and a sparse key domain (declined)"""
+    monkeypatch.setenv("AQGPU_MC_MIN_ROWS", "4096")
+    n = 3_000_000
+    rng = np.random.default_rng(23)
+    def table():
+        return {"k": rng.integers(0, 300_000, n).astype(np.int32), "v": rng.integers(0, 10, n).astype(np.int32),
+                "f": np.round(rng.random(n) * 100, 6).astype(np.float32)}
+    t = table(); t["k"][2_999_999] = 5_000_000
+    check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "f")])
+    t = table(); t["f"][1_234_567] = np.float32(1e-30)
+    check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "f"), ("count",)])
+    t = table(); t["v"][2_999_998] = 2_000_000_000; t["v"][1_999_998] = -2_000_000_000
+    t["k"][2_999_998] = t["k"][5]; t["k"][1_999_998] = t["k"][5]
+    check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("max", "v")])
+    t = table(); t["k"] = (t["k"].astype(np.int64) * 5003 - 700_000_000).astype(np.int32)
+    _, took = _took_mc(gpu, lambda: check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "f")]))
+    assert not took

@@ -49,6 +49,8 @@ EXPORTS = [
     "aqgpu_synth_column", "aqgpu_groupby_run", "aqgpu_result_size", "aqgpu_result_key", "aqgpu_result_agg",
     "aqgpu_result_first_row", "aqgpu_result_free", "aqgpu_trim_pool", "aqgpu_col_upload_async",
     "aqgpu_col_download_async",
+    "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
+    "aqgpu_result_replicated",
 ]
 
 
@@ -566,6 +568,59 @@ class AutoQuery:
         L = lib()
         ng = ctypes.c_uint32(0)
         check(L.aqgpu_result_size(h, ctypes.byref(ng)))
+        n = self.ngroups = ng.value
+        p, t = ctypes.c_void_p(0), ctypes.c_int(0)
+        for k in range(self.nk):
+            check(L.aqgpu_result_key(h, k, ctypes.byref(p), ctypes.byref(t)))
+            self.kouts.append(ColumnView(p.value, n, t.value))
+        for a in range(self.na):
+            check(L.aqgpu_result_agg(h, a, ctypes.byref(p), ctypes.byref(t)))
+            self.outs.append(ColumnView(p.value, n, t.value))
+        if self.want_fr:
+            check(L.aqgpu_result_first_row(h, ctypes.byref(p)))
+            self.fr = ColumnView(p.value, n, UINT32)
+        return n
+
+
+# ---- multi-GPU (one process per GPU): NCCL communicator inside the library, sharded group-by ------------------
+def comm_unique_id() -> bytes:
+    buf = ctypes.create_string_buffer(128)
+    check(lib().aqgpu_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init(nranks: int, rank: int, unique_id: bytes) -> None:
+    check(lib().aqgpu_comm_init(int(nranks), int(rank), ctypes.c_char_p(unique_id)))
+
+
+def comm_destroy() -> None:
+    check(lib().aqgpu_comm_destroy())
+
+
+class ShardQuery(AutoQuery):
+    """aqgpu_groupby_run_dist over this rank's row shard (rows [row_base, row_base + n) of rows_total): called
+    collectively.  run() returns the number of groups this rank holds, or None when the library declines the
+    shape (the caller then exchanges rows / partials itself, aquery2_b200/dist.py).  ``replicated`` tells
+    whether every rank holds all groups."""
+
+    def __init__(self, keys, aggs, row_base: int, rows_total: int, row_order: int = ROWS_DESC, want_first_row: bool = True):
+        super().__init__(keys, aggs, row_order=row_order, want_first_row=want_first_row)
+        self.row_base, self.rows_total, self.replicated = int(row_base), int(rows_total), True
+
+    def run(self):
+        self.free()
+        h, used = ctypes.c_void_p(0), ctypes.c_int(0)
+        check(lib().aqgpu_groupby_run_dist(self.kp, self.kt, self.nk, ctypes.c_uint32(self.nrows), ctypes.c_uint64(self.row_base),
+                                           ctypes.c_uint64(self.rows_total), self.row_order, self.specs, self.na, self.want_fr,
+                                           ctypes.byref(h), ctypes.byref(used)))
+        if not used.value:
+            return None
+        self.h = h
+        L = lib()
+        ng, rep = ctypes.c_uint32(0), ctypes.c_int(0)
+        check(L.aqgpu_result_size(h, ctypes.byref(ng)))
+        check(L.aqgpu_result_replicated(h, ctypes.byref(rep)))
+        self.replicated = bool(rep.value)
         n = self.ngroups = ng.value
         p, t = ctypes.c_void_p(0), ctypes.c_int(0)
         for k in range(self.nk):

@@ -1,0 +1,143 @@
+// dist.cu -- multi-GPU group-by: row shards, one process per GPU, dense record tables exchanged over NVLink.
+//
+// rows are sharded contiguously by global row index; every rank aggregates its shard,
+// partial states are exchanged, the owner merges.  The reference has no multi-process path (single engine thread,
+// server/server.cpp:236-238), so there is no reference code to cite for the exchange itself; results are those of
+// the reference's single-process loops (server/hasher.h:176-198, server/aggregations.h) on the whole table.
+//
+// The design rests on the single-GPU paths keeping their partial state in DENSE, DIRECTLY INDEXED record tables
+// (lc.cu: one record per mixed-radix key slot; mc.cu: the same, 1e7 slots) whose cells are integers / 128-bit fixed
+// point (cells.cuh): the sum of two ranks' records is exact and order-independent, so "merge" is an element-wise
+// combination of equally laid out arrays -- no second hash build, no partial-row repartitioning:
+//   * few groups (lc.cu):  all-gather of the G-record tables (<= 4 MB per rank), every rank combines all of them
+//     and emits the whole result (replicated);
+//   * 1e5..2.6e7 slots (mc.cu): rank d owns the slot range [d * Gd, (d + 1) * Gd); one grouped ncclSend/ncclRecv
+//     all-to-all moves every rank's slice of that range to d (contiguous, nothing to pack), d combines and emits
+//     the groups it owns in ascending GLOBAL first-row order.
+// First-appearance order: every rank finds the first LOCAL row of its groups, adds its shard's row offset, and the
+// combination keeps the minimum: the global first-appearance row, hence the reference's group order
+// (server/unordered_dense.h:1142-1146).  What the sample-driven planner speculates (key bounds, fixed-point base)
+// is agreed on by one small all-reduce before anything runs; a rank whose rows violate it makes EVERY rank decline.
+#include "comm.cuh"
+#include "groupby.cuh"
+#include <cstring>
+
+namespace aq {
+
+DistCtx& dist() { static DistCtx d; return d; }
+
+__global__ void k_dist_globalize(uint32_t* __restrict__ gfirst, uint32_t G, uint32_t base) {
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < G; g += gridDim.x * blockDim.x) {
+        const uint32_t f = gfirst[g];
+        if (f != 0xffffffffu) gfirst[g] = f + base;
+    }
+}
+__global__ void k_dist_or_flags(const uint32_t* __restrict__ all, int n, uint32_t* __restrict__ flags) {
+    uint32_t v = 0;
+    for (int i = 0; i < n; ++i) if (all[i]) v = all[i];
+    if (threadIdx.x == 0 && blockIdx.x == 0 && v) flags[FLAG_ABORT] = v;
+}
+
+// out record i = combination of record i of each of the nr input tables (nr x n records, table r at in_tab + r * stride_rec
+// records); empty records (cnt word 0) are skipped.  first rows: minimum.
+__global__ void __launch_bounds__(256)
+k_dist_combine(unsigned long long* __restrict__ out_tab, uint32_t* __restrict__ out_first, const unsigned long long* __restrict__ in_tab,
+               const uint32_t* __restrict__ in_first, const uint32_t n, const int nr, const size_t stride_rec, const RecLayout L) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        unsigned long long acc[16];
+#pragma unroll
+        for (int w = 0; w < 16; ++w) acc[w] = 0ull;
+        for (int a = 0; a < L.n; ++a) {
+            if (L.kind[a] == RK_MIN64) acc[L.word[a]] = 0x7fffffffffffffffULL;
+            if (L.kind[a] == RK_MAX64) acc[L.word[a]] = 0x8000000000000000ULL;
+        }
+        uint32_t first = 0xffffffffu;
+        for (int r = 0; r < nr; ++r) {
+            const unsigned long long* rec = in_tab + (size_t(r) * stride_rec + i) * L.gw;
+            first = min(first, in_first[size_t(r) * stride_rec + i]);
+            if (rec[L.cnt_word] == 0ull) continue;
+            for (int a = 0; a < L.n; ++a) {
+                const uint32_t w = L.word[a];
+                switch (L.kind[a]) {
+                case RK_ADD64: acc[w] += rec[w]; break;
+                case RK_ADD128: {
+                    const unsigned long long lo = acc[w] + rec[w];
+                    acc[w + 1] += rec[w + 1] + (lo < acc[w] ? 1ull : 0ull);
+                    acc[w] = lo;
+                    break; }
+                case RK_MIN64: acc[w] = (unsigned long long)min((long long)acc[w], (long long)rec[w]); break;
+                case RK_MAX64: acc[w] = (unsigned long long)max((long long)acc[w], (long long)rec[w]); break;
+                default: break;
+                }
+            }
+        }
+        unsigned long long* o = out_tab + size_t(i) * L.gw;
+        for (uint32_t w = 0; w < L.gw; ++w) o[w] = acc[w];
+        out_first[i] = first;
+    }
+}
+
+static int exchange_flags(uint32_t* flags) {
+    DistCtx& d = dist();
+    DevBuf all;
+    AQ_TRY(all.alloc(size_t(d.nranks) * 4));
+    AQ_TRY(comm_allgather(flags + FLAG_ABORT, all.p, 4));
+    AQ_LAUNCH(k_dist_or_flags, 1, 32, 0, all.as<uint32_t>(), d.nranks, flags);
+    return 0;
+}
+
+int dist_combine_replicated(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, const RecLayout& L, uint32_t* flags, uint32_t* any_abort) {
+    (void)any_abort;
+    DistCtx& d = dist();
+    const int nr = d.nranks;
+    AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);
+    AQ_TRY(exchange_flags(flags));
+    DevBuf tabs, firsts;
+    const size_t tb = size_t(G) * L.gw * 8, fb = size_t(G) * 4;
+    AQ_TRY(tabs.alloc(tb * nr));
+    AQ_TRY(firsts.alloc(fb * nr));
+    AQ_TRY(comm_allgather(gtab, tabs.p, tb));
+    AQ_TRY(comm_allgather(gfirst, firsts.p, fb));
+    AQ_LAUNCH(k_dist_combine, grid_for(G, 256), 256, 0, gtab, gfirst, tabs.as<unsigned long long>(), firsts.as<uint32_t>(), G, nr, (size_t)G, L);
+    d.replicated = true;
+    d.exchange_bytes += (tb + fb) * (nr - 1);
+    return 0;
+}
+
+int dist_combine_owned(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, uint32_t Gd, const RecLayout& L, uint32_t* flags, uint32_t* any_abort) {
+    (void)any_abort;
+    DistCtx& d = dist();
+    const int nr = d.nranks, me = d.rank;
+    AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);
+    AQ_TRY(exchange_flags(flags));
+    auto lo_of = [&](int r) { return (uint32_t)std::min<unsigned long long>(G, (unsigned long long)r * Gd); };
+    const uint32_t my_lo = lo_of(me), my_n = lo_of(me + 1) - my_lo;
+    DevBuf tabs, firsts;
+    AQ_TRY(tabs.alloc(size_t(Gd) * L.gw * 8 * nr + 16));
+    AQ_TRY(firsts.alloc(size_t(Gd) * 4 * nr + 16));
+    size_t so[64], sb[64], ro[64], rb[64];
+    if (nr > 64) return fail("multi-GPU: more than 64 ranks");
+    for (int r = 0; r < nr; ++r) {
+        const uint32_t lo = lo_of(r), n = lo_of(r + 1) - lo;
+        so[r] = size_t(lo) * L.gw * 8; sb[r] = size_t(n) * L.gw * 8;
+        ro[r] = size_t(r) * Gd * L.gw * 8; rb[r] = size_t(my_n) * L.gw * 8;
+    }
+    AQ_TRY(comm_alltoallv(gtab, so, sb, tabs.p, ro, rb));
+    size_t moved = 0;
+    for (int r = 0; r < nr; ++r) if (r != me) moved += rb[r];
+    for (int r = 0; r < nr; ++r) {
+        const uint32_t lo = lo_of(r), n = lo_of(r + 1) - lo;
+        so[r] = size_t(lo) * 4; sb[r] = size_t(n) * 4;
+        ro[r] = size_t(r) * Gd * 4; rb[r] = size_t(my_n) * 4;
+    }
+    AQ_TRY(comm_alltoallv(gfirst, so, sb, firsts.p, ro, rb));
+    for (int r = 0; r < nr; ++r) if (r != me) moved += rb[r];
+    if (my_n)
+        AQ_LAUNCH(k_dist_combine, grid_for(my_n, 256), 256, 0, gtab + size_t(my_lo) * L.gw, gfirst + my_lo, tabs.as<unsigned long long>(),
+                  firsts.as<uint32_t>(), my_n, nr, (size_t)Gd, L);
+    d.replicated = false;
+    d.exchange_bytes += moved;
+    return 0;
+}
+
+} // namespace aq

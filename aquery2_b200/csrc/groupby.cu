@@ -16,6 +16,7 @@
 // row among all first rows -- a prefix-popcount over an nrows-bit bitmap, no sort of the groups --
 // which is exactly the insertion index m_values gives (server/unordered_dense.h:1142-1146).
 #include "groupby.cuh"
+#include "comm.cuh"
 #include "emit.cuh"
 #include <algorithm>
 #include <cstring>
@@ -754,6 +755,7 @@ using namespace aq;
 // group build first, then col.resize(g.size) (engine/ast.py:681-701).
 struct aqgpu_result {
     uint32_t ngroups = 0;
+    int replicated = 1;                   // multi-GPU: 1 = every rank holds all groups, 0 = the groups this rank owns
     int nkeys = 0, naggs = 0;
     int key_type[MAX_KEY_COLS];
     int agg_type[MAX_AGGS];
@@ -817,7 +819,7 @@ int OutSink::finish(uint32_t ng, const AggPlan& plan) {
 // The whole fused group-by: bind inputs, plan, pick a path, emit into `sink`.
 static int groupby_core(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
                         const int64_t* key_min, const int64_t* key_max, int row_order, uint32_t groups_hint,
-                        const aqgpu_agg_t* aggs, int n_aggs, OutSink& sink, uint32_t* ngroups) {
+                        const aqgpu_agg_t* aggs, int n_aggs, OutSink& sink, uint32_t* ngroups, bool* declined = nullptr) {
     if (n_aggs < 0 || n_aggs > MAX_AGGS || (n_aggs && !aggs)) return fail("need 0..%d aggregates", MAX_AGGS);
     if (!ngroups) return fail("ngroups must not be null");
     if (row_order != AQ_ROWS_DESC && row_order != AQ_ROWS_ASC) return fail("bad row_order %d", row_order);
@@ -878,6 +880,10 @@ static int groupby_core(const void* const* keys, const int* key_types, int nkeys
             for (int k = 0; k < kc.n; ++k) staged |= kc.col[k].tmp.p != nullptr;
             if (staged || std::any_of(vin.begin(), vin.end(), [](const InCol& c) { return c.tmp.p != nullptr; }))
                 AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+            return 0;
+        }
+        if (dist().active) {                                     // row shards: only the record-table paths know how to merge
+            if (declined) *declined = true;
             return 0;
         }
     }
@@ -941,6 +947,42 @@ extern "C" int aqgpu_groupby_run(const void* const* keys, const int* key_types, 
     r->ngroups = ng;
     guard.r = nullptr;
     *out = r;
+    return 0;
+}
+
+extern "C" int aqgpu_groupby_run_dist(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows_local,
+                                      uint64_t row_base, uint64_t rows_total, int row_order,
+                                      const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out, int* used) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (!out || !used) return fail("null result pointer");
+    *out = nullptr; *used = 0;
+    if (!comm_ready()) return fail("aqgpu_groupby_run_dist: call aqgpu_comm_init first");
+    if (rows_total >= 0xffffffffull || row_base + nrows_local > rows_total) return fail("aqgpu_groupby_run_dist: global row ids must fit 32 bits");
+    DistCtx& d = dist();
+    d = DistCtx();
+    d.active = true; d.nranks = comm_nranks(); d.rank = comm_rank(); d.row_base = row_base; d.rows_total = rows_total;
+    struct Off { ~Off() { dist().active = false; } } off;
+    aqgpu_result* r = new aqgpu_result();
+    struct Guard { aqgpu_result* r; ~Guard() { delete r; } } guard{r};
+    r->nkeys = nkeys > 0 && nkeys <= MAX_KEY_COLS ? nkeys : 0;
+    r->naggs = n_aggs > 0 && n_aggs <= MAX_AGGS ? n_aggs : 0;
+    for (int k = 0; k < r->nkeys; ++k) r->key_type[k] = key_types ? key_types[k] : 0;
+    OutSink sink;
+    sink.res = r; sink.want_first_row = want_first_row != 0;
+    uint32_t ng = 0;
+    bool declined = false;
+    AQ_TRY(groupby_core(keys, key_types, nkeys, nrows_local, nullptr, nullptr, row_order, 0, aggs, n_aggs, sink, &ng, &declined));
+    if (declined) return 0;                                      // *used = 0: the caller takes another strategy
+    r->ngroups = ng;
+    r->replicated = d.replicated ? 1 : 0;
+    guard.r = nullptr;
+    *out = r; *used = 1;
+    return 0;
+}
+extern "C" int aqgpu_result_replicated(const aqgpu_result_t* r, int* replicated) {
+    if (!r || !replicated) return fail("null argument");
+    *replicated = r->replicated;
     return 0;
 }
 

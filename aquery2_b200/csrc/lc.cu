@@ -24,6 +24,7 @@
 #include "stream.cuh"
 #include "cells.cuh"
 #include "emit.cuh"
+#include "comm.cuh"
 #include <algorithm>
 #include <cstring>
 
@@ -502,6 +503,8 @@ bool lc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
                int* threads_out, size_t* smem_out) {
     Context& c = ctx();
     memset(&P, 0, sizeof(P)); memset(&K, 0, sizeof(K));
+    const uint32_t nrows_local = nrows;
+    if (dist().active) nrows = dist().rows_max;                  // row shards: the same layout on every rank
     if (!st.have_bounds || kc.n > LC_MAX_KEYS || nrows < 4096) return false;
     unsigned long long G = 1;
     for (int k = 0; k < kc.n; ++k) {
@@ -513,7 +516,7 @@ bool lc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         G *= (unsigned long long)range + 1ull;
         if (G > LC_MAX_G) return false;
     }
-    P.nkeys = kc.n; P.G = (uint32_t)G; P.nrows = nrows; P.nacc = plan.n_acc; P.flags = c.d_flags;
+    P.nkeys = kc.n; P.G = (uint32_t)G; P.nrows = nrows_local; P.nacc = plan.n_acc; P.flags = c.d_flags;
     K.nkeys = kc.n;
     for (int k = 0; k < kc.n; ++k) { K.key[k] = static_cast<const uint32_t*>(kc.col[k].d); K.klo[k] = P.klo[k]; K.krange[k] = P.krange[k]; K.kmul[k] = P.kmul[k]; }
     // ---- ring columns: keys, then every value column once
@@ -630,11 +633,25 @@ int run_lc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, LcParams& P, const 
     AQ_TRY(launch_lc_agg(P, grid, threads, smem));
     AQ_LAUNCH(k_lc_count, grid_for(P.G, 256, 1, 4), 256, 0, P.gtab, P.G, P.gw, P.acc[cnt_acc].gword, slots.as<uint32_t>(), ctl);
     AQ_LAUNCH(k_lc_first, c.sm_count * 4, LCF_THREADS, 0, K, nrows, gfirst.as<uint32_t>(), ctl);
+    const bool sharded = dist().active;
+    if (sharded) {
+        // row shards: all-gather the record tables, combine element-wise (exact integer / fixed-point cells), recount
+        RecLayout L;
+        memset(&L, 0, sizeof(L));
+        L.gw = P.gw; L.n = P.nacc; L.cnt_word = P.acc[cnt_acc].gword;
+        for (int a = 0; a < P.nacc; ++a) {
+            L.word[a] = P.acc[a].gword;
+            L.kind[a] = P.acc[a].kind == LCK_FX ? RK_ADD128 : (P.acc[a].kind == LCK_MIN32 ? RK_MIN64 : (P.acc[a].kind == LCK_MAX32 ? RK_MAX64 : RK_ADD64));
+        }
+        AQ_TRY(dist_combine_replicated(P.gtab, gfirst.as<uint32_t>(), P.G, L, c.d_flags, nullptr));
+        AQ_CUDA(cudaMemsetAsync(ctl, 0, 4, c.stream));
+        AQ_LAUNCH(k_lc_count, grid_for(P.G, 256, 1, 4), 256, 0, P.gtab, P.G, P.gw, P.acc[cnt_acc].gword, slots.as<uint32_t>(), ctl);
+    }
     AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 24 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
     AQ_CUDA(cudaStreamSynchronize(c.stream));
-    if (c.h_flags[FLAG_ABORT] != 0) return 0;                     // speculation failed: generic path
+    if (c.h_flags[FLAG_ABORT] != 0) return 0;                     // speculation failed (on some rank): generic path
     const uint32_t ng = c.h_flags[16];
-    if (c.h_flags[18] != ng) return fail("internal: low-cardinality path found first rows of %u of %u groups", c.h_flags[18], ng);
+    if (!sharded && c.h_flags[18] != ng) return fail("internal: low-cardinality path found first rows of %u of %u groups", c.h_flags[18], ng);
     if (!sink.res && ng > sink.max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.max_groups);
     AQ_TRY(sink.prepare(ng, plan));
     KeyOut ko;

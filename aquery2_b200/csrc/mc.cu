@@ -36,6 +36,7 @@
 #include "cells.cuh"
 #include "emit.cuh"
 #include "sort.cuh"
+#include "comm.cuh"
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -622,6 +623,49 @@ k_mc_emit(const McParams M, const uint32_t* __restrict__ bitmap, const uint32_t*
     }
 }
 
+// ---- row shards (dist.cu): the groups of the slot range this rank owns, in ascending GLOBAL first-row order ------
+__global__ void k_mc_count_range(const unsigned long long* __restrict__ gtab, uint32_t gw, uint32_t cnt_word, uint32_t lo, uint32_t n,
+                                 uint32_t* __restrict__ ctl) {
+    uint32_t mine = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        if (gtab[size_t(lo + i) * gw + cnt_word] != 0ull) ++mine;
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(ctl + 0, mine);
+}
+// order[gid] = slot, gid = rank of the group's first row among the first rows marked in the bitmap
+__global__ void k_mc_order(const uint32_t* __restrict__ gfirst, uint32_t lo, uint32_t n, const uint32_t* __restrict__ bitmap,
+                           const uint32_t* __restrict__ wordprefix, uint32_t* __restrict__ order) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t fr = gfirst[lo + i];
+        if (fr == 0xffffffffu) continue;
+        const uint32_t w = fr >> 5, b = fr & 31u;
+        order[wordprefix[w] + __popc(bitmap[w] & ((1u << b) - 1u))] = lo + i;
+    }
+}
+__global__ void __launch_bounds__(256)
+k_mc_emit_ord(const McParams M, const uint32_t* __restrict__ order, const uint32_t ng, const KeyOut ko, uint32_t* __restrict__ first_row_out,
+              const EmitProg ep, const uint32_t max_groups) {
+    for (uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x; gid < ng && gid < max_groups; gid += gridDim.x * blockDim.x) {
+        const uint32_t g = order[gid];
+        const uint32_t fr = M.gfirst[g];
+        for (int k = 0; k < M.nkeys; ++k) {
+            if (!ko.dst[k]) continue;
+            const uint32_t digit = (g / M.kmul[k]) % (M.krange[k] + 1u);
+            static_cast<uint32_t*>(ko.dst[k])[gid] = digit + M.klo[k];
+        }
+        if (first_row_out) first_row_out[gid] = fr;
+        const unsigned long long* rec = M.gtab + size_t(g) * M.gw;
+        unsigned long long cell[1 + MAX_ACC];
+        for (int a = 0; a < M.nacc; ++a) {
+            const McAcc& A = M.acc[a];
+            unsigned long long v = rec[A.gword];
+            if (A.kind == MCK_FX) v = (unsigned long long)__double_as_longlong(fx_to_double(v, rec[A.gword + 1], A.fxB));
+            cell[1 + a] = v;
+        }
+        for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], cell, gid, fr, ep.row_order);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host
 // ------------------------------------------------------------------------------------------------
@@ -677,6 +721,9 @@ static uint32_t mc_min_rows() {                // AQGPU_MC_MIN_ROWS: tests drive
 bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st, McParams& M, size_t* smem_scatter, size_t* smem_agg) {
     Context& c = ctx();
     memset(&M, 0, sizeof(M));
+    const uint32_t nrows_local = nrows;
+    const bool sharded = dist().active;
+    if (sharded) nrows = dist().rows_max;                                  // row shards: the same layout on every rank
     if (!st.have_bounds || kc.n > 2 || nrows < mc_min_rows() || st.est_groups <= 0.0) return false;
     if (st.est_groups * 4.0 > (double)nrows) return false;                  // fewer than ~4 rows per group: not this path
     unsigned long long G = 1;
@@ -697,7 +744,7 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         M.keys[k] = static_cast<const uint32_t*>(kc.col[k].d);
     }
     if ((double)G > 16.0 * st.est_groups + 65536.0) return false;           // sparse key domain: hash paths
-    M.nkeys = kc.n; M.G = (uint32_t)G; M.nrows = nrows; M.nacc = plan.n_acc; M.flags = c.d_flags; M.ctl = c.d_flags + 16;
+    M.nkeys = kc.n; M.G = (uint32_t)G; M.nrows = nrows_local; M.nacc = plan.n_acc; M.flags = c.d_flags; M.ctl = c.d_flags + 16;
     M.C = (uint32_t)c.sm_count;
     // ---- tuple fields and accumulator cells
     M.nv = 0; M.row_field = -1; M.cnt_acc = -1;
@@ -725,6 +772,7 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         default: return false;
         }
         if (A.kind == MCK_MAXROW || A.kind == MCK_TOP2) {
+            if (sharded) return false;                                         // row-valued cells: the caller exchanges rows
             if (M.row_field < 0) { if (M.nv >= MC_MAX_V) return false; M.row_field = M.nv; M.vals[M.nv++] = nullptr; }
             A.c0 = M.row_field;
         } else if (A.kind != MCK_CNT) {
@@ -791,7 +839,7 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         if (mc_scatter_layout(M.P, ncol, st).total <= budget) { M.stages = st; break; }
     if (!M.stages) return false;
     *smem_scatter = mc_scatter_layout(M.P, ncol, M.stages).total;
-    const uint64_t per = (uint64_t(nrows) + M.C - 1) / M.C;
+    const uint64_t per = (uint64_t(nrows_local) + M.C - 1) / M.C;
     M.rpc = (uint32_t)((per + MC_SUB - 1) / MC_SUB * MC_SUB);
     return true;
 }
@@ -822,11 +870,31 @@ int run_mc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, McParams& M, size_t
     AQ_TRY(launch_agg(M, smem_agg));
     if (M.nkeys == 1) AQ_LAUNCH(k_mc_first<1>, c.sm_count * 8, MCF_THREADS, 0, M);
     else AQ_LAUNCH(k_mc_first<2>, c.sm_count * 8, MCF_THREADS, 0, M);
+    const bool sharded = dist().active;
+    uint32_t own_lo = 0, own_n = M.G;
+    if (sharded) {
+        // row shards: rank d owns the slots [d * Gd, (d + 1) * Gd); every rank's slice of that range goes to d in one
+        // grouped send / receive, d combines the records element-wise (exact cells) and keeps the smallest global first row
+        const uint32_t nr = (uint32_t)dist().nranks;
+        const uint32_t Gd = (uint32_t)(((unsigned long long)M.G + nr - 1) / nr + 7ull) & ~7u;
+        RecLayout L;
+        memset(&L, 0, sizeof(L));
+        L.gw = M.gw; L.n = M.nacc; L.cnt_word = M.acc[M.cnt_acc].gword;
+        for (int a = 0; a < M.nacc; ++a) {
+            L.word[a] = M.acc[a].gword;
+            L.kind[a] = M.acc[a].kind == MCK_FX ? RK_ADD128 : (M.acc[a].kind == MCK_MIN32 ? RK_MIN64 : (M.acc[a].kind == MCK_MAX32 ? RK_MAX64 : RK_ADD64));
+        }
+        AQ_TRY(dist_combine_owned(M.gtab, M.gfirst, M.G, Gd, L, c.d_flags, nullptr));
+        own_lo = (uint32_t)std::min<unsigned long long>(M.G, (unsigned long long)dist().rank * Gd);
+        own_n = (uint32_t)std::min<unsigned long long>(M.G, (unsigned long long)(dist().rank + 1) * Gd) - own_lo;
+        AQ_CUDA(cudaMemsetAsync(M.ctl, 0, 4, c.stream));
+        if (own_n) AQ_LAUNCH(k_mc_count_range, grid_for(own_n, 256, 4), 256, 0, M.gtab, M.gw, M.acc[M.cnt_acc].gword, own_lo, own_n, M.ctl);
+    }
     AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 24 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
     AQ_CUDA(cudaStreamSynchronize(c.stream));
-    if (c.h_flags[FLAG_ABORT] != 0) { *abort_code = c.h_flags[FLAG_ABORT]; return 0; }    // speculation failed: generic path
+    if (c.h_flags[FLAG_ABORT] != 0) { *abort_code = c.h_flags[FLAG_ABORT]; return 0; }    // speculation failed (on some rank): generic path
     const uint32_t ng = c.h_flags[16];
-    if (c.h_flags[18] != ng) return fail("internal: range-partitioned path found first rows of %u of %u groups", c.h_flags[18], ng);
+    if (!sharded && c.h_flags[18] != ng) return fail("internal: range-partitioned path found first rows of %u of %u groups", c.h_flags[18], ng);
     if (!sink.res && ng > sink.max_groups) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.max_groups);
     AQ_TRY(sink.prepare(ng, plan));
     KeyOut ko;
@@ -834,7 +902,17 @@ int run_mc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, McParams& M, size_t
     ko.n = kc.n;
     for (int k = 0; k < kc.n; ++k) { ko.src[k] = kc.col[k].d; ko.size[k] = 4; ko.dst[k] = sink.key_dst[k]; }
     for (int a = 0; a < plan.emit.n; ++a) plan.emit.agg[a].out = sink.agg_dst[a];
-    if (ng) {
+    if (ng && sharded) {
+        const uint32_t nw = (uint32_t)((dist().rows_total + 31) / 32 + 1);            // first rows are GLOBAL row ids
+        DevBuf order;
+        AQ_TRY(bitmap.alloc_zero(size_t(nw) * 4));
+        AQ_TRY(wordprefix.alloc(size_t(nw) * 4));
+        AQ_TRY(order.alloc(size_t(ng) * 4));
+        AQ_LAUNCH(k_mc_mark, grid_for(own_n, 256, 4), 256, 0, M.gfirst + own_lo, own_n, bitmap.as<uint32_t>());
+        AQ_TRY(bitmap_rank(bitmap.as<uint32_t>(), nw, wordprefix.as<uint32_t>()));
+        AQ_LAUNCH(k_mc_order, grid_for(own_n, 256, 4), 256, 0, M.gfirst, own_lo, own_n, bitmap.as<uint32_t>(), wordprefix.as<uint32_t>(), order.as<uint32_t>());
+        AQ_LAUNCH(k_mc_emit_ord, grid_for(ng, 256, 1, 8), 256, 0, M, order.as<uint32_t>(), ng, ko, sink.fr_dst, plan.emit, sink.cap);
+    } else if (ng) {
         AQ_TRY(bitmap.alloc_zero(size_t(nwords_bm) * 4));
         AQ_TRY(wordprefix.alloc(size_t(nwords_bm) * 4));
         AQ_LAUNCH(k_mc_mark, grid_for(M.G, 256, 4), 256, 0, M.gfirst, M.G, bitmap.as<uint32_t>());

@@ -14,6 +14,7 @@
 // the scan kernels check each row against it and raise FLAG_ABORT, upon which the query re-runs on a path that
 // assumes nothing.  Bounds or hints passed by the caller replace the sampled ones.
 #include "lc.cuh"
+#include "comm.cuh"
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -213,6 +214,39 @@ static int sample_inputs(const KeyCols& kc, uint32_t nrows, const AggPlan& plan,
     return 0;
 }
 
+// Row shards (dist.cu): every rank has sampled its own rows; one small all-reduce (max) makes the statistics -- and with
+// them every path / layout decision -- identical on all ranks.
+static int merge_stats_across_ranks(const KeyCols& kc, const AggPlan& plan, PlanStats& st, uint32_t nrows) {
+    constexpr long long BIG = 0x7fffffffffffffffLL;
+    long long v[4 + 2 * MAX_KEY_COLS + 3 * MAX_ACC];
+    int n = 0;
+    v[n++] = st.have_bounds ? 0 : 1;
+    v[n++] = -(long long)nrows;
+    v[n++] = (long long)nrows;
+    v[n++] = (long long)std::ceil(st.est_groups);
+    for (int k = 0; k < kc.n; ++k) { v[n++] = st.have_bounds ? -st.kmin[k] : 0; v[n++] = st.have_bounds ? st.kmax[k] : 0; }
+    for (int a = 0; a < plan.n_acc; ++a) {
+        v[n++] = st.fx_maxexp[a] < 0 ? 1 : 0;
+        v[n++] = st.fx_maxexp[a];
+        v[n++] = st.isum_maxabs[a] > (unsigned long long)BIG ? BIG : (long long)st.isum_maxabs[a];
+    }
+    AQ_TRY(comm_allreduce_max_i64(v, n));
+    n = 0;
+    st.have_bounds = v[n++] == 0;
+    dist().rows_min = (uint32_t)(-v[n++]);
+    dist().rows_max = (uint32_t)v[n++];
+    st.est_groups = (double)v[n++];
+    for (int k = 0; k < kc.n; ++k) { st.kmin[k] = -v[n++]; st.kmax[k] = v[n++]; }
+    for (int a = 0; a < plan.n_acc; ++a) {
+        const bool unusable = v[n++] != 0;
+        st.fx_maxexp[a] = unusable ? -1 : (int)v[n];
+        ++n;
+        st.isum_maxabs[a] = v[n] == BIG ? ~0ull : (unsigned long long)v[n];
+        ++n;
+    }
+    return 0;
+}
+
 // what the generic paths get: the sampled group estimate and key bounds (expanded: a sample rarely sees the extreme keys)
 static void fill_hints(const PlanStats& st, const KeyCols& kc, uint32_t nrows, uint32_t groups_hint, PlanHints& out) {
     PlanHints* hints_out = &out;
@@ -261,7 +295,8 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
                       uint32_t groups_hint, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used,
                       PlanHints* hints_out) {
     *used = false;
-    if (nrows < 4096 || path_disabled("plan")) return 0;
+    const bool sharded = dist().active;
+    if (!sharded && (nrows < 4096 || path_disabled("plan"))) return 0;
     // value columns the sampler / the fast paths read as 4-byte cells must be 4-byte types; others keep their kind 0
     PlanStats st;
     if (key_min && key_max) {
@@ -272,6 +307,7 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
     const bool had_count = plan.find(ACC_COUNT) >= 0;
     if (!had_count && plan.n_acc < MAX_ACC) plan.add_count();      // the direct-table path tells empty slots by their count
     AQ_TRY(sample_inputs(kc, nrows, plan, st));
+    if (sharded) AQ_TRY(merge_stats_across_ranks(kc, plan, st, nrows));
 
     if (!path_disabled("lc")) {
         LcParams P; LcKeys K; int threads = 0; size_t smem = 0;
@@ -287,6 +323,7 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
         if (*used) return 0;
         if (code == 3) st.have_bounds = st.bounds_given;            // a sampled bound was wrong: drop them
     }
+    if (sharded) return 0;                                      // only the record-table paths merge across ranks
     if (!path_disabled("hcfp") && hcfp_qualifies(kc, nrows, plan, st)) {
         AQ_TRY(run_hcfp(kc, nrows, plan, sink, ngroups, used));
         if (*used) return 0;

@@ -504,7 +504,7 @@ class DistPlan:
             self.epilogue[q] = epi
 
     def run(self, q: str) -> int:
-        ng, keys, res, _ = self.dq[q].run()
+        ng, keys, res, fg = self.dq[q].run()
         epi = self.epilogue[q]
         if epi == "sub":
             out = aq.DeviceColumn(max(ng, 1), aq.INT32)
@@ -513,6 +513,7 @@ class DistPlan:
             out = aq.DeviceColumn(max(ng, 1), aq.DOUBLE)
             aq.vec_pow(res[0], 2.0, out, ng)
         self.last = (ng, keys, res)
+        self.last_first_global = fg
         if self.comm.stream is not None:
             # one query at a time on the device (the reference's engine thread does the same, server.cpp:236-238):
             # letting the host run ahead into the next query's collectives made steps 2-3x slower at 2 and 4 GPUs
@@ -545,3 +546,112 @@ class DistPlan:
 
     def verify(self, table, queries, args, n_total, ngs) -> dict:
         return {"status": "skipped (multi-GPU result checks: tests/test_dist_gpu.py)"}
+
+
+class ShardPlan(DistPlan):
+    """the h2o queries over row shards through the library's own multi-GPU entry point (aqgpu_groupby_run_dist:
+    NCCL communicator inside libaqgpu, dense record tables combined over NVLink); a query whose shape the library
+    declines (groups ~ rows, first / second) runs through DistQuery (row / partial exchange driven from here)."""
+
+    def __init__(self, comm: Comm, table: dict, queries, n_total: int, k: int, lo: int, use_bounds: bool = False):
+        from . import h2o
+        self.comm, self.queries = comm, list(queries)
+        self.eng = GpuEngine(comm)
+        self.table, self.n_total, self.k, self.lo, self.use_bounds = table, n_total, k, lo, use_bounds
+        self.nrows = next(iter(table.values())).n
+        uid = [aq.comm_unique_id() if comm.rank == 0 else None]
+        comm.dist.broadcast_object_list(uid, src=0)
+        aq.comm_init(comm.world, comm.rank, uid[0])
+        self.sq, self.dq, self.epilogue, self.extra, self.native = {}, {}, {}, {}, {}
+        for q in self.queries:
+            keys, aggs, epi = h2o.QUERIES[q]
+            specs = [(a[0],) + tuple(table[c] for c in a[1:]) for a in aggs]
+            self.sq[q] = aq.ShardQuery([table[c] for c in keys], specs, row_base=lo, rows_total=n_total)
+            self.epilogue[q] = epi
+            self.native[q] = None
+        self.exbytes = {}
+
+    def _fallback(self, q: str):
+        from . import h2o
+        if q not in self.dq:
+            keys, aggs, _ = h2o.QUERIES[q]
+            codes = {c: d.code for c, d in self.table.items()}
+            mg = h2o.max_groups(q, self.n_total, self.k, self.nrows)
+            bounds = [h2o.key_bound(c, self.n_total, self.k) for c in keys] if self.use_bounds else None
+            self.dq[q] = DistQuery(self.comm, self.eng, self.table, codes, keys, aggs, self.lo, mg, hint=mg, bounds=bounds,
+                                   global_hint=h2o.max_groups(q, self.n_total, self.k, self.n_total))
+        return self.dq[q]
+
+    def run(self, q: str) -> int:
+        if self.native[q] is not False:
+            ng = self.sq[q].run()
+            self.native[q] = ng is not None
+            if ng is not None:
+                res = self.sq[q].outs
+                epi = self.epilogue[q]
+                if epi:
+                    code = aq.INT32 if epi == "sub" else aq.DOUBLE
+                    e = self.extra.get(q)
+                    if e is None or e.n < ng:
+                        if e is not None:
+                            e.free()
+                        e = self.extra[q] = aq.DeviceColumn(max(ng, 1), code)
+                    if epi == "sub":
+                        aq.vec_sub(res[0], res[1], e, ng, code)
+                    else:
+                        aq.vec_pow(res[0], 2.0, e, ng)
+                return ng
+        self._fallback(q)
+        return DistPlan.run(self, q)
+
+    def total_groups(self, ngs: dict) -> dict:
+        out = {}
+        for q, ng in ngs.items():
+            if self.native[q]:
+                out[q] = ng if self.sq[q].replicated else int(self.comm.sum_float(float(ng)))
+            else:
+                out[q] = ng if self.dq[q].strategy == "allgather" else int(self.comm.sum_float(float(ng)))
+        return out
+
+    def exchange_report(self) -> dict:
+        rep = {}
+        for q in self.queries:
+            if self.native[q]:
+                rep[q] = {"strategy": "record tables: all-gather (replicated result)" if self.sq[q].replicated
+                          else "record tables: all-to-all of slot ranges (owner emits)", "native": True}
+            else:
+                rep[q] = {"strategy": self.dq[q].strategy, "bytes_in_per_rank": self.dq[q].exchanged_bytes, "native": False}
+        return rep
+
+    def gather_ordered(self, q: str):
+        """the result of the last run(q) assembled in the reference's order (global first appearance) on every
+        rank: (key columns, aggregate columns, first rows) as numpy arrays.  Replicated results are already in
+        that order; partitioned ones (each rank: the groups it owns, ascending first row) are gathered and merged
+        by first row.  For result checking and small results -- a consumer that keeps working on the GPUs uses
+        the partitioned form."""
+        import numpy as np
+        if self.native[q]:
+            sq = self.sq[q]
+            ng = sq.ngroups
+            keys = [c.numpy(ng) for c in sq.kouts]
+            aggs = [c.numpy(ng) for c in sq.outs]
+            first = sq.fr.numpy(ng).astype(np.int64)
+            replicated = sq.replicated
+        else:
+            ng, kcols, res = self.last
+            keys = [self.eng.to_numpy(c, ng) for c in kcols]
+            aggs = [self.eng.to_numpy(c, ng) for c in res]
+            first = self.eng.to_numpy(self.last_first_global, ng).astype(np.int64)
+            replicated = self.dq[q].strategy == "allgather"
+        if replicated:
+            return keys, aggs, first
+        parts = [None] * self.comm.world
+        self.comm.dist.all_gather_object(parts, (keys, aggs, first))
+        first = np.concatenate([p[2] for p in parts])
+        order = np.argsort(first, kind="stable")
+        keys = [np.concatenate([p[0][i] for p in parts])[order] for i in range(len(keys))]
+        aggs = [np.concatenate([p[1][i] for p in parts])[order] for i in range(len(aggs))]
+        return keys, aggs, first[order]
+
+    def close(self):
+        aq.comm_destroy()

@@ -152,4 +152,4 @@ class Plan:
 
 def dist_plan(comm, table, queries, args, n_total, lo, hints=False):
     from . import dist
-    return dist.DistPlan(comm, table, queries, n_total, args.k, lo, use_bounds=hints)
+    return dist.ShardPlan(comm, table, queries, n_total, args.k, lo, use_bounds=hints)

@@ -325,6 +325,8 @@ def run_b200(args, wl, queries):
                 "kernels": kernels, "exchange": exchange}
         print(json.dumps(line), flush=True)
     if comm is not None:
+        if hasattr(runner, "close"):
+            runner.close()
         comm.close()
     if verify is not None and not str(verify.get("status", "")).startswith(("ok", "skipped")):
         sys.exit(3)

@@ -183,6 +183,28 @@ int aqgpu_result_agg(const aqgpu_result_t* r, int a, void** dptr, int* dtype);
 int aqgpu_result_first_row(const aqgpu_result_t* r, uint32_t** dptr);
 int aqgpu_result_free(aqgpu_result_t* r);
 
+/* ---- multi-GPU: one process per GPU, rows sharded contiguously by global row index.
+ * The reference is a single process (server/server.cpp:236-238); these entry points have no counterpart there.
+ * aqgpu_comm_unique_id: rank 0 obtains the 128-byte NCCL id and the host program hands it to every rank (any
+ * channel); aqgpu_comm_init: every rank, after aqgpu_init on its own device.  libnccl.so.2 is bound at run time. */
+int aqgpu_comm_unique_id(void* id128);
+int aqgpu_comm_init(int nranks, int rank, const void* id128);
+int aqgpu_comm_destroy(void);
+int aqgpu_comm_size(int* nranks, int* rank);
+/* aqgpu_groupby_run over a row SHARD, called collectively by every rank: keys / value columns hold the rows
+ * [row_base, row_base + nrows_local) of a table of rows_total rows (< 2^32).  Every rank aggregates its shard into
+ * a dense record table, the tables are combined over NVLink (all-gather for few groups; an all-to-all of slot
+ * ranges otherwise) and the result is what aqgpu_groupby_run gives on the whole table: first rows are GLOBAL row
+ * ids and groups come in global first-appearance order.  aqgpu_result_replicated tells whether every rank holds
+ * all groups (1) or the groups of the key-slot range it owns (0; concatenating the ranks' results and ordering by
+ * first row gives the reference's order).  *used = 0 (and no result): the key / aggregate shape has no
+ * record-table path (groups ~ rows, FIRST / LAST / SECOND, wide or 64-bit keys) -- the caller exchanges rows or
+ * partial results itself (aquery2_b200/dist.py).  A speculation failure on ANY rank makes every rank decline. */
+int aqgpu_groupby_run_dist(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows_local,
+                           uint64_t row_base, uint64_t rows_total, int row_order,
+                           const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out, int* used);
+int aqgpu_result_replicated(const aqgpu_result_t* r, int* replicated);
+
 /* ---- group handle: ids, row lists, per-group vectors ----------------------------------------
  * aqgpu_groupby_build replaces HashTableFactory<...>::get(cols...) / AQHashTable (server/hasher.h:
  * 146-199, 324-357): the handle is the HashTableComponents {size, keys, values, offsets}

@@ -14,12 +14,17 @@ int comm_alltoallv(const void* d_send, const size_t* send_off, const size_t* sen
 int comm_allreduce_max_i64(long long* h_vals, int n);
 
 // How one accumulator's u64 words in a dense group record combine across ranks.
-enum RecKind : int { RK_ADD64 = 0, RK_ADD128 = 1, RK_MIN64 = 2, RK_MAX64 = 3 };
+enum RecKind : int {
+    RK_ADD64 = 0, RK_ADD128 = 1, RK_MIN64 = 2, RK_MAX64 = 3,
+    RK_UMAX64 = 4, RK_UMIN64 = 5,    // (row key << 32 | 32-bit value): the value travels with the largest / smallest row key
+    RK_TOP2 = 6                       // two such words, best and second best: the pair of the two largest over all ranks
+};
+constexpr int REC_MAX_FIELDS = 40;
 struct RecLayout {
     uint32_t gw;                 // u64 words per record
-    int n;                       // accumulators
-    int kind[16];
-    uint32_t word[16];
+    int n;                       // fields
+    int kind[REC_MAX_FIELDS];
+    uint32_t word[REC_MAX_FIELDS];
     uint32_t cnt_word;           // a record with cnt_word == 0 is empty
 };
 

@@ -25,6 +25,7 @@
 namespace aq {
 
 DistCtx& dist() { static DistCtx d; return d; }
+constexpr int REC_WORDS_MAX = 24;            // u64 words of a record (accumulator cells + row-valued extras)
 
 __global__ void k_dist_globalize(uint32_t* __restrict__ gfirst, uint32_t G, uint32_t base) {
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < G; g += gridDim.x * blockDim.x) {
@@ -44,12 +45,13 @@ __global__ void __launch_bounds__(256)
 k_dist_combine(unsigned long long* __restrict__ out_tab, uint32_t* __restrict__ out_first, const unsigned long long* __restrict__ in_tab,
                const uint32_t* __restrict__ in_first, const uint32_t n, const int nr, const size_t stride_rec, const RecLayout L) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        unsigned long long acc[16];
+        unsigned long long acc[REC_WORDS_MAX];
 #pragma unroll
-        for (int w = 0; w < 16; ++w) acc[w] = 0ull;
+        for (int w = 0; w < REC_WORDS_MAX; ++w) acc[w] = 0ull;
         for (int a = 0; a < L.n; ++a) {
             if (L.kind[a] == RK_MIN64) acc[L.word[a]] = 0x7fffffffffffffffULL;
             if (L.kind[a] == RK_MAX64) acc[L.word[a]] = 0x8000000000000000ULL;
+            if (L.kind[a] == RK_UMIN64) acc[L.word[a]] = ~0ull;
         }
         uint32_t first = 0xffffffffu;
         for (int r = 0; r < nr; ++r) {
@@ -67,6 +69,13 @@ k_dist_combine(unsigned long long* __restrict__ out_tab, uint32_t* __restrict__ 
                     break; }
                 case RK_MIN64: acc[w] = (unsigned long long)min((long long)acc[w], (long long)rec[w]); break;
                 case RK_MAX64: acc[w] = (unsigned long long)max((long long)acc[w], (long long)rec[w]); break;
+                case RK_UMAX64: acc[w] = max(acc[w], rec[w]); break;
+                case RK_UMIN64: acc[w] = min(acc[w], rec[w]); break;
+                case RK_TOP2: {
+                    const unsigned long long a0 = acc[w], a1 = acc[w + 1], b0 = rec[w], b1 = rec[w + 1];
+                    acc[w] = max(a0, b0);
+                    acc[w + 1] = max(min(a0, b0), max(a1, b1));
+                    break; }
                 default: break;
                 }
             }
@@ -88,6 +97,7 @@ static int exchange_flags(uint32_t* flags) {
 
 int dist_combine_replicated(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, const RecLayout& L, uint32_t* flags, uint32_t* any_abort) {
     (void)any_abort;
+    if (L.gw > REC_WORDS_MAX) return fail("internal: %u-word records", L.gw);
     DistCtx& d = dist();
     const int nr = d.nranks;
     AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);
@@ -106,6 +116,7 @@ int dist_combine_replicated(unsigned long long* gtab, uint32_t* gfirst, uint32_t
 
 int dist_combine_owned(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, uint32_t Gd, const RecLayout& L, uint32_t* flags, uint32_t* any_abort) {
     (void)any_abort;
+    if (L.gw > REC_WORDS_MAX) return fail("internal: %u-word records", L.gw);
     DistCtx& d = dist();
     const int nr = d.nranks, me = d.rank;
     AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);

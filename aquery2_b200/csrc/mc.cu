@@ -82,6 +82,13 @@ struct McParams {
     uint32_t* flags;
     uint32_t* ctl;                              // [0] groups, [1] ticket, [2] groups whose first row is known
     int stages;
+    // row shards only: row-valued aggregates (FIRST / LAST / SECOND) carry their 32-bit value with the row key in
+    // extra record words, so that the owner of a group never has to read another rank's rows
+    int nx;
+    struct Extra { int agg, mode, acc; uint32_t word; const uint32_t* v; } x[MAX_AGGS];   // mode 0: value at the largest row (MAXROW cell),
+                                                                                          // 1: at the first row, 2: top-2 rows (two words)
+    int xof[MAX_AGGS];                          // extra of emit aggregate a, or -1
+    unsigned long long row_base;
 };
 
 __device__ __forceinline__ uint2 lds64(const void* p) {
@@ -642,6 +649,37 @@ __global__ void k_mc_order(const uint32_t* __restrict__ gfirst, uint32_t lo, uin
         order[wordprefix[w] + __popc(bitmap[w] & ((1u << b) - 1u))] = lo + i;
     }
 }
+// local row-valued cells -> (global row key << 32 | value) words, before the record tables are exchanged
+__global__ void __launch_bounds__(256)
+k_mc_localize(const McParams M) {
+    const uint32_t base = (uint32_t)M.row_base;
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < M.G; g += gridDim.x * blockDim.x) {
+        unsigned long long* rec = M.gtab + size_t(g) * M.gw;
+        if (rec[M.acc[M.cnt_acc].gword] == 0ull) continue;
+        for (int i = 0; i < M.nx; ++i) {
+            const McParams::Extra& X = M.x[i];
+            if (X.mode == 0) {
+                const uint32_t r = (uint32_t)rec[M.acc[X.acc].gword];
+                rec[X.word] = ((unsigned long long)(r + base + 1u) << 32) | X.v[r];
+            } else if (X.mode == 1) {
+                const uint32_t r = M.gfirst[g];                       // still the LOCAL first row here
+                rec[X.word] = ((unsigned long long)(r + base) << 32) | X.v[r];
+            } else {
+                const unsigned long long c = rec[M.acc[X.acc].gword];
+                const uint32_t k0 = (uint32_t)(c >> 32), k1 = (uint32_t)c;
+                const bool desc = M.acc[X.acc].xform == AQ_ROWS_DESC;
+                auto one = [&](uint32_t k) -> unsigned long long {
+                    if (k == 0u) return 0ull;
+                    const uint32_t r = desc ? k - 1u : 0xffffffffu - k;
+                    const uint32_t gk = desc ? k + base : k - base;
+                    return ((unsigned long long)gk << 32) | X.v[r];
+                };
+                rec[X.word] = one(k0);
+                rec[X.word + 1] = one(k1);
+            }
+        }
+    }
+}
 __global__ void __launch_bounds__(256)
 k_mc_emit_ord(const McParams M, const uint32_t* __restrict__ order, const uint32_t ng, const KeyOut ko, uint32_t* __restrict__ first_row_out,
               const EmitProg ep, const uint32_t max_groups) {
@@ -662,7 +700,13 @@ k_mc_emit_ord(const McParams M, const uint32_t* __restrict__ order, const uint32
             if (A.kind == MCK_FX) v = (unsigned long long)__double_as_longlong(fx_to_double(v, rec[A.gword + 1], A.fxB));
             cell[1 + a] = v;
         }
-        for (int a = 0; a < ep.n; ++a) emit_one(ep.agg[a], cell, gid, fr, ep.row_order);
+        for (int a = 0; a < ep.n; ++a) {
+            const int xi = M.xof[a];
+            if (xi < 0) { emit_one(ep.agg[a], cell, gid, fr, ep.row_order); continue; }
+            const McParams::Extra& X = M.x[xi];                      // the value came with the row key
+            const unsigned long long w = rec[X.mode == 2 ? X.word + 1 : X.word];
+            static_cast<uint32_t*>(ep.agg[a].out)[gid] = (X.mode == 2 && (w >> 32) == 0ull) ? 0u : (uint32_t)w;
+        }
     }
 }
 
@@ -772,7 +816,6 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         default: return false;
         }
         if (A.kind == MCK_MAXROW || A.kind == MCK_TOP2) {
-            if (sharded) return false;                                         // row-valued cells: the caller exchanges rows
             if (M.row_field < 0) { if (M.nv >= MC_MAX_V) return false; M.row_field = M.nv; M.vals[M.nv++] = nullptr; }
             A.c0 = M.row_field;
         } else if (A.kind != MCK_CNT) {
@@ -798,6 +841,22 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
     const int nvm = M.nv - (M.row_field >= 0 ? 1 : 0);
     if (M.nv > 3) return false;                                           // a tuple is a slot word + at most 3 value words
     M.tw = M.nv <= 1 ? 2 : 4; M.lb = 32 / M.tw;
+    M.nx = 0; M.row_base = sharded ? dist().row_base : 0ull;
+    for (int a = 0; a < MAX_AGGS; ++a) M.xof[a] = -1;
+    if (sharded) {
+        for (int a = 0; a < plan.emit.n; ++a) {
+            const EmitAgg& e = plan.emit.agg[a];
+            if (e.op != AQ_FIRST && e.op != AQ_LAST && e.op != AQ_SECOND) continue;
+            if (e.vtype != AQ_INT32 && e.vtype != AQ_FLOAT) return false;
+            McParams::Extra& X = M.x[M.nx];
+            X.agg = a; X.v = static_cast<const uint32_t*>(e.v); X.word = gw;
+            if (e.op == AQ_SECOND) { X.mode = 2; X.acc = e.top2; gw += 2; }
+            else if ((e.op == AQ_FIRST) == (plan.emit.row_order == AQ_ROWS_DESC)) { X.mode = 0; X.acc = e.maxrow; gw += 1; }
+            else { X.mode = 1; X.acc = -1; gw += 1; }
+            if (X.mode != 1 && X.acc < 0) return false;
+            M.xof[a] = M.nx++;
+        }
+    }
     M.gw = gw;
     // ---- table of k_mc_agg: R groups per partition
     const size_t budget = c.smem_optin - 1024;
@@ -882,8 +941,15 @@ int run_mc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, McParams& M, size_t
         L.gw = M.gw; L.n = M.nacc; L.cnt_word = M.acc[M.cnt_acc].gword;
         for (int a = 0; a < M.nacc; ++a) {
             L.word[a] = M.acc[a].gword;
-            L.kind[a] = M.acc[a].kind == MCK_FX ? RK_ADD128 : (M.acc[a].kind == MCK_MIN32 ? RK_MIN64 : (M.acc[a].kind == MCK_MAX32 ? RK_MAX64 : RK_ADD64));
+            const int kd = M.acc[a].kind;
+            L.kind[a] = kd == MCK_FX ? RK_ADD128 : (kd == MCK_MIN32 ? RK_MIN64 : (kd == MCK_MAX32 ? RK_MAX64 : RK_ADD64));
+            if (kd == MCK_MAXROW || kd == MCK_TOP2) L.kind[a] = RK_UMAX64;          // local row ids: meaningless after the merge (the extras carry the values)
         }
+        for (int i = 0; i < M.nx; ++i) {
+            L.word[L.n] = M.x[i].word;
+            L.kind[L.n++] = M.x[i].mode == 0 ? RK_UMAX64 : (M.x[i].mode == 1 ? RK_UMIN64 : RK_TOP2);
+        }
+        if (M.nx) AQ_LAUNCH(k_mc_localize, grid_for(M.G, 256, 2), 256, 0, M);
         AQ_TRY(dist_combine_owned(M.gtab, M.gfirst, M.G, Gd, L, c.d_flags, nullptr));
         own_lo = (uint32_t)std::min<unsigned long long>(M.G, (unsigned long long)dist().rank * Gd);
         own_n = (uint32_t)std::min<unsigned long long>(M.G, (unsigned long long)(dist().rank + 1) * Gd) - own_lo;

@@ -605,7 +605,7 @@ class ShardQuery(AutoQuery):
 
     def __init__(self, keys, aggs, row_base: int, rows_total: int, row_order: int = ROWS_DESC, want_first_row: bool = True):
         super().__init__(keys, aggs, row_order=row_order, want_first_row=want_first_row)
-        self.row_base, self.rows_total, self.replicated = int(row_base), int(rows_total), True
+        self.row_base, self.rows_total, self.replicated, self.spread = int(row_base), int(rows_total), True, 1
 
     def run(self):
         self.free()
@@ -620,7 +620,7 @@ class ShardQuery(AutoQuery):
         ng, rep = ctypes.c_uint32(0), ctypes.c_int(0)
         check(L.aqgpu_result_size(h, ctypes.byref(ng)))
         check(L.aqgpu_result_replicated(h, ctypes.byref(rep)))
-        self.replicated = bool(rep.value)
+        self.replicated, self.spread = rep.value == 1, rep.value
         n = self.ngroups = ng.value
         p, t = ctypes.c_void_p(0), ctypes.c_int(0)
         for k in range(self.nk):

@@ -91,6 +91,13 @@ int comm_alltoallv(const void* d_send, const size_t* send_off, const size_t* sen
     return 0;
 }
 
+// element-wise sum of n uint32 values over all ranks, in place on the device
+int comm_allreduce_sum_u32(uint32_t* d_vals, size_t n) {
+    if (!g_comm) return fail("multi-GPU: aqgpu_comm_init has not been called");
+    AQ_NCCL(g_nccl.AllReduce(d_vals, d_vals, n, 3 /* ncclUint32 */, NCCL_SUM, g_comm, ctx().stream));
+    return 0;
+}
+
 // element-wise max of n int64 values over all ranks, result on the host (synchronises the stream)
 int comm_allreduce_max_i64(long long* h_vals, int n) {
     if (!g_comm) return 0;

@@ -12,6 +12,7 @@ int comm_allgather(const void* d_send, void* d_recv, size_t bytes_per_rank);
 int comm_alltoallv(const void* d_send, const size_t* send_off, const size_t* send_bytes,
                    void* d_recv, const size_t* recv_off, const size_t* recv_bytes);
 int comm_allreduce_max_i64(long long* h_vals, int n);
+int comm_allreduce_sum_u32(uint32_t* d_vals, size_t n);
 
 // How one accumulator's u64 words in a dense group record combine across ranks.
 enum RecKind : int {
@@ -36,10 +37,14 @@ struct DistCtx {
     unsigned long long rows_total = 0;
     uint32_t rows_min = 0, rows_max = 0;  // smallest / largest shard: path and layout decisions must agree on every rank
     bool replicated = false;              // out: every rank holds all groups (else: the groups whose slot range it owns)
+    int by_first_row = 0;                 // out: 1 = a rank holds the groups whose first row lies in its shard (hcfp.cu)
     double exchange_ms = 0.0;
     size_t exchange_bytes = 0;
 };
 DistCtx& dist();
+
+// flags[FLAG_ABORT] of every rank -> the same non-zero value on all ranks if any rank raised it (stream-ordered)
+int dist_exchange_flags(uint32_t* flags);
 
 // ---- dist.cu: record-table exchanges used by lc.cu / mc.cu ------------------------------------------------
 // every rank ends up with the element-wise combination of all ranks' tables (G records) and first rows (global ids,

@@ -86,7 +86,7 @@ k_dist_combine(unsigned long long* __restrict__ out_tab, uint32_t* __restrict__ 
     }
 }
 
-static int exchange_flags(uint32_t* flags) {
+int dist_exchange_flags(uint32_t* flags) {
     DistCtx& d = dist();
     DevBuf all;
     AQ_TRY(all.alloc(size_t(d.nranks) * 4));
@@ -101,7 +101,7 @@ int dist_combine_replicated(unsigned long long* gtab, uint32_t* gfirst, uint32_t
     DistCtx& d = dist();
     const int nr = d.nranks;
     AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);
-    AQ_TRY(exchange_flags(flags));
+    AQ_TRY(dist_exchange_flags(flags));
     DevBuf tabs, firsts;
     const size_t tb = size_t(G) * L.gw * 8, fb = size_t(G) * 4;
     AQ_TRY(tabs.alloc(tb * nr));
@@ -120,7 +120,7 @@ int dist_combine_owned(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, u
     DistCtx& d = dist();
     const int nr = d.nranks, me = d.rank;
     AQ_LAUNCH(k_dist_globalize, grid_for(G, 256), 256, 0, gfirst, G, (uint32_t)d.row_base);
-    AQ_TRY(exchange_flags(flags));
+    AQ_TRY(dist_exchange_flags(flags));
     auto lo_of = [&](int r) { return (uint32_t)std::min<unsigned long long>(G, (unsigned long long)r * Gd); };
     const uint32_t my_lo = lo_of(me), my_n = lo_of(me + 1) - my_lo;
     DevBuf tabs, firsts;

@@ -975,7 +975,7 @@ extern "C" int aqgpu_groupby_run_dist(const void* const* keys, const int* key_ty
     AQ_TRY(groupby_core(keys, key_types, nkeys, nrows_local, nullptr, nullptr, row_order, 0, aggs, n_aggs, sink, &ng, &declined));
     if (declined) return 0;                                      // *used = 0: the caller takes another strategy
     r->ngroups = ng;
-    r->replicated = d.replicated ? 1 : 0;
+    r->replicated = d.replicated ? 1 : (d.by_first_row ? 2 : 0);
     guard.r = nullptr;
     *out = r; *used = 1;
     return 0;

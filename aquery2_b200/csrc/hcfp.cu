@@ -25,6 +25,7 @@
 #include "lc.cuh"
 #include "emit.cuh"
 #include "sort.cuh"
+#include "comm.cuh"
 #include <cmath>
 #include <cstring>
 
@@ -125,7 +126,7 @@ __device__ __forceinline__ void fp_tile_scatter(FpSmem& S, const unsigned long l
 // ---- level 1: key columns -> (row, fingerprint) tuples in P1 partitions -------------------------------------
 __global__ void __launch_bounds__(FP_THREADS, 1)
 k_fp_part1(const KeySpec ks, const uint32_t nrows, const uint32_t P1, uint32_t* __restrict__ cursor,
-           unsigned long long* __restrict__ out, const uint32_t cap, uint32_t* __restrict__ flags) {
+           unsigned long long* __restrict__ out, const uint32_t cap, uint32_t* __restrict__ flags, const uint32_t row_base) {
     extern __shared__ __align__(16) unsigned char fp_sm[];
     FpSmem& S = *reinterpret_cast<FpSmem*>(fp_sm);
     for (uint32_t i = threadIdx.x; i < FP_PMAX; i += FP_THREADS) S.hist[i] = 0u;
@@ -178,7 +179,7 @@ k_fp_part1(const KeySpec ks, const uint32_t nrows, const uint32_t P1, uint32_t* 
                 uint64_t hsh = hs[i] * 0xc4ceb9fe1a85ec53ULL;
                 hsh ^= hsh >> 29;
                 part[i] = __umulhi((uint32_t)(hsh >> 32), P1);
-                tup[i] = ((unsigned long long)(uint32_t)hsh << 32) | (unsigned long long)(row0[h] + r);
+                tup[i] = ((unsigned long long)(uint32_t)hsh << 32) | (unsigned long long)(row_base + row0[h] + r);      // row shards: GLOBAL row id
                 vmask |= 1u << i;
             }
         fp_tile_scatter(S, tup, part, vmask, P1, cursor, out, cap, flags);
@@ -189,7 +190,9 @@ k_fp_part1(const KeySpec ks, const uint32_t nrows, const uint32_t P1, uint32_t* 
 __global__ void __launch_bounds__(FP_THREADS, 1)
 k_fp_part2(const unsigned long long* __restrict__ in, const uint32_t* __restrict__ cursor1, const uint32_t cap1,
            const uint32_t P1, const uint32_t P2, uint32_t* __restrict__ cursor2, unsigned long long* __restrict__ out,
-           const uint32_t cap2, uint32_t* __restrict__ flags) {
+           const uint32_t cap2, uint32_t* __restrict__ flags, const uint32_t PG) {
+    // PG: input region p1 feeds the sub-partitions of group p1 % PG (one GPU: PG = P1; row shards: the regions of
+    // one level-1 partition received from every rank share a group)
     extern __shared__ __align__(16) unsigned char fp_sm[];
     FpSmem& S = *reinterpret_cast<FpSmem*>(fp_sm);
     for (uint32_t i = threadIdx.x; i < FP_PMAX; i += FP_THREADS) S.hist[i] = 0u;
@@ -221,7 +224,7 @@ k_fp_part2(const unsigned long long* __restrict__ in, const uint32_t* __restrict
                 part[i] = 0;
                 if ((uint32_t)tup[i] != 0xffffffffu) { part[i] = __umulhi((uint32_t)(tup[i] >> 32), P2); vmask |= 1u << i; }
             }
-            fp_tile_scatter(S, tup, part, vmask, P2, cursor2 + size_t(p1) * P2, out + size_t(p1) * P2 * cap2, cap2, flags);
+            fp_tile_scatter(S, tup, part, vmask, P2, cursor2 + size_t(p1 % PG) * P2, out + size_t(p1 % PG) * P2 * cap2, cap2, flags);
         }
         tix += nt;
     }
@@ -240,6 +243,11 @@ struct FpAggArgs {
     uint32_t* flags;
     uint32_t* plist;                      // partitions with duplicated key tuples (k_fp_screen -> k_fp_agg)
     uint32_t* nlist;
+    // row shards: rows are GLOBAL ids and may live on another rank, so equal fingerprints cannot be settled here:
+    // the pair goes on a candidate list that every rank resolves after a small exchange (k_fp_resolve)
+    uint32_t* cand;                       // nullptr on one GPU
+    uint32_t* ncand;
+    uint32_t cand_cap;
 };
 
 // Screen: almost every final partition holds distinct key tuples only.  One 32-bit compare-and-swap per
@@ -289,7 +297,13 @@ k_fp_screen(const KeySpec ks, const FpAggArgs A) {
             if (old == FPS_EMPTY) { idx += FPS_THREADS; fresh = true; continue; }
             if (((old ^ mine) >> 14) == 0u) {                     // 18 tag bits agree: look at the other tuple
                 const unsigned long long other = stage[old & 0x1fffu];
-                if ((uint32_t)(other >> 32) == (uint32_t)(t >> 32) && keys_equal(ks, (uint32_t)t, (uint32_t)other)) dup = true;
+                if ((uint32_t)(other >> 32) == (uint32_t)(t >> 32)) {
+                    if (A.cand) {
+                        const uint32_t ci = atomicAdd(A.ncand, 2u);
+                        if (ci + 1u < A.cand_cap) { A.cand[ci] = (uint32_t)t; A.cand[ci + 1u] = (uint32_t)other; }
+                        else atomicCAS(A.flags + FLAG_ABORT, 0u, 2u);            // many equal keys: not this path
+                    } else if (keys_equal(ks, (uint32_t)t, (uint32_t)other)) dup = true;
+                }
             }
             s = (s + 1u) & mask;
         }
@@ -633,12 +647,12 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
         AQ_CUDA(cudaFuncSetAttribute(k_fp_screen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FPS_SMEM));
         attr_done = true;
     }
-    AQ_LAUNCH(k_fp_part1, c.sm_count, FP_THREADS, sizeof(FpSmem), ks, nrows, P1, cursor1, part1.as<unsigned long long>(), cap1, c.d_flags);
+    AQ_LAUNCH(k_fp_part1, c.sm_count, FP_THREADS, sizeof(FpSmem), ks, nrows, P1, cursor1, part1.as<unsigned long long>(), cap1, c.d_flags, 0u);
     const unsigned long long* fin = part1.as<unsigned long long>();
     const uint32_t* fcur = cursor1;
     if (P2 > 1) {
         AQ_LAUNCH(k_fp_part2, c.sm_count, FP_THREADS, sizeof(FpSmem), part1.as<unsigned long long>(), cursor1, cap1, P1, P2, cursor2,
-                  part2.as<unsigned long long>(), cap2, c.d_flags);
+                  part2.as<unsigned long long>(), cap2, c.d_flags, P1);
         fin = part2.as<unsigned long long>(); fcur = cursor2;
     }
     FpAggArgs A;
@@ -646,6 +660,7 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
     A.rflags = rflags.as<unsigned char>(); A.rec_of_row = rec_of_row.as<uint32_t>();
     A.rec = rec.as<unsigned long long>(); A.rec_cap = rec_cap; A.nrec = nrec; A.flags = c.d_flags;
     A.plist = plist.as<uint32_t>(); A.nlist = nlist;
+    A.cand = nullptr; A.ncand = nullptr; A.cand_cap = 0;
     HcIdentity ident;
     for (int a = 0; a < MAX_ACC; ++a) ident.w[a] = 0ull;
     for (int a = 0; a < plan.n_acc; ++a) {
@@ -707,6 +722,338 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
     const uint32_t ng = c.h_flags[FLAG_NGROUPS];
     if (ng > sink.cap) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.cap);
     AQ_TRY(sink.finish(ng, plan));
+    *ngroups = ng;
+    *used = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// row shards (dist.cu): groups ~ rows over several GPUs WITHOUT moving the rows
+// ------------------------------------------------------------------------------------------------
+// Only the 8-byte (global row, fingerprint) tuples travel: rank d owns the level-1 partitions [d * PG, (d + 1) * PG),
+// every rank sends its regions of those partitions to d (one grouped send / receive), d splits them further and
+// screens every final partition for equal fingerprints.  Equal fingerprints are CANDIDATES (~n^2 / 2^51 false ones
+// for all-distinct keys, a few hundred at 1e9 rows): the candidate rows are all-gathered, their home ranks publish
+// key tuples and values (an all-reduce over a table that is zero elsewhere), and every rank settles the candidates
+// identically (k_fp_resolve): a row that is not its key's first appearance gets flag 2 on its home rank, a first row
+// of a multi-row group gets a record.  Every other row stays what the zero-filled flags say -- the first row of a
+// one-row group -- and the emit is the single-GPU one over the LOCAL rows: a rank emits the groups whose first row it
+// holds, in row order, so the ranks' results concatenated in rank order are in global first-appearance order.
+// Key tuples that really repeat more than FPC_TOTAL / 2 times overall make every rank decline.
+constexpr uint32_t FPC_TOTAL = 8192;            // candidate list entries over all ranks
+
+// entry i of the gathered candidate list: key words and value words of row cand[i] if it lives here, zeros otherwise
+__global__ void k_fp_cand_fill(const KeySpec ks, const AccProg prog, const uint32_t* __restrict__ cand, const uint32_t m,
+                               const uint32_t row_base, const uint32_t nrows, uint32_t* __restrict__ tab, const uint32_t stride) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const uint32_t r = cand[i] - row_base;
+        uint32_t* t = tab + size_t(i) * stride;
+        for (uint32_t w = 0; w < stride; ++w) t[w] = 0u;
+        if (r >= nrows) continue;
+        for (int w = 0; w < ks.nwords; ++w) t[w] = ks.base[w][size_t(r) * ks.stride[w]];
+        for (int c = 0; c < prog.nv; ++c) t[ks.nwords + c] = static_cast<const uint32_t*>(prog.vcol[c])[r];
+    }
+}
+
+// first filter of the candidates: a second, independent 64-bit hash of the key tuple, computed by the row's home rank
+// (zeros elsewhere, so an all-reduce sum publishes it); list slot e holds a row id or 0xffffffff
+__global__ void k_fp_cand_hash(const KeySpec ks, const uint32_t* __restrict__ slots, const uint32_t nslots, const uint32_t row_base,
+                               const uint32_t nrows, uint32_t* __restrict__ h2) {
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < nslots; e += gridDim.x * blockDim.x) {
+        const uint32_t r = slots[e] - row_base;
+        uint32_t lo = 0u, hi = 0u;
+        if (slots[e] != 0xffffffffu && r < nrows) {
+            uint64_t h = 0x2545F4914F6CDD1DULL;
+            for (int w = 0; w < ks.nwords; ++w) { h = (h ^ ks.base[w][size_t(r) * ks.stride[w]]) * 0x9E3779B97F4A7C15ULL; h ^= h >> 29; }
+            h *= 0xD6E8FEB86659FD93ULL; h ^= h >> 32;
+            lo = (uint32_t)h; hi = (uint32_t)(h >> 32);
+        }
+        h2[2 * size_t(e)] = lo; h2[2 * size_t(e) + 1] = hi;
+    }
+}
+// my pairs whose second hashes agree too -> the short list that is settled exactly
+__global__ void k_fp_cand_filter(const uint32_t* __restrict__ mine, const uint32_t cap_in, const uint32_t* __restrict__ h2_mine,
+                                 uint32_t* __restrict__ out, const uint32_t cap_out, uint32_t* __restrict__ flags) {
+    const uint32_t n = min(mine[0], cap_in) / 2u;                    // pairs; mine[1 + 2i], mine[2 + 2i]
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const size_t a = 1 + 2 * size_t(i), b = a + 1;
+        if (h2_mine[2 * a] != h2_mine[2 * b] || h2_mine[2 * a + 1] != h2_mine[2 * b + 1]) continue;
+        const uint32_t j = atomicAdd(out, 2u);
+        if (j + 1u < cap_out) { out[1 + j] = mine[a]; out[2 + j] = mine[b]; }
+        else atomicCAS(flags + FLAG_ABORT, 0u, 2u);                  // key tuples really repeat a lot: not this path
+    }
+}
+
+// canon[i] = 1 iff entry i is the first occurrence of its row in the list
+__global__ void k_fp_canon(const uint32_t* __restrict__ cand, const uint32_t m, unsigned char* __restrict__ canon) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const uint32_t row = cand[i];
+        unsigned char c = 1;
+        for (uint32_t j = 0; j < i; ++j) if (cand[j] == row) { c = 0; break; }
+        canon[i] = c;
+    }
+}
+
+// one thread per list entry; identical on every rank
+__global__ void __launch_bounds__(256)
+k_fp_resolve(const AccProg prog, const HcIdentity ident, const uint32_t* __restrict__ cand, const unsigned char* __restrict__ canon, const uint32_t m, const uint32_t* __restrict__ tab,
+             const uint32_t stride, const int nkw, const uint32_t row_base, const uint32_t nrows, unsigned char* __restrict__ rflags,
+             uint32_t* __restrict__ rec_of_row, unsigned long long* __restrict__ rec, const uint32_t rec_cap, uint32_t* __restrict__ nrec,
+             uint32_t* __restrict__ flags) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const uint32_t row = cand[i];
+        const uint32_t local = row - row_base;
+        if (local >= nrows) continue;                               // another rank's row: its home settles it
+        if (!canon[i]) continue;
+        const uint32_t* ki = tab + size_t(i) * stride;
+        uint32_t first = row, members = 0;
+        for (uint32_t j = 0; j < m; ++j) {
+            const uint32_t* kj = tab + size_t(j) * stride;
+            bool eq = true;
+            for (int w = 0; w < nkw; ++w) eq &= ki[w] == kj[w];
+            if (!eq) continue;
+            if (!canon[j]) continue;                                  // count every row once
+            ++members;
+            first = min(first, cand[j]);
+        }
+        if (members < 2u) continue;                                  // a false candidate: equal fingerprints, different keys
+        if (row != first) { rflags[local] = 2; continue; }
+        const uint32_t ridx = atomicAdd(nrec, 1u);
+        if (ridx >= rec_cap) { atomicCAS(flags + FLAG_ABORT, 0u, 2u); continue; }
+        unsigned long long cell[MAX_ACC];
+        for (int a = 0; a < prog.n; ++a) cell[a] = ident.w[a];
+        for (uint32_t j = 0; j < m; ++j) {
+            const uint32_t* kj = tab + size_t(j) * stride;
+            bool eq = true;
+            for (int w = 0; w < nkw; ++w) eq &= ki[w] == kj[w];
+            if (!eq) continue;
+            if (!canon[j]) continue;
+            for (int a = 0; a < prog.n; ++a) {
+                const AccOp& o = prog.op[a];
+                long long xi = 0; double xd = 0.0;
+                if (acc_needs_value(o)) {
+                    const uint32_t u = kj[nkw + o.ci];
+                    const uint32_t u2 = o.xform == X_PRODUCT ? kj[nkw + o.ci2] : u;
+                    if (o.vtype == AQ_INT32) { xi = (long long)(int)u; if (o.xform != X_IDENT) xi *= (long long)(int)u2; }
+                    else { const float f = __uint_as_float(u); xd = o.xform == X_IDENT ? (double)f : (double)__fmul_rn(f, __uint_as_float(u2)); }
+                }
+                const bool isint = o.vtype == AQ_INT32;
+                switch (o.kind) {
+                case ACC_COUNT: cell[a] += 1ull; break;
+                case ACC_ADD_I64: cell[a] += (unsigned long long)xi; break;
+                case ACC_ADD_F64: cell[a] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)cell[a]) + (isint ? (double)xi : xd)); break;
+                case ACC_MIN_I64: cell[a] = (unsigned long long)min((long long)cell[a], isint ? xi : f64_to_ordered(xd)); break;
+                case ACC_MAX_I64: cell[a] = (unsigned long long)max((long long)cell[a], isint ? xi : f64_to_ordered(xd)); break;
+                default: break;
+                }
+            }
+        }
+        for (int a = 0; a < prog.n; ++a) rec[size_t(ridx) * prog.n + a] = cell[a];
+        rec_of_row[local] = ridx;
+        rflags[local] = 1;
+    }
+}
+
+__global__ void k_fp_add_base(uint32_t* __restrict__ rows, const uint32_t* __restrict__ n_dev, uint32_t base) {
+    const uint32_t n = *n_dev;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) rows[i] += base;
+}
+
+bool hcfp_sharded_qualifies(const KeyCols& kc, const AggPlan& plan, const PlanStats& st) {
+    (void)kc;
+    const DistCtx& d = dist();
+    if (d.rows_min < (1u << 18)) return false;
+    if (st.est_groups < 0.9 * (double)d.rows_max) return false;
+    if (plan.prog.nv < 0) return false;
+    for (int c = 0; c < plan.prog.nv; ++c) if (plan.prog.vctype[c] != AQ_INT32 && plan.prog.vctype[c] != AQ_FLOAT) return false;
+    for (int a = 0; a < plan.n_acc; ++a) {
+        const int k = plan.prog.op[a].kind;
+        if (k == ACC_MAXROW || k == ACC_TOP2ROW) return false;       // row-valued cells would need remote rows
+        if (k != ACC_COUNT && plan.prog.op[a].vtype != AQ_INT32 && plan.prog.op[a].vtype != AQ_FLOAT) return false;
+    }
+    return true;
+}
+
+int run_hcfp_sharded(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used) {
+    Context& c = ctx();
+    DistCtx& D = dist();
+    *used = false;
+    const uint32_t N = (uint32_t)D.nranks;
+    KeySpec ks;
+    AQ_TRY(kc.make_spec(nullptr, nullptr, ks));
+    // ---- partitions: sized from the WHOLE table, level 1 split evenly over the ranks
+    const double ntot = (double)D.rows_total;
+    const double parts = std::ceil(ntot / FP_MEAN);
+    uint32_t P1 = parts <= FP_PMAX ? (uint32_t)parts : (uint32_t)std::ceil(std::sqrt(parts));
+    if (P1 < N) P1 = N;
+    P1 = (P1 + N - 1) / N * N;
+    if (P1 > FP_PMAX) return 0;
+    const uint32_t P2 = std::max<uint32_t>(1u, (uint32_t)std::ceil(parts / P1));
+    if (P2 > FP_PMAX) return 0;
+    const uint32_t PG = P1 / N;                                   // level-1 partitions this rank owns
+    const double nmax = (double)D.rows_max;
+    const uint32_t cap1 = region_cap(nmax / P1, std::ceil(nmax / FP_T));            // a region holds ONE rank's tuples of a partition
+    const double tiles2 = std::ceil((double)cap1 / FP_T) * N;
+    const uint32_t cap2 = region_cap(ntot / P1 / P2, tiles2);
+    if (cap2 > (uint32_t)FPA_THREADS * FPA_TPT) return 0;
+    const uint32_t nfinal = PG * P2;
+    const uint32_t cand_cap = FPC_TOTAL / N;
+    // equal 32-bit fingerprints inside a final partition: its sub-partition index has used log2(P2) of the bits, so
+    // ~ rows x FP_MEAN / 2 / 2^(32 - log2 P2) pairs are expected for all-distinct keys (2e5 at 1e9 rows)
+    const double exp_pairs = ntot * FP_MEAN / 2.0 / (4294967296.0 / P2);
+    const uint32_t cand1_cap = (uint32_t)std::min<double>(64.0 * 1024 * 1024, 8.0 * exp_pairs / N + 16384.0) & ~1u;
+    DevBuf part1, recv1, part2, cur, rflags, rec_of_row, rec, state, plist, cand, candall, cand1, cand1all, h2;
+    AQ_TRY(part1.alloc(size_t(P1) * cap1 * 8));
+    AQ_TRY(recv1.alloc(size_t(P1) * cap1 * 8));
+    AQ_TRY(part2.alloc(size_t(nfinal) * cap2 * 8));
+    AQ_TRY(cur.alloc_zero((size_t(2) * P1 + nfinal + 8) * 4));
+    AQ_TRY(rflags.alloc_zero(size_t(nrows) + 4));
+    AQ_TRY(rec_of_row.alloc(size_t(nrows) * 4 + 4));
+    const uint32_t rec_cap = FPC_TOTAL;
+    AQ_TRY(rec.alloc(size_t(rec_cap) * std::max(plan.n_acc, 1) * 8));
+    const uint32_t ntiles_e = (nrows + FPE_ROWS - 1) / FPE_ROWS;
+    AQ_TRY(state.alloc(size_t(ntiles_e) * 8 + 16));
+    AQ_TRY(plist.alloc(size_t(nfinal) * 4 + 4));
+    AQ_TRY(cand.alloc_zero(size_t(cand_cap + 1) * 4));           // [0] = count, then the rows
+    AQ_TRY(candall.alloc(size_t(cand_cap + 1) * 4 * N));
+    AQ_TRY(cand1.alloc(size_t(cand1_cap + 1) * 4));
+    AQ_TRY(cand1all.alloc(size_t(cand1_cap + 1) * 4 * N));
+    AQ_TRY(h2.alloc(size_t(cand1_cap + 1) * 8 * N));
+    AQ_CUDA(cudaMemsetAsync(cand1.p, 0xff, size_t(cand1_cap + 1) * 4, c.stream));
+    AQ_CUDA(cudaMemsetAsync(cand1.p, 0, 4, c.stream));
+    uint32_t* cursor1 = cur.as<uint32_t>();
+    uint32_t* rcursor1 = cursor1 + P1;
+    uint32_t* cursor2 = rcursor1 + P1;
+    uint32_t* nrec = cursor2 + nfinal;
+    uint32_t* nlist = nrec + 1;
+    AQ_CUDA(cudaMemsetAsync(c.d_flags, 0, 8 * sizeof(uint32_t), c.stream));
+    static bool attr_done = false;
+    if (!attr_done) {
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_part1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_part2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FpSmem)));
+        AQ_CUDA(cudaFuncSetAttribute(k_fp_screen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FPS_SMEM));
+        attr_done = true;
+    }
+    AQ_LAUNCH(k_fp_part1, c.sm_count, FP_THREADS, sizeof(FpSmem), ks, nrows, P1, cursor1, part1.as<unsigned long long>(), cap1, c.d_flags,
+              (uint32_t)D.row_base);
+    // ---- regions of the partitions rank d owns -> d (tuples and fill counts)
+    {
+        size_t so[64], sb[64], ro[64], rb[64];
+        if (N > 64) return fail("multi-GPU: more than 64 ranks");
+        for (uint32_t r = 0; r < N; ++r) { so[r] = size_t(r) * PG * cap1 * 8; sb[r] = size_t(PG) * cap1 * 8; ro[r] = so[r]; rb[r] = sb[r]; }
+        AQ_TRY(comm_alltoallv(part1.p, so, sb, recv1.p, ro, rb));
+        for (uint32_t r = 0; r < N; ++r) { so[r] = size_t(r) * PG * 4; sb[r] = size_t(PG) * 4; ro[r] = so[r]; rb[r] = sb[r]; }
+        AQ_TRY(comm_alltoallv(cursor1, so, sb, rcursor1, ro, rb));
+        D.exchange_bytes += size_t(N - 1) * PG * (size_t(cap1) * 8 + 4);
+    }
+    // ---- level 2 over the N x PG received regions (region s * PG + j feeds group j)
+    AQ_LAUNCH(k_fp_part2, c.sm_count, FP_THREADS, sizeof(FpSmem), recv1.as<unsigned long long>(), rcursor1, cap1, P1, P2, cursor2,
+              part2.as<unsigned long long>(), cap2, c.d_flags, PG);
+    FpAggArgs A;
+    A.tuples = part2.as<unsigned long long>(); A.cursor = cursor2; A.npart = nfinal; A.cap = cap2;
+    A.rflags = rflags.as<unsigned char>(); A.rec_of_row = rec_of_row.as<uint32_t>();
+    A.rec = rec.as<unsigned long long>(); A.rec_cap = rec_cap; A.nrec = nrec; A.flags = c.d_flags;
+    A.plist = plist.as<uint32_t>(); A.nlist = nlist;
+    A.cand = cand1.as<uint32_t>() + 1; A.ncand = cand1.as<uint32_t>(); A.cand_cap = cand1_cap;
+    AQ_LAUNCH(k_fp_screen, (int)std::min<uint32_t>(nfinal, (uint32_t)c.sm_count * 3), FPS_THREADS, FPS_SMEM, ks, A);
+    // ---- candidates, first filter: the rows' home ranks publish a second 64-bit hash; pairs that still agree go on
+    {
+        const uint32_t nslots = (cand1_cap + 1) * N;
+        AQ_TRY(comm_allgather(cand1.p, cand1all.p, size_t(cand1_cap + 1) * 4));
+        AQ_LAUNCH(k_fp_cand_hash, grid_for(nslots, 256, 1, 16), 256, 0, ks, cand1all.as<uint32_t>(), nslots, (uint32_t)D.row_base, nrows, h2.as<uint32_t>());
+        AQ_TRY(comm_allreduce_sum_u32(h2.as<uint32_t>(), size_t(nslots) * 2));
+        AQ_LAUNCH(k_fp_cand_filter, grid_for(cand1_cap / 2 + 1, 256, 1, 16), 256, 0, cand1.as<uint32_t>(), cand1_cap,
+                  h2.as<uint32_t>() + size_t(D.rank) * (cand1_cap + 1) * 2, cand.as<uint32_t>(), cand_cap, c.d_flags);
+    }
+    // ---- second step: all-gather the short lists, publish keys / values of the local rows, settle exactly
+    AQ_TRY(comm_allgather(cand.p, candall.p, size_t(cand_cap + 1) * 4));
+    AQ_TRY(dist_exchange_flags(c.d_flags));
+    std::vector<uint32_t> hc(size_t(cand_cap + 1) * N);
+    AQ_CUDA(cudaMemcpyAsync(hc.data(), candall.p, hc.size() * 4, cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    if (c.h_flags[FLAG_ABORT] != 0) return 0;                     // on every rank alike: a region or a list overflowed
+    std::vector<uint32_t> list;
+    for (uint32_t r = 0; r < N; ++r) {
+        const uint32_t* p = hc.data() + size_t(r) * (cand_cap + 1);
+        const uint32_t cnt = std::min(p[0], cand_cap);
+        list.insert(list.end(), p + 1, p + 1 + cnt);
+    }
+    const uint32_t m = (uint32_t)list.size();
+    HcIdentity ident;
+    for (int a = 0; a < MAX_ACC; ++a) ident.w[a] = 0ull;
+    for (int a = 0; a < plan.n_acc; ++a) {
+        if (plan.prog.op[a].kind == ACC_MIN_I64) ident.w[a] = 0x7fffffffffffffffULL;
+        if (plan.prog.op[a].kind == ACC_MAX_I64) ident.w[a] = 0x8000000000000000ULL;
+    }
+    if (m) {
+        const uint32_t stride = (uint32_t)(ks.nwords + std::max(plan.prog.nv, 0));
+        DevBuf dl, tab, canon;
+        AQ_TRY(dl.alloc(size_t(m) * 4));
+        AQ_TRY(canon.alloc(size_t(m) + 4));
+        AQ_TRY(tab.alloc(size_t(m) * stride * 4));
+        AQ_CUDA(cudaMemcpyAsync(dl.p, list.data(), size_t(m) * 4, cudaMemcpyHostToDevice, c.stream));
+        AQ_LAUNCH(k_fp_cand_fill, grid_for(m, 256), 256, 0, ks, plan.prog, dl.as<uint32_t>(), m, (uint32_t)D.row_base, nrows, tab.as<uint32_t>(), stride);
+        AQ_TRY(comm_allreduce_sum_u32(tab.as<uint32_t>(), size_t(m) * stride));
+        AQ_LAUNCH(k_fp_canon, grid_for(m, 256), 256, 0, dl.as<uint32_t>(), m, canon.as<unsigned char>());
+        AQ_LAUNCH(k_fp_resolve, grid_for(m, 256), 256, 0, plan.prog, ident, dl.as<uint32_t>(), canon.as<unsigned char>(), m, tab.as<uint32_t>(), stride, ks.nwords,
+                  (uint32_t)D.row_base, nrows, rflags.as<unsigned char>(), rec_of_row.as<uint32_t>(), rec.as<unsigned long long>(), rec_cap, nrec, c.d_flags);
+        AQ_CUDA(cudaStreamSynchronize(c.stream));                 // `list` is read by the copy above
+    }
+    // ---- emit: the single-GPU one over the local rows
+    AQ_TRY(sink.prepare(sink.res ? nrows : sink.max_groups, plan));
+    KeyOut ko;
+    memset(&ko, 0, sizeof(ko));
+    ko.n = kc.n;
+    for (int k = 0; k < kc.n; ++k) { ko.src[k] = kc.col[k].d; ko.size[k] = (int)dtype_size(kc.type[k]); ko.dst[k] = sink.key_dst[k]; }
+    for (int a = 0; a < plan.emit.n; ++a) plan.emit.agg[a].out = sink.agg_dst[a];
+    FpOutCols oc;
+    memset(&oc, 0, sizeof(oc));
+    oc.simple = 1;
+    auto add_col = [&](int conv, const void* src, void* dst) { oc.conv[oc.n] = conv; oc.src[oc.n] = src; oc.dst[oc.n] = dst; ++oc.n; };
+    for (int k = 0; k < kc.n; ++k)
+        if (ko.dst[k]) add_col(-1 - (ko.size[k] == 4 ? FC_COPY4 : FC_COPY8), ko.src[k], ko.dst[k]);
+    if (sink.fr_dst) add_col(-1 - FC_ROW, nullptr, sink.fr_dst);
+    const int nfixed = oc.n;
+    for (int a = 0; a < plan.emit.n && oc.simple; ++a) {
+        const EmitAgg& e = plan.emit.agg[a];
+        const AccOp* o = (e.a[0] >= 0 && e.a[0] < plan.n_acc) ? &plan.prog.op[e.a[0]] : nullptr;
+        const bool v4 = e.vtype == AQ_INT32 || e.vtype == AQ_FLOAT;
+        int conv = -1; const void* src = nullptr;
+        switch (e.op) {
+        case AQ_SUM:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = e.vtype == AQ_FLOAT ? FC_F32_F64 : (e.out_type == AQ_INT128 ? FC_I32_I128 : FC_I32_I64); }
+            break;
+        case AQ_AVG:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = e.vtype == AQ_FLOAT ? FC_F32_F64 : FC_I32_F64; }
+            break;
+        case AQ_MIN: case AQ_MAX:
+            if (o && o->xform == X_IDENT && v4) { src = o->v; conv = (e.op == AQ_MAX && e.vtype == AQ_FLOAT) ? FC_MAXF32 : FC_COPY4; }
+            break;
+        case AQ_COUNT: conv = e.out_type == AQ_INT64 ? FC_ONE_I64 : FC_ONE_U32; break;
+        default: break;
+        }
+        if (conv < 0) { oc.simple = 0; break; }
+        add_col(conv, src, e.out);
+    }
+    if (!oc.simple) oc.n = nfixed;
+    uint32_t* tile_count = state.as<uint32_t>();
+    uint32_t* tile_excl = tile_count + ntiles_e + 1;
+    AQ_LAUNCH(k_fp_tilecount, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_count, c.d_flags);
+    AQ_TRY(exclusive_scan_u32(tile_count, tile_excl, ntiles_e, c.d_flags + FLAG_NGROUPS));
+    AQ_LAUNCH(k_fp_emit, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_excl, oc, sink.cap, c.d_flags);
+    AQ_LAUNCH(k_fp_emit_rest, (int)ntiles_e, FPE_THREADS, 0, nrows, rflags.as<unsigned char>(), tile_excl, rec_of_row.as<uint32_t>(),
+              rec.as<unsigned long long>(), nrec, oc.simple ? 0 : 1, plan.emit, plan.prog, sink.cap, c.d_flags);
+    if (sink.fr_dst && D.row_base)
+        AQ_LAUNCH(k_fp_add_base, c.sm_count * 4, 256, 0, sink.fr_dst, c.d_flags + FLAG_NGROUPS, (uint32_t)D.row_base);
+    AQ_TRY(dist_exchange_flags(c.d_flags));
+    AQ_CUDA(cudaMemcpyAsync(c.h_flags, c.d_flags, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    if (c.h_flags[FLAG_ABORT] != 0) return 0;
+    const uint32_t ng = c.h_flags[FLAG_NGROUPS];
+    if (ng > sink.cap) return fail("capacity: %u groups exceed max_groups=%u", ng, sink.cap);
+    AQ_TRY(sink.finish(ng, plan));
+    D.replicated = false; D.by_first_row = 1;
     *ngroups = ng;
     *used = true;
     return 0;

@@ -67,5 +67,8 @@ int try_mc(const KeyCols& kc, uint32_t nrows, AggPlan& plan, const PlanStats& st
 // groups ~ rows: fingerprint-partitioned path (hcfp.cu)
 bool hcfp_qualifies(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const PlanStats& st);
 int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used);
+// row shards: only (global row, fingerprint) tuples travel; every rank emits the groups whose first row it holds
+bool hcfp_sharded_qualifies(const KeyCols& kc, const AggPlan& plan, const PlanStats& st);
+int run_hcfp_sharded(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, uint32_t* ngroups, bool* used);
 
 } // namespace aq

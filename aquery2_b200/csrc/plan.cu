@@ -323,7 +323,10 @@ int run_planned_paths(KeyCols& kc, uint32_t nrows, const int64_t* key_min, const
         if (*used) return 0;
         if (code == 3) st.have_bounds = st.bounds_given;            // a sampled bound was wrong: drop them
     }
-    if (sharded) return 0;                                      // only the record-table paths merge across ranks
+    if (sharded) {                                              // row shards: record tables above, fingerprints here, nothing else
+        if (!path_disabled("hcfp") && hcfp_sharded_qualifies(kc, plan, st)) AQ_TRY(run_hcfp_sharded(kc, nrows, plan, sink, ngroups, used));
+        return 0;
+    }
     if (!path_disabled("hcfp") && hcfp_qualifies(kc, nrows, plan, st)) {
         AQ_TRY(run_hcfp(kc, nrows, plan, sink, ngroups, used));
         if (*used) return 0;

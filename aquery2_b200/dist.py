@@ -617,8 +617,10 @@ class ShardPlan(DistPlan):
         rep = {}
         for q in self.queries:
             if self.native[q]:
-                rep[q] = {"strategy": "record tables: all-gather (replicated result)" if self.sq[q].replicated
-                          else "record tables: all-to-all of slot ranges (owner emits)", "native": True}
+                rep[q] = {"strategy": {1: "record tables: all-gather (replicated result)",
+                                       0: "record tables: all-to-all of slot ranges (owner emits)",
+                                       2: "fingerprints: all-to-all of (row, fingerprint) tuples (home of the first row emits)"}[self.sq[q].spread],
+                          "native": True}
             else:
                 rep[q] = {"strategy": self.dq[q].strategy, "bytes_in_per_rank": self.dq[q].exchanged_bytes, "native": False}
         return rep

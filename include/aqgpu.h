@@ -195,11 +195,13 @@ int aqgpu_comm_size(int* nranks, int* rank);
  * [row_base, row_base + nrows_local) of a table of rows_total rows (< 2^32).  Every rank aggregates its shard into
  * a dense record table, the tables are combined over NVLink (all-gather for few groups; an all-to-all of slot
  * ranges otherwise) and the result is what aqgpu_groupby_run gives on the whole table: first rows are GLOBAL row
- * ids and groups come in global first-appearance order.  aqgpu_result_replicated tells whether every rank holds
- * all groups (1) or the groups of the key-slot range it owns (0; concatenating the ranks' results and ordering by
- * first row gives the reference's order).  *used = 0 (and no result): the key / aggregate shape has no
- * record-table path (groups ~ rows, FIRST / LAST / SECOND, wide or 64-bit keys) -- the caller exchanges rows or
- * partial results itself (aquery2_b200/dist.py).  A speculation failure on ANY rank makes every rank decline. */
+ * ids and groups come in global first-appearance order.  aqgpu_result_replicated tells how the result is spread:
+ * 1 = every rank holds all groups; 0 = a rank holds the groups of the key-slot range it owns (the ranks' results
+ * merged by first row give the reference's order); 2 = groups ~ rows: only (row, fingerprint) tuples were exchanged
+ * and a rank holds the groups whose FIRST ROW lies in its shard, in row order (the results concatenated in rank order
+ * are in the reference's order).  *used = 0 (and no result): the shape has no sharded path (64-bit value columns,
+ * sparse wide keys with many rows per group, ...) -- the caller exchanges rows or partial results itself
+ * (aquery2_b200/dist.py).  A speculation failure on ANY rank makes every rank decline. */
 int aqgpu_groupby_run_dist(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows_local,
                            uint64_t row_base, uint64_t rows_total, int row_order,
                            const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out, int* used);

@@ -26,6 +26,13 @@ def main():
     queries = queries or list(h2o.ORDER)
     cols = h2o.columns_of(queries)
     full = synth.h2o_table(n, k, seed=42, columns=cols)
+    ndup = int(os.environ.get("AQ_CHECK_DUPS", "0"))
+    if ndup:                                   # rows that repeat another row's whole key tuple (across shards too): q10's rare path
+        rng = np.random.default_rng(7)
+        src, dst = rng.integers(0, n, ndup), rng.integers(0, n, ndup)
+        for c in ("id1", "id2", "id3", "id4", "id5", "id6"):
+            if c in full:
+                full[c][dst] = full[c][src]
     lo, hi = comm.rank * n // comm.world, (comm.rank + 1) * n // comm.world
     table = {c: aq.DeviceColumn.from_numpy(np.ascontiguousarray(a[lo:hi])) for c, a in full.items()}
     plan = dist.ShardPlan(comm, table, queries, n, k, lo)

@@ -655,5 +655,55 @@ class ShardPlan(DistPlan):
         aggs = [np.concatenate([p[1][i] for p in parts])[order] for i in range(len(aggs))]
         return keys, aggs, first[order]
 
+    def verify(self, table, queries, args, n_total, ngs) -> dict:
+        """size-independent checks of the results the timed loop left in HBM, over all ranks: first rows strictly
+        ascending on every rank; the key columns of first rows that lie in this rank's shard equal the table's key
+        columns there; sum over all groups of every integer SUM / COUNT = the column total / the row count
+        (all-reduced).  Bit-exact parity with the oracle at small sizes: tests/test_dist_gpu.py."""
+        from . import h2o
+        T, comm = self.comm.torch, self.comm
+        dev = comm.device
+        rep = {}
+
+        def view(col, n, dt):
+            return self.eng.bytes_of(col, n).view(dt) if n else T.zeros(0, dtype=dt, device=dev)
+
+        for q in self.queries:
+            if not self.native[q]:
+                rep[q] = "not checked (row / partial exchange path)"
+                continue
+            sq = self.sq[q]
+            keys, aggs, _ = h2o.QUERIES[q]
+            ng = sq.ngroups
+            fr = view(sq.fr, ng, T.int32).to(T.int64) & 0xffffffff
+            if ng > 1 and not bool((fr[1:] > fr[:-1]).all()):
+                raise RuntimeError(f"{q}: first rows not strictly ascending on rank {comm.rank}")
+            local = (fr >= self.lo) & (fr < self.lo + self.nrows)
+            idx = (fr[local] - self.lo)
+            for i, c in enumerate(keys):
+                col = view(table[c], self.nrows, T.int32)
+                if not bool((view(sq.kouts[i], ng, T.int32)[local] == col[idx]).all()):
+                    raise RuntimeError(f"{q}: key column {c} differs from the table at the groups' first rows")
+            share = 1.0 if not sq.replicated else 1.0 / comm.world        # replicated results count once
+            checked = []
+            for a, agg in enumerate(aggs):
+                if agg[0] == "count":
+                    got = float(view(sq.outs[a], ng, T.int32).sum(dtype=T.int64)) * share
+                    want = float(self.nrows)
+                elif agg[0] == "sum" and table[agg[1]].code == aq.INT32:
+                    got = float(view(sq.outs[a], ng, T.int64)[0::2].sum(dtype=T.int64)) * share      # low words of the int128 cells
+                    want = float(view(table[agg[1]], self.nrows, T.int32).sum(dtype=T.int64))
+                else:
+                    continue
+                got, want = comm.sum_float(got), comm.sum_float(want)
+                if got != want:
+                    raise RuntimeError(f"{q}: sum over groups of {agg} = {got}, column total {want}")
+                checked.append(agg[0])
+            total = int(ngs[q]) if sq.replicated else int(comm.sum_float(float(ng)))
+            rep[q] = {"groups": total, "totals_checked": checked, "spread": sq.spread}
+        return {"status": "ok", "rows": n_total, "per_query": rep,
+                "checks": "per rank: first rows ascending, keys == table[first_row] for local first rows; over all ranks: "
+                          "sum(count) = rows, sum of integer sums = column totals; oracle parity at small sizes: tests/test_dist_gpu.py"}
+
     def close(self):
         aq.comm_destroy()

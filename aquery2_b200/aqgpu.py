@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(HERE, "libaqgpu.so")
 # dtype codes = reference types::Type_t (server/aquery_types.h:1-5)
 INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
 SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND, SUMSQ, SUMXY = range(13)
-SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
+SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW, VARS, STDDEVS, VARW, STDDEVW = range(16)
 ROWS_DESC, ROWS_ASC = 0, 1
 
 REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
@@ -26,7 +26,7 @@ REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, 
                 "sumxy": SUMXY}
 SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
               "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
-              "ratiow": RATIOW}
+              "ratiow": RATIOW, "vars": VARS, "stddevs": STDDEVS, "varw": VARW, "stddevw": STDDEVW}
 
 NP2CODE = {np.dtype(np.int32): INT32, np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE,
            np.dtype(np.int64): INT64, np.dtype(np.uint32): UINT32}

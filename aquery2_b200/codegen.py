@@ -75,7 +75,8 @@ SCALAR_AGGS = {"sum", "avg", "min", "max", "first", "last", "second", "stddev", 
 VECTOR_AGGS = {"sums": ("AQ_SUMS", "AQ_SUMW", "types::GetLongType<{T}>"), "avgs": ("AQ_AVGS", "AQ_AVGW", "double"),
                "mins": ("AQ_MINS", "AQ_MINW", "{T}"), "maxs": ("AQ_MAXS", "AQ_MAXW", "{T}"),
                "deltas": ("AQ_DELTAS", None, "{T}"), "prev": ("AQ_PREV", None, "{T}"), "next": ("AQ_NEXT", None, "{T}"),
-               "ratios": (None, "AQ_RATIOW", "types::GetFPType<{T}>")}
+               "ratios": (None, "AQ_RATIOW", "types::GetFPType<{T}>"),
+               "vars": ("AQ_VARS", "AQ_VARW", "double"), "stddevs": ("AQ_STDDEVS", "AQ_STDDEVW", "double")}
 
 
 class Emitter:

@@ -378,6 +378,7 @@ int aqgpu_scan_out_type(int op, int vtype) {
     switch (op) {
     case AQ_SUMS: case AQ_SUMW: return is_int_type(vtype) ? AQ_INT128 : AQ_DOUBLE;
     case AQ_AVGS: case AQ_AVGW: return AQ_DOUBLE;                       // GetFPType<GetLongType<T>>
+    case AQ_VARS: case AQ_STDDEVS: case AQ_VARW: case AQ_STDDEVW: return AQ_DOUBLE;
     case AQ_RATIOW: return (vtype == AQ_INT32 || vtype == AQ_FLOAT) ? AQ_FLOAT : AQ_DOUBLE;  // types.h:199-204
     case AQ_MINS: case AQ_MAXS: case AQ_MINW: case AQ_MAXW:
     case AQ_DELTAS: case AQ_PREV: case AQ_NEXT: return vtype;

@@ -11,6 +11,7 @@
 // Segmented scan = 3 phases per level (tile aggregates -> recursive scan of the aggregates -> tile
 // scans with carry); no spin-waiting between CTAs, deterministic summation order.
 #include "scan.cuh"
+#include <type_traits>
 
 namespace aq {
 
@@ -53,6 +54,19 @@ template <class A> struct ColLoader {           // level 1: the gathered column,
         case AQ_FLOAT: return (A) static_cast<const float*>(gv)[p];
         default:       return (A) static_cast<const double*>(gv)[p];
         }
+    }
+};
+template <class A> struct SqLoader {            // x * x in the accumulator type (moments)
+    const void* gv; int vtype;
+    __device__ A operator()(uint32_t p) const {
+        A x;
+        switch (vtype) {
+        case AQ_INT32: x = (A) static_cast<const int*>(gv)[p]; break;
+        case AQ_INT64: x = (A) static_cast<const long long*>(gv)[p]; break;
+        case AQ_FLOAT: x = (A) static_cast<const float*>(gv)[p]; break;
+        default:       x = (A) static_cast<const double*>(gv)[p]; break;
+        }
+        return x * x;
     }
 };
 template <class A> struct ArrLoader {            // level >= 2: tile aggregates
@@ -329,6 +343,43 @@ __global__ void k_seg_len(const uint32_t* __restrict__ perm, const uint32_t* __r
     }
 }
 
+// running (w == 0) / sliding population variance from the segmented prefix sums of x (S) and x * x (S2):
+// var = (c * sum(x^2) - sum(x)^2) / c^2 over the last c = min(w, i + 1) elements; integers in 128-bit arithmetic
+// floating-point columns with short windows (w <= VAR_DIRECT_W) are evaluated from the window's own elements (two
+// passes: the difference of two long prefix sums would carry the rounding of the whole prefix into a short window)
+constexpr uint32_t VAR_DIRECT_W = 64;
+template <class L>
+__global__ void __launch_bounds__(256)
+k_var_window(const uint32_t w, const int sd, const L* __restrict__ S, const L* __restrict__ S2, const uint32_t* __restrict__ start,
+             const uint32_t n, double* __restrict__ out, const void* __restrict__ gv, const int vtype) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+        const uint32_t i = p - start[p];
+        const uint32_t c = (w == 0u || w > i + 1u) ? i + 1u : w;
+        if (!std::is_integral<L>::value && w != 0u && w <= VAR_DIRECT_W) {
+            auto at = [&](uint32_t q) -> double { return vtype == AQ_FLOAT ? (double)static_cast<const float*>(gv)[q] : static_cast<const double*>(gv)[q]; };
+            double m = 0.0, q2 = 0.0;
+            for (uint32_t j = p + 1u - c; j <= p; ++j) m += at(j);
+            m /= (double)c;
+            for (uint32_t j = p + 1u - c; j <= p; ++j) { const double d = at(j) - m; q2 += d * d; }
+            q2 /= (double)c;
+            out[p] = sd ? sqrt(q2) : q2;
+            continue;
+        }
+        L s = S[p], s2 = S2[p];
+        if (i >= c) { s -= S[p - c]; s2 -= S2[p - c]; }
+        double v;
+        if (std::is_integral<L>::value) {                                // integer sums: exact numerator
+            const __int128 num = (__int128)c * (__int128)(long long)s2 - (__int128)(long long)s * (__int128)(long long)s;
+            v = (double)num / ((double)c * (double)c);
+        } else {
+            const double ds = (double)s, ds2 = (double)s2;
+            v = (ds2 - ds * ds / (double)c) / (double)c;
+        }
+        if (v < 0.0) v = 0.0;
+        out[p] = sd ? sqrt(v) : v;
+    }
+}
+
 template <class T>
 static int window_t(int op, uint32_t w, const void* gv, const void* S, const uint32_t* start,
                     const uint32_t* seg_len, uint32_t n, void* out, int out_type) {
@@ -374,6 +425,29 @@ int group_scan_device(int op, uint32_t w, int vtype, const void* d_v, uint32_t n
         return seg_scan<double, OP_MIN, ColLoader<double>, OutStorer<double>>(n, d_start, ld, st);
     }
     default: break;
+    }
+
+    if (op == AQ_VARS || op == AQ_STDDEVS || op == AQ_VARW || op == AQ_STDDEVW) {
+        if ((op == AQ_VARW || op == AQ_STDDEVW) && w == 0) return fail("window length 0");
+        const uint32_t ww = (op == AQ_VARS || op == AQ_STDDEVS) ? 0u : w;
+        const int sd = (op == AQ_STDDEVS || op == AQ_STDDEVW) ? 1 : 0;
+        DevBuf S1, S2;
+        AQ_TRY(S1.alloc(size_t(n) * 8));
+        AQ_TRY(S2.alloc(size_t(n) * 8));
+        if (isint) {
+            ColLoader<long long> ld{gv.p, vtype}; SqLoader<long long> lq{gv.p, vtype};
+            OutStorer<long long> st1{S1.p, ST_RAW, vtype, 0}, st2{S2.p, ST_RAW, vtype, 0};
+            AQ_TRY((seg_scan<long long, OP_ADD, ColLoader<long long>, OutStorer<long long>>(n, d_start, ld, st1)));
+            AQ_TRY((seg_scan<long long, OP_ADD, SqLoader<long long>, OutStorer<long long>>(n, d_start, lq, st2)));
+            AQ_LAUNCH(k_var_window<long long>, grid_for(n, 256, 1, 32), 256, 0, ww, sd, S1.as<long long>(), S2.as<long long>(), d_start, n, static_cast<double*>(d_out), gv.p, vtype);
+        } else {
+            ColLoader<double> ld{gv.p, vtype}; SqLoader<double> lq{gv.p, vtype};
+            OutStorer<double> st1{S1.p, ST_RAW, vtype, 0}, st2{S2.p, ST_RAW, vtype, 0};
+            AQ_TRY((seg_scan<double, OP_ADD, ColLoader<double>, OutStorer<double>>(n, d_start, ld, st1)));
+            AQ_TRY((seg_scan<double, OP_ADD, SqLoader<double>, OutStorer<double>>(n, d_start, lq, st2)));
+            AQ_LAUNCH(k_var_window<double>, grid_for(n, 256, 1, 32), 256, 0, ww, sd, S1.as<double>(), S2.as<double>(), d_start, n, static_cast<double*>(d_out), gv.p, vtype);
+        }
+        return 0;
     }
 
     if (w == 0 && (op == AQ_SUMW || op == AQ_AVGW || op == AQ_MINW || op == AQ_MAXW || op == AQ_RATIOW))

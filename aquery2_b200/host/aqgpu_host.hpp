@@ -10,7 +10,7 @@
 //   HashTableFactory<K,H>::get(cols...) -> {size, keys, values, offsets}   server/hasher.h:201-207, 324-357
 //   AQHashTable<K,H>: hashtable_push / hashtable_push_all / ht_postproc    server/hasher.h:146-199
 //   count sum avg min max first last, sums avgs mins maxs, sumw avgw minw maxw (SQL sums(w,x) ...),
-//   deltas prev aggnext ratios ratiow, var stddev corr     server/aggregations.h
+//   deltas prev aggnext ratios ratiow, var stddev corr, vars stddevs varw stddevw     server/aggregations.h
 //
 // A column's `container` may point to host memory or into the HBM column store (ColRef::to_device());
 // every library call accepts both.  Two ways to use it:
@@ -530,9 +530,15 @@ AQ_SCANW(avgw, AQ_AVGW, double)                     // :258-281
 AQ_SCANW(minw, AQ_MINW, T)                          // :127-146
 AQ_SCANW(maxw, AQ_MAXW, T)                          // :148-167
 AQ_SCANW(ratiow, AQ_RATIOW, types::GetFPType<T>)    // :169-201
+AQ_SCAN0(vars, AQ_VARS, double)                     // :350-381
+AQ_SCAN0(stddevs, AQ_STDDEVS, double)               // :419-425
+AQ_SCANW(varw, AQ_VARW, double)                     // :283-330 (see include/aqgpu.h: the reference's recurrence is undefined at i == w)
+AQ_SCANW(stddevw, AQ_STDDEVW, double)               // :427-436
 template <class T> vector_type<types::GetFPType<T>> ratios(const aq::GroupVec<T>& v) { return aq::scan_view<types::GetFPType<T>, T>(v, AQ_RATIOW, 1); }
 // SQL spellings with a window argument (common/types.py:285-290, 349-352): sums(w, x) == sumw(w, x) ...
 template <class T> auto sums(uint32_t w, const aq::GroupVec<T>& v) { return sumw(w, v); }
+template <class T> auto vars(uint32_t w, const aq::GroupVec<T>& v) { return varw(w, v); }
+template <class T> auto stddevs(uint32_t w, const aq::GroupVec<T>& v) { return stddevw(w, v); }
 template <class T> auto avgs(uint32_t w, const aq::GroupVec<T>& v) { return avgw(w, v); }
 template <class T> auto mins(uint32_t w, const aq::GroupVec<T>& v) { return minw(w, v); }
 template <class T> auto maxs(uint32_t w, const aq::GroupVec<T>& v) { return maxw(w, v); }
@@ -588,6 +594,8 @@ AQ_WSCAN0(sums, AQ_SUMS, types::GetLongType<T>) AQ_WSCAN0(avgs, AQ_AVGS, double)
 AQ_WSCAN0(deltas, AQ_DELTAS, T) AQ_WSCAN0(prev, AQ_PREV, T) AQ_WSCAN0(aggnext, AQ_NEXT, T)
 AQ_WSCANW(sumw, AQ_SUMW, types::GetLongType<T>) AQ_WSCANW(avgw, AQ_AVGW, double) AQ_WSCANW(minw, AQ_MINW, T) AQ_WSCANW(maxw, AQ_MAXW, T)
 AQ_WSCANW(ratiow, AQ_RATIOW, types::GetFPType<T>)
+AQ_WSCAN0(vars, AQ_VARS, double) AQ_WSCAN0(stddevs, AQ_STDDEVS, double) AQ_WSCANW(varw, AQ_VARW, double) AQ_WSCANW(stddevw, AQ_STDDEVW, double)
+AQ_WSCANW(vars, AQ_VARW, double) AQ_WSCANW(stddevs, AQ_STDDEVW, double)      // SQL: stddevs(3, price) (benchmark/quries/Aquery/q10.a)
 AQ_WSCANW(sums, AQ_SUMW, types::GetLongType<T>) AQ_WSCANW(avgs, AQ_AVGW, double) AQ_WSCANW(mins, AQ_MINW, T) AQ_WSCANW(maxs, AQ_MAXW, T)
 template <class T> aq::VecCol<types::GetFPType<T>> ratios(const aq::GroupedCol<T>& c) { return aq::scan_col<types::GetFPType<T>, T>(c, AQ_RATIOW, 1); }
 #undef AQ_SCAN0

@@ -75,7 +75,14 @@ enum aqgpu_scan_op {
     AQ_DELTAS = 8,  /* aggregations.h:439-446 */
     AQ_PREV = 9,    /* aggregations.h:455-462 */
     AQ_NEXT = 10,   /* aggregations.h:471-478 (aggnext) */
-    AQ_RATIOW = 11  /* aggregations.h:169-184 ratios(x) == ratiow(1, x) */
+    AQ_RATIOW = 11, /* aggregations.h:169-184 ratios(x) == ratiow(1, x) */
+    /* moments, second wave (benchmark/quries/Aquery/q10.a: MAX(stddevs(3, price))); results AQ_DOUBLE.
+     * AQ_VARS / AQ_STDDEVS: running population variance of the group's first i+1 elements (aggregations.h:350-381,
+     * 419-425: Welford; evaluated here from exact prefix sums of x and x*x, <= 1e-12 apart).
+     * AQ_VARW / AQ_STDDEVW: population variance of the last min(w, i+1) elements.  The reference's recurrence
+     * (aggregations.h:283-330) reads arr[i-w-1] -- arr[-1] at i == w -- and mixes sqrt'ed and plain cells in its
+     * stddev form, so it has no defined result to match: this is the definition its warm-up loop states. */
+    AQ_VARS = 12, AQ_STDDEVS = 13, AQ_VARW = 14, AQ_STDDEVW = 15
 };
 
 /* Order of the rows inside a group's row list. */

@@ -131,6 +131,7 @@ int aqo_scan_out_type(int op, int vtype) {
     switch (op) {
     case AQO_SUMS: case AQO_SUMW: return is_int(vtype) ? AQO_INT128 : AQO_DOUBLE;
     case AQO_AVGS: case AQO_AVGW: return AQO_DOUBLE;
+    case AQO_VARS: case AQO_STDDEVS: case AQO_VARW: case AQO_STDDEVW: return AQO_DOUBLE;
     case AQO_RATIOW: return (vtype == AQO_INT32 || vtype == AQO_FLOAT) ? AQO_FLOAT : AQO_DOUBLE;
     case AQO_MINS: case AQO_MAXS: case AQO_MINW: case AQO_MAXW:
     case AQO_DELTAS: case AQO_PREV: case AQO_NEXT: return vtype;
@@ -252,6 +253,28 @@ static int scan_##SFX(int op, uint32_t w0, const T* v, uint32_t ng, const uint32
             if (n) ret[0] = 0;                                                                      \
             for (uint32_t i = 0; i < w && i < n; ++i) ret[i] = v[r[i]] / (FP)v[r[0]];               \
             for (uint32_t i = w; i < n; ++i) ret[i] = v[r[i]] / (FP)v[r[i - w]]; } break;           \
+        case AQO_VARS: case AQO_STDDEVS: { double* ret = (double*)out + o; /* aggregations.h:350-381, 419-425: Welford;   \
+            the reference's loop also printf()s every element (:368, a debug leftover) -- not restated */                  \
+            L s = 0; double MnX = 0, EnX = 0;                                                       \
+            if (n) { s = v[r[0]]; EnX = v[r[0]]; ret[0] = 0; }                                      \
+            for (uint32_t i = 1; i < n; ++i) {                                                      \
+                s += v[r[i]];                                                                       \
+                const double e2 = s / (double)(i + 1);                                              \
+                MnX += (v[r[i]] - EnX) * (v[r[i]] - e2); EnX = e2;                                  \
+                ret[i] = MnX / (double)(i + 1);                                                     \
+                if (op == AQO_STDDEVS) ret[i] = sqrt(ret[i]); } } break;                            \
+        case AQO_VARW: case AQO_STDDEVW: { double* ret = (double*)out + o;                          \
+            /* NOT a reference result: aggregations.h:283-330 reads arr[i-w-1] (arr[-1] at i == w) and its stddev   \
+               form feeds sqrt'ed cells back into the recurrence.  This states what its warm-up loop defines:      \
+               the population variance of the last min(w, i+1) elements, two-pass per window. */                  \
+            if (w == 0) return -2;                                                                  \
+            for (uint32_t i = 0; i < n; ++i) {                                                      \
+                const uint32_t c = w > i + 1 ? i + 1 : w; double m = 0, q = 0;                      \
+                for (uint32_t j = i + 1 - c; j <= i; ++j) m += (double)v[r[j]];                     \
+                m /= (double)c;                                                                     \
+                for (uint32_t j = i + 1 - c; j <= i; ++j) q += ((double)v[r[j]] - m) * ((double)v[r[j]] - m); \
+                q /= (double)c;                                                                     \
+                ret[i] = op == AQO_STDDEVW ? sqrt(q) : q; } } break;                                \
         default: free(dq_v); free(dq_i); return -2; } }                                             \
     free(dq_v); free(dq_i);                                                                         \
     return 0; }

@@ -40,7 +40,8 @@ enum aqo_reduce_op {
 enum aqo_scan_op {
     AQO_SUMS = 0, AQO_AVGS = 1, AQO_MINS = 2, AQO_MAXS = 3,
     AQO_SUMW = 4, AQO_AVGW = 5, AQO_MINW = 6, AQO_MAXW = 7,
-    AQO_DELTAS = 8, AQO_PREV = 9, AQO_NEXT = 10, AQO_RATIOW = 11
+    AQO_DELTAS = 8, AQO_PREV = 9, AQO_NEXT = 10, AQO_RATIOW = 11,
+    AQO_VARS = 12, AQO_STDDEVS = 13, AQO_VARW = 14, AQO_STDDEVW = 15
 };
 
 /* Which oracle is this?  "reference" (built from /root/reference) or "port" (C restatement). */

@@ -26,13 +26,13 @@ INT32, FLOAT, DOUBLE, INT64, INT128, UINT32 = 0, 1, 3, 5, 6, 11
 # aqo_reduce_op
 SUM, AVG, MIN, MAX, COUNT, FIRST, LAST, VAR, STDDEV, CORR, SECOND = range(11)
 # aqo_scan_op
-SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW = range(12)
+SUMS, AVGS, MINS, MAXS, SUMW, AVGW, MINW, MAXW, DELTAS, PREV, NEXT, RATIOW, VARS, STDDEVS, VARW, STDDEVW = range(16)
 
 REDUCE_NAMES = {"sum": SUM, "avg": AVG, "min": MIN, "max": MAX, "count": COUNT, "first": FIRST,
                 "last": LAST, "var": VAR, "stddev": STDDEV, "corr": CORR, "second": SECOND}
 SCAN_NAMES = {"sums": SUMS, "avgs": AVGS, "mins": MINS, "maxs": MAXS, "sumw": SUMW, "avgw": AVGW,
               "minw": MINW, "maxw": MAXW, "deltas": DELTAS, "prev": PREV, "next": NEXT,
-              "ratiow": RATIOW}
+              "ratiow": RATIOW, "vars": VARS, "stddevs": STDDEVS, "varw": VARW, "stddevw": STDDEVW}
 
 _NP2CODE = {np.dtype(np.int32): INT32, np.dtype(np.float32): FLOAT, np.dtype(np.float64): DOUBLE,
             np.dtype(np.int64): INT64, np.dtype(np.uint32): UINT32}

@@ -1,3 +1,5 @@
+#include <fcntl.h>
+#include <unistd.h>
 /*
  * ref_harness.cpp -- the REFERENCE'S OWN post-processor library compiled as a CPU oracle.
  *
@@ -180,7 +182,17 @@ int scan_t(int op, uint32_t w, const void* v, uint32_t ng, const uint32_t* off,
     case AQO_PREV:   per_group_vec<T, T>(v, ng, off, perm, out, [&](V& a, vector_type<T>& r) { prev(a, r); }); return 0;
     case AQO_NEXT:   per_group_vec<T, T>(v, ng, off, perm, out, [&](V& a, vector_type<T>& r) { aggnext(a, r); }); return 0;
     case AQO_RATIOW: per_group_vec<T, FP>(v, ng, off, perm, out, [&](V& a, vector_type<FP>& r) { ratiow(w, a, r); }); return 0;
-    default: return -2;
+    case AQO_VARS: case AQO_STDDEVS: {
+        // the reference's loop printf()s every element (aggregations.h:368): stdout is parked on /dev/null meanwhile
+        fflush(stdout);
+        const int keep = ::dup(1), nul = ::open("/dev/null", O_WRONLY);
+        dup2(nul, 1);
+        if (op == AQO_VARS) per_group_vec<T, LFP>(v, ng, off, perm, out, [&](V& a, vector_type<LFP>& r) { vars<T, vector_type, vector_type<LFP>, false>(a, r); });
+        else per_group_vec<T, LFP>(v, ng, off, perm, out, [&](V& a, vector_type<LFP>& r) { vars<T, vector_type, vector_type<LFP>, true>(a, r); });
+        fflush(stdout);
+        dup2(keep, 1); close(keep); close(nul);
+        return 0; }
+    default: return -2;                            // AQO_VARW / AQO_STDDEVW: the reference reads arr[-1] (aggregations.h:311): no defined result
     }
 }
 
@@ -204,7 +216,7 @@ template <class T> int reduce_out_t(int op) {
 template <class T> int scan_out_t(int op) {
     switch (op) {
     case AQO_SUMS: case AQO_SUMW: return code_of<types::GetLongType<T>>::v;
-    case AQO_AVGS: case AQO_AVGW: return code_of<types::GetFPType<types::GetLongType<T>>>::v;
+    case AQO_AVGS: case AQO_AVGW: case AQO_VARS: case AQO_STDDEVS: return code_of<types::GetFPType<types::GetLongType<T>>>::v;
     case AQO_RATIOW: return code_of<std::decay_t<types::GetFPType<T>>>::v;
     case AQO_MINS: case AQO_MAXS: case AQO_MINW: case AQO_MAXW:
     case AQO_DELTAS: case AQO_PREV: case AQO_NEXT: return code_of<T>::v;

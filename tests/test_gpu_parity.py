@@ -726,3 +726,23 @@ def test_range_partitioned_speculation_fails(gpu, port, monkeypatch):
     t = table(); t["k"] = (t["k"].astype(np.int64) * 5003 - 700_000_000).astype(np.int32)
     _, took = _took_mc(gpu, lambda: check_query_vs_oracle(gpu, port, t, ["k"], [("sum", "v"), ("avg", "f")]))
     assert not took
+
+
+# ---- A9 second wave: running / windowed variance and standard deviation -------------------------------------
+@pytest.mark.parametrize("n,nsym", [(200_000, 1000), (30_000, 7)])
+def test_moment_scans_vs_oracle(gpu, port, n, nsym):
+    """vars / stddevs (aggregations.h:350-381, 419-425) and varw / stddevw against the oracle; the GPU evaluates
+    exact prefix sums of x and x*x instead of Welford's recurrence: fp64 results within 1e-12 of the value scale^2"""
+    t = synth.trade_table(n, nsym, seed=13)
+    vals = trade_values(t)
+    h = gpu.Groups([t["sym"]])
+    ng, gid, off, perm = port.groupby([t["sym"]])
+    for vn in ("price_i32", "price_f32", "signed_i32", "qty_f64"):
+        v = vals[vn]
+        sc = float(np.abs(v.astype(np.float64)).max())
+        for op, w in (("vars", 0), ("stddevs", 0), ("varw", 1), ("varw", 3), ("varw", 64), ("stddevw", 3), ("stddevw", 50)):
+            got, want = h.scan(op, v, w=w), port.scan(op, v, off, perm, w=w)
+            if op.startswith("stddev"):            # the tolerance is stated on the variance: sqrt amplifies rounding noise near 0
+                got, want = got * got, want * want
+            assert_same(got, want, f"{op}({w}) {vn}", scale=sc * sc)
+    h.free()

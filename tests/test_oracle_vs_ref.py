@@ -60,3 +60,35 @@ def test_h2o_1e5(port, ref):
         assert a[0] == b[0]
         for x, y in zip(a[1:], b[1:]):
             assert_same(x, y)
+
+
+def test_moment_scans_port_vs_reference_and_definition():
+    """vars / stddevs: the C port against the reference's own Welford loops (aggregations.h:350-381, 419-425; the
+    harness parks stdout because the reference printf()s every element).  varw / stddevw have no defined reference
+    result (arr[i-w-1] at i == w, aggregations.h:311): the port states the windowed population variance, checked
+    here against numpy."""
+    from oracle import aqo
+    ref = aqo.load_ref()
+    if ref is None:
+        pytest.skip("reference build not available")
+    port = aqo.load_port()
+    rng = np.random.default_rng(1)
+    n = 3000
+    k = rng.integers(0, 9, n).astype(np.int32)
+    ng, gid, off, perm = port.groupby([k])
+    for dt in (np.int32, np.int64, np.float32, np.float64):
+        v = rng.integers(-500, 500, n).astype(dt) if np.issubdtype(dt, np.integer) else (rng.random(n) * 100).astype(dt)
+        for op in ("vars", "stddevs"):
+            a, b = port.scan(op, v, off, perm), ref.scan(op, v, off, perm)
+            assert np.all(np.abs(a - b) <= 1e-12 * np.maximum(np.abs(b), 1.0)), (dt, op)
+        for w in (1, 3, 50):
+            got = port.scan("varw", v, off, perm, w=w)
+            sd = port.scan("stddevw", v, off, perm, w=w)
+            want = np.zeros(n)
+            for g in range(ng):
+                x = v[perm[off[g]:off[g + 1]]].astype(np.float64)
+                for i in range(len(x)):
+                    c = min(w, i + 1)
+                    want[off[g] + i] = np.var(x[i + 1 - c:i + 1])
+            assert np.all(np.abs(got - want) <= 1e-9 * np.maximum(np.abs(want), 1.0)), (dt, w)
+            assert np.all(np.abs(sd - np.sqrt(want)) <= 1e-9 * np.maximum(np.sqrt(want), 1.0)), (dt, w)

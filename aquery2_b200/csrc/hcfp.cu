@@ -740,7 +740,7 @@ int run_hcfp(const KeyCols& kc, uint32_t nrows, AggPlan& plan, OutSink& sink, ui
 // one-row group -- and the emit is the single-GPU one over the LOCAL rows: a rank emits the groups whose first row it
 // holds, in row order, so the ranks' results concatenated in rank order are in global first-appearance order.
 // Key tuples that really repeat more than FPC_TOTAL / 2 times overall make every rank decline.
-constexpr uint32_t FPC_TOTAL = 8192;            // candidate list entries over all ranks
+constexpr uint32_t FPC_TOTAL = 65536;           // candidate list entries over all ranks (the exact resolve is O(entries^2): ~5 ms at the cap)
 
 // entry i of the gathered candidate list: key words and value words of row cand[i] if it lives here, zeros otherwise
 __global__ void k_fp_cand_fill(const KeySpec ks, const AccProg prog, const uint32_t* __restrict__ cand, const uint32_t m,

@@ -867,8 +867,12 @@ bool mc_layout(const KeyCols& kc, uint32_t nrows, const AggPlan& plan, const Pla
         R = R > 8 ? ((R - 8u) & ~7u) : 0u;
         if (R > 65528u) R = 65528u;
         if (R < 1024u) return false;
+        // one CTA aggregates one partition: few slots still want at least ~2 partitions per SM
+        const uint32_t Rpar = (uint32_t)(((G + 2ull * M.C - 1) / (2ull * M.C) + 7ull) & ~7ull);
+        if (Rpar < R) R = Rpar < 64u ? 64u : Rpar;
         const uint32_t P = (uint32_t)((G + R - 1) / R);
         if (P > MC_PMAX) return false;
+        if (P < 32u) return false;                                        // a handful of slots: the shared-memory paths
         // spread the slots evenly over the partitions (smaller tables, same partition count)
         uint32_t Re = (uint32_t)((G + P - 1) / P);
         Re = (Re + 7u) & ~7u;

@@ -70,6 +70,16 @@ __device__ __forceinline__ void fx_global_add(unsigned long long* glo, unsigned 
 // false: the value has no exact image (the caller raises the abort flag).  Q, R: see the header.
 __device__ __forceinline__ bool fx_add(uint32_t* lo, uint32_t* hi, unsigned long long* glo, unsigned long long* ghi,
                                        float x, int B, int Q, int R) {
+    // fast path: x scaled to the cell's unit 2^(B+Q-150) is an integer of at most 24 + R bits.  Power-of-two scaling
+    // in double is exact, and so is the round trip through int64 exactly when the scaled value is an integer (this
+    // also admits values below the window whose low mantissa bits are zero); inf / nan fail the comparison.
+    {
+        const double sc = __longlong_as_double((long long)(1023 + 150 - B - Q) << 52);
+        const double lim = __longlong_as_double((long long)(1023 + 24 + R) << 52);
+        const double xd = (double)x * sc;
+        const long long X = __double2ll_rn(xd);
+        if ((double)X == xd && fabs(xd) <= lim) { isum2_add(lo, hi, X); return true; }
+    }
     const uint32_t bits = __float_as_uint(x);
     uint32_t m = bits & 0x7fffffu;
     int e = (int)((bits >> 23) & 0xffu);

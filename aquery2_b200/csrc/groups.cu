@@ -435,12 +435,16 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
     ArenaScope scope;
     if (!g || !cols || !col_types || ncols < 1) return fail("bad order_by arguments");
     if (g->nrows == 0) return 0;
-    AQ_TRY(ensure_perm(g));
     const uint32_t n = g->nrows;
+    // ties keep the current order of the row lists: the lists built so far, or -- when none has been materialised yet --
+    // the implicit ascending / descending row order (no need to sort by group first: the regroup pass below is stable)
+    const bool implicit = !g->has_perm;
+    if (implicit) { AQ_TRY(ensure_offsets(g)); AQ_TRY(g->perm.alloc(size_t(n) * 4)); }
     DevBuf a, b;
     AQ_TRY(a.alloc(size_t(n) * 4));
     AQ_TRY(b.alloc(size_t(n) * 4));
-    const uint32_t* cur = g->perm.as<uint32_t>();
+    const uint32_t* cur = implicit ? nullptr : g->perm.as<uint32_t>();
+    bool first_pass = true;
     uint32_t* bufs[2] = { a.as<uint32_t>(), b.as<uint32_t>() };
     int which = 0;
     std::vector<InCol> in(ncols);
@@ -452,6 +456,7 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
         job.n = n; job.key_bits = 32;
         if (t == AQ_INT32 || t == AQ_UINT32 || t == AQ_FLOAT) {
             job.rows_in = cur; job.col = static_cast<const uint32_t*>(in[c].d); job.col_stride = 1;
+            job.reverse = (first_pass && implicit && g->row_order == AQ_ROWS_DESC) ? 1 : 0; first_pass = false;
             job.float_flip = t == AQ_FLOAT;
             const uint32_t asc_mask = t == AQ_INT32 ? 0x80000000u : 0u;
             job.xor_mask = d ? ~asc_mask : asc_mask;
@@ -461,6 +466,7 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
         } else if (t == AQ_INT64) {
             for (int half = 0; half < 2; ++half) {           // low word (unsigned) then high word (signed)
                 job.rows_in = cur; job.col = static_cast<const uint32_t*>(in[c].d) + half; job.col_stride = 2;
+                job.reverse = (first_pass && implicit && g->row_order == AQ_ROWS_DESC) ? 1 : 0; first_pass = false;
                 const uint32_t asc_mask = half ? 0x80000000u : 0u;
                 job.xor_mask = d ? ~asc_mask : asc_mask;
                 job.rows_out = bufs[which];
@@ -480,6 +486,7 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
     if (bits == 0) AQ_CUDA(cudaMemcpyAsync(g->perm.p, cur, size_t(n) * 4, cudaMemcpyDeviceToDevice, ctx().stream));
     else AQ_TRY(sort_rows_by_key(job));
     g->custom_order = true;
+    g->has_perm = true;
     AQ_CUDA(cudaStreamSynchronize(ctx().stream));
     return 0;
 }

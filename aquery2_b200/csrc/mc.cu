@@ -531,14 +531,16 @@ k_mc_agg(const McParams M) {
 
 // ---- first rows -------------------------------------------------------------------------------------------------
 constexpr int MCF_THREADS = 256;
-constexpr int MCF_ROWS = MCF_THREADS * 4;
+constexpr int MCF_Q = 4;                                  // quads of rows per thread and tile: the ticket / counter round trips are per tile
+constexpr int MCF_ROWS = MCF_THREADS * 4 * MCF_Q;
 template <int NK>
 __global__ void __launch_bounds__(MCF_THREADS)
 k_mc_first(const McParams M) {
     __shared__ uint32_t s_tile;
     if (*reinterpret_cast<volatile uint32_t*>(M.flags + FLAG_ABORT)) return;
     const uint32_t nquad = (M.nrows + 3u) >> 2;
-    const uint32_t ntiles = (nquad + MCF_THREADS - 1) / MCF_THREADS;
+    const uint32_t tile_quads = MCF_THREADS * MCF_Q;
+    const uint32_t ntiles = (nquad + tile_quads - 1) / tile_quads;
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -548,33 +550,47 @@ k_mc_first(const McParams M) {
         __syncthreads();
         const uint32_t tile = s_tile;
         if (tile >= ntiles) return;
-        const uint32_t q = tile * MCF_THREADS + threadIdx.x;
-        const uint32_t row0 = q << 2;
-        const int cnt = q < nquad ? (int)min(4u, M.nrows - row0) : 0;      // (no early exit: the warp reduction below is full-mask)
-        uint32_t slot[4] = {0u, 0u, 0u, 0u};
-        bool ok[4] = {true, true, true, true};
+        uint32_t slot[MCF_Q][4];
+        uint32_t okm = 0;                                  // bit 4 * i + r: row r of quad i is a row with in-range keys
 #pragma unroll
-        for (int k = 0; k < NK; ++k) {
-            uint32_t kv[4] = {0u, 0u, 0u, 0u};
-            if (cnt) load4_b32(M.keys[k], row0, cnt, true, kv);
+        for (int i = 0; i < MCF_Q; ++i) {
+            const uint32_t q = tile * tile_quads + i * MCF_THREADS + threadIdx.x;
+            const uint32_t row0 = q << 2;
+            const int cnt = q < nquad ? (int)min(4u, M.nrows - row0) : 0;      // (no early exit: the warp reduction below is full-mask)
+            bool ok[4] = {cnt > 0, cnt > 1, cnt > 2, cnt > 3};
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const uint32_t d = kv[r] - M.klo[k];
-                ok[r] &= d <= M.krange[k];
-                slot[r] += d * M.kmul[k];
+            for (int r = 0; r < 4; ++r) slot[i][r] = 0u;
+#pragma unroll
+            for (int k = 0; k < NK; ++k) {
+                uint32_t kv[4] = {0u, 0u, 0u, 0u};
+                if (cnt) load4_b32(M.keys[k], row0, cnt, true, kv);
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const uint32_t d = kv[r] - M.klo[k];
+                    ok[r] &= d <= M.krange[k];
+                    slot[i][r] += d * M.kmul[k];
+                }
             }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) if (ok[r]) okm |= 1u << (4 * i + r);
         }
+        uint32_t cur[MCF_Q][4];
+#pragma unroll
+        for (int i = 0; i < MCF_Q; ++i)
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                cur[i][r] = (okm >> (4 * i + r)) & 1u ? *reinterpret_cast<volatile uint32_t*>(M.gfirst + slot[i][r]) : 0u;
         uint32_t fresh = 0;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            if (r >= cnt || !ok[r]) continue;
-            const uint32_t row = row0 + r;
-            const uint32_t cur = *reinterpret_cast<volatile uint32_t*>(M.gfirst + slot[r]);
-            if (row < cur) {
-                const uint32_t old = atomicMin(M.gfirst + slot[r], row);
-                if (old == 0xffffffffu) ++fresh;
+        for (int i = 0; i < MCF_Q; ++i)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const uint32_t row = ((tile * tile_quads + i * MCF_THREADS + threadIdx.x) << 2) + r;
+                if (((okm >> (4 * i + r)) & 1u) && row < cur[i][r]) {
+                    const uint32_t old = atomicMin(M.gfirst + slot[i][r], row);
+                    if (old == 0xffffffffu) ++fresh;
+                }
             }
-        }
         fresh = __reduce_add_sync(0xffffffffu, fresh);
         if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(M.ctl + 2, fresh);
     }

@@ -50,7 +50,7 @@ EXPORTS = [
     "aqgpu_result_first_row", "aqgpu_result_free", "aqgpu_trim_pool", "aqgpu_col_upload_async",
     "aqgpu_col_download_async",
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
-    "aqgpu_result_replicated",
+    "aqgpu_result_replicated", "aqgpu_group_median",
 ]
 
 
@@ -387,6 +387,13 @@ class Groups:
         check(lib().aqgpu_group_scan(self.h, op, ctypes.c_uint32(w), vt, ctypes.c_void_p(vp), ot,
                                      ctypes.c_void_p(_out_ptr(ob))))
         return ob
+
+    def median(self, v):
+        """aqgpu_group_median: fp64 median of v per group (not a reference aggregate: checked against numpy)"""
+        vp, vt, keep = _col(v)
+        out = np.zeros(self.ngroups, np.float64)
+        check(lib().aqgpu_group_median(self.h, vt, ctypes.c_void_p(vp), out.ctypes.data_as(ctypes.c_void_p)))
+        return out
 
     def window(self, exprs, device_out: bool = False):
         """Several vector-valued expressions in one call (aqgpu_group_window).  exprs: tuples

@@ -245,6 +245,18 @@ static int build_direct(aqgpu_groups* g, const KeyCols& kc, const PlanHints& ph,
     return 0;
 }
 
+// perm: row lists ordered by (group, v); the middle element(s) of every list
+template <class T>
+__global__ void k_median_pick(const T* __restrict__ v, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
+                              uint32_t ngroups, double* __restrict__ out) {
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+        const uint32_t lo = offsets[g], n = offsets[g + 1] - lo;
+        if (n == 0) { out[g] = 0.0; continue; }
+        const double a = (double)v[perm[lo + (n - 1) / 2]], b = (double)v[perm[lo + n / 2]];
+        out[g] = (n & 1u) ? a : 0.5 * (a + b);
+    }
+}
+
 extern "C" {
 
 int aqgpu_groupby_build(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
@@ -383,6 +395,43 @@ int aqgpu_group_reduce(aqgpu_groups_t* g, int op, int vtype, const void* v, cons
     AQ_TRY(aqgpu_groupby_agg(keys, kt, 1, g->nrows, nullptr, nullptr, g->row_order, g->ngroups, &a, 1, g->ngroups,
                              nullptr, nullptr, &ng));
     if (ng != g->ngroups) return fail("internal: reduce saw %u groups, handle has %u", ng, g->ngroups);
+    return 0;
+}
+
+int aqgpu_group_median(aqgpu_groups_t* g, int vtype, const void* v, double* out) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (!g || !v || !out) return fail("null argument");
+    if (vtype != AQ_INT32 && vtype != AQ_UINT32 && vtype != AQ_FLOAT) return fail("median: unsupported value dtype %d (int32, uint32, float)", vtype);
+    if (g->ngroups == 0) return 0;
+    const uint32_t n = g->nrows;
+    AQ_TRY(ensure_offsets(g));
+    InCol in;
+    AQ_TRY(in.bind(v, size_t(4) * n));
+    OutCol oc;
+    AQ_TRY(oc.bind(out, size_t(8) * g->ngroups));
+    DevBuf byval, bygroup;
+    AQ_TRY(byval.alloc(size_t(n) * 4));
+    AQ_TRY(bygroup.alloc(size_t(n) * 4));
+    SortJob job;                                              // rows by value ...
+    job.n = n; job.rows_in = nullptr; job.col = static_cast<const uint32_t*>(in.d); job.col_stride = 1; job.key_bits = 32;
+    job.float_flip = vtype == AQ_FLOAT;
+    job.xor_mask = vtype == AQ_INT32 ? 0x80000000u : 0u;
+    job.rows_out = byval.as<uint32_t>();
+    AQ_TRY(sort_rows_by_key(job));
+    SortJob rg;                                               // ... then (stable) by group
+    rg.n = n; rg.rows_in = byval.as<uint32_t>(); rg.col = g->gid.as<uint32_t>();
+    int bits = 0;
+    while (bits < 32 && (uint64_t(1) << bits) < uint64_t(g->ngroups)) ++bits;
+    rg.key_bits = bits;
+    rg.rows_out = bygroup.as<uint32_t>();
+    const uint32_t* perm = bygroup.as<uint32_t>();
+    if (bits == 0) perm = byval.as<uint32_t>(); else AQ_TRY(sort_rows_by_key(rg));
+    if (vtype == AQ_FLOAT) AQ_LAUNCH(k_median_pick<float>, grid_for(g->ngroups, 256), 256, 0, static_cast<const float*>(in.d), perm, g->offsets.as<uint32_t>(), g->ngroups, static_cast<double*>(oc.d));
+    else if (vtype == AQ_INT32) AQ_LAUNCH(k_median_pick<int>, grid_for(g->ngroups, 256), 256, 0, static_cast<const int*>(in.d), perm, g->offsets.as<uint32_t>(), g->ngroups, static_cast<double*>(oc.d));
+    else AQ_LAUNCH(k_median_pick<uint32_t>, grid_for(g->ngroups, 256), 256, 0, static_cast<const uint32_t*>(in.d), perm, g->offsets.as<uint32_t>(), g->ngroups, static_cast<double*>(oc.d));
+    AQ_TRY(oc.finish(size_t(8) * g->ngroups));
+    AQ_CUDA(cudaStreamSynchronize(ctx().stream));
     return 0;
 }
 

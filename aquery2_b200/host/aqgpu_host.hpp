@@ -598,6 +598,41 @@ AQ_WSCAN0(vars, AQ_VARS, double) AQ_WSCAN0(stddevs, AQ_STDDEVS, double) AQ_WSCAN
 AQ_WSCANW(vars, AQ_VARW, double) AQ_WSCANW(stddevs, AQ_STDDEVW, double)      // SQL: stddevs(3, price) (benchmark/quries/Aquery/q10.a)
 AQ_WSCANW(sums, AQ_SUMW, types::GetLongType<T>) AQ_WSCANW(avgs, AQ_AVGW, double) AQ_WSCANW(mins, AQ_MINW, T) AQ_WSCANW(maxs, AQ_MAXW, T)
 template <class T> aq::VecCol<types::GetFPType<T>> ratios(const aq::GroupedCol<T>& c) { return aq::scan_col<types::GetFPType<T>, T>(c, AQ_RATIOW, 1); }
+
+// (3) non-grouped forms: the whole column is ONE group in table order -- `SELECT avgs(3, sales) FROM sale ASSUMING ASC month`
+// (tests/moving_avg.a:7; the vector functions of server/aggregations.h applied to a plain ColRef).  One row per input row.
+namespace aq {
+template <class T> GroupedCol<T> whole_column(const ColRef<T>& c) {
+    auto g = std::make_shared<GroupsHandle>();
+    std::vector<uint32_t> zero(c.size ? c.size : 1, 0u);
+    const void* kp[1] = { zero.data() };
+    const int kt[1] = { AQ_UINT32 };
+    const int64_t lo[1] = {0}, hi[1] = {0};
+    check(aqgpu_groupby_build(kp, kt, 1, c.size, lo, hi, AQ_ROWS_ASC, 1, &g->h));
+    g->nrows = c.size;
+    check(aqgpu_groups_size(g->h, &g->ngroups));
+    return GroupedCol<T>{c.container, c.size, g};
+}
+}  // namespace aq
+#define AQ_PSCAN0(NAME) template <class T> auto NAME(const ColRef<T>& c) { return NAME(aq::whole_column(c)).flat; }
+#define AQ_PSCANW(NAME) template <class T> auto NAME(uint32_t w, const ColRef<T>& c) { return NAME(w, aq::whole_column(c)).flat; }
+AQ_PSCAN0(sums) AQ_PSCAN0(avgs) AQ_PSCAN0(mins) AQ_PSCAN0(maxs) AQ_PSCAN0(deltas) AQ_PSCAN0(prev) AQ_PSCAN0(aggnext) AQ_PSCAN0(ratios)
+AQ_PSCAN0(vars) AQ_PSCAN0(stddevs)
+AQ_PSCANW(sums) AQ_PSCANW(avgs) AQ_PSCANW(mins) AQ_PSCANW(maxs) AQ_PSCANW(sumw) AQ_PSCANW(avgw) AQ_PSCANW(minw) AQ_PSCANW(maxw) AQ_PSCANW(ratiow)
+AQ_PSCANW(vars) AQ_PSCANW(stddevs) AQ_PSCANW(varw) AQ_PSCANW(stddevw)
+#undef AQ_PSCAN0
+#undef AQ_PSCANW
+// scalar aggregates of a whole column (aggregations.h:10-86, 332-415): one cell
+#define AQ_PRED(NAME, RT) template <class T> RT NAME(const ColRef<T>& c) { auto r = NAME(aq::whole_column(c)); return c.size ? aq::cell0(r) : RT{}; }
+namespace aq {
+template <class R> R cell0(const ColRef<R>& r) {          // first cell of a result column that lives where the input lives
+    R v{};
+    if (r.size) { if (aqgpu_ptr_is_device(r.container) == 1) check(aqgpu_col_download(&v, r.container, sizeof(R))); else v = r.container[0]; }
+    return v;
+}
+}  // namespace aq
+AQ_PRED(sum, types::GetLongType<T>) AQ_PRED(avg, double) AQ_PRED(max, T) AQ_PRED(min, T) AQ_PRED(var, double) AQ_PRED(stddev, double)
+#undef AQ_PRED
 #undef AQ_SCAN0
 #undef AQ_SCANW
 #undef AQ_WSCAN0

@@ -175,6 +175,25 @@ int main() {
         EXPECT(g_w_off[gi + 1] - g_w_off[gi] == r.size());
         EXPECT(std::fabs(g_w_avgs[g_w_off[gi]] - (double)v1[r.back()]) < 1e-12);       // first cell = last row of the group
     }
+    {   // non-grouped forms (tests/moving_avg.a:7 `avgs(3, sales)`): the whole column is one group in table order
+        ColRef<int> sales((uint32_t)n, v1.data());
+        auto ma = avgs(3, sales);                       // ColRef<double>, one cell per row
+        auto rs = sums(sales);
+        auto dl = deltas(sales);
+        EXPECT(ma.size == n && rs.size == n && dl.size == n);
+        long long run = 0;
+        for (uint32_t i = 0; i < n && fails < 5; ++i) {
+            run += v1[i];
+            const uint32_t c = i < 3 ? i + 1 : 3;
+            double w = 0; for (uint32_t j = i + 1 - c; j <= i; ++j) w += v1[j];
+            EXPECT(std::fabs(ma[i] - w / c) <= 1e-9);
+            EXPECT((long long)rs[i] == run);
+            EXPECT(dl[i] == (i ? v1[i] - v1[i - 1] : 0));
+        }
+        EXPECT((long long)sum(sales) == run);
+        int mx = v1[0]; for (uint32_t i = 1; i < n; ++i) mx = std::max(mx, v1[i]);
+        EXPECT(max(sales) == mx);
+    }
     printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
     return fails ? 1 : 0;
 }

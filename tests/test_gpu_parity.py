@@ -746,3 +746,20 @@ def test_moment_scans_vs_oracle(gpu, port, n, nsym):
                 got, want = got * got, want * want
             assert_same(got, want, f"{op}({w}) {vn}", scale=sc * sc)
     h.free()
+
+
+def test_group_median_vs_numpy(gpu, port):
+    """h2o q6's median(v3) by id4, id5 (benchmark/h2o/groupby.sql:11-12).  The reference library has no median: the
+    check is numpy's, per group, on the oracle's row lists -- NOT a reference result."""
+    n, k = 300_000, 40
+    t = synth.h2o_table(n, k, seed=21, columns=["id4", "id5", "v1", "v3"])
+    h = gpu.Groups([t["id4"], t["id5"]])
+    ng, gid, off, perm = port.groupby([t["id4"], t["id5"]])
+    assert h.ngroups == ng
+    for col in ("v3", "v1"):
+        got = h.median(t[col])
+        want = np.array([np.median(t[col][perm[off[g]:off[g + 1]]].astype(np.float64)) for g in range(ng)])
+        assert_same(got, want, f"median({col})")
+    o2, p2 = h.csr()
+    assert_same(p2, perm)                      # the handle's own row lists are untouched
+    h.free()

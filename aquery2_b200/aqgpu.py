@@ -50,7 +50,7 @@ EXPORTS = [
     "aqgpu_result_first_row", "aqgpu_result_free", "aqgpu_trim_pool", "aqgpu_col_upload_async",
     "aqgpu_col_download_async",
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
-    "aqgpu_result_replicated", "aqgpu_group_median",
+    "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows",
 ]
 
 
@@ -602,6 +602,26 @@ def comm_init(nranks: int, rank: int, unique_id: bytes) -> None:
 
 def comm_destroy() -> None:
     check(lib().aqgpu_comm_destroy())
+
+
+def repartition_rows(keys, cols, row_base: int):
+    """aqgpu_repartition_rows (collective): rows of this rank's shard -> the rank that owns their key tuple.  keys / cols are
+    DeviceColumns; returns (the columns on their new rank..., the rows' global ids) as owning DeviceColumns."""
+    nk, nc = len(keys), len(cols)
+    kp = (ctypes.c_void_p * nk)(*[k.ptr for k in keys])
+    kt = (ctypes.c_int * nk)(*[k.code for k in keys])
+    cp = (ctypes.c_void_p * nc)(*[c.ptr for c in cols])
+    eb = (ctypes.c_int * nc)(*[c.itemsize for c in cols])
+    out = (ctypes.c_void_p * (nc + 1))()
+    n = ctypes.c_uint32(0)
+    check(lib().aqgpu_repartition_rows(kp, kt, nk, ctypes.c_uint32(keys[0].n), ctypes.c_uint64(int(row_base)), cp, eb, nc, out, ctypes.byref(n)))
+    res = []
+    for i in range(nc + 1):
+        d = DeviceColumn.__new__(DeviceColumn)
+        code = cols[i].code if i < nc else UINT32
+        d.n, d.code, d.itemsize, d.ptr = int(n.value), code, CODE_SIZE[code], out[i]
+        res.append(d)
+    return res
 
 
 class ShardQuery(AutoQuery):

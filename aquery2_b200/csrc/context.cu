@@ -1,6 +1,9 @@
 // context.cu -- process context, error reporting, HBM column store primitives of libaqgpu.
 #include "common.cuh"
+#include <cuda.h>
+#include <algorithm>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -39,13 +42,89 @@ struct Arena {
 static Arena g_arena;
 static constexpr size_t ARENA_ALIGN = 256;
 
+// The arena's block is a virtual-address reservation that is backed on demand (driver virtual memory management:
+// cuMemAddressReserve + cuMemCreate / cuMemMap, bound at run time through cudaGetDriverEntryPoint) and only ever GROWS,
+// in place.  Freeing and re-allocating a larger block through the stream-ordered pool (the first version) fragmented
+// the pool: the first handful of 1e9-row steps each stalled for 0.2-0.8 s while the pool re-shuffled tens of GB
+// (profiles/r02/arena_warmup.txt).  Memory is returned by aqgpu_trim_pool.
+struct VmmArena {
+    bool tried = false, ok = false;
+    CUresult (*AddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*Create)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
+    CUresult (*Map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
+    CUresult (*Unmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*Release)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*GetGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
+    CUdeviceptr va = 0;
+    size_t reserved = 0, mapped = 0, gran = 0;
+    CUmemAllocationProp prop;
+    std::vector<std::pair<CUmemGenericAllocationHandle, size_t>> chunks;
+};
+static VmmArena g_vmm;
+
+static bool vmm_init() {
+    VmmArena& v = g_vmm;
+    if (v.tried) return v.ok;
+    v.tried = true;
+    if (getenv("AQGPU_NO_VMM")) return false;
+    auto sym = [](const char* name, void** fn) {
+        cudaDriverEntryPointQueryResult st;
+        return cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &st) == cudaSuccess && st == cudaDriverEntryPointSuccess && *fn;
+    };
+    if (!sym("cuMemAddressReserve", (void**)&v.AddressReserve) || !sym("cuMemCreate", (void**)&v.Create) || !sym("cuMemMap", (void**)&v.Map) ||
+        !sym("cuMemSetAccess", (void**)&v.SetAccess) || !sym("cuMemUnmap", (void**)&v.Unmap) || !sym("cuMemRelease", (void**)&v.Release) ||
+        !sym("cuMemGetAllocationGranularity", (void**)&v.GetGranularity)) { cudaGetLastError(); return false; }
+    memset(&v.prop, 0, sizeof(v.prop));
+    v.prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    v.prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    v.prop.location.id = ctx().device;
+    if (v.GetGranularity(&v.gran, &v.prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || v.gran == 0) return false;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return false; }
+    v.reserved = (total_b + v.gran - 1) / v.gran * v.gran;
+    if (v.AddressReserve(&v.va, v.reserved, 0, 0, 0) != CUDA_SUCCESS) return false;
+    v.ok = true;
+    return true;
+}
+// backs the reservation up to at least `want` bytes; false: out of memory (the caller falls back to the pool)
+static bool vmm_grow(size_t want) {
+    VmmArena& v = g_vmm;
+    if (!vmm_init() || want > v.reserved) return false;
+    while (v.mapped < want) {
+        size_t chunk = want - v.mapped;
+        const size_t step = size_t(1) << 30;
+        if (chunk < step) chunk = step;
+        chunk = (chunk + v.gran - 1) / v.gran * v.gran;
+        if (v.mapped + chunk > v.reserved) chunk = v.reserved - v.mapped;
+        CUmemGenericAllocationHandle h;
+        if (v.Create(&h, chunk, &v.prop, 0) != CUDA_SUCCESS) return false;
+        if (v.Map(v.va + v.mapped, chunk, 0, h, 0) != CUDA_SUCCESS) { v.Release(h); return false; }
+        CUmemAccessDesc acc;
+        memset(&acc, 0, sizeof(acc));
+        acc.location = v.prop.location;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        if (v.SetAccess(v.va + v.mapped, chunk, &acc, 1) != CUDA_SUCCESS) { v.Unmap(v.va + v.mapped, chunk); v.Release(h); return false; }
+        v.chunks.push_back({h, chunk});
+        v.mapped += chunk;
+    }
+    return true;
+}
+static void vmm_release_all() {
+    VmmArena& v = g_vmm;
+    size_t off = 0;
+    for (auto& c : v.chunks) { v.Unmap(v.va + off, c.second); v.Release(c.first); off += c.second; }
+    v.chunks.clear();
+    v.mapped = 0;
+}
+
 ArenaScope::ArenaScope() { ++g_arena.depth; }
 ArenaScope::~ArenaScope() {
     Arena& a = g_arena;
     if (--a.depth > 0) return;
     for (void* q : a.spilled) cudaFreeAsync(q, ctx().stream);
     a.spilled.clear();
-    if (a.need > a.cap) {                // grow to what this call needed (stream-ordered: earlier work still sees the old block)
+    if (a.need > a.cap && !g_vmm.ok) {   // no virtual memory management: grow to what this call needed through the pool
         if (a.base) cudaFreeAsync(a.base, ctx().stream);
         a.base = nullptr; a.cap = 0;
         const size_t want = a.need + a.need / 16 + (size_t(1) << 20);
@@ -67,7 +146,14 @@ int DevBuf::alloc(size_t n) {
             if (a.off + a.overflow > a.need) a.need = a.off + a.overflow;
             return 0;
         }
-        // does not fit (first call of this size): serve from the pool now, grow the arena when the scope closes
+        // does not fit: back more of the reservation (in place, at least a quarter more than before)
+        if ((a.base == nullptr || g_vmm.ok) && vmm_grow(std::max(a.off + m, a.cap + a.cap / 4))) {
+            a.base = reinterpret_cast<char*>(g_vmm.va); a.cap = g_vmm.mapped;
+            p = a.base + a.off; a.off += m; bytes = n; from_arena = true;
+            if (a.off + a.overflow > a.need) a.need = a.off + a.overflow;
+            return 0;
+        }
+        // no more memory to map (or no VMM): serve from the pool now
         cudaError_t e = cudaMallocAsync(&p, n, ctx().stream);
         if (e != cudaSuccess) { p = nullptr; return fail("cudaMallocAsync(%zu bytes): %s", n, cudaGetErrorString(e)); }
         a.spilled.push_back(p);
@@ -338,8 +424,9 @@ int aqgpu_col_download_async(void* host, const void* dptr, size_t bytes) {
 
 int aqgpu_trim_pool(void) {
     AQ_REQUIRE_INIT();
-    if (g_arena.depth == 0 && g_arena.base) { cudaFreeAsync(g_arena.base, g_ctx.stream); g_arena.base = nullptr; g_arena.cap = 0; g_arena.off = 0; }
+    if (g_arena.depth == 0 && g_arena.base && !g_vmm.ok) { cudaFreeAsync(g_arena.base, g_ctx.stream); g_arena.base = nullptr; g_arena.cap = 0; g_arena.off = 0; }
     AQ_CUDA(cudaStreamSynchronize(g_ctx.stream));
+    if (g_arena.depth == 0 && g_vmm.ok) { vmm_release_all(); g_arena.base = nullptr; g_arena.cap = 0; g_arena.off = 0; }
     cudaMemPool_t pool;
     AQ_CUDA(cudaDeviceGetDefaultMemPool(&pool, g_ctx.device));
     AQ_CUDA(cudaMemPoolTrimTo(pool, 0));

@@ -151,4 +151,73 @@ int dist_combine_owned(unsigned long long* gtab, uint32_t* gfirst, uint32_t G, u
     return 0;
 }
 
+__global__ void k_dist_iota(uint32_t* __restrict__ out, uint32_t n, uint32_t base) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = base + i;
+}
+
 } // namespace aq
+
+using namespace aq;
+
+// Rows of a sharded table repartitioned by hash(key tuple) mod ranks, so that every group lies whole on one rank:
+// SURVEY.md section 8(e), "windowed / order-sensitive aggregates".  A stable split by owner (aqgpu_key_owner +
+// aqgpu_partition_rows), the per-destination row counts all-gathered, then ONE grouped ncclSend / ncclRecv per column.
+// Blocks arrive in source-rank order and the split is stable, so the received rows are in ascending GLOBAL row order:
+// a table that was in time order still is, inside every group.  The extra output column holds the global row ids.
+extern "C" int aqgpu_repartition_rows(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows, uint64_t row_base,
+                                      const void* const* cols, const int* elem_bytes, int ncols, void** out_cols, uint32_t* out_nrows) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (!comm_ready()) return fail("aqgpu_repartition_rows: call aqgpu_comm_init first");
+    if (!keys || !key_types || nkeys < 1 || !cols || !elem_bytes || ncols < 1 || ncols > 30 || !out_cols || !out_nrows)
+        return fail("aqgpu_repartition_rows: bad arguments");
+    if (row_base + nrows >= 0xffffffffull) return fail("aqgpu_repartition_rows: global row ids must fit 32 bits");
+    Context& c = ctx();
+    const int N = comm_nranks(), me = comm_rank();
+    if (N > 64) return fail("multi-GPU: more than 64 ranks");
+    for (int k = 0; k < ncols + 1; ++k) out_cols[k] = nullptr;
+    // ---- owner of every row, stable split of the columns (+ the global row ids)
+    DevBuf owner, grow, counts_d, counts_all;
+    AQ_TRY(owner.alloc(size_t(nrows ? nrows : 1) * 4));
+    AQ_TRY(grow.alloc(size_t(nrows ? nrows : 1) * 4));
+    if (nrows) {
+        AQ_TRY(aqgpu_key_owner(keys, key_types, nkeys, nrows, (uint32_t)N, owner.as<uint32_t>()));
+        AQ_LAUNCH(k_dist_iota, grid_for(nrows, 256, 4), 256, 0, grow.as<uint32_t>(), nrows, (uint32_t)row_base);
+    }
+    std::vector<DevBuf> parted(ncols + 1);
+    std::vector<const void*> src(ncols + 1);
+    std::vector<void*> dst(ncols + 1);
+    std::vector<int> eb(ncols + 1);
+    for (int k = 0; k < ncols; ++k) { src[k] = cols[k]; eb[k] = elem_bytes[k]; }
+    src[ncols] = grow.p; eb[ncols] = 4;
+    for (int k = 0; k <= ncols; ++k) { AQ_TRY(parted[k].alloc(size_t(nrows ? nrows : 1) * eb[k])); dst[k] = parted[k].p; }
+    uint32_t send[64];
+    AQ_TRY(aqgpu_partition_rows(owner.as<uint32_t>(), nrows, (uint32_t)N, src.data(), eb.data(), ncols + 1, dst.data(), send));
+    // ---- who sends how much to whom
+    AQ_TRY(counts_d.alloc(size_t(N) * 4));
+    AQ_TRY(counts_all.alloc(size_t(N) * N * 4));
+    AQ_CUDA(cudaMemcpyAsync(counts_d.p, send, size_t(N) * 4, cudaMemcpyHostToDevice, c.stream));
+    AQ_TRY(comm_allgather(counts_d.p, counts_all.p, size_t(N) * 4));
+    std::vector<uint32_t> m(size_t(N) * N);
+    AQ_CUDA(cudaMemcpyAsync(m.data(), counts_all.p, m.size() * 4, cudaMemcpyDeviceToHost, c.stream));
+    AQ_CUDA(cudaStreamSynchronize(c.stream));
+    size_t soff[64], roff[64], nrecv = 0, acc = 0;
+    for (int r = 0; r < N; ++r) { soff[r] = acc; acc += send[r]; }
+    for (int s2 = 0; s2 < N; ++s2) { roff[s2] = nrecv; nrecv += m[size_t(s2) * N + me]; }
+    if (nrecv >= 0xffffffffull) return fail("aqgpu_repartition_rows: %zu rows on one rank", nrecv);
+    // ---- one grouped exchange per column, into columns that outlive the call (aqgpu_col_free)
+    for (int k = 0; k <= ncols; ++k) {
+        void* p = nullptr;
+        AQ_TRY(aqgpu_col_alloc((nrecv ? nrecv : 1) * eb[k], &p));
+        out_cols[k] = p;
+        size_t so[64], sb[64], ro[64], rb[64];
+        for (int r = 0; r < N; ++r) {
+            so[r] = soff[r] * eb[k]; sb[r] = size_t(send[r]) * eb[k];
+            ro[r] = roff[r] * eb[k]; rb[r] = size_t(m[size_t(r) * N + me]) * eb[k];
+        }
+        AQ_TRY(comm_alltoallv(parted[k].p, so, sb, p, ro, rb));
+    }
+    AQ_CUDA(cudaStreamSynchronize(c.stream));                    // the split copies live in the call's scratch
+    *out_nrows = (uint32_t)nrecv;
+    return 0;
+}

@@ -600,6 +600,8 @@ class ShardPlan(DistPlan):
                         aq.vec_sub(res[0], res[1], e, ng, code)
                     else:
                         aq.vec_pow(res[0], 2.0, e, ng)
+                if self.comm.stream is not None:
+                    self.comm.stream.synchronize()      # one query at a time on the device (as DistPlan.run does)
                 return ng
         self._fallback(q)
         return DistPlan.run(self, q)
@@ -706,4 +708,92 @@ class ShardPlan(DistPlan):
                           "sum(count) = rows, sum of integer sums = column totals; oracle parity at small sizes: tests/test_dist_gpu.py"}
 
     def close(self):
+        aq.comm_destroy()
+
+
+class DistWindowPlan:
+    """the windowed trade queries (aquery2_b200/trade.py) over row shards: the rows are repartitioned by the owner of
+    their symbol (aqgpu_repartition_rows: stable split + one grouped NCCL exchange per column, rows arrive in global
+    row order), then every rank runs the single-GPU pipeline on the symbols it owns -- group build (+ order_by) + one
+    fused window call.  Results stay partitioned by symbol owner (order-sensitive aggregates)."""
+
+    def __init__(self, comm: Comm, table: dict, queries, args, n_total: int, lo: int):
+        self.comm, self.table, self.queries, self.lo, self.n_total = comm, table, list(queries), lo, n_total
+        uid = [aq.comm_unique_id() if comm.rank == 0 else None]
+        comm.dist.broadcast_object_list(uid, src=0)
+        aq.comm_init(comm.world, comm.rank, uid[0])
+        self.local, self.handles, self.results, self.moved = {}, {}, {}, {}
+
+    def _free(self, q):
+        h = self.handles.pop(q, None)
+        if h is not None:
+            h.free()
+        for c in self.results.pop(q, []):
+            c.free()
+        for c in self.local.pop(q, {}).values():
+            c.free()
+
+    def run(self, q: str) -> int:
+        from . import trade
+        trace = os.environ.get("AQ_DIST_TRACE") and self.comm.rank == 0
+        t0 = [time.perf_counter()]
+
+        def mark(what):
+            if trace:
+                aq.sync()
+                t1 = time.perf_counter()
+                print(f"[dist window] {q} {what}: {1e3 * (t1 - t0[0]):.1f} ms", file=sys.stderr, flush=True)
+                t0[0] = t1
+        self._free(q)
+        mark("free")
+        names = trade.COLUMNS[q]
+        cols = [self.table[c] for c in names]
+        out = aq.repartition_rows([self.table["sym"]], cols, self.lo)
+        mark("repartition")
+        t = dict(zip(names, out[:-1]))
+        t["_row"] = out[-1]
+        self.local[q] = t
+        self.moved[q] = sum(c.itemsize for c in cols) + 4
+        h = aq.Groups([t["sym"]], row_order=aq.ROWS_ASC)
+        mark("group build")
+        if q == "w_unsorted":
+            h.order_by([t["time_shuffled"]], desc=[0])
+            mark("order_by")
+        self.results[q] = h.window(trade.expressions(t), device_out=True)
+        mark("window")
+        self.handles[q] = h
+        aq.sync()             # one query at a time on the device: a host that runs ahead into the next query's collectives made steps slower
+        return h.ngroups
+
+    def step(self) -> dict:
+        return {q: self.run(q) for q in self.queries}
+
+    def total_groups(self, ngs: dict) -> dict:
+        return {q: int(self.comm.sum_float(float(ng))) for q, ng in ngs.items()}
+
+    def exchange_report(self) -> dict:
+        return {q: {"strategy": "rows repartitioned by hash(sym) mod ranks (stable split + grouped send / receive per column)",
+                    "bytes_per_row": self.moved.get(q), "native": True} for q in self.queries}
+
+    def verify(self, table, queries, args, n_total, ngs) -> dict:
+        """every row arrived exactly once (sum of local rows = table rows, sum of global row ids = n (n - 1) / 2), the global
+        row ids ascend on every rank; oracle parity of the windowed results at small sizes: tests/test_dist_gpu.py"""
+        T = self.comm.torch
+        rep = {}
+        for q in self.queries:
+            rows = self.local[q]["_row"]
+            r = T.as_tensor(_CudaBytes(rows.ptr, rows.n * 4), device=self.comm.device).view(T.int32).to(T.int64) & 0xffffffff if rows.n else T.zeros(0, dtype=T.int64, device=self.comm.device)
+            if rows.n > 1 and not bool((r[1:] > r[:-1]).all()):
+                raise RuntimeError(f"{q}: received rows are not in ascending global row order on rank {self.comm.rank}")
+            tot_n = self.comm.sum_float(float(rows.n))
+            tot_s = self.comm.sum_float(float(r.sum()))
+            if tot_n != float(n_total) or tot_s != float(n_total) * float(n_total - 1) / 2.0:
+                raise RuntimeError(f"{q}: {tot_n} rows arrived (sum of ids {tot_s}), table has {n_total}")
+            rep[q] = {"rows_here": rows.n, "groups": int(self.comm.sum_float(float(ngs[q])))}
+        return {"status": "ok", "rows": n_total, "per_query": rep,
+                "checks": "every row arrives exactly once, in ascending global row order; oracle parity at small sizes: tests/test_dist_gpu.py"}
+
+    def close(self):
+        for q in list(self.local):
+            self._free(q)
         aq.comm_destroy()

@@ -218,8 +218,11 @@ def run_b200(args, wl, queries):
     barrier()
     launches0 = aq.launch_count()
     aq.timer_begin()
+    step_wall = []
     for _ in range(args.steps):
+        t_s = time.perf_counter()
         ngs = runner.step()
+        step_wall.append(round(1e3 * (time.perf_counter() - t_s), 2))      # host view of each step (diagnostic; the metric is the event time)
     ms = aq.timer_end()
     barrier()
     launches = aq.launch_count() - launches0
@@ -321,7 +324,7 @@ def run_b200(args, wl, queries):
                            "parallelism": "1 GPU" if world == 1 else f"{world} GPUs: row-range shards, local partial aggregation, NCCL merge"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches // max(args.steps, 1) * args.steps,
                 "verify": verify["status"] if verify else "skipped (--no-verify)", "verify_detail": verify,
-                "roofline": roofline, "step_hbm_frac": step_frac, "cpu_baseline": cpu, "per_query": per_query,
+                "step_ms_host": step_wall, "roofline": roofline, "step_hbm_frac": step_frac, "cpu_baseline": cpu, "per_query": per_query,
                 "kernels": kernels, "exchange": exchange}
         print(json.dumps(line), flush=True)
     if comm is not None:

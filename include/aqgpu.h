@@ -213,6 +213,15 @@ int aqgpu_groupby_run_dist(const void* const* keys, const int* key_types, int nk
                            uint64_t row_base, uint64_t rows_total, int row_order,
                            const aqgpu_agg_t* aggs, int n_aggs, int want_first_row, aqgpu_result_t** out, int* used);
 int aqgpu_result_replicated(const aqgpu_result_t* r, int* replicated);
+/* Order-sensitive (windowed) aggregates over row shards: the ROWS are repartitioned by hash(key tuple) mod ranks so
+ * that every group lies whole on one rank; called collectively.  cols[k]: device columns of
+ * nrows cells of elem_bytes[k] (4, 8 or 16) -- pass the key columns among them if they are needed afterwards.
+ * out_cols[0..ncols) receive library-allocated device columns (aqgpu_col_free) of *out_nrows cells; out_cols[ncols] is
+ * an extra uint32 column with the rows' GLOBAL ids.  The received rows are in ascending global row order, so a table
+ * that was in time order still is inside every group; aqgpu_groupby_build / aqgpu_groups_order_by / aqgpu_group_window
+ * then run locally and the results stay partitioned by key owner. */
+int aqgpu_repartition_rows(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows, uint64_t row_base,
+                           const void* const* cols, const int* elem_bytes, int ncols, void** out_cols, uint32_t* out_nrows);
 
 /* ---- group handle: ids, row lists, per-group vectors ----------------------------------------
  * aqgpu_groupby_build replaces HashTableFactory<...>::get(cols...) / AQHashTable (server/hasher.h:

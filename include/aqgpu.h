@@ -40,6 +40,8 @@ enum aqgpu_dtype {
 /* ---- per-group scalar aggregates (server/aggregations.h) ------------------------------------
  * Result cell types follow the reference (server/types.h:199-210):
  *   SUM(int32|int64) -> AQ_INT128 (or AQ_INT64 on request), SUM(float|double) -> AQ_DOUBLE,
+ *   (integer sums, sums of squares and of products accumulate in 64 bits and are widened on write: |sum| < 2^63 is
+ *   the documented limit -- the reference's __int128 accumulator, server/types.h:155, has none in practice either)
  *   AVG/VAR/STDDEV/CORR -> AQ_DOUBLE, MIN/MAX/FIRST/LAST -> the input type, COUNT -> AQ_UINT32.  */
 enum aqgpu_reduce_op {
     AQ_SUM = 0,     /* aggregations.h:19-27  */

@@ -811,6 +811,31 @@ AQ_OFFSET_IS(Context, aquery_root_path, 136);
 #ifdef AQGPU_HOST_THREADING
 AQ_OFFSET_IS(Context, thread_pool, 144); AQ_OFFSET_IS(Context, gc, 152); AQ_OFFSET_IS(Context, print, 160);
 AQ_OFFSET_IS(Context, tables, 168); AQ_OFFSET_IS(Context, cols, 224); AQ_OFFSET_IS(Context, it_host, 392);
+
+// ---- HBM column store behind cxt->tables (north_star item 1) ---------------------------------------------------------
+// The GPU build's counterpart of the 'C' cache message (server/server.cpp:552-583: `server->getDSTable(name, tbl);
+// cxt->tables[name] = tbl;`): every column of a host-resident table is ingested into the HBM column store ONCE and the
+// device-backed TableInfo is registered under the table's name.  The emitter's cached-table route
+// (engine/ast.py:344-365: `static_cast<TableInfo<...>*>(cxt->tables["name"])` + `->get_col<i>()`) then hands HBM-resident
+// ColRefs to the post-processor; results live where their inputs live.
+namespace aq {
+template <class... Ts, size_t... I>
+inline void cache_cols(TableInfo<Ts...>& dev, TableInfo<Ts...>& host, std::index_sequence<I...>) {
+    ((void)[&] {
+        auto d = host.template get_col<(int)I>().to_device();
+        auto& c = dev.template get_col<(int)I>();
+        c.init_from(d.size, d.container);              // the cached table keeps the column for the session
+        c.name = host.template get_col<(int)I>().name;
+        d.capacity = 0;
+    }(), ...);
+}
+template <class... Ts> TableInfo<Ts...>* cache_table(Context* cxt, const char* name, TableInfo<Ts...>& host) {
+    auto* dev = new TableInfo<Ts...>(name, nullptr);
+    cache_cols(*dev, host, std::index_sequence_for<Ts...>());
+    cxt->tables[name] = dev;
+    return dev;
+}
+}  // namespace aq
 static_assert(sizeof(Context) == 408, "Context size differs from the reference");
 #endif
 #pragma GCC diagnostic pop

@@ -116,6 +116,24 @@ __AQEXPORT__(int) dll_whole(Context* cxt) {
     return 0;
 }
 
+// ---- (4) the cached-table route (engine/ast.py:344-365): columns come from cxt->tables, HBM-resident ------
+static std::vector<int> g_c_keys;
+static std::vector<__int128> g_c_sum;
+static std::vector<double> g_c_avg;
+__AQEXPORT__(int) dll_cached(Context* cxt) {
+    TableInfo<int, int, float, int>* tbl_source = static_cast<TableInfo<int, int, float, int>*>(cxt->tables["source"]);
+    decltype(auto) id1 = tbl_source->get_col<0>();
+    decltype(auto) v1 = tbl_source->get_col<1>();
+    decltype(auto) v3 = tbl_source->get_col<2>();
+    EXPECT(id1.on_device() && v1.on_device() && v3.on_device());
+    auto g = aq::group_by(id1);
+    auto s1 = sum(v1[g]);
+    auto a3 = avg(v3[g]);
+    EXPECT(s1.on_device() && a3.on_device());
+    g_c_keys = g.key<0>().to_host(); g_c_sum = s1.to_host(); g_c_avg = a3.to_host();
+    return 0;
+}
+
 int main() {
     if (aqgpu_init(0) != 0) { printf("no CUDA device: %s\n", aqgpu_last_error()); return 2; }
     const uint32_t n = 100003;
@@ -174,6 +192,22 @@ int main() {
         EXPECT(g_w_min[gi] == mn);
         EXPECT(g_w_off[gi + 1] - g_w_off[gi] == r.size());
         EXPECT(std::fabs(g_w_avgs[g_w_off[gi]] - (double)v1[r.back()]) < 1e-12);       // first cell = last row of the group
+    }
+    {   // the 'C' cache message of the GPU build: the table is ingested once, the post-processor reads cxt->tables
+        const char* names[] = {"id1", "v1", "v3", "id2"};
+        TableInfo<int, int, float, int> host("source", names);
+        host.get_col<0>().init_from(n, id1.data()); host.get_col<1>().init_from(n, v1.data());
+        host.get_col<2>().init_from(n, v3.data()); host.get_col<3>().init_from(n, id2.data());
+        aq::cache_table(&cxt, "source", host);
+        EXPECT(dll_cached(&cxt) == 0);
+        EXPECT(g_c_keys == order);
+        for (size_t gi = 0; gi < order.size() && fails < 5; ++gi) {
+            const auto& r = rows[order[gi]];
+            long long s = 0; double fs = 0;
+            for (uint32_t i : r) { s += v1[i]; fs += (double)v3[i]; }
+            EXPECT((long long)g_c_sum[gi] == s);
+            EXPECT(std::fabs(g_c_avg[gi] - fs / r.size()) <= 1e-12 * std::fabs(fs / r.size()));
+        }
     }
     {   // non-grouped forms (tests/moving_avg.a:7 `avgs(3, sales)`): the whole column is one group in table order
         ColRef<int> sales((uint32_t)n, v1.data());

@@ -50,7 +50,7 @@ EXPORTS = [
     "aqgpu_result_first_row", "aqgpu_result_free", "aqgpu_trim_pool", "aqgpu_col_upload_async",
     "aqgpu_col_download_async",
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
-    "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows",
+    "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
 ]
 
 
@@ -395,7 +395,7 @@ class Groups:
         check(lib().aqgpu_group_median(self.h, vt, ctypes.c_void_p(vp), out.ctypes.data_as(ctypes.c_void_p)))
         return out
 
-    def window(self, exprs, device_out: bool = False):
+    def window(self, exprs, device_out: bool = False, order_by=None, desc: bool = False):
         """Several vector-valued expressions in one call (aqgpu_group_window).  exprs: tuples
         (op, v[, w[, minus_from_v[, reduce]]]) with op a scan name, reduce None / "max" / "min".
         Returns one output per expression: nrows cells in CSR order, or ngroups cells when reduced."""
@@ -416,7 +416,12 @@ class Groups:
             ob = _out_buf(ot, self.ngroups if red >= 0 else self.nrows, device_out)
             outs.append(ob)
             arr[i] = WindowSpec(op, w, vt, vp, minus, red, ot, _out_ptr(ob))
-        check(lib().aqgpu_group_window(self.h, arr, n))
+        if order_by is None:
+            check(lib().aqgpu_group_window(self.h, arr, n))
+        else:                               # ASSUMING order evaluated inside the call (aqgpu_group_window_ordered)
+            op_, ot_, k_ = _col(order_by)
+            keep.append(k_)
+            check(lib().aqgpu_group_window_ordered(self.h, ctypes.c_void_p(op_), ot_, int(bool(desc)), arr, n))
         return outs
 
     def order_by(self, cols, desc=None):

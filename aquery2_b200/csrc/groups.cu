@@ -540,7 +540,14 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
     return 0;
 }
 
-int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops) {
+static int group_window_impl(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops, const void* ocol, int ocol_type, int odesc);
+int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops) { return group_window_impl(g, ops, n_ops, nullptr, 0, 0); }
+int aqgpu_group_window_ordered(aqgpu_groups_t* g, const void* order_col, int order_type, int desc, const aqgpu_window_t* ops, int n_ops) {
+    if (!order_col) return fail("window: null order column");
+    if (order_type != AQ_INT32 && order_type != AQ_UINT32 && order_type != AQ_FLOAT) return fail("window: order column dtype %d (int32, uint32, float)", order_type);
+    return group_window_impl(g, ops, n_ops, order_col, order_type, desc);
+}
+static int group_window_impl(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops, const void* ocol, int ocol_type, int odesc) {
     AQ_REQUIRE_INIT();
     ArenaScope scope;
     if (!g || !ops || n_ops < 1 || n_ops > 64) return fail("bad window arguments");
@@ -570,11 +577,26 @@ int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops) 
         any_host |= oc[q].host != nullptr || in[q].tmp.p != nullptr;
     }
     AQ_TRY(ensure_offsets(g));
+    InCol oin;
+    if (ocol) AQ_TRY(oin.bind(ocol, size_t(4) * n));
     bool handled = false;
-    if (n_ops <= WIN_MAX_OPS) {
+    for (int attempt = 0; attempt < 2 && !handled; ++attempt) {
+        if (attempt == 1) {                // the fused path declined the in-call ordering (a very long group, three value columns,
+            if (!ocol) break;              // a handle with its own order ...): sort the row lists globally, then carry on as usual
+            const void* oc1[1] = { oin.d }; const int ot1[1] = { ocol_type }; const int od1[1] = { odesc };
+            AQ_TRY(aqgpu_groups_order_by(g, oc1, ot1, od1, 1));
+        }
+        if (n_ops > WIN_MAX_OPS) continue;
         WinGroups G;
         G.nrows = n; G.ngroups = ng; G.row_order = g->row_order; G.gid = g->gid.as<uint32_t>(); G.offsets = g->offsets.as<uint32_t>();
         G.perm = g->custom_order ? g->perm.as<uint32_t>() : nullptr;
+        if (ocol && attempt == 0) {
+            if (g->custom_order) continue;
+            G.order_key = static_cast<const uint32_t*>(oin.d);
+            const uint32_t asc = ocol_type == AQ_INT32 ? 0x80000000u : 0u;
+            G.order_xor = odesc ? ~asc : asc;
+            G.order_float = ocol_type == AQ_FLOAT;
+        }
         WinOp w[WIN_MAX_OPS];
         for (int q = 0; q < n_ops; ++q) {
             w[q].op = ops[q].op; w[q].w = ops[q].w; w[q].vtype = ops[q].vtype; w[q].v = in[q].d; w[q].minus = ops[q].minus_from_v;

@@ -207,9 +207,9 @@ k_ws_scatter(const WsArgs A) {
                 if (A.pass == 1) {
                     const uint32_t row = ws_row(A, tlo + e);
                     t.x = ld_stream_u32(A.gid + row);
-                    t.y = A.ncols > 0 ? ld_stream_u32(A.col[0] + row) : 0u;
-                    t.z = A.ncols > 1 ? ld_stream_u32(A.col[1] + row) : 0u;
-                    t.w = A.ncols > 2 ? ld_stream_u32(A.col[2] + row) : 0u;
+                    t.y = A.col[0] ? ld_stream_u32(A.col[0] + row) : 0u;
+                    t.z = A.col[1] ? ld_stream_u32(A.col[1] + row) : 0u;
+                    t.w = A.col[2] ? ld_stream_u32(A.col[2] + row) : 0u;
                 } else {
                     t = __ldg(A.in + tlo + e);
                 }
@@ -747,6 +747,74 @@ __global__ void k_fill(T* __restrict__ p, T v, uint32_t n) {
 }
 
 // ====================================================================================================
+// 1b. ASSUMING order inside the call: every group's tuples sorted by the key they carry (field w)
+// ====================================================================================================
+// One CTA per group: the tuples and a composite (key image << 32 | position) go to shared memory, a bitonic network
+// sorts the composites (the position makes the order total, i.e. the sort stable), the tuples are written back in that
+// order.  Replaces, for groups of up to SEG_MAX rows, the 7 global radix passes of aqgpu_groups_order_by AND the random
+// gathers through the resulting row list (k_ws_gather: 96 bytes of DRAM traffic per 4-byte cell).
+constexpr uint32_t SEG_MAX = 8192;
+constexpr int SEG_THREADS = 256;
+__global__ void k_seg_maxlen(const uint32_t* __restrict__ offsets, uint32_t ngroups, uint32_t* __restrict__ out) {
+    uint32_t m = 0;
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) m = max(m, offsets[g + 1] - offsets[g]);
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+__global__ void __launch_bounds__(SEG_THREADS)
+k_seg_sort(uint4* __restrict__ tup, const uint32_t* __restrict__ offsets, const uint32_t ngroups, const uint32_t cap,
+           const uint32_t xor_mask, const int float_flip) {
+    extern __shared__ __align__(16) unsigned char seg_sm[];
+    uint4* const st = reinterpret_cast<uint4*>(seg_sm);                                   // cap tuples
+    unsigned long long* const comp = reinterpret_cast<unsigned long long*>(st + cap);   // cap composites
+    for (uint32_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const uint32_t lo = offsets[g], n = offsets[g + 1] - lo;
+        if (n < 2u) continue;                                   // (uniform per CTA)
+        uint32_t m = 64;                                        // >= 64: a warp's 32 pairs span 64 elements
+        while (m < n) m <<= 1;
+        for (uint32_t i = threadIdx.x; i < m; i += SEG_THREADS) {
+            unsigned long long c = ~0ull;
+            if (i < n) {
+                const uint4 t = tup[size_t(lo) + i];
+                st[i] = t;
+                uint32_t k = t.w;
+                if (float_flip) k ^= (uint32_t)((int)k >> 31) | 0x80000000u;
+                c = ((unsigned long long)(k ^ xor_mask) << 32) | i;
+            }
+            comp[i] = c;
+        }
+        __syncthreads();
+        for (uint32_t k = 2; k <= m; k <<= 1) {
+            uint32_t j = k >> 1;
+            for (; j > 32u; j >>= 1) {                           // partners in other warps' elements: CTA-wide steps
+                for (uint32_t p = threadIdx.x; p < (m >> 1); p += SEG_THREADS) {
+                    const uint32_t i = ((p & ~(j - 1u)) << 1) | (p & (j - 1u));
+                    const uint32_t l = i | j;
+                    const unsigned long long a = comp[i], b = comp[l];
+                    const bool up = (i & k) == 0u;
+                    if ((a > b) == up) { comp[i] = b; comp[l] = a; }
+                }
+                __syncthreads();
+            }
+            // j <= 32: the 32 consecutive pairs of a warp stay inside one aligned block of 64 elements -> warp-level steps
+            for (uint32_t p = threadIdx.x; p < (m >> 1); p += SEG_THREADS) {
+                for (uint32_t jj = j; jj > 0; jj >>= 1) {
+                    const uint32_t i = ((p & ~(jj - 1u)) << 1) | (p & (jj - 1u));
+                    const uint32_t l = i | jj;
+                    const unsigned long long a = comp[i], b = comp[l];
+                    const bool up = (i & k) == 0u;
+                    if ((a > b) == up) { comp[i] = b; comp[l] = a; }
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+        }
+        for (uint32_t i = threadIdx.x; i < n; i += SEG_THREADS) tup[size_t(lo) + i] = st[(uint32_t)comp[i]];
+        __syncthreads();
+    }
+}
+
+// ====================================================================================================
 // host
 // ====================================================================================================
 static bool win_supported(const WinOp& o) {
@@ -787,6 +855,19 @@ int window_fused(const WinGroups& G, const WinOp* ops, int n_ops, bool* handled)
     while ((uint64_t(1) << bits) < uint64_t(G.ngroups)) ++bits;
     if (bits > 2 * (int)WS_MAXBITS) return 0;
     const uint32_t n = G.nrows;
+    uint32_t seg_cap = 0;
+    if (G.order_key) {                                          // ASSUMING order inside the call
+        if (G.perm || ncols >= WIN_MAX_COLS) return 0;          // the key needs the third tuple field
+        DevBuf mx;
+        AQ_TRY(mx.alloc_zero(4));
+        AQ_LAUNCH(k_seg_maxlen, grid_for(G.ngroups, 256, 4), 256, 0, G.offsets, G.ngroups, mx.as<uint32_t>());
+        uint32_t longest = 0;
+        AQ_CUDA(cudaMemcpyAsync(&longest, mx.p, 4, cudaMemcpyDeviceToHost, c.stream));
+        AQ_CUDA(cudaStreamSynchronize(c.stream));
+        if (longest > SEG_MAX) return 0;                        // a group too long for one SM's shared memory: the caller sorts globally
+        for (seg_cap = 256; seg_cap < longest; seg_cap <<= 1) {}
+        cols[WIN_MAX_COLS - 1] = G.order_key;
+    }
     // ---- 1. tuples in CSR order
     DevBuf ta, tb, hist, bstart, tick;
     AQ_TRY(ta.alloc(size_t(n) * 16 + 16));
@@ -798,7 +879,7 @@ int window_fused(const WinGroups& G, const WinOp* ops, int n_ops, bool* handled)
     } else {
         WsArgs W;
         memset(&W, 0, sizeof(W));
-        W.n = n; W.gid = G.gid; W.ncols = ncols; W.ngroups = G.ngroups;
+        W.n = n; W.gid = G.gid; W.ncols = G.order_key ? WIN_MAX_COLS : ncols; W.ngroups = G.ngroups;
         for (int i = 0; i < WIN_MAX_COLS; ++i) W.col[i] = cols[i];
         W.reverse = G.row_order == AQ_ROWS_DESC;
         const int npass = bits > (int)WS_MAXBITS ? 2 : 1;
@@ -832,6 +913,14 @@ int window_fused(const WinGroups& G, const WinOp* ops, int n_ops, bool* handled)
             AQ_LAUNCH(k_ws_scatter, (int)std::min<uint32_t>(V.nchunks, (uint32_t)c.sm_count * 2), WS_THREADS, smem2, V);
         }
         sorted = ta.as<uint4>();
+        if (G.order_key) {
+            static size_t seg_attr = 0;
+            const size_t seg_smem = size_t(seg_cap) * 24;
+            if (seg_smem > seg_attr) { AQ_CUDA(cudaFuncSetAttribute(k_seg_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seg_smem)); seg_attr = seg_smem; }
+            const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (c.smem_optin - 1024) / (seg_smem + 1024)));
+            AQ_LAUNCH(k_seg_sort, (int)std::min<uint32_t>(G.ngroups, (uint32_t)(c.sm_count * per_sm * 4)), SEG_THREADS, seg_smem, ta.as<uint4>(), G.offsets,
+                      G.ngroups, seg_cap, G.order_xor, G.order_float);
+        }
     }
     // ---- 2. the expressions
     K.n = n; K.ntiles = (n + WK_T - 1) / WK_T; K.ngroups = G.ngroups; K.tup = sorted; K.offsets = G.offsets;

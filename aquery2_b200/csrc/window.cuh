@@ -25,6 +25,11 @@ struct WinGroups {
     const uint32_t* gid;        // nrows
     const uint32_t* offsets;    // ngroups + 1
     const uint32_t* perm;       // nullptr: row lists in table order (row_order); else the handle's own order (order_by)
+    // ASSUMING order evaluated inside the call (only with perm == nullptr): every group's rows are ordered by this 4-byte
+    // column (ties: table order) -- it rides through the scatter as a tuple field and the groups are sorted in shared memory
+    const uint32_t* order_key = nullptr;
+    uint32_t order_xor = 0;     // key image = (float_flip(k)) ^ order_xor, ascending unsigned (sort.cuh's convention)
+    int order_float = 0;
 };
 
 // *handled = false: the combination is not served here (the caller runs the per-op path).

@@ -756,10 +756,7 @@ class DistWindowPlan:
         self.moved[q] = sum(c.itemsize for c in cols) + 4
         h = aq.Groups([t["sym"]], row_order=aq.ROWS_ASC)
         mark("group build")
-        if q == "w_unsorted":
-            h.order_by([t["time_shuffled"]], desc=[0])
-            mark("order_by")
-        self.results[q] = h.window(trade.expressions(t), device_out=True)
+        self.results[q] = h.window(trade.expressions(t), device_out=True, order_by=t["time_shuffled"] if q == "w_unsorted" else None)
         mark("window")
         self.handles[q] = h
         aq.sync()             # one query at a time on the device: a host that runs ahead into the next query's collectives made steps slower

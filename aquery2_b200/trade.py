@@ -13,6 +13,8 @@ w_unsorted  time is a permutation of 1..N: group build + the per-group sort of T
 Host-side mirror only: every number is produced by libaqgpu through aquery2_b200.aqgpu."""
 from __future__ import annotations
 
+import os
+
 from . import synth
 
 METRIC = "windowed aggregation rows/sec (trade: avgs sums deltas mins max by sym)"
@@ -94,9 +96,12 @@ class Plan:
         for col in self.results.pop(q, []):
             col.free()
         h = aq.Groups([t["sym"]], row_order=aq.ROWS_ASC, groups_hint=self.hint, key_bounds=self.bounds)
-        if q == "w_unsorted":
+        # ASSUMING ASC time: ordered inside the window call (aqgpu_group_window_ordered; AQ_TRADE_TWO_CALLS=1: order_by + window)
+        if q == "w_unsorted" and os.environ.get("AQ_TRADE_TWO_CALLS"):
             h.order_by([t["time_shuffled"]], desc=[0])
-        self.results[q] = h.window(expressions(t), device_out=True)
+            self.results[q] = h.window(expressions(t), device_out=True)
+        else:
+            self.results[q] = h.window(expressions(t), device_out=True, order_by=t["time_shuffled"] if q == "w_unsorted" else None)
         self.handles[q] = h
         return h.ngroups
 

@@ -284,6 +284,14 @@ typedef struct aqgpu_window {
     void* out;         /* device or host */
 } aqgpu_window_t;
 int aqgpu_group_window(aqgpu_groups_t* g, const aqgpu_window_t* ops, int n_ops);
+/* The same with ASSUMING order evaluated inside the call: every group's rows are first ordered by order_col (AQ_INT32,
+ * AQ_UINT32 or AQ_FLOAT; desc != 0: descending; ties keep the row lists' order), exactly as aqgpu_groups_order_by +
+ * aqgpu_group_window would (common/groupby.py:54-59 -> TableInfo::order_by, server/table.h:447-461), but for groups of
+ * up to 8192 rows the key rides through the group scatter as a tuple field and every group is sorted in one SM's shared
+ * memory -- no global sort passes, no gathers through a row list.  Other shapes take the two-call route internally
+ * (the handle's row lists are then left re-ordered; on the fused route they are untouched). */
+int aqgpu_group_window_ordered(aqgpu_groups_t* g, const void* order_col, int order_type, int desc,
+                               const aqgpu_window_t* ops, int n_ops);
 /* out[offsets[g] + j] = v[row j of group g]  -- the gather col[vecs[g]] of server/table.h:184-189 for
  * ALL groups at once, in the CSR order of the row lists.  out has nrows cells of vtype. */
 int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out);

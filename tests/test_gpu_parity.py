@@ -763,3 +763,26 @@ def test_group_median_vs_numpy(gpu, port):
     o2, p2 = h.csr()
     assert_same(p2, perm)                      # the handle's own row lists are untouched
     h.free()
+
+
+@pytest.mark.parametrize("n,nsym,desc", [(300_000, 400, False), (120_000, 9, True), (50_000, 30_000, False)])
+def test_window_ordered_inside_the_call(gpu, port, n, nsym, desc):
+    """aqgpu_group_window_ordered (ASSUMING order inside the call: key carried through the scatter, groups sorted in shared
+    memory; 120000 / 9 = groups longer than 8192 rows -> the two-call route) against order_by + window on a second handle,
+    and against the oracle over numpy's lexsort"""
+    t = synth.trade_table(n, nsym, seed=31, columns=["sym", "price", "quantity", "time_shuffled"])
+    exprs = [("avgw", t["price"], 5), ("sumw", t["quantity"], 5), ("deltas", t["price"]), ("minw", t["price"], 5), ("mins", t["price"], 0, True, "max")]
+    for key in (t["time_shuffled"], (t["time_shuffled"] % 1000).astype(np.int32)):          # unique keys / many ties (stability)
+        h1 = gpu.Groups([t["sym"]], row_order=gpu.ROWS_ASC)
+        got = h1.window(exprs, order_by=key, desc=desc)
+        h2 = gpu.Groups([t["sym"]], row_order=gpu.ROWS_ASC)
+        h2.order_by([key], desc=[int(desc)])
+        want = h2.window(exprs)
+        for a, b in zip(got, want):
+            assert_same(np.asarray(a), np.asarray(b), "ordered window vs order_by + window")
+        ng, gid, off, perm = port.groupby([t["sym"]])
+        k64 = key.astype(np.int64)
+        order = np.lexsort((np.arange(n), -k64 if desc else k64, gid)).astype(np.uint32)
+        ref = port.scan("avgw", t["price"], off, order, w=5)
+        assert_same(np.asarray(got[0]), ref, "ordered window vs oracle", scale=float(np.abs(t["price"]).max()))
+        h1.free(); h2.free()

@@ -19,7 +19,7 @@ the emitter reads:
      "select": [("id3", {"col": "id3"}), ("sum_v1", {"fn": "sum", "args": [{"col": "v1"}]}), ...]}
 
 Expression nodes: {"col": name} | {"lit": number} | {"fn": name, "args": [...]} | {"op": "-", "l": node, "r": node}.
-`python -m aquery2_b200.codegen q3` prints the translation unit of one of the fifteen built-in queries.
+`python -m aquery2_b200.codegen q3` prints the translation unit of one of the sixteen built-in queries.
 """
 from __future__ import annotations
 
@@ -44,9 +44,12 @@ def _h2o(name, keys, select):
             "select": [(k, col(k)) for k in keys] + select}
 
 
-def _trade(name, select):
-    return {"name": name, "table": "trade", "schema": TRADE_SCHEMA, "group_by": ["sym"], "row_order": "asc",
-            "select": [("sym", col("sym"))] + select}
+def _trade(name, select, assuming=None):
+    q = {"name": name, "table": "trade", "schema": TRADE_SCHEMA, "group_by": ["sym"], "row_order": "asc",
+         "select": [("sym", col("sym"))] + select}
+    if assuming:
+        q["assuming"] = assuming           # (column, "asc" | "desc"): FROM trade ASSUMING ASC time (aquery_parser/parser.py:300-301)
+    return q
 
 
 # benchmark/h2o/groupby.sql:1-23 and the windowed shapes of benchmark/quries/Aquery/q7.a, q10.a, tests/moving_avg.a
@@ -68,6 +71,9 @@ QUERIES = {
     "w5": _trade("w5", [("avg5", fn("avgs", 5, col("price"))), ("sum5", fn("sums", 5, col("quantity"))), ("d", fn("deltas", col("price"))),
                         ("min5", fn("mins", 5, col("price"))),
                         ("drawup", fn("max", {"op": "-", "l": col("price"), "r": fn("mins", col("price"))}))]),
+    # the same over an UNSORTED table: ASSUMING ASC time orders every group's rows inside the window call
+    "w6": _trade("w6", [("avg5", fn("avgs", 5, col("price"))), ("d", fn("deltas", col("price"))),
+                        ("drawup", fn("max", {"op": "-", "l": col("price"), "r": fn("mins", col("price"))}))], assuming=("time", "asc")),
 }
 
 SCALAR_AGGS = {"sum", "avg", "min", "max", "first", "last", "second", "stddev", "var"}
@@ -160,6 +166,8 @@ class Emitter:
             body.append((name, self.expr(e)))
         for k in q["group_by"]:
             self.cname(k)
+        if q.get("assuming"):
+            self.cname(q["assuming"][0])
         out = ['#include "./server/libaquery.h"', '#include "./server/monetdb_conn.h"', '#include "./server/aggregations.h"',
                '#include "./server/hasher.h"', "",
                f"// {q['name']}: whole-column post-processor generated by aquery2_b200/codegen.py (engine/ast.py:628-793 restated)",
@@ -174,11 +182,15 @@ class Emitter:
             self.emit(f"auto {self.cname(c)} = ColRef<{CTYPE[ty]}>(len, server->getCol({self.colpos[c]}, {AQTYPE[ty]})){dev};")
         keys = ", ".join(self.cname(k) for k in q["group_by"])
         if q.get("row_order") == "asc":
-            self.emit(f"auto g = aq::group_by_rows_ascending({keys});     // table sorted by time: row lists in time order")
+            note = "ties of the ASSUMING order keep table order" if q.get("assuming") else "table sorted by time: row lists in time order"
+            self.emit(f"auto g = aq::group_by_rows_ascending({keys});     // {note}")
         else:
             self.emit(f"auto g = aq::group_by({keys});")
         if self.batch:
             self.emit("aq::WindowBatch wb(g);")
+            if q.get("assuming"):
+                oc, direction = q["assuming"]
+                self.emit(f"wb.assuming({self.cname(oc)}, {str(direction == 'desc').lower()});     // ASSUMING {direction.upper()} {oc}: TableInfo::order_by per group, inside the call")
             for b in self.batch:
                 self.emit(b)
             self.emit("wb.run();")

@@ -673,7 +673,16 @@ struct WindowBatch {
         ops.push_back(aqgpu_window_t{op, w, dtype_of<T>(), col.container, minus ? 1 : 0, reduce, dtype_of<T>(), out.container});
         return out;
     }
-    void run() { if (!ops.empty() && handle->nrows) check(aqgpu_group_window(handle->h, ops.data(), (int)ops.size())); ops.clear(); }
+    // ASSUMING ASC / DESC col (common/groupby.py:54-59 -> TableInfo::order_by per group): evaluated inside the window call
+    const void* order_col = nullptr; int order_type = 0, order_desc = 0;
+    template <class T> void assuming(const ColRef<T>& col, bool desc = false) { order_col = col.container; order_type = dtype_of<T>(); order_desc = desc ? 1 : 0; }
+    void run() {
+        if (!ops.empty() && handle->nrows) {
+            if (order_col) check(aqgpu_group_window_ordered(handle->h, order_col, order_type, order_desc, ops.data(), (int)ops.size()));
+            else check(aqgpu_group_window(handle->h, ops.data(), (int)ops.size()));
+        }
+        ops.clear();
+    }
 };
 }  // namespace aq
 

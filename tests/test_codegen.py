@@ -41,6 +41,10 @@ def _oracle_columns(port, q, t):
     order = perm
     if q.get("row_order") == "asc":
         order = np.concatenate([perm[off[g]:off[g + 1]][::-1] for g in range(ng)]).astype(np.uint32) if ng else perm
+    if q.get("assuming"):                                          # TableInfo::order_by per group (table.h:447-461): stable, by the column
+        oc, direction = q["assuming"]
+        k = t[oc].astype(np.int64)
+        order = np.lexsort((np.arange(len(gid)), -k if direction == "desc" else k, gid)).astype(np.uint32)
     first = np.array([perm[off[g + 1] - 1] for g in range(ng)], dtype=np.int64)
 
     def ev(e):
@@ -81,6 +85,8 @@ def test_generated_unit_runs_and_matches_the_oracle(gpu, port, tmp_path, name):
                 t[c] = (t[c] % 3).astype(np.int32)
     else:
         t = synth.trade_table(n, 300, seed=3)
+        if q.get("assuming"):                                      # an unsorted table: the time column is a permutation
+            t["time"] = np.random.default_rng(5).permutation(n).astype(np.int32)
     w = _workdir(tmp_path)
     (w / "out.cpp").write_text(codegen.generate(name, dump=True))
     for i, (c, _) in enumerate(q["schema"]):

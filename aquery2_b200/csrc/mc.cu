@@ -480,12 +480,16 @@ k_mc_agg(const McParams M) {
             for (int a = 0; a < M.nacc; ++a) {
                 const McAcc A = M.acc[a];
                 uint32_t u[U], u2[U];
+                // value fields are picked out of the tuple only where the accumulator reads them (counts read none)
+                const bool need1 = A.kind != MCK_CNT;
+                const bool need2 = need1 && A.xform != X_IDENT && A.kind != MCK_TOP2 && A.kind != MCK_MAXROW;
 #pragma unroll
                 for (int j = 0; j < U; ++j) {
+                    u[j] = u2[j] = 0u;
                     if (TW == 4) {
-                        u[j] = A.c0 == 0 ? cv[j].y : (A.c0 == 1 ? cv[j].z : cv[j].w);
-                        u2[j] = A.c1 == 0 ? cv[j].y : (A.c1 == 1 ? cv[j].z : cv[j].w);
-                    } else {
+                        if (need1) u[j] = A.c0 == 0 ? cv[j].y : (A.c0 == 1 ? cv[j].z : cv[j].w);
+                        if (need2) u2[j] = A.c1 == 0 ? cv[j].y : (A.c1 == 1 ? cv[j].z : cv[j].w);
+                    } else if (need1) {
                         u[j] = u2[j] = half ? cv[j].w : cv[j].y;
                     }
                 }

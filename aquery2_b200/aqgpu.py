@@ -51,6 +51,7 @@ EXPORTS = [
     "aqgpu_col_download_async",
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
+    "aqgpu_partition_counts_noalloc",
 ]
 
 

@@ -124,3 +124,81 @@ extern "C" int aqgpu_partition_rows(const uint32_t* owner, uint32_t nrows, uint3
     for (uint32_t p = 0; p < nparts; ++p) counts[p] = starts[p + 1] - starts[p];
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the counting step (no counterpart in the reference):
+// some callers cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops,
+// harnesses that forbid it.  k_split_count's scratch (cnt[owner * nchunks + chunk], what aqgpu_partition_rows
+// takes from the arena) lives in a file-scope device array instead, so the entry point below performs no
+// cudaMalloc / cudaFree / pool or arena allocation at all.
+//   limit: NOALLOC_MAX_ROWS rows (= NOALLOC_MAX_CHUNKS chunks of SPLIT_ROWS rows) x SPLIT_MAX_PARTS owners
+//          -> 64 x 8192 x 4 B = 2 MiB of device memory, held by every GPU that loads the library until exit.
+//   Every call shares the array and it keeps the previous call's contents.  Nothing in it has to start at zero:
+//   k_split_count overwrites every cell [0, nparts * nchunks) that k_split_total then reads.  Calls that overlap
+//   on the GPU (two streams, two host threads) race on it: callers serialise them.
+// In host code the array's NAME is a host-side stand-in, not a device address; the address a kernel may be given
+// comes from cudaGetSymbolAddress, resolved once per device with that device current.
+// ------------------------------------------------------------------------------------------------------------
+namespace aq {
+
+constexpr uint32_t NOALLOC_MAX_CHUNKS = 8192;
+constexpr uint32_t NOALLOC_MAX_ROWS = NOALLOC_MAX_CHUNKS * SPLIT_ROWS;             // 16,777,216 rows
+constexpr int NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) uint32_t g_split_scratch[size_t(SPLIT_MAX_PARTS) * NOALLOC_MAX_CHUNKS];
+static uint32_t* g_split_scratch_ptr[NOALLOC_MAX_DEVICES];                         // device address, per device
+
+// rows of owner p = sum over chunks of cnt[p * nchunks + chunk]; one CTA per owner
+__global__ void __launch_bounds__(SPLIT_THREADS)
+k_split_total(const uint32_t* __restrict__ cnt, const uint32_t nchunks, uint32_t* __restrict__ out_counts) {
+    __shared__ uint32_t ws[SPLIT_THREADS / 32];
+    const uint32_t* row = cnt + size_t(blockIdx.x) * nchunks;
+    uint32_t s = 0;
+    for (uint32_t c = threadIdx.x; c < nchunks; c += SPLIT_THREADS) s += row[c];
+    s = __reduce_add_sync(0xffffffffu, s);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < SPLIT_THREADS / 32; ++w) t += ws[w];
+        out_counts[blockIdx.x] = t;
+    }
+}
+
+} // namespace aq
+
+extern "C" int aqgpu_partition_counts_noalloc(const uint32_t* owner, uint32_t nrows, uint32_t nparts, uint32_t* out_counts) {
+    Context& c = ctx();
+    if (!c.ready) return fail("partition_counts_noalloc: call aqgpu_init first (set-up allocates, this call does not)");
+    if (nparts == 0 || nparts > SPLIT_MAX_PARTS) return fail("partition_counts_noalloc: 1..%d owners", SPLIT_MAX_PARTS);
+    if (nrows > NOALLOC_MAX_ROWS)
+        return fail("partition_counts_noalloc: %u rows exceed the maximum of %u rows of the static scratch (use aqgpu_partition_rows)",
+                    nrows, NOALLOC_MAX_ROWS);
+    if (!out_counts || !is_device_ptr(out_counts)) return fail("partition_counts_noalloc: out_counts must be device memory (%u x uint32)", nparts);
+    if (nrows && (!owner || !is_device_ptr(owner))) return fail("partition_counts_noalloc: owner must be a device column");
+    int cur = -1;
+    AQ_CUDA(cudaGetDevice(&cur));
+    if (cur != c.device) return fail("partition_counts_noalloc: device %d is current, the library runs on device %d", cur, c.device);
+    if (cur < 0 || cur >= NOALLOC_MAX_DEVICES) return fail("partition_counts_noalloc: device ordinal %d", cur);
+    if (!g_split_scratch_ptr[cur]) {                                 // set-up, once per device, that device current
+        uint32_t* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_split_scratch);
+        if (e != cudaSuccess || !p) return fail("partition_counts_noalloc: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
+        g_split_scratch_ptr[cur] = p;
+    }
+    uint32_t* cnt = g_split_scratch_ptr[cur];
+    if (nrows == 0) {
+        AQ_CUDA(cudaMemsetAsync(out_counts, 0, size_t(nparts) * 4, c.stream));
+        return 0;
+    }
+    const uint32_t nchunks = (nrows + SPLIT_ROWS - 1) / SPLIT_ROWS;
+    const int grid = (int)std::min<size_t>(nchunks, size_t(c.sm_count) * 8);
+    // plain launches: no profiling hooks (they create events), same launch counter as AQ_LAUNCH
+    k_split_count<<<grid, SPLIT_THREADS, 0, c.stream>>>(owner, nrows, nparts, nchunks, cnt);
+    k_split_total<<<(int)nparts, SPLIT_THREADS, 0, c.stream>>>(cnt, nchunks, out_counts);
+    c.launches.fetch_add(2, std::memory_order_relaxed);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("partition_counts_noalloc: launch -> %s", cudaGetErrorString(e));
+    return 0;
+}

@@ -325,6 +325,17 @@ int aqgpu_key_owner(const void* const* keys, const int* key_types, int nkeys, ui
  * (host) = rows of owner p.  elem_bytes[k] in {4, 8, 16}.  The step before the all-to-all exchange. */
 int aqgpu_partition_rows(const uint32_t* owner, uint32_t nrows, uint32_t nparts, const void* const* cols,
                          const int* elem_bytes, int ncols, void* const* out_cols, uint32_t* counts);
+/* Allocation-free variant of the counting step of aqgpu_partition_rows: out_counts[p] (DEVICE memory, nparts x
+ * uint32) = rows of owner p.  No counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+ * call performs no cudaMalloc / cudaFree / pool allocation: its scratch is a static device array of 2 MiB
+ * (64 owners x 8192 chunks of 2048 rows) that every GPU loading the library holds until exit.
+ *   limits: nrows <= 16,777,216 and nparts <= 64, beyond that the call fails with a message (use
+ *           aqgpu_partition_rows); owner and out_counts must be device pointers; aqgpu_init must have run.
+ *   Asynchronous on the library stream (aqgpu_sync / stream order before reading out_counts).
+ *   Every call shares the one scratch array: calls that overlap on the GPU race -- serialise them.  The first
+ *   call on a device resolves the array's address (cudaGetSymbolAddress); make it outside a graph capture. */
+int aqgpu_partition_counts_noalloc(const uint32_t* owner, uint32_t nrows, uint32_t nparts, uint32_t* out_counts);
 /* AQ_SECOND across shards: out = cnt_top >= 2 ? second_top : (nparts >= 2 ? first_prev : 0), cells of
  * vtype; cnt_top and nparts are AQ_INT64 columns. */
 int aqgpu_second_merge(int vtype, const int64_t* cnt_top, const int64_t* nparts, const void* second_top,

@@ -51,7 +51,7 @@ EXPORTS = [
     "aqgpu_col_download_async",
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
-    "aqgpu_partition_counts_noalloc",
+    "aqgpu_partition_counts_noalloc", "aqgpu_key_cell_size", "aqgpu_key_split", "aqgpu_key_join", "aqgpu_string_dict",
 ]
 
 
@@ -698,3 +698,50 @@ class PinnedArray:
             self.array = None
             lib().aqgpu_host_free(ctypes.c_void_p(self.ptr))
             self.ptr = None
+
+
+# ---- key columns that are not plain integers (include/aqgpu.h: aqgpu_key_split / aqgpu_key_join / aqgpu_string_dict) ----
+KEY_DATE, KEY_TIME, KEY_TIMESTAMP = 1, 2, 3
+# the reference's cells as numpy records (server/types.h:82-86,105-109,128-130)
+DATE_DT = np.dtype([("day", "u1"), ("month", "u1"), ("year", "<i2")])
+TIME_DT = np.dtype([("ms", "<u4"), ("seconds", "u1"), ("minutes", "u1"), ("hours", "u1"), ("pad", "u1")])
+TIMESTAMP_DT = np.dtype([("date", DATE_DT), ("time", TIME_DT)])
+_KEY_KIND = {DATE_DT: KEY_DATE, TIME_DT: KEY_TIME, TIMESTAMP_DT: KEY_TIMESTAMP}
+
+
+def key_split(col: np.ndarray):
+    """date / time / timestamp cells -> the integer key columns that stand for them: [uint32], [int64] or [uint32, int64]"""
+    col = np.ascontiguousarray(col)
+    kind, n = _KEY_KIND[col.dtype], len(col)
+    a = np.zeros(n, np.int64 if kind == KEY_TIME else np.uint32)
+    b = np.zeros(n, np.int64) if kind == KEY_TIMESTAMP else None
+    check(lib().aqgpu_key_split(kind, col.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(n), a.ctypes.data_as(ctypes.c_void_p),
+                                b.ctypes.data_as(ctypes.c_void_p) if b is not None else None))
+    return [a] if b is None else [a, b]
+
+
+def key_join(kind_dtype: np.dtype, cols) -> np.ndarray:
+    """inverse of key_split for the key columns of a result"""
+    kind, n = _KEY_KIND[np.dtype(kind_dtype)], len(cols[0])
+    out = np.zeros(n, kind_dtype)
+    a = np.ascontiguousarray(cols[0])
+    b = np.ascontiguousarray(cols[1]) if len(cols) > 1 else None
+    check(lib().aqgpu_key_join(kind, a.ctypes.data_as(ctypes.c_void_p), b.ctypes.data_as(ctypes.c_void_p) if b is not None else None,
+                               ctypes.c_uint32(n), out.ctypes.data_as(ctypes.c_void_p)))
+    return out
+
+
+def string_dict(data: np.ndarray, offsets: np.ndarray, max_distinct: int | None = None):
+    """Arrow-style strings (uint8 bytes, uint64 offsets[n + 1]) -> (codes uint32[n] in first-appearance order,
+    first_row uint32[ndistinct])."""
+    data = np.ascontiguousarray(data, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    n = len(offsets) - 1
+    cap = n if max_distinct is None else int(max_distinct)
+    codes = np.zeros(max(n, 1), np.uint32)
+    first = np.zeros(max(cap, 1), np.uint32)
+    nd = ctypes.c_uint32(0)
+    check(lib().aqgpu_string_dict(data.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint64(data.size), offsets.ctypes.data_as(ctypes.c_void_p),
+                                  ctypes.c_uint32(n), codes.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(cap),
+                                  first.ctypes.data_as(ctypes.c_void_p), ctypes.byref(nd)))
+    return codes[:n], first[: nd.value]

@@ -63,7 +63,44 @@ AQ_TYPE(__int128, AINT128) AQ_TYPE(unsigned int, AUINT32) AQ_TYPE(unsigned long,
 template <class T> using GetLongType = std::conditional_t<std::is_floating_point<std::decay_t<T>>::value, double,
                                        std::conditional_t<std::is_unsigned<std::decay_t<T>>::value, unsigned __int128, __int128>>;
 template <class T> using GetFPType = std::conditional_t<sizeof(std::decay_t<T>) == sizeof(float), float, double>;
+// key-capable cell types, bit-compatible with server/types.h:82-86,105-109,128-130
+struct date_t {
+    unsigned char day = 0, month = 0; short year = 0;
+    date_t() = default;
+    date_t(unsigned char d, unsigned char m, short y) : day(d), month(m), year(y) {}
+    bool operator==(const date_t& o) const { return year == o.year && month == o.month && day == o.day; }      // libaquery.cpp:112-114
+    bool operator!=(const date_t& o) const { return !(*this == o); }
+};
+struct time_t {
+    unsigned int ms = 0; unsigned char seconds = 0, minutes = 0, hours = 0;
+    time_t() = default;
+    time_t(unsigned int ms, unsigned char s, unsigned char m, unsigned char h) : ms(ms), seconds(s), minutes(m), hours(h) {}
+    bool operator==(const time_t& o) const { return hours == o.hours && minutes == o.minutes && seconds == o.seconds && ms == o.ms; }   // :162-164
+    bool operator!=(const time_t& o) const { return !(*this == o); }
+};
+struct timestamp_t {
+    date_t date; time_t time;
+    timestamp_t() = default;
+    timestamp_t(const date_t& d, const time_t& t) : date(d), time(t) {}
+    bool operator==(const timestamp_t& o) const { return date == o.date && time == o.time; }                    // :201-203
+    bool operator!=(const timestamp_t& o) const { return !(*this == o); }
+};
+static_assert(sizeof(date_t) == 4 && sizeof(time_t) == 8 && sizeof(timestamp_t) == 12, "cells of server/types.h");
+template <> struct Types<date_t> { static constexpr Type_t getType() { return ADATE; } };
+template <> struct Types<time_t> { static constexpr Type_t getType() { return ATIME; } };
+template <> struct Types<timestamp_t> { static constexpr Type_t getType() { return ATIMESTAMP; } };
 }  // namespace types
+
+// server/types.h:280-333: a string cell is a char pointer into the data source's heap
+union astring_view {
+    const unsigned char* str = nullptr; const signed char* sstr; const char* rstr; size_t ptr;
+    constexpr astring_view(const char* s) noexcept : rstr(s) {}
+    constexpr astring_view(const unsigned char* s) noexcept : str(s) {}
+    constexpr astring_view() noexcept = default;
+    bool operator==(const astring_view& r) const { return std::strcmp(rstr, r.rstr) == 0; }                     // types.h:299-309
+    operator const char*() const { return rstr; }
+};
+template <> struct types::Types<astring_view> { static constexpr Type_t getType() { return ASTR; } };
 
 // ---- error handling -----------------------------------------------------------------------------------
 namespace aq {
@@ -308,9 +345,78 @@ namespace aq {
 struct GroupRows {                 // `vecs[i]` of the generated loop: the row list of group i, unevaluated
     GroupsHandle* g; uint32_t gid; uint32_t size;     // .size: count(*) is emitted as val.size (engine/ast.py:763)
 };
+// A key column as the library sees it: one or two integer columns that are equal exactly when the reference's operator==
+// holds (include/aqgpu.h "key columns that are not plain integers"; server/hasher.h:97-132).
+struct LoweredKey {
+    int kind = 0;                           // 0 plain / date image, AQ_KEY_TIME, AQ_KEY_TIMESTAMP, 4 = string
+    int nparts = 1, first = 0;              // columns of the library's key tuple: [first, first + nparts)
+    const void* p[2] = {nullptr, nullptr};
+    int t[2] = {0, 0};
+    std::vector<std::shared_ptr<void>> keep;        // device temporaries
+    std::vector<uint32_t> dict_first;       // string: code -> first row
+    const void* src = nullptr;              // string: the pointer array the codes index
+};
+inline std::shared_ptr<void> device_tmp(size_t bytes) {
+    void* q = nullptr;
+    check(aqgpu_col_alloc(bytes ? bytes : 16, &q));
+    return std::shared_ptr<void>(q, [](void* x) { aqgpu_col_free(x); });
+}
+template <class T> inline LoweredKey lower_key(const T* col, uint32_t n) {
+    LoweredKey k;
+    if constexpr (std::is_same<T, types::date_t>::value) {
+        k.p[0] = col; k.t[0] = AQ_UINT32;                                   // the 4-byte image is the key
+    } else if constexpr (std::is_same<T, types::time_t>::value) {
+        k.kind = AQ_KEY_TIME; k.t[0] = AQ_INT64;
+        k.keep.push_back(device_tmp(size_t(n) * 8)); k.p[0] = k.keep[0].get();
+        check(aqgpu_key_split(AQ_KEY_TIME, col, n, k.keep[0].get(), nullptr));
+    } else if constexpr (std::is_same<T, types::timestamp_t>::value) {
+        k.kind = AQ_KEY_TIMESTAMP; k.nparts = 2; k.t[0] = AQ_UINT32; k.t[1] = AQ_INT64;
+        k.keep.push_back(device_tmp(size_t(n) * 4)); k.keep.push_back(device_tmp(size_t(n) * 8));
+        k.p[0] = k.keep[0].get(); k.p[1] = k.keep[1].get();
+        check(aqgpu_key_split(AQ_KEY_TIMESTAMP, col, n, k.keep[0].get(), k.keep[1].get()));
+    } else if constexpr (std::is_same<T, astring_view>::value) {
+        // ingest: the heap pointers mean nothing on the device -> pack the characters (Arrow layout), encode on the GPU
+        k.kind = 4; k.t[0] = AQ_UINT32; k.src = col;
+        std::vector<uint64_t> off(size_t(n) + 1, 0);
+        for (uint32_t i = 0; i < n; ++i) off[i + 1] = off[i] + std::strlen(col[i].rstr);
+        std::vector<char> bytes(off[n] ? off[n] : 1);
+        for (uint32_t i = 0; i < n; ++i) std::memcpy(bytes.data() + off[i], col[i].rstr, off[i + 1] - off[i]);
+        k.keep.push_back(device_tmp(size_t(n) * 4)); k.p[0] = k.keep[0].get();
+        k.dict_first.resize(n ? n : 1);
+        uint32_t nd = 0;
+        check(aqgpu_string_dict(bytes.data(), off[n], off.data(), n, static_cast<uint32_t*>(k.keep[0].get()), n, k.dict_first.data(), &nd));
+        k.dict_first.resize(nd);
+    } else {
+        static_assert(dtype_of<T>() >= 0, "key columns: int32 / uint32 / int64, date / time / timestamp, astring_view");
+        k.p[0] = col; k.t[0] = dtype_of<T>();
+    }
+    return k;
+}
+
 struct GroupsHandle {
     aqgpu_groups_t* h = nullptr;
     uint32_t nrows = 0, ngroups = 0;
+    std::vector<LoweredKey> lowered;                  // one per key column of the query
+    // key column i of the result, ngroups cells of K, first-appearance order
+    template <class K> void fetch_key(int i, K* out) {
+        const LoweredKey& k = lowered[i];
+        if (!ngroups) return;
+        if (k.kind == AQ_KEY_TIMESTAMP) {
+            std::vector<uint32_t> a(ngroups); std::vector<long long> b(ngroups);
+            check(aqgpu_groups_keys(h, k.first, a.data()));
+            check(aqgpu_groups_keys(h, k.first + 1, b.data()));
+            check(aqgpu_key_join(AQ_KEY_TIMESTAMP, a.data(), b.data(), ngroups, out));
+        } else if (k.kind == 4) {
+            if constexpr (std::is_same<K, astring_view>::value) {
+                std::vector<uint32_t> code(ngroups);
+                check(aqgpu_groups_keys(h, k.first, code.data()));
+                const astring_view* src = static_cast<const astring_view*>(k.src);
+                for (uint32_t g = 0; g < ngroups; ++g) out[g] = src[k.dict_first[code[g]]];
+            }
+        } else {
+            check(aqgpu_groups_keys(h, k.first, out));            // plain cells; date / time images are valid cells
+        }
+    }
     std::vector<uint32_t> offsets;                    // host copy of ht_base + terminal (ngroups + 1)
     std::vector<GroupRows> rows;                      // backing store of HashTableComponents::values
     std::shared_ptr<void> keys;                       // backing store of HashTableComponents::keys
@@ -371,21 +477,24 @@ template <class... Ts, size_t... I>
 inline std::shared_ptr<GroupsHandle> build_groups(std::index_sequence<I...>, int row_order, const ColRef<Ts>&... cols) {
     constexpr int nk = sizeof...(Ts);
     static_assert(nk >= 1, "group by needs at least one key column");
-    static_assert(((dtype_of<Ts>() >= 0) && ...), "key columns: int32 / uint32 / int64");
-    const void* kp[nk] = { cols.container... };
-    const int kt[nk] = { dtype_of<Ts>()... };
     const uint32_t n = std::get<0>(std::tie(cols...)).size;
-    int64_t lo[nk], hi[nk];
+    auto g = std::make_shared<GroupsHandle>();
+    g->lowered = { lower_key<Ts>(cols.container, n)... };
+    const void* kp[2 * nk]; int kt[2 * nk];
+    int64_t lo[2 * nk], hi[2 * nk];
     bool have = true;
     double prod = 1.0;
-    int k = 0;
-    (void)std::initializer_list<int>{ ([&] {
-        auto it = col_stats().find(cols.container);
-        if (it == col_stats().end()) have = false; else { lo[k] = it->second.lo; hi[k] = it->second.hi; prod *= double(hi[k] - lo[k] + 1); }
-        ++k; }(), 0)... };
-    auto g = std::make_shared<GroupsHandle>();
+    int m = 0;
+    for (auto& k : g->lowered) {
+        k.first = m;
+        for (int j = 0; j < k.nparts; ++j, ++m) {
+            kp[m] = k.p[j]; kt[m] = k.t[j];
+            auto it = k.kind == 0 ? col_stats().find(k.p[j]) : col_stats().end();
+            if (it == col_stats().end()) have = false; else { lo[m] = it->second.lo; hi[m] = it->second.hi; prod *= double(hi[m] - lo[m] + 1); }
+        }
+    }
     const uint32_t hint = have ? (uint32_t)std::min<double>(prod, double(n)) : 0u;
-    check(aqgpu_groupby_build(kp, kt, nk, n, have ? lo : nullptr, have ? hi : nullptr, row_order, hint, &g->h));
+    check(aqgpu_groupby_build(kp, kt, m, n, have ? lo : nullptr, have ? hi : nullptr, row_order, hint, &g->h));
     g->nrows = n;
     check(aqgpu_groups_size(g->h, &g->ngroups));
     return g;
@@ -398,7 +507,7 @@ template <class... Ts> struct Groups {
     template <int i> ColRef<std::tuple_element_t<i, std::tuple<Ts...>>> key() const {
         typedef std::tuple_element_t<i, std::tuple<Ts...>> K;
         ColRef<K> out(handle->ngroups);
-        if (handle->ngroups) check(aqgpu_groups_keys(handle->h, i, out.container));
+        handle->template fetch_key<K>(i, out.container);
         return out;
     }
     ColRef<uint32_t> offsets() const { handle->fetch_offsets(); ColRef<uint32_t> o((uint32_t)handle->offsets.size()); std::copy(handle->offsets.begin(), handle->offsets.end(), o.container); return o; }
@@ -434,7 +543,7 @@ inline HashTableComponents<Ts...> make_components(std::index_sequence<I...>, std
     g->fetch_offsets();
     auto keys = std::make_shared<std::vector<std::tuple<Ts...>>>(g->ngroups);
     std::tuple<std::vector<Ts>...> cols{ std::vector<Ts>(g->ngroups)... };
-    if (g->ngroups) (check(aqgpu_groups_keys(g->h, (int)I, std::get<I>(cols).data())), ...);
+    (g->template fetch_key<Ts>((int)I, std::get<I>(cols).data()), ...);
     for (uint32_t i = 0; i < g->ngroups; ++i) (*keys)[i] = std::make_tuple(std::get<I>(cols)[i]...);
     g->keys = keys;
     return HashTableComponents<Ts...>{g->ngroups, keys.get(), g->rows.data(), g->offsets.data(), g};

@@ -228,6 +228,52 @@ int main() {
         int mx = v1[0]; for (uint32_t i = 1; i < n; ++i) mx = std::max(mx, v1[i]);
         EXPECT(max(sales) == mx);
     }
+    {   // string / time / timestamp key columns (benchmark/quries/Aquery/load_data.a:1 `stocksymbol STRING`; hasher.h:97-132)
+        const char* syms[] = {"IBM", "AAPL", "", "A", "AA", "MSFT", "IBM.N", "GOOG"};
+        std::vector<std::string> heap(n);                           // the data source's string heap: every row its own copy
+        std::vector<astring_view> sym(n);
+        std::vector<types::time_t> tm(n);
+        std::vector<types::timestamp_t> ts(n);
+        for (uint32_t i = 0; i < n; ++i) {
+            heap[i] = syms[rnd() % 8]; sym[i] = astring_view(heap[i].c_str());
+            tm[i] = types::time_t((unsigned)(rnd() % 3) * 500u, (unsigned char)(rnd() % 2), 0, (unsigned char)(rnd() % 3));
+            reinterpret_cast<unsigned char*>(&tm[i])[7] = (unsigned char)rnd();      // padding garbage: not part of the key
+            ts[i] = types::timestamp_t(types::date_t((unsigned char)(1 + rnd() % 2), 7, 2024), tm[i]);
+        }
+        ColRef<astring_view> c_sym(n, sym.data());
+        ColRef<types::time_t> c_tm(n, tm.data());
+        ColRef<types::timestamp_t> c_ts(n, ts.data());
+        ColRef<int> c_v(n, v1.data());
+        ColRef<int> c_id2(n, id2.data());
+        {   // (sym, id2) -> sum(v1), the unchanged per-group loop
+            auto g = HashTableFactory<record<astring_view, int>, transTypes<record<astring_view, int>, hasher>>::get(c_sym, c_id2);
+            std::vector<std::pair<std::string, int>> ord; std::map<std::pair<std::string, int>, long long> acc;
+            for (uint32_t i = 0; i < n; ++i) { auto k = std::make_pair(heap[i], id2[i]); if (!acc.count(k)) ord.push_back(k); acc[k] += v1[i]; }
+            EXPECT(g.size == ord.size());
+            for (uint32_t i = 0; i < g.size && fails < 5; ++i) {
+                auto& key = (*g.keys)[i];
+                EXPECT(std::string(std::get<0>(key).rstr) == ord[i].first && std::get<1>(key) == ord[i].second);
+                EXPECT((long long)sum(c_v[g.values[i]]) == acc[ord[i]]);
+            }
+        }
+        {   // time key, whole-column form
+            auto g = aq::group_by(c_tm);
+            auto img = [](const types::time_t& t) { return ((unsigned long long)t.hours << 48) | ((unsigned long long)t.minutes << 40) | ((unsigned long long)t.seconds << 32) | t.ms; };
+            std::vector<unsigned long long> ord; std::map<unsigned long long, long long> acc;
+            for (uint32_t i = 0; i < n; ++i) { auto k = img(tm[i]); if (!acc.count(k)) ord.push_back(k); acc[k] += v1[i]; }
+            auto keys = g.key<0>(); auto s = sum(c_v[g]).to_host();
+            EXPECT(g.size == ord.size() && g.size == 18);
+            for (uint32_t i = 0; i < g.size && fails < 5; ++i) { EXPECT(img(keys[i]) == ord[i]); EXPECT((long long)s[i] == acc[ord[i]]); }
+        }
+        {   // timestamp key
+            auto g = aq::group_by(c_ts);
+            std::vector<uint32_t> firsts; std::vector<types::timestamp_t> seen;
+            for (uint32_t i = 0; i < n; ++i) { bool f = false; for (auto& t : seen) if (t == ts[i]) { f = true; break; } if (!f) { seen.push_back(ts[i]); firsts.push_back(i); } }
+            auto keys = g.key<0>();
+            EXPECT(g.size == seen.size() && g.size == 36);
+            for (uint32_t i = 0; i < g.size && fails < 5; ++i) EXPECT(keys[i] == seen[i]);
+        }
+    }
     printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
     return fails ? 1 : 0;
 }

@@ -340,6 +340,31 @@ int aqgpu_partition_counts_noalloc(const uint32_t* owner, uint32_t nrows, uint32
  * vtype; cnt_top and nparts are AQ_INT64 columns. */
 int aqgpu_second_merge(int vtype, const int64_t* cnt_top, const int64_t* nparts, const void* second_top,
                        const void* first_prev, void* out, uint32_t n);
+/* ---- key columns that are not plain integers -----------------------------------------
+ * The reference groups date / time / timestamp / string columns through AQHashTable with the hashes of
+ * server/hasher.h:97-132 and the types' operator== (server/libaquery.cpp:112-114,162-164,201-203,
+ * server/types.h:299-309).  Only equality and first-appearance order are observable, so such a column is
+ * lowered to integer key columns that are equal exactly when operator== holds, and passed to the group-by
+ * entry points above:
+ *   AQ_KEY_DATE       types::date_t, 4-byte cells {day, month, year}     -> out_a: AQ_UINT32 (the image; the
+ *                     column may equally be passed as AQ_UINT32 without calling anything)
+ *   AQ_KEY_TIME       types::time_t, 8-byte cells {ms, s, m, h, padding} -> out_a: AQ_INT64, padding cleared
+ *   AQ_KEY_TIMESTAMP  types::timestamp_t, 12-byte cells {date, time}     -> out_a: AQ_UINT32, out_b: AQ_INT64
+ * aqgpu_key_join is the inverse, for the key columns of a result (padding bytes come back as zero). */
+enum aqgpu_key_kind { AQ_KEY_DATE = 1, AQ_KEY_TIME = 2, AQ_KEY_TIMESTAMP = 3 };
+size_t aqgpu_key_cell_size(int key_kind);
+int aqgpu_key_split(int key_kind, const void* col, uint32_t nrows, void* out_a, void* out_b);
+int aqgpu_key_join(int key_kind, const void* a, const void* b, uint32_t nrows, void* out);
+/* String key column -> dictionary codes: out_codes[i] = index of row i's string among the distinct strings in
+ * FIRST-APPEARANCE order, i.e. the group id AQHashTable<astring_view> gives it (server/hasher.h:97-106,176-179);
+ * out_first_row[c] = first row holding string c (may be NULL; room for max_distinct cells, else a "capacity"
+ * error).  Strings are Arrow-style: row i = bytes[offsets[i] .. offsets[i+1]) (no terminator; the reference's
+ * astring_view is a char pointer into the data source's heap, which packing replaces at ingest).  Two 64-bit
+ * hashes per string are grouped by the integer path and every row is then compared byte for byte with its
+ * group's first row: a hash collision fails the call, it never merges two strings.  Group by the codes
+ * (AQ_UINT32 keys) alone or with other key columns; map result codes back through out_first_row. */
+int aqgpu_string_dict(const void* bytes, uint64_t nbytes, const uint64_t* offsets, uint32_t nrows,
+                      uint32_t* out_codes, uint32_t max_distinct, uint32_t* out_first_row, uint32_t* ndistinct);
 /* out[i] = pow(x[i], p) in fp64 (q9 pow(corr, 2); aggregations.h:409-411). */
 int aqgpu_vec_pow(const double* x, double p, double* out, uint32_t n);
 

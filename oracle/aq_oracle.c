@@ -45,11 +45,56 @@ static inline uint64_t key_at(const void* col, int type, uint32_t i) {
                              : (uint64_t)(int64_t)((const int32_t*)col)[i];
 }
 
+/* Keys that are not plain integers.  The reference's table decides with the types' operator==:
+ *   AQO_STR        column of `const char*` (astring_view, server/types.h:280-284): same characters up to the NUL
+ *                  (server/types.h:299-309)
+ *   AQO_DATE       4-byte cells {day u8, month u8, year i16}; year, month, day equal (server/libaquery.cpp:112-114)
+ *   AQO_TIME       8-byte cells {ms u32, seconds u8, minutes u8, hours u8, padding}; the four fields equal
+ *                  (server/libaquery.cpp:162-164) -- the padding byte is not compared
+ *   AQO_TIMESTAMP  12-byte cells {date, time}; both equal (server/libaquery.cpp:201-203)
+ * The hash values (server/hasher.h:97-132) are not observable. */
+static inline int key_is_plain(int type) { return type == AQO_INT32 || type == AQO_INT64; }
+static inline int key_known(int type) {
+    return key_is_plain(type) || type == AQO_STR || type == AQO_DATE || type == AQO_TIME || type == AQO_TIMESTAMP;
+}
+static inline uint64_t time_image(const unsigned char* c) {       /* ms, seconds, minutes, hours; padding dropped */
+    uint32_t ms; memcpy(&ms, c, 4);
+    return (uint64_t)ms | ((uint64_t)c[4] << 32) | ((uint64_t)c[5] << 40) | ((uint64_t)c[6] << 48);
+}
+static inline uint64_t key_hash1(const void* col, int type, uint32_t i) {
+    switch (type) {
+    case AQO_STR: {
+        const unsigned char* p = (const unsigned char*)((const char* const*)col)[i];
+        uint64_t h = 0xcbf29ce484222325ULL;
+        for (; *p; ++p) h = (h ^ *p) * 0x100000001b3ULL;
+        return h; }
+    case AQO_DATE: { uint32_t w; memcpy(&w, (const unsigned char*)col + (size_t)i * 4, 4); return w; }
+    case AQO_TIME: return time_image((const unsigned char*)col + (size_t)i * 8);
+    case AQO_TIMESTAMP: {
+        const unsigned char* c = (const unsigned char*)col + (size_t)i * 12;
+        uint32_t w; memcpy(&w, c, 4);
+        return mix64(w) ^ time_image(c + 4); }
+    default: return key_at(col, type, i);
+    }
+}
+static inline int key_eq1(const void* col, int type, uint32_t i, uint32_t r) {
+    switch (type) {
+    case AQO_STR: return strcmp(((const char* const*)col)[i], ((const char* const*)col)[r]) == 0;
+    case AQO_DATE: return memcmp((const unsigned char*)col + (size_t)i * 4, (const unsigned char*)col + (size_t)r * 4, 4) == 0;
+    case AQO_TIME: return time_image((const unsigned char*)col + (size_t)i * 8) == time_image((const unsigned char*)col + (size_t)r * 8);
+    case AQO_TIMESTAMP: {
+        const unsigned char* a = (const unsigned char*)col + (size_t)i * 12;
+        const unsigned char* b = (const unsigned char*)col + (size_t)r * 12;
+        return memcmp(a, b, 4) == 0 && time_image(a + 4) == time_image(b + 4); }
+    default: return key_at(col, type, i) == key_at(col, type, r);
+    }
+}
+
 int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
                 uint32_t* ngroups, uint32_t* gid_out, uint32_t* offsets, uint32_t* perm) {
     if (nkeys < 1 || nkeys > 16) return -2;
     for (int k = 0; k < nkeys; ++k)
-        if (key_types[k] != AQO_INT32 && key_types[k] != AQO_INT64) return -2;
+        if (!key_known(key_types[k])) return -2;
     if (nrows == 0) { *ngroups = 0; if (offsets) offsets[0] = 0; return 0; }
 
     uint64_t cap = 16;
@@ -65,7 +110,7 @@ int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32
     uint32_t ng = 0;
     for (uint32_t i = 0; i < nrows; ++i) {
         uint64_t h = 0x9e3779b97f4a7c15ULL;
-        for (int k = 0; k < nkeys; ++k) h = mix64(h ^ key_at(keys[k], key_types[k], i));
+        for (int k = 0; k < nkeys; ++k) h = mix64(h ^ key_hash1(keys[k], key_types[k], i));
         uint64_t s = h & mask;
         uint32_t g;
         for (;;) {
@@ -79,7 +124,7 @@ int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32
             const uint32_t r = rep_row[g];
             int eq = 1;
             for (int k = 0; k < nkeys && eq; ++k)
-                eq = key_at(keys[k], key_types[k], i) == key_at(keys[k], key_types[k], r);
+                eq = key_eq1(keys[k], key_types[k], i, r);
             if (eq) break;
             s = (s + 1) & mask;
         }

@@ -25,7 +25,9 @@ extern "C" {
 #endif
 
 enum aqo_dtype {
-    AQO_INT32 = 0, AQO_FLOAT = 1, AQO_DOUBLE = 3, AQO_INT64 = 5, AQO_INT128 = 6, AQO_UINT32 = 11
+    AQO_INT32 = 0, AQO_FLOAT = 1, AQO_DOUBLE = 3, AQO_INT64 = 5, AQO_INT128 = 6, AQO_UINT32 = 11,
+    /* key columns only (aqo_groupby): ASTR = column of const char*, ADATE 4-byte, ATIME 8-byte, ATIMESTAMP 12-byte cells */
+    AQO_STR = 2, AQO_DATE = 8, AQO_TIME = 9, AQO_TIMESTAMP = 18
 };
 
 /* per-group scalar aggregates (server/aggregations.h:10-32,71-86,332-348,383-407,413-415,487-497) */
@@ -48,7 +50,9 @@ enum aqo_scan_op {
 const char* aqo_kind(void);
 
 /* Hash group-by: AQHashTable::hashtable_push per row + ht_postproc (server/hasher.h:146-199).
- *   keys[k]      : key column k, nrows elements of key_types[k] (AQO_INT32 or AQO_INT64)
+ *   keys[k]      : key column k, nrows elements of key_types[k] (AQO_INT32 or AQO_INT64; the port also takes any mix
+ *                  with AQO_STR / AQO_DATE / AQO_TIME / AQO_TIMESTAMP, the reference build a single such key or
+ *                  the pair (AQO_STR, AQO_INT32))
  *   ngroups      : out, number of distinct key tuples
  *   gid[nrows]   : out, "reversemap": dense group id of every row, ids in FIRST-APPEARANCE order
  *   offsets[ngroups+1] : out, CSR starts ("ht_base" after ht_postproc) plus the terminal nrows

@@ -40,6 +40,34 @@ _CODE2NP = {INT32: np.int32, FLOAT: np.float32, DOUBLE: np.float64, INT64: np.in
             UINT32: np.uint32}
 
 
+# key-only cell types (aqo_groupby): the reference's structs as numpy records (server/types.h:82-86,105-109,128-130)
+STR, DATE, TIME, TIMESTAMP = 2, 8, 9, 18
+DATE_DT = np.dtype([("day", "u1"), ("month", "u1"), ("year", "<i2")])
+TIME_DT = np.dtype([("ms", "<u4"), ("seconds", "u1"), ("minutes", "u1"), ("hours", "u1"), ("pad", "u1")])
+TIMESTAMP_DT = np.dtype([("date", DATE_DT), ("time", TIME_DT)])
+assert DATE_DT.itemsize == 4 and TIME_DT.itemsize == 8 and TIMESTAMP_DT.itemsize == 12
+_KEY_DT2CODE = {DATE_DT: DATE, TIME_DT: TIME, TIMESTAMP_DT: TIMESTAMP}
+
+
+class StrColumn:
+    """A string key column the way the reference holds it: an array of char pointers (ColRef<astring_view>)."""
+
+    def __init__(self, strings):
+        self.strings = [x if isinstance(x, bytes) else str(x).encode() for x in strings]
+        self.bufs = [ctypes.create_string_buffer(x) for x in self.strings]      # NUL-terminated, distinct addresses
+        self.ptrs = (ctypes.c_void_p * max(len(self.bufs), 1))(*[ctypes.addressof(b) for b in self.bufs])
+
+    def __len__(self):
+        return len(self.strings)
+
+    def packed(self):
+        """(bytes uint8[], offsets uint64[n + 1]): the Arrow-style layout aqgpu_string_dict takes"""
+        lens = np.fromiter((len(x) for x in self.strings), np.uint64, len(self.strings))
+        off = np.zeros(len(self.strings) + 1, np.uint64)
+        np.cumsum(lens, out=off[1:])
+        return np.frombuffer(b"".join(self.strings), np.uint8).copy(), off
+
+
 def build(which: str = "all") -> None:
     """Run oracle/Makefile (``port``, ``ref`` or ``all``).  Building the checker is not using it."""
     subprocess.run(["make", "-s", "-C", HERE, which], check=True)
@@ -75,10 +103,11 @@ class Oracle:
 
     # -- A1 + A2 -----------------------------------------------------------------------------
     def groupby(self, keys):
-        keys = [np.ascontiguousarray(k) for k in keys]
+        keys = [k if isinstance(k, StrColumn) else np.ascontiguousarray(k) for k in keys]
         n = len(keys[0])
-        kp = (ctypes.c_void_p * len(keys))(*[k.ctypes.data for k in keys])
-        kt = (ctypes.c_int * len(keys))(*[_NP2CODE[k.dtype] for k in keys])
+        kp = (ctypes.c_void_p * len(keys))(*[ctypes.addressof(k.ptrs) if isinstance(k, StrColumn) else k.ctypes.data for k in keys])
+        kt = (ctypes.c_int * len(keys))(*[STR if isinstance(k, StrColumn) else _KEY_DT2CODE.get(k.dtype, None) or _NP2CODE[k.dtype]
+                                          for k in keys])
         ng = ctypes.c_uint32(0)
         gid = np.empty(n, np.uint32)
         offsets = np.empty(n + 1, np.uint32)

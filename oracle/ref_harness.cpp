@@ -84,6 +84,32 @@ int groupby_k(int nkeys, const void* const* keys, uint32_t n,
     }
 }
 
+/* Key tuples of mixed / non-integer element types (astring_view, types::date_t, types::time_t, types::timestamp_t):
+ * the same hashtable_push + ht_postproc, the reference's own hashes (server/hasher.h:97-132) and operator==. */
+template <class... KT, size_t... I>
+int groupby_mixed(std::index_sequence<I...>, const void* const* keys, uint32_t n,
+                  uint32_t* ngroups, uint32_t* gid, uint32_t* offsets, uint32_t* perm) {
+    typedef record<KT...> rec_t;
+    if (n == 0) { *ngroups = 0; if (offsets) offsets[0] = 0; return 0; }
+    std::tuple<const KT*...> k{ static_cast<const KT*>(keys[I])... };
+    AQHashTable<rec_t, transTypes<rec_t, hasher>> g{n};
+    for (uint32_t i = 0; i < n; ++i)
+        g.hashtable_push(std::forward_as_tuple(std::get<I>(k)[i]...), i);
+    auto vecs = g.ht_postproc(n);
+    const uint32_t ng = static_cast<uint32_t>(g.size());
+    *ngroups = ng;
+    if (gid) memcpy(gid, g.reversemap, sizeof(uint32_t) * n);
+    if (perm) memcpy(perm, g.mapbase, sizeof(uint32_t) * n);
+    if (offsets) {
+        for (uint32_t j = 0; j < ng; ++j) offsets[j] = g.ht_base[j];
+        offsets[ng] = n;
+    }
+    free(vecs); free(g.reversemap); free(g.ht_base);
+    return 0;
+}
+static_assert(sizeof(astring_view) == sizeof(const char*), "a string key column is an array of char pointers");
+static_assert(sizeof(types::date_t) == 4 && sizeof(types::time_t) == 8 && sizeof(types::timestamp_t) == 12, "key cell sizes");
+
 /* The emitted per-group loop: gather through the row list, hand the gathered vector to f. */
 template <class T, class F>
 void per_group(const void* v, uint32_t ng, const uint32_t* off, const uint32_t* perm, F f) {
@@ -242,6 +268,16 @@ const char* aqo_kind(void) { return "reference"; }
 int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32_t nrows,
                 uint32_t* ngroups, uint32_t* gid, uint32_t* offsets, uint32_t* perm) {
     if (nkeys < 1) return -2;
+    if (nkeys == 1 && key_types[0] == AQO_STR)
+        return groupby_mixed<astring_view>(std::make_index_sequence<1>{}, keys, nrows, ngroups, gid, offsets, perm);
+    if (nkeys == 1 && key_types[0] == AQO_DATE)
+        return groupby_mixed<types::date_t>(std::make_index_sequence<1>{}, keys, nrows, ngroups, gid, offsets, perm);
+    if (nkeys == 1 && key_types[0] == AQO_TIME)
+        return groupby_mixed<types::time_t>(std::make_index_sequence<1>{}, keys, nrows, ngroups, gid, offsets, perm);
+    if (nkeys == 1 && key_types[0] == AQO_TIMESTAMP)
+        return groupby_mixed<types::timestamp_t>(std::make_index_sequence<1>{}, keys, nrows, ngroups, gid, offsets, perm);
+    if (nkeys == 2 && key_types[0] == AQO_STR && key_types[1] == AQO_INT32)
+        return groupby_mixed<astring_view, int>(std::make_index_sequence<2>{}, keys, nrows, ngroups, gid, offsets, perm);
     for (int k = 1; k < nkeys; ++k) if (key_types[k] != key_types[0]) return -2;
     if (key_types[0] == AQO_INT32) return groupby_k<int>(nkeys, keys, nrows, ngroups, gid, offsets, perm);
     if (key_types[0] == AQO_INT64) return groupby_k<long>(nkeys, keys, nrows, ngroups, gid, offsets, perm);

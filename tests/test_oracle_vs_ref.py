@@ -92,3 +92,30 @@ def test_moment_scans_port_vs_reference_and_definition():
                     want[off[g] + i] = np.var(x[i + 1 - c:i + 1])
             assert np.all(np.abs(got - want) <= 1e-9 * np.maximum(np.abs(want), 1.0)), (dt, w)
             assert np.all(np.abs(sd - np.sqrt(want)) <= 1e-9 * np.maximum(np.sqrt(want), 1.0)), (dt, w)
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_groupby_special_keys_port_vs_reference(port, ref, seed):
+    """string / date / time / timestamp keys: the restatement's equality rules against AQHashTable with
+    the reference's own hashes (server/hasher.h:97-132) and operator== (types.h:299-309, libaquery.cpp:112-203)"""
+    import keydata
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(2000, 6000))
+    cols = {"str": keydata.strings(rng, n, 300, long_tail=True), "date": keydata.dates(rng, n, 900),
+            "time": keydata.times(rng, n, 64), "timestamp": keydata.timestamps(rng, n, 64)}
+    for name, c in cols.items():
+        a, b = port.groupby([c]), ref.groupby([c])
+        assert a[0] == b[0] and 1 < a[0] < n, name
+        for x, y in zip(a[1:], b[1:]):
+            assert_same(x, y, name)
+    k2 = rng.integers(0, 4, n).astype(np.int32)
+    a, b = port.groupby([cols["str"], k2]), ref.groupby([cols["str"], k2])
+    assert a[0] == b[0]
+    for x, y in zip(a[1:], b[1:]):
+        assert_same(x, y, "(str, int32)")
+    # the padding byte of time_t is not part of the key: same cells with other padding give the same groups
+    t2 = cols["time"].copy(); t2["pad"] = 0
+    assert_same(ref.groupby([t2])[1], ref.groupby([cols["time"]])[1], "time padding")
+    # a single row, and all rows equal
+    one = keydata.strings(rng, 1, 5)
+    assert port.groupby([one])[0] == ref.groupby([one])[0] == 1

@@ -52,6 +52,7 @@ EXPORTS = [
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
     "aqgpu_partition_counts_noalloc", "aqgpu_key_cell_size", "aqgpu_key_split", "aqgpu_key_join", "aqgpu_string_dict",
+    "aqgpu_vec_out_type", "aqgpu_vec_binary",
 ]
 
 
@@ -745,3 +746,37 @@ def string_dict(data: np.ndarray, offsets: np.ndarray, max_distinct: int | None 
                                   ctypes.c_uint32(n), codes.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(cap),
                                   first.ctypes.data_as(ctypes.c_void_p), ctypes.byref(nd)))
     return codes[:n], first[: nd.value]
+
+
+# ---- element-wise vector arithmetic / compare (aqgpu_vec_binary) -------------------------------------------------------
+BOOL = 16
+V_ADD, V_SUB, V_MUL, V_DIV, V_AND, V_OR, V_XOR, V_GT, V_LT, V_GTE, V_LTE, V_EQ, V_NEQ = range(13)
+_VEC_NP = {INT32: np.int32, INT64: np.int64, FLOAT: np.float32, DOUBLE: np.float64, BOOL: np.uint8}
+
+
+def _vec_operand(x):
+    """(array of cells, dtype code, is_scalar): numpy arrays are vectors, 0-d arrays / numpy scalars are scalar operands"""
+    x = np.asarray(x)
+    scalar = x.ndim == 0
+    x = np.ascontiguousarray(x.reshape(1) if scalar else x)
+    if x.dtype == np.bool_:
+        x = x.view(np.uint8)
+    return x, (BOOL if x.dtype == np.uint8 else NP2CODE[x.dtype]), int(scalar)
+
+
+def vec_out_type(op: int, a, b) -> int:
+    (_, ta, sa), (_, tb, sb) = _vec_operand(a), _vec_operand(b)
+    return int(lib().aqgpu_vec_out_type(op, ta, sa, tb, sb))
+
+
+def vec_binary(op: int, a, b, out_type: int = -1) -> np.ndarray:
+    """out = a op b, element-wise.  __int128 results come back as (n, 2) int64 [lo, hi], AQ_BOOL as uint8."""
+    (a, ta, sa), (b, tb, sb) = _vec_operand(a), _vec_operand(b)
+    n = len(b) if sa else len(a)
+    ot = out_type if out_type >= 0 else int(lib().aqgpu_vec_out_type(op, ta, sa, tb, sb))
+    if ot < 0:
+        raise AqgpuError(f"vec_binary: no result type for op {op} on dtypes {ta}, {tb}")
+    out = np.zeros((n, 2), np.int64) if ot == INT128 else np.zeros(n, _VEC_NP[ot])
+    check(lib().aqgpu_vec_binary(op, ta, a.ctypes.data_as(ctypes.c_void_p), sa, tb, b.ctypes.data_as(ctypes.c_void_p), sb,
+                                 ot, out.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(n)))
+    return out

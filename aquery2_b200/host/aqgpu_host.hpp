@@ -111,7 +111,8 @@ template <class T> constexpr int dtype_of() {
     return std::is_same<D, int>::value ? AQ_INT32 : std::is_same<D, unsigned>::value ? AQ_UINT32
          : std::is_same<D, float>::value ? AQ_FLOAT : std::is_same<D, double>::value ? AQ_DOUBLE
          : (std::is_same<D, long long>::value || std::is_same<D, long>::value) ? AQ_INT64
-         : (std::is_same<D, __int128>::value || std::is_same<D, unsigned __int128>::value) ? AQ_INT128 : -1;
+         : (std::is_same<D, __int128>::value || std::is_same<D, unsigned __int128>::value) ? AQ_INT128
+         : std::is_same<D, bool>::value ? AQ_BOOL : -1;
 }
 struct GroupsHandle;
 struct GroupRows;
@@ -753,6 +754,69 @@ AQ_PRED(sum, types::GetLongType<T>) AQ_PRED(avg, double) AQ_PRED(max, T) AQ_PRED
 template <class T> ColRef<T> operator-(const ColRef<T>& a, const ColRef<T>& b) {                    // q7: max(v1) - min(v2)
     ColRef<T> out = aq::alloc_like_input<T>(a.container, a.size);
     if (a.size) aq::check(aqgpu_vec_sub(aq::dtype_of<T>(), a.container, b.container, out.container, a.size));
+    return out;
+}
+// General forms (server/vector_type.hpp:372-396, server/table.h:826-973): `a op b` for columns of different element types,
+// column op scalar, scalar op column; comparisons give ColRef<bool>.  Result element types are the reference's
+// (aqgpu_vec_out_type mirrors its templates; tests/test_gpu_vecops.py pins the table to the reference build).
+namespace aq {
+template <class A, class B> struct coercion {               // types::Coercion<T1, T2> for {int, long long, float, double} (types.h:264-275)
+    static constexpr bool fp = std::is_floating_point<A>::value || std::is_floating_point<B>::value;
+    static constexpr bool wide = sizeof(A) == 8 || sizeof(B) == 8;
+    typedef std::conditional_t<fp, std::conditional_t<wide, double, float>, std::conditional_t<wide, long long, int>> type;
+};
+template <class T> struct is_vec_cell : std::integral_constant<bool, std::is_same<T, int>::value || std::is_same<T, long long>::value ||
+    std::is_same<T, long>::value || std::is_same<T, float>::value || std::is_same<T, double>::value || std::is_same<T, bool>::value> {};
+template <class T> using cell_t = std::conditional_t<std::is_same<T, long>::value, long long, std::conditional_t<std::is_same<T, bool>::value, int, T>>;
+template <class R, class A, class B>
+ColRef<R> vec_op(int op, const A* a, uint32_t na, bool a_scalar, const B* b, uint32_t nb, bool b_scalar) {
+    const uint32_t n = a_scalar ? nb : na;
+    ColRef<R> out = alloc_like_input<R>(a_scalar ? (const void*)b : (const void*)a, n);
+    if (n) check(aqgpu_vec_binary(op, dtype_of<A>(), a, a_scalar, dtype_of<B>(), b, b_scalar, dtype_of<R>(), out.container, n));
+    return out;
+}
+}  // namespace aq
+#define AQ_VECOP(SYM, OP, VV, VS)                                                                                                   \
+    template <class A, class B, class = std::enable_if_t<aq::is_vec_cell<A>::value && aq::is_vec_cell<B>::value && !std::is_same<A, B>::value>> \
+    auto operator SYM(const ColRef<A>& a, const ColRef<B>& b) { using K [[maybe_unused]] = typename aq::coercion<aq::cell_t<A>, aq::cell_t<B>>::type; \
+        return aq::vec_op<VV>(OP, a.container, a.size, false, b.container, b.size, false); }                                        \
+    template <class A, class B, class = std::enable_if_t<aq::is_vec_cell<A>::value && std::is_arithmetic<B>::value>>                \
+    auto operator SYM(const ColRef<A>& a, const B& b) { using K [[maybe_unused]] = typename aq::coercion<aq::cell_t<A>, aq::cell_t<B>>::type;        \
+        const aq::cell_t<B> s = b; return aq::vec_op<VS>(OP, a.container, a.size, false, &s, 1u, true); }                           \
+    template <class A, class B, class = std::enable_if_t<aq::is_vec_cell<A>::value && std::is_arithmetic<B>::value>>                \
+    auto operator SYM(const B& b, const ColRef<A>& a) { using K [[maybe_unused]] = typename aq::coercion<aq::cell_t<A>, aq::cell_t<B>>::type;        \
+        const aq::cell_t<B> s = b; return aq::vec_op<VS>(OP, &s, 1u, true, a.container, a.size, false); }
+AQ_VECOP(+, AQ_V_ADD, K, K)
+AQ_VECOP(-, AQ_V_SUB, K, K)
+AQ_VECOP(*, AQ_V_MUL, K, types::GetLongType<K>)
+AQ_VECOP(/, AQ_V_DIV, K, types::GetFPType<K>)
+AQ_VECOP(>, AQ_V_GT, bool, bool) AQ_VECOP(<, AQ_V_LT, bool, bool) AQ_VECOP(>=, AQ_V_GTE, bool, bool)
+AQ_VECOP(<=, AQ_V_LTE, bool, bool) AQ_VECOP(==, AQ_V_EQ, bool, bool) AQ_VECOP(!=, AQ_V_NEQ, bool, bool)
+#undef AQ_VECOP
+// same-type column pairs (operator- above keeps its aqgpu_vec_sub fast path)
+#define AQ_VECOP_SAME(SYM, OP, RT)                                                                                                  \
+    template <class T, class = std::enable_if_t<aq::is_vec_cell<T>::value>>                                                        \
+    ColRef<RT> operator SYM(const ColRef<T>& a, const ColRef<T>& b) { return aq::vec_op<RT>(OP, a.container, a.size, false, b.container, b.size, false); }
+AQ_VECOP_SAME(+, AQ_V_ADD, T) AQ_VECOP_SAME(*, AQ_V_MUL, T) AQ_VECOP_SAME(/, AQ_V_DIV, T)
+AQ_VECOP_SAME(>, AQ_V_GT, bool) AQ_VECOP_SAME(<, AQ_V_LT, bool) AQ_VECOP_SAME(>=, AQ_V_GTE, bool)
+AQ_VECOP_SAME(<=, AQ_V_LTE, bool) AQ_VECOP_SAME(==, AQ_V_EQ, bool) AQ_VECOP_SAME(!=, AQ_V_NEQ, bool)
+#undef AQ_VECOP_SAME
+// aqop_x(lhs, rhs, ret): the root of an emitted expression writes into a container of the emitter's type (table.h:949-973)
+#define AQ_AQOP(NAME, OP)                                                                                                           \
+    template <class A, class B, class R> void aqop_##NAME(const ColRef<A>& a, const ColRef<B>& b, ColRef<R>& ret) {                 \
+        const int rt = sizeof(R) == 1 ? AQ_BOOL : aq::dtype_of<R>();          /* the emitter's ByteT for logical results: 0 / 1 cells */ \
+        if (ret.size) aq::check(aqgpu_vec_binary(OP, aq::dtype_of<A>(), a.container, 0, aq::dtype_of<B>(), b.container, 0, rt, ret.container, ret.size)); }
+AQ_AQOP(add, AQ_V_ADD) AQ_AQOP(minus, AQ_V_SUB) AQ_AQOP(mul, AQ_V_MUL) AQ_AQOP(div, AQ_V_DIV) AQ_AQOP(and, AQ_V_AND) AQ_AQOP(or, AQ_V_OR)
+AQ_AQOP(xor, AQ_V_XOR) AQ_AQOP(gt, AQ_V_GT) AQ_AQOP(lt, AQ_V_LT) AQ_AQOP(gte, AQ_V_GTE) AQ_AQOP(lte, AQ_V_LTE) AQ_AQOP(eq, AQ_V_EQ) AQ_AQOP(neq, AQ_V_NEQ)
+#undef AQ_AQOP
+// sums over a comparison result, the session counter of tests/network.a:11 `sums(deltas(_time) > 120)`.  The running count is
+// returned as int64 cells (the reference's GetLongType<bool> is a 128-bit integer) so that it can serve as a key column.
+inline ColRef<long long> sums(const ColRef<bool>& c) {
+    const int zero = 0;
+    ColRef<int> wide = aq::vec_op<int>(AQ_V_ADD, c.container, c.size, false, &zero, 1u, true);
+    auto g = aq::whole_column(wide);
+    ColRef<long long> out = aq::alloc_like_input<long long>(c.container, c.size);
+    if (c.size) aq::check(aqgpu_group_scan(g.handle->h, AQ_SUMS, 0, AQ_INT32, wide.container, AQ_INT64, out.container));
     return out;
 }
 inline ColRef<double> pow(const ColRef<double>& x, double p) {                                      // q9: pow(corr(v1, v2), 2)

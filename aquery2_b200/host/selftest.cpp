@@ -274,6 +274,53 @@ int main() {
             for (uint32_t i = 0; i < g.size && fails < 5; ++i) EXPECT(keys[i] == seen[i]);
         }
     }
+    {   // element-wise operators (table.h:826-973) and tests/network.a:8-11: GROUP BY src, sums(deltas(_time) > 120)
+        std::vector<int> tm(n); std::vector<std::string> heap(n); std::vector<astring_view> srcv(n);
+        const char* hosts[] = {"a1", "b2", "c3", "a1b"};
+        int clock = 0;
+        for (uint32_t i = 0; i < n; ++i) { clock += 1 + (int)(rnd() % 200); tm[i] = clock; heap[i] = hosts[rnd() % 4]; srcv[i] = astring_view(heap[i].c_str()); }
+        ColRef<int> c_t(n, tm.data()), c_v(n, v1.data());
+        ColRef<float> c_f(n, v3.data());
+        ColRef<astring_view> c_src(n, srcv.data());
+        auto gap = deltas(c_t) > 120;                       // ColRef<bool>
+        auto sess = sums(gap);                              // ColRef<long long>: running count of gaps = session id
+        auto g = aq::group_by(c_src, sess);
+        auto cnt = g.counts();
+        auto av = avg(c_v[g]).to_host();
+        std::vector<std::pair<std::string, long long>> ord; std::map<std::pair<std::string, long long>, std::pair<long long, uint32_t>> acc;
+        long long sid = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            if (i && tm[i] - tm[i - 1] > 120) ++sid;
+            EXPECT(fails > 5 || sess[i] == sid);
+            auto k = std::make_pair(heap[i], sid);
+            if (!acc.count(k)) ord.push_back(k);
+            acc[k].first += v1[i]; acc[k].second++;
+        }
+        EXPECT(g.size == ord.size());
+        auto k0 = g.key<0>(); auto k1 = g.key<1>();
+        for (uint32_t i = 0; i < g.size && fails < 5; ++i) {
+            EXPECT(std::string(k0[i].rstr) == ord[i].first && k1[i] == ord[i].second);
+            EXPECT(cnt[i] == acc[ord[i]].second);
+            EXPECT(std::fabs(av[i] - (double)acc[ord[i]].first / acc[ord[i]].second) <= 1e-12 * (1 + std::fabs(av[i])));
+        }
+        // result element types and cells of the infix forms
+        auto s1 = c_v + c_f;   static_assert(std::is_same<decltype(s1), ColRef<float>>::value, "int + float -> float");
+        auto s2 = c_v * 3;     static_assert(std::is_same<decltype(s2), ColRef<__int128>>::value, "int column * scalar -> __int128 (GetLongType)");
+        auto s3 = c_v / 2;     static_assert(std::is_same<decltype(s3), ColRef<float>>::value, "int column / scalar -> float (GetFPType), integer division inside");
+        auto s4 = 10 - c_v;    static_assert(std::is_same<decltype(s4), ColRef<int>>::value, "scalar - int column -> int");
+        auto s5 = c_v * c_v;   static_assert(std::is_same<decltype(s5), ColRef<int>>::value, "column * column -> Coercion (vector_type.hpp:386-396)");
+        auto s6 = c_f >= 50.f; static_assert(std::is_same<decltype(s6), ColRef<bool>>::value, "comparison -> bool");
+        ColRef<signed char> r8(n); aqop_lt(c_v, c_t, r8);   // root of an emitted expression: aqop_lt(lhs, rhs, ret) with the emitter's byte type
+        for (uint32_t i = 0; i < n && fails < 5; ++i) {
+            EXPECT(s1[i] == (float)v1[i] + v3[i]);
+            EXPECT((long long)s2[i] == (long long)v1[i] * 3);
+            EXPECT(s3[i] == (float)(v1[i] / 2));
+            EXPECT(s4[i] == 10 - v1[i]);
+            EXPECT(s5[i] == v1[i] * v1[i]);
+            EXPECT(s6[i] == (v3[i] >= 50.f));
+            EXPECT(r8[i] == (v1[i] < tm[i] ? 1 : 0));
+        }
+    }
     printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
     return fails ? 1 : 0;
 }

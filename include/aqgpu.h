@@ -34,7 +34,8 @@ extern "C" {
 
 /* ---- dtypes: types::Type_t (server/aquery_types.h:1-5) ------------------------------------- */
 enum aqgpu_dtype {
-    AQ_INT32 = 0, AQ_FLOAT = 1, AQ_DOUBLE = 3, AQ_INT64 = 5, AQ_INT128 = 6, AQ_UINT32 = 11
+    AQ_INT32 = 0, AQ_FLOAT = 1, AQ_DOUBLE = 3, AQ_INT64 = 5, AQ_INT128 = 6, AQ_UINT32 = 11,
+    AQ_BOOL = 16        /* 1-byte cells: results of comparisons (aqgpu_vec_binary only) */
 };
 
 /* ---- per-group scalar aggregates (server/aggregations.h) ------------------------------------
@@ -304,6 +305,23 @@ int aqgpu_groups_order_by(aqgpu_groups_t* g, const void* const* cols, const int*
 /* ---- element-wise helpers used by generated code around the aggregates ----------------------- */
 /* out[i] = a[i] - b[i] (same dtype); q7 max(v1) - min(v2) (server/table.h:820-973 vector arith). */
 int aqgpu_vec_sub(int dtype, const void* a, const void* b, void* out, uint32_t n);
+/* out[i] = a[i] op b[i]: the element-wise operators of server/vector_type.hpp:372-396 and server/table.h:826-973
+ * (`price - mins(price)`, `deltas(_time) > 120`, ...).  Operand cells: AQ_INT32, AQ_INT64, AQ_FLOAT, AQ_DOUBLE (and
+ * AQ_BOOL, promoted to int like C++ does); with x_scalar != 0 the operand is a pointer to ONE host cell.  Every
+ * cell is computed like the C++ expression `lhs[i] op rhs[i]` (usual arithmetic conversions: int32 wraps, int / int
+ * is integer division, int64 with float is float arithmetic) and converted to out_type.  out_type < 0 selects the
+ * element type the reference's templates give the result, aqgpu_vec_out_type(): Coercion<T1,T2> for vector-vector
+ * forms; with a scalar operand `*` gives GetLongType (AQ_INT128 | AQ_DOUBLE) and `/` GetFPType (AQ_FLOAT for int32);
+ * comparisons give AQ_BOOL.  An explicit out_type is the `Ret&` of aqop_x(lhs, rhs, ret) (table.h:949-973).
+ * Deviations: the reference's `vector < scalar` (<=, >=, ==, !=) all evaluate `>` (vector_type.hpp:372-385);
+ * here each comparison means what it says.  Integer division by zero gives 0 (the reference traps). */
+enum aqgpu_vec_op {
+    AQ_V_ADD = 0, AQ_V_SUB = 1, AQ_V_MUL = 2, AQ_V_DIV = 3, AQ_V_AND = 4, AQ_V_OR = 5, AQ_V_XOR = 6,
+    AQ_V_GT = 7, AQ_V_LT = 8, AQ_V_GTE = 9, AQ_V_LTE = 10, AQ_V_EQ = 11, AQ_V_NEQ = 12
+};
+int aqgpu_vec_out_type(int op, int a_type, int a_scalar, int b_type, int b_scalar);
+int aqgpu_vec_binary(int op, int a_type, const void* a, int a_scalar, int b_type, const void* b, int b_scalar,
+                     int out_type, void* out, uint32_t n);
 /* out[i] = sum[i] / double(count[i]): AVG finalisation after a multi-GPU merge. sum is AQ_INT64,
  * AQ_INT128 or AQ_DOUBLE. */
 int aqgpu_avg_finalize(int sum_type, const void* sum, const uint32_t* count, double* out, uint32_t n);

@@ -46,6 +46,21 @@ enum aqo_scan_op {
     AQO_VARS = 12, AQO_STDDEVS = 13, AQO_VARW = 14, AQO_STDDEVW = 15
 };
 
+/* element-wise vector arithmetic / compare (server/table.h:820-973) */
+enum aqo_vec_op {
+    AQO_V_ADD = 0, AQO_V_SUB = 1, AQO_V_MUL = 2, AQO_V_DIV = 3, AQO_V_AND = 4, AQO_V_OR = 5, AQO_V_XOR = 6,
+    AQO_V_GT = 7, AQO_V_LT = 8, AQO_V_GTE = 9, AQO_V_LTE = 10, AQO_V_EQ = 11, AQO_V_NEQ = 12
+};
+#define AQO_BOOL 16     /* types::ABOOL: 1-byte cells */
+
+/* out[i] = a[i] op b[i] with the reference's operators: infix + - * / > for vector-vector, vector-scalar and
+ * scalar-vector operands (a scalar operand is a pointer to one cell), aqop_lt/gte/lte/eq/neq for two vectors with a
+ * bool result.  *out_type = Type_t code of the result cells as the reference's templates deduce it; returns the
+ * cell size in bytes, or < 0.  out may be NULL (type query).  REFERENCE BUILD ONLY (oracle/_ref): the plain-C port does
+ * not export it -- the expected cells are otherwise restated with numpy in tests/test_gpu_vecops.py. */
+int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n,
+                   void* out, int* out_type);
+
 /* Which oracle is this?  "reference" (built from /root/reference) or "port" (C restatement). */
 const char* aqo_kind(void);
 

@@ -118,6 +118,28 @@ class Oracle:
             raise RuntimeError(f"aqo_groupby rc={rc}")
         return ng.value, gid, offsets[: ng.value + 1].copy(), perm
 
+    # -- A10 (reference build only) -------------------------------------------------------------
+    def vec_binary(self, op: int, a, b):
+        """a op b through the reference's own operators (server/vector_type.hpp:372-396, server/table.h:826-973);
+        returns (cells, Type_t code of the result cells).  0-d operands are scalars."""
+        if not hasattr(self.lib, "aqo_vec_binary"):
+            raise RuntimeError("aqo_vec_binary is exported by the reference build only")
+        a, b = np.asarray(a), np.asarray(b)
+        sa, sb = int(a.ndim == 0), int(b.ndim == 0)
+        a, b = np.ascontiguousarray(a.reshape(1) if sa else a), np.ascontiguousarray(b.reshape(1) if sb else b)
+        n = len(b) if sa else len(a)
+        out = np.zeros(2 * n + 2, np.int64)
+        ot = ctypes.c_int(-1)
+        sz = self.lib.aqo_vec_binary(op, _NP2CODE[a.dtype], _ptr(a), sa, _NP2CODE[b.dtype], _ptr(b), sb, ctypes.c_uint32(n),
+                                     _ptr(out), ctypes.byref(ot))
+        if sz < 0:
+            raise RuntimeError(f"aqo_vec_binary rc={sz}")
+        raw = out.view(np.uint8)[: sz * n]
+        code = ot.value
+        if code == INT128:
+            return raw.view(np.int64).reshape(n, 2).copy(), code
+        return raw.view({16: np.uint8, **_CODE2NP}[code]).copy(), code
+
     # -- A5 / A9 -----------------------------------------------------------------------------
     def reduce(self, op, v, offsets, perm, v2=None, raw128=False):
         if isinstance(op, str):

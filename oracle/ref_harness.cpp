@@ -250,6 +250,60 @@ template <class T> int scan_out_t(int op) {
     }
 }
 
+/* Element-wise vector arithmetic / compare: the reference's own operators (server/table.h:820-973).  The element type of
+ * the result is whatever the reference's templates deduce (Coercion / GetLongType / GetFPType, server/types.h:194-275);
+ * its Type_t code is reported with the cells. */
+template <class R> int vec_emit(const vector_type<R>& r, void* out, int* out_type) {
+    *out_type = std::is_same<R, bool>::value ? AQO_BOOL : (int)types::Types<R>::getType();
+    if (out) memcpy(out, r.container, sizeof(R) * r.size);
+    return (int)sizeof(R);
+}
+template <class A, class B>
+int vec_binary_t(int op, const void* a, int a_scalar, const void* b, int b_scalar, uint32_t n, void* out, int* out_type) {
+    ensure_gc();
+    GC::scratch_space = nullptr;                                   /* results on the heap */
+    vector_type<A> va(a_scalar ? 0 : n, const_cast<void*>(a));
+    vector_type<B> vb(b_scalar ? 0 : n, const_cast<void*>(b));
+    const A sa = *static_cast<const A*>(a);
+    const B sb = *static_cast<const B*>(b);
+    if (a_scalar && b_scalar) return -2;
+    switch (op) {
+#define AQ_INFIX(CODE, OP)                                                                              \
+    case CODE:                                                                                          \
+        if (b_scalar) return vec_emit(va OP sb, out, out_type);                                         \
+        if (a_scalar) return vec_emit(sa OP vb, out, out_type);                                         \
+        return vec_emit(va OP vb, out, out_type);
+    AQ_INFIX(AQO_V_ADD, +) AQ_INFIX(AQO_V_SUB, -) AQ_INFIX(AQO_V_MUL, *) AQ_INFIX(AQO_V_DIV, /)
+#undef AQ_INFIX
+    case AQO_V_GT:
+        /* vector > scalar resolves to the member template (server/vector_type.hpp:372-381); vector > vector does not
+         * compile as an infix expression at HEAD (the member wins and assigns a vector to a bool), so two vectors go
+         * through aqop_gt (server/table.h:949-958) like the other comparisons */
+        if (b_scalar) return vec_emit(va > sb, out, out_type);
+        if (a_scalar) return -2;
+        { vector_type<bool> r(n); aqop_gt(va, vb, r); return vec_emit(r, out, out_type); }
+#define AQ_FN(CODE, NAME)                                                                               \
+    case CODE: {                                                                                        \
+        if (a_scalar || b_scalar) return -2;                      /* aqop_x takes two vectors */        \
+        vector_type<bool> r(n);                                                                         \
+        aqop_##NAME(va, vb, r);                                                                         \
+        return vec_emit(r, out, out_type); }
+    AQ_FN(AQO_V_LT, lt) AQ_FN(AQO_V_GTE, gte) AQ_FN(AQO_V_LTE, lte) AQ_FN(AQO_V_EQ, eq) AQ_FN(AQO_V_NEQ, neq)
+#undef AQ_FN
+    default: return -2;
+    }
+}
+template <class A>
+int vec_binary_a(int op, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n, void* out, int* out_type) {
+    switch (tb) {
+    case AQO_INT32:  return vec_binary_t<A, int>(op, a, a_scalar, b, b_scalar, n, out, out_type);
+    case AQO_INT64:  return vec_binary_t<A, long>(op, a, a_scalar, b, b_scalar, n, out, out_type);
+    case AQO_FLOAT:  return vec_binary_t<A, float>(op, a, a_scalar, b, b_scalar, n, out, out_type);
+    case AQO_DOUBLE: return vec_binary_t<A, double>(op, a, a_scalar, b, b_scalar, n, out, out_type);
+    default: return -2;
+    }
+}
+
 #define DISPATCH_VTYPE(vtype, CALL)                 \
     switch (vtype) {                                \
     case AQO_INT32:  return CALL(int);              \
@@ -282,6 +336,13 @@ int aqo_groupby(const void* const* keys, const int* key_types, int nkeys, uint32
     if (key_types[0] == AQO_INT32) return groupby_k<int>(nkeys, keys, nrows, ngroups, gid, offsets, perm);
     if (key_types[0] == AQO_INT64) return groupby_k<long>(nkeys, keys, nrows, ngroups, gid, offsets, perm);
     return -2;
+}
+
+int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n,
+                   void* out, int* out_type) {
+#define CALL(T) vec_binary_a<T>(op, a, a_scalar, tb, b, b_scalar, n, out, out_type)
+    DISPATCH_VTYPE(ta, CALL)
+#undef CALL
 }
 
 int aqo_reduce_out_type(int op, int vtype) {

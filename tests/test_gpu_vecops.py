@@ -1,0 +1,128 @@
+"""Element-wise vector arithmetic / compare (include/aqgpu.h aqgpu_vec_binary) against the reference's
+own operators (server/vector_type.hpp:372-396, server/table.h:826-973) compiled into oracle/_ref, cell for cell and type
+for type: bit-exact, floating point included (one IEEE operation per cell, the same on both sides).  Forms the reference
+cannot evaluate (its `vector < scalar` evaluates `>`) are checked against the C++ semantics restated in numpy."""
+import itertools
+
+import numpy as np
+import pytest
+
+from util import assert_same
+
+DT = {"i32": np.int32, "i64": np.int64, "f32": np.float32, "f64": np.float64}
+
+
+def operands(rng, dt, n):
+    if np.dtype(dt).kind == "i":
+        v = rng.integers(-2000, 2000, n).astype(dt)
+        v[v == 0] = 7                                   # integer division by zero traps in the reference
+        if dt == np.int64:
+            v[::5] *= 3_000_000_007                     # beyond 32 bits, beyond the 24-bit float mantissa
+        return v
+    v = (rng.standard_normal(n) * 1000).astype(dt)
+    v[::7] = np.round(v[::7])
+    return v
+
+
+@pytest.fixture(scope="module")
+def refop(ref):
+    return ref
+
+
+def test_result_types_follow_the_reference_templates(refop):
+    """aqgpu_vec_out_type (host code, no device needed) == the element type the reference's templates deduce"""
+    from aquery2_b200 import aqgpu as aq
+    rng = np.random.default_rng(0)
+    for (na, ta), (nb, tb) in itertools.product(DT.items(), DT.items()):
+        a, b = operands(rng, ta, 8), operands(rng, tb, 8)
+        for op in (aq.V_ADD, aq.V_SUB, aq.V_MUL, aq.V_DIV, aq.V_GT):
+            forms = [(a, b), (a, b[0])] + ([(a[0], b)] if op != aq.V_GT else [])
+            for x, y in forms:
+                _, code = refop.vec_binary(op, x, y)
+                assert aq.vec_out_type(op, x, y) == code, (op, na, nb, np.ndim(x), np.ndim(y))
+        for op in (aq.V_LT, aq.V_GTE, aq.V_LTE, aq.V_EQ, aq.V_NEQ):
+            assert aq.vec_out_type(op, a, b) == refop.vec_binary(op, a, b)[1] == aq.BOOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("na,nb", list(itertools.product(DT, DT)))
+def test_cells_equal_the_reference_operators(gpu, refop, na, nb):
+    rng = np.random.default_rng(len(na) * 7 + len(nb))
+    n = 20_011
+    a, b = operands(rng, DT[na], n), operands(rng, DT[nb], n)
+    b[::3] = a[::3].astype(DT[nb])                      # equal cells for == / != / >=
+    for op in (gpu.V_ADD, gpu.V_SUB, gpu.V_MUL, gpu.V_DIV, gpu.V_GT):
+        forms = [(a, b), (a, b[1])] + ([(a[1], b)] if op != gpu.V_GT else [])
+        for x, y in forms:
+            want, code = refop.vec_binary(op, x, y)
+            got = gpu.vec_binary(op, x, y)
+            assert got.dtype == want.dtype, (op, na, nb, got.dtype, want.dtype, code)
+            assert got.tobytes() == want.tobytes(), f"op {op} {na} {nb} forms {np.ndim(x)} {np.ndim(y)}: " \
+                f"first difference at {np.flatnonzero((got != want).reshape(len(got), -1).any(axis=1))[:5]}"
+    for op in (gpu.V_LT, gpu.V_GTE, gpu.V_LTE, gpu.V_EQ, gpu.V_NEQ):
+        want, _ = refop.vec_binary(op, a, b)            # aqop_lt ... (table.h:949-973)
+        assert_same(gpu.vec_binary(op, a, b), want, f"aqop {op} {na} {nb}")
+
+
+@pytest.mark.gpu
+def test_comparisons_with_a_scalar_mean_what_they_say(gpu):
+    """waived quirk: the reference evaluates `>` for every `vector OP scalar` comparison (vector_type.hpp:372-385)"""
+    rng = np.random.default_rng(3)
+    a = operands(rng, np.int32, 5000)
+    f = operands(rng, np.float64, 5000)
+    import operator as o
+    for op, fn in ((gpu.V_GT, o.gt), (gpu.V_LT, o.lt), (gpu.V_GTE, o.ge), (gpu.V_LTE, o.le), (gpu.V_EQ, o.eq), (gpu.V_NEQ, o.ne)):
+        assert_same(gpu.vec_binary(op, a, np.int32(120)), fn(a, 120).astype(np.uint8), f"int32 op {op} 120")
+        assert_same(gpu.vec_binary(op, f, np.float64(a[3])), fn(f, float(a[3])).astype(np.uint8), f"f64 op {op}")
+        assert_same(gpu.vec_binary(op, np.int64(5), a), fn(5, a).astype(np.uint8), f"5 op {op} int32")
+
+
+@pytest.mark.gpu
+def test_explicit_result_types_bitwise_and_bool_operands(gpu):
+    rng = np.random.default_rng(4)
+    n = 10_000
+    a, b = operands(rng, np.int32, n), operands(rng, np.int32, n)
+    # aqop_x(lhs, rhs, ret): the caller's Ret decides the cell type (table.h:949-973)
+    assert_same(gpu.vec_binary(gpu.V_GT, a, b, out_type=gpu.INT32), (a > b).astype(np.int32), "gt -> int32")
+    assert_same(gpu.vec_binary(gpu.V_ADD, a, b, out_type=gpu.INT64), (a + b).astype(np.int64), "add -> int64")
+    assert_same(gpu.vec_binary(gpu.V_MUL, a, b, out_type=gpu.DOUBLE), (a * b).astype(np.float64), "mul -> f64")
+    assert_same(gpu.vec_binary(gpu.V_AND, a, b), a & b, "and"); assert_same(gpu.vec_binary(gpu.V_OR, a, b), a | b, "or")
+    assert_same(gpu.vec_binary(gpu.V_XOR, a, b.astype(np.int64)), a ^ b.astype(np.int64), "xor")
+    p, q = a > 0, b > 0                                   # bool cells promote to int like C++
+    assert_same(gpu.vec_binary(gpu.V_AND, p, q, out_type=gpu.BOOL), (p & q).astype(np.uint8), "bool and")
+    assert_same(gpu.vec_binary(gpu.V_ADD, p, np.int32(0), out_type=gpu.INT32), p.astype(np.int32), "bool -> int32")
+    # int32 wraps, integer division truncates toward zero, x / 0 = 0 here, INT_MIN / -1 wraps
+    big = np.array([2**31 - 1, -2**31, 7, -7, 5], np.int32)
+    d = np.array([1, -1, 2, 2, 0], np.int32)
+    assert_same(gpu.vec_binary(gpu.V_ADD, big, np.int32(1)), np.array([-2**31, -2**31 + 1, 8, -6, 6], np.int32), "wrap")
+    assert_same(gpu.vec_binary(gpu.V_DIV, big, d), np.array([2**31 - 1, -2**31, 3, -3, 0], np.int32), "int division")
+    # errors
+    import ctypes
+    L = gpu.lib()
+    f = np.zeros(4, np.float32)
+    assert L.aqgpu_vec_binary(gpu.V_AND, gpu.FLOAT, f.ctypes.data, 0, gpu.FLOAT, f.ctypes.data, 0, -1, f.ctypes.data, 4) != 0
+    assert L.aqgpu_vec_binary(99, gpu.FLOAT, f.ctypes.data, 0, gpu.FLOAT, f.ctypes.data, 0, -1, f.ctypes.data, 4) != 0
+    assert L.aqgpu_vec_binary(gpu.V_ADD, gpu.FLOAT, f.ctypes.data, 1, gpu.FLOAT, f.ctypes.data, 1, -1, f.ctypes.data, 4) != 0
+
+
+@pytest.mark.gpu
+def test_network_a_session_key(gpu, port):
+    """tests/network.a:8-11: GROUP BY src, dst, sums(deltas(_time) > 120) -- string keys + a key computed by vector ops"""
+    import keydata
+    rng = np.random.default_rng(8)
+    n = 60_000
+    src, dst = keydata.strings(rng, n, 12), keydata.strings(rng, n, 9)
+    t = np.cumsum(rng.integers(1, 200, n)).astype(np.int32)
+    ln = rng.integers(40, 1500, n).astype(np.int32)
+    one = gpu.Groups([np.zeros(n, np.uint32)], row_order=gpu.ROWS_ASC)           # non-grouped deltas: the table is one group
+    deltas = one.scan("deltas", t)
+    gap = gpu.vec_binary(gpu.V_GT, deltas, np.int32(120), out_type=gpu.INT32)     # aqop_gt(deltas, 120, ret<int>)
+    sess = gpu.i128_to_int64(one.scan("sums", gap))
+    want_sess = np.cumsum(np.diff(t, prepend=t[0]) > 120).astype(np.int64)
+    assert_same(sess, want_sess, "sums(deltas(_time) > 120)")
+    cs, _ = gpu.string_dict(*src.packed()); cd, _ = gpu.string_dict(*dst.packed())
+    res = gpu.groupby_agg([cs, cd, sess], [("count",), ("avg", ln)])
+    ng, gid, off, perm = port.groupby([src, dst, want_sess])
+    assert res.ngroups == ng
+    assert_same(res.first_row, perm[off[1:] - 1].astype(np.uint32), "first rows")
+    assert_same(res.aggs[1], port.reduce("avg", ln, off, perm), "avg(len)")

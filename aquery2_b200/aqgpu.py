@@ -52,7 +52,7 @@ EXPORTS = [
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
     "aqgpu_partition_counts_noalloc", "aqgpu_key_cell_size", "aqgpu_key_split", "aqgpu_key_join", "aqgpu_string_dict",
-    "aqgpu_vec_out_type", "aqgpu_vec_binary",
+    "aqgpu_vec_out_type", "aqgpu_vec_binary", "aqgpu_take",
 ]
 
 
@@ -779,4 +779,13 @@ def vec_binary(op: int, a, b, out_type: int = -1) -> np.ndarray:
     out = np.zeros((n, 2), np.int64) if ot == INT128 else np.zeros(n, _VEC_NP[ot])
     check(lib().aqgpu_vec_binary(op, ta, a.ctypes.data_as(ctypes.c_void_p), sa, tb, b.ctypes.data_as(ctypes.c_void_p), sb,
                                  ot, out.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(n)))
+    return out
+
+
+def take(col: np.ndarray, idx: np.ndarray) -> np.ndarray:
+    """out[j] = col[idx[j]] (aqgpu_take); col: any 1/2/4/8/12/16-byte cells"""
+    col, idx = np.ascontiguousarray(col), np.ascontiguousarray(idx, np.uint32)
+    out = np.zeros(len(idx), col.dtype)
+    check(lib().aqgpu_take(col.dtype.itemsize, col.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(len(col)),
+                           idx.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(len(idx)), out.ctypes.data_as(ctypes.c_void_p)))
     return out

@@ -115,6 +115,18 @@ __global__ void __launch_bounds__(256) k_vec_binary(const VecArgs A) {
     }
 }
 
+// out[j] = col[idx[j]] for cells of 1, 2, 4, 8, 12 or 16 bytes; an index beyond the column raises the flag (cell left zero)
+template <class T>
+__global__ void __launch_bounds__(256)
+k_take(const T* __restrict__ col, const uint32_t rows, const uint32_t* __restrict__ idx, const uint32_t n, T* __restrict__ out, uint32_t* __restrict__ bad) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        const uint32_t i = idx[j];
+        if (i < rows) out[j] = col[i];
+        else { out[j] = T{}; atomicExch(bad, 1u); }
+    }
+}
+struct Cell12 { uint32_t w[3]; };
+
 // 0 int32, 1 int64, 2 float, 3 double
 inline int vec_rank(int t) { return t == AQ_INT32 || t == AQ_BOOL ? 0 : t == AQ_INT64 ? 1 : t == AQ_FLOAT ? 2 : t == AQ_DOUBLE ? 3 : -1; }
 inline int vec_compute_rank(int ra, int rb) {            // usual arithmetic conversions
@@ -191,5 +203,37 @@ extern "C" int aqgpu_vec_binary(int op, int a_type, const void* a, int a_scalar,
     }
     AQ_TRY(oc.finish(osz * n));
     if (oc.host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+
+extern "C" int aqgpu_take(int elem_bytes, const void* col, uint32_t col_rows, const uint32_t* idx, uint32_t nidx, void* out) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8 && elem_bytes != 12 && elem_bytes != 16)
+        return fail("take: %d-byte cells (1, 2, 4, 8, 12 or 16)", elem_bytes);
+    if (nidx == 0) return 0;
+    if (!idx || !out || (col_rows && !col)) return fail("take: null argument");
+    if (col_rows == 0) return fail("take: %u indices into an empty column", nidx);
+    InCol ic, ii; OutCol oc;
+    AQ_TRY(ic.bind(col, size_t(elem_bytes) * col_rows));
+    AQ_TRY(ii.bind(idx, size_t(nidx) * 4));
+    AQ_TRY(oc.bind(out, size_t(elem_bytes) * nidx));
+    DevBuf bad;
+    AQ_TRY(bad.alloc_zero(16));
+    const int grid = grid_for(nidx, 256, 1, 16);
+    const uint32_t* di = static_cast<const uint32_t*>(ii.d);
+    switch (elem_bytes) {
+    case 1: AQ_LAUNCH(k_take<unsigned char>, grid, 256, 0, static_cast<const unsigned char*>(ic.d), col_rows, di, nidx, static_cast<unsigned char*>(oc.d), bad.as<uint32_t>()); break;
+    case 2: AQ_LAUNCH(k_take<unsigned short>, grid, 256, 0, static_cast<const unsigned short*>(ic.d), col_rows, di, nidx, static_cast<unsigned short*>(oc.d), bad.as<uint32_t>()); break;
+    case 4: AQ_LAUNCH(k_take<uint32_t>, grid, 256, 0, static_cast<const uint32_t*>(ic.d), col_rows, di, nidx, static_cast<uint32_t*>(oc.d), bad.as<uint32_t>()); break;
+    case 8: AQ_LAUNCH(k_take<unsigned long long>, grid, 256, 0, static_cast<const unsigned long long*>(ic.d), col_rows, di, nidx, static_cast<unsigned long long*>(oc.d), bad.as<uint32_t>()); break;
+    case 12: AQ_LAUNCH(k_take<Cell12>, grid, 256, 0, static_cast<const Cell12*>(ic.d), col_rows, di, nidx, static_cast<Cell12*>(oc.d), bad.as<uint32_t>()); break;
+    default: AQ_LAUNCH(k_take<uint4>, grid, 256, 0, static_cast<const uint4*>(ic.d), col_rows, di, nidx, static_cast<uint4*>(oc.d), bad.as<uint32_t>()); break;
+    }
+    uint32_t flag = 0;
+    AQ_CUDA(cudaMemcpyAsync(&flag, bad.p, 4, cudaMemcpyDeviceToHost, ctx().stream));
+    AQ_TRY(oc.finish(size_t(elem_bytes) * nidx));
+    AQ_CUDA(cudaStreamSynchronize(ctx().stream));
+    if (flag) return fail("take: an index is beyond the column's %u rows", col_rows);
     return 0;
 }

@@ -280,6 +280,17 @@ public:
         d.container = static_cast<_Ty*>(p); d.size = this->size; d.capacity = this->size ? this->size : 1; d.name = name;
         return d;
     }
+    // gather by an explicit index vector (table.h:184-189): out[j] = col[idx[j]], on the device; the result lives where the column lives
+    ColRef<_Ty> operator[](const vector_type<uint32_t>& idx) const {
+        ColRef<_Ty> out;
+        if (this->on_device()) {
+            void* p = nullptr;
+            aq::check(aqgpu_col_alloc(sizeof(_Ty) * (idx.size ? idx.size : 1), &p));
+            out.container = static_cast<_Ty*>(p); out.size = idx.size; out.capacity = idx.size ? idx.size : 1;
+        } else out = ColRef<_Ty>(idx.size);
+        if (idx.size) aq::check(aqgpu_take((int)sizeof(_Ty), this->container, this->size, idx.container, idx.size, out.container));
+        return out;
+    }
     // gather col[vecs[g]] (table.h:184-189): a proxy, evaluated by the aggregate that consumes it
     aq::GroupVec<_Ty> operator[](const aq::GroupRows& rows) const;
     template <class G, class = decltype(std::declval<const G&>().handle)> aq::GroupedCol<_Ty> operator[](const G& groups) const;
@@ -309,7 +320,29 @@ template <class... Types> struct TableInfo {
         print_impl(sep, end, limit, std::index_sequence_for<Types...>());
     }
     void printall(const char* sep = ",", const char* end = "\n", const char* = nullptr, FILE* = nullptr, uint32_t limit = 0xffffffffu) { print(sep, end, limit); }
+    // in-place gather of every column by row ids (table.h:429-440); materialize_copy leaves this table alone (:441-445)
+    void materialize(const vector_type<uint32_t>& idxs, TableInfo<Types...>* tbl = nullptr) {
+        if (!tbl) tbl = this;
+        materialize_impl(idxs, tbl, std::index_sequence_for<Types...>());
+    }
+    TableInfo<Types...>* materialize_copy(const vector_type<uint32_t>& idxs) {
+        auto tbl = new TableInfo<Types...>(name, nullptr);
+        for (uint32_t i = 0; i < n_cols; ++i) tbl->colrefs[i].name = colrefs[i].name;
+        materialize(idxs, tbl);
+        return tbl;
+    }
+    // row ids sorted by columns (table.h:446-461): cols >= 0 ascending by that column, cols < 0 descending by column -1 - cols;
+    // `ord` (e.g. one group's row list, common/groupby.py:58) is sorted in place.  The reference uses std::sort, which leaves the
+    // order of ties unspecified; here ties keep their current order (a stable sort: one of the orders the reference may produce).
+    template <int... cols> vector_type<uint32_t>* order_by(vector_type<uint32_t>* ord = nullptr);
+    // the distinct records (table.h:601-614).  The reference iterates an std::unordered_set (unspecified order); here the records
+    // come in first-appearance order.
+    TableInfo<Types...>* distinct();
 private:
+    template <size_t... I> void distinct_impl(std::index_sequence<I...>);
+    template <size_t... I> void materialize_impl(const vector_type<uint32_t>& idxs, TableInfo<Types...>* tbl, std::index_sequence<I...>) {
+        (void)std::initializer_list<int>{ (tbl->template get_col<(int)I>() = get_col<(int)I>()[idxs], 0)... };
+    }
     template <size_t... I> void init_cols(const char** names, std::index_sequence<I...>) { ((get_col<(int)I>().init(names ? names[I] : "")), ...); }
     template <class C> static void print_one(const std::vector<C>& h, uint32_t r) {
         if constexpr (is_vector_type_impl<C>::value) h[r].out(8);
@@ -528,6 +561,54 @@ template <class... Ts> Groups<Ts...> group_by(const ColRef<Ts>&... cols) {
 
 template <class _Ty> aq::GroupVec<_Ty> ColRef<_Ty>::operator[](const aq::GroupRows& r) const { return aq::GroupVec<_Ty>{this->container, r.g, r.gid, r.size}; }
 template <class _Ty> template <class G, class> aq::GroupedCol<_Ty> ColRef<_Ty>::operator[](const G& g) const { return aq::GroupedCol<_Ty>{this->container, this->size, g.handle}; }
+
+// ---- TableInfo::order_by / distinct (server/table.h:446-461, 601-614) on the device --------------------------------------
+template <class... Types> template <int... cols>
+vector_type<uint32_t>* TableInfo<Types...>::order_by(vector_type<uint32_t>* ord) {
+    constexpr int nc = sizeof...(cols);
+    static_assert(nc >= 1, "order_by needs at least one column");
+    const uint32_t rows = n_cols ? colrefs[0].size : 0;
+    const bool subset = ord != nullptr;
+    const uint32_t m = subset ? ord->size : rows;
+    if (!ord) ord = new vector_type<uint32_t>(rows);
+    if (m == 0) return ord;
+    // the sort columns, restricted to the rows of `ord` when a row list is given
+    const void* cp[nc]; int ct[nc]; const int desc[nc] = { (cols < 0 ? 1 : 0)... };
+    std::vector<std::shared_ptr<void>> keep;
+    int k = 0;
+    auto bind = [&](auto& col) {
+        typedef typename std::decay_t<decltype(col)>::value_t C;
+        static_assert(aq::dtype_of<C>() >= 0, "order_by: integer / float columns");
+        ct[k] = aq::dtype_of<C>();
+        if (subset) {
+            auto tmp = std::make_shared<ColRef<C>>(col[*ord]);
+            cp[k] = tmp->container; keep.push_back(tmp);
+        } else cp[k] = col.container;
+        ++k;
+    };
+    (void)std::initializer_list<int>{ (bind(get_col<(cols >= 0 ? cols : -1 - cols)>()), 0)... };
+    // one group holding every row in table order, its row list re-ordered by the segmented radix sort
+    std::vector<uint32_t> zero(m, 0u);
+    const void* kp[1] = { zero.data() }; const int kt[1] = { AQ_UINT32 }; const int64_t lo[1] = {0}, hi[1] = {0};
+    aqgpu_groups_t* h = nullptr;
+    aq::check(aqgpu_groupby_build(kp, kt, 1, m, lo, hi, AQ_ROWS_ASC, 1, &h));
+    std::shared_ptr<void> guard(h, [](void* x) { aqgpu_groups_free(static_cast<aqgpu_groups_t*>(x)); });
+    aq::check(aqgpu_groups_order_by(h, cp, ct, desc, nc));
+    std::vector<uint32_t> perm(m), off(2);
+    aq::check(aqgpu_groups_csr(h, off.data(), perm.data()));
+    if (subset) { std::vector<uint32_t> old(ord->container, ord->container + m); for (uint32_t j = 0; j < m; ++j) ord->container[j] = old[perm[j]]; }
+    else std::copy(perm.begin(), perm.end(), ord->container);
+    return ord;
+}
+template <class... Types> template <size_t... I> void TableInfo<Types...>::distinct_impl(std::index_sequence<I...>) {
+    auto g = aq::group_by(get_col<(int)I>()...);
+    auto keys = std::make_tuple(g.template key<(int)I>()...);              // fetched before any column is replaced
+    (void)std::initializer_list<int>{ (get_col<(int)I>() = std::move(std::get<I>(keys)), 0)... };
+}
+template <class... Types> TableInfo<Types...>* TableInfo<Types...>::distinct() {
+    if (n_cols && colrefs[0].size) distinct_impl(std::index_sequence_for<Types...>());
+    return this;
+}
 
 // ---- HashTableComponents / HashTableFactory / AQHashTable (server/hasher.h:146-357) --------------------------------
 template <class... Ty> struct HashTableComponents {

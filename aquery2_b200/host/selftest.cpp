@@ -10,6 +10,7 @@
 #include "./server/hasher.h"
 #include "./server/monetdb_conn.h"
 #include "./server/aggregations.h"
+#include <algorithm>
 #include <cassert>
 #include <map>
 
@@ -320,6 +321,34 @@ int main() {
             EXPECT(s6[i] == (v3[i] >= 50.f));
             EXPECT(r8[i] == (v1[i] < tm[i] ? 1 : 0));
         }
+    }
+    {   // TableInfo::order_by / materialize / distinct (table.h:429-461, 601-614) and the gather col[idx] (table.h:184-189)
+        const char* names[] = {"id1", "id2", "v3"};
+        TableInfo<int, int, float> t("t", names);
+        t.get_col<0>().init_from(n, id1.data()); t.get_col<1>().init_from(n, id2.data()); t.get_col<2>().init_from(n, v3.data());
+        auto* ord = t.order_by<0, -2>();                                   // ASC id1, DESC id2; ties keep table order
+        std::vector<uint32_t> want(n);
+        for (uint32_t i = 0; i < n; ++i) want[i] = i;
+        std::stable_sort(want.begin(), want.end(), [&](uint32_t a, uint32_t b) { return std::make_tuple(id1[a], -id2[a]) < std::make_tuple(id1[b], -id2[b]); });
+        EXPECT(ord->size == n);
+        for (uint32_t i = 0; i < n && fails < 5; ++i) EXPECT((*ord)[i] == want[i]);
+        vector_type<uint32_t> part(1000);                                  // a row list (one group's rows): sorted in place
+        for (uint32_t i = 0; i < 1000; ++i) part[i] = (uint32_t)((i * 7919u) % n);
+        std::vector<uint32_t> pw(part.container, part.container + 1000);
+        std::stable_sort(pw.begin(), pw.end(), [&](uint32_t a, uint32_t b) { return v3[a] > v3[b]; });
+        t.order_by<-3>(&part);                                             // DESC v3
+        for (uint32_t i = 0; i < 1000 && fails < 5; ++i) EXPECT(part[i] == pw[i]);
+        auto* sorted = t.materialize_copy(*ord);
+        EXPECT(sorted->get_col<0>().size == n);
+        for (uint32_t i = 0; i < n && fails < 5; ++i) { EXPECT(sorted->get_col<0>()[i] == id1[want[i]]); EXPECT(sorted->get_col<2>()[i] == v3[want[i]]); }
+        TableInfo<int, int> d("d", names);
+        d.get_col<0>().init_from(n, id1.data()); d.get_col<1>().init_from(n, id2.data());
+        d.distinct();
+        std::vector<std::pair<int, int>> seen; std::map<std::pair<int, int>, int> have;
+        for (uint32_t i = 0; i < n; ++i) { auto k = std::make_pair(id1[i], id2[i]); if (!have.count(k)) { have[k] = 1; seen.push_back(k); } }
+        EXPECT(d.get_col<0>().size == seen.size() && d.get_col<1>().size == seen.size());
+        for (size_t i = 0; i < seen.size() && fails < 5; ++i) EXPECT(d.get_col<0>()[i] == seen[i].first && d.get_col<1>()[i] == seen[i].second);
+        delete ord;
     }
     printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
     return fails ? 1 : 0;

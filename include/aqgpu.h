@@ -296,6 +296,10 @@ int aqgpu_group_window_ordered(aqgpu_groups_t* g, const void* order_col, int ord
 /* out[offsets[g] + j] = v[row j of group g]  -- the gather col[vecs[g]] of server/table.h:184-189 for
  * ALL groups at once, in the CSR order of the row lists.  out has nrows cells of vtype. */
 int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out);
+/* out[j] = col[idx[j]], j < nidx: the gather ColRef<T>::operator[](vector_type<uint32_t>&) (server/table.h:184-189) and
+ * TableInfo::materialize (server/table.h:429-440) for an explicit index vector.  Cells of 1, 2, 4, 8, 12 or 16 bytes;
+ * an index >= col_rows fails the call (the reference reads out of bounds). */
+int aqgpu_take(int elem_bytes, const void* col, uint32_t col_rows, const uint32_t* idx, uint32_t nidx, void* out);
 /* ASSUMING-ordered evaluation for unsorted input (common/groupby.py:54-59 ->
  * TableInfo::order_by, server/table.h:447-461): re-orders every group's row list by the given
  * columns (desc[c] != 0 = descending), ties by the current order.  Integer / float keys. */

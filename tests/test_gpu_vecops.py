@@ -126,3 +126,21 @@ def test_network_a_session_key(gpu, port):
     assert res.ngroups == ng
     assert_same(res.first_row, perm[off[1:] - 1].astype(np.uint32), "first rows")
     assert_same(res.aggs[1], port.reduce("avg", ln, off, perm), "avg(len)")
+
+
+@pytest.mark.gpu
+def test_take_is_the_gather_of_table_h(gpu):
+    """out[j] = col[idx[j]] (server/table.h:184-189; TableInfo::materialize :429-440) for every cell width"""
+    import keydata
+    rng = np.random.default_rng(9)
+    n, m = 50_000, 80_000
+    idx = rng.integers(0, n, m).astype(np.uint32)
+    cols = [rng.integers(-9, 9, n).astype(np.int32), rng.standard_normal(n), rng.integers(0, 2, n).astype(np.uint8),
+            rng.integers(0, 1 << 15, n).astype(np.int16), keydata.timestamps(rng, n, 64), keydata.times(rng, n, 64),
+            rng.integers(-5, 5, (n, 2)).astype(np.int64).view([("lo", "<i8"), ("hi", "<i8")]).reshape(n)]
+    for c in cols:
+        got = gpu.take(c, idx)
+        assert got.tobytes() == c[idx].tobytes(), c.dtype
+    assert len(gpu.take(cols[0], np.zeros(0, np.uint32))) == 0
+    with pytest.raises(gpu.AqgpuError, match="beyond"):
+        gpu.take(cols[0], np.array([0, n], np.uint32))

@@ -53,6 +53,7 @@ EXPORTS = [
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
     "aqgpu_partition_counts_noalloc", "aqgpu_key_cell_size", "aqgpu_key_split", "aqgpu_key_join", "aqgpu_string_dict",
     "aqgpu_vec_out_type", "aqgpu_vec_binary", "aqgpu_take",
+    "aqgpu_ingest_async", "aqgpu_ingest_fence", "aqgpu_writeback_async", "aqgpu_writeback_fence", "aqgpu_writeback_wait",
 ]
 
 
@@ -789,3 +790,24 @@ def take(col: np.ndarray, idx: np.ndarray) -> np.ndarray:
     check(lib().aqgpu_take(col.dtype.itemsize, col.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(len(col)),
                            idx.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(len(idx)), out.ctypes.data_as(ctypes.c_void_p)))
     return out
+
+
+# ---- ingest / write-back on the copy streams (aqgpu_ingest_async ...) ------------------------------------------------------
+def ingest_async(dst: DeviceColumn, pinned_ptr: int, nbytes: int | None = None) -> None:
+    check(lib().aqgpu_ingest_async(ctypes.c_void_p(dst.ptr), ctypes.c_void_p(pinned_ptr), ctypes.c_size_t(dst.nbytes if nbytes is None else nbytes)))
+
+
+def ingest_fence() -> None:
+    check(lib().aqgpu_ingest_fence())
+
+
+def writeback_async(pinned_ptr: int, src_ptr: int, nbytes: int) -> None:
+    check(lib().aqgpu_writeback_async(ctypes.c_void_p(pinned_ptr), ctypes.c_void_p(src_ptr), ctypes.c_size_t(nbytes)))
+
+
+def writeback_fence() -> None:
+    check(lib().aqgpu_writeback_fence())
+
+
+def writeback_wait() -> None:
+    check(lib().aqgpu_writeback_wait())

@@ -422,6 +422,73 @@ int aqgpu_col_download_async(void* host, const void* dptr, size_t bytes) {
     return 0;
 }
 
+// ---- ingest / write-back on their own copy streams ------------------------------------------------
+// The reference hands the post-processor pointers into the data source's buffers (server/monetdb_conn.cpp:203-224, the 'C'
+// cache message server/server.cpp:552-583) and appends result tables back (server/table_ext_monetdb.hpp:35-86); here the two
+// directions of the host link run on dedicated streams, so that PCIe carries columns in and results out at the same time
+// while the library stream computes.  Ordering is by events, never by the host:
+//   ingest_async     the copy starts after everything ALREADY enqueued on the library stream (queries still reading the
+//                    column's previous contents) and runs on the ingest stream
+//   ingest_fence     work enqueued on the library stream from now on waits for every ingest enqueued so far
+//   writeback_async  the copy starts after everything already enqueued on the library stream (the query that produced the
+//                    column) and runs on the write-back stream
+//   writeback_fence  work enqueued on the library stream from now on waits for every write-back enqueued so far (call it
+//                    before a query overwrites result buffers whose write-back may still be in flight)
+//   writeback_wait   blocks the host until every write-back has landed in host memory
+static cudaStream_t g_ingest_stream = nullptr, g_writeback_stream = nullptr;
+static int copy_streams() {
+    if (!g_ingest_stream) AQ_CUDA(cudaStreamCreateWithFlags(&g_ingest_stream, cudaStreamNonBlocking));
+    if (!g_writeback_stream) AQ_CUDA(cudaStreamCreateWithFlags(&g_writeback_stream, cudaStreamNonBlocking));
+    return 0;
+}
+static int order_after(cudaStream_t waiter, cudaStream_t producer) {      // waiter's next work starts after producer's current tail
+    cudaEvent_t e;
+    AQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    cudaError_t rc = cudaEventRecord(e, producer);
+    if (rc == cudaSuccess) rc = cudaStreamWaitEvent(waiter, e, 0);
+    cudaEventDestroy(e);                                                  // released once the wait has been satisfied
+    AQ_CUDA(rc);
+    return 0;
+}
+// Measured on the B200 box (profiles/r02/e2e_pipeline_trace.txt): copies of ONE direction execute in submission order ACROSS
+// streams -- a query's 100-byte flag read-back enqueued on the library stream after a 36 GB write-back completes only when the
+// write-back does, whether the write-back is one copy or 16 MB pieces -- while the two directions do overlap (8 GiB each way:
+// 55 / 52 GB/s alone, 45 + 45 GB/s together, profiles/microbench/pcie_duplex.py).  So callers enqueue the big write-backs LAST
+// in a step (they then overlap the NEXT step's ingest), not first.
+int aqgpu_ingest_async(void* dptr, const void* pinned_host, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    if (!bytes) return 0;
+    if (!dptr || !pinned_host) return fail("ingest_async: null argument");
+    AQ_TRY(copy_streams());
+    AQ_TRY(order_after(g_ingest_stream, g_ctx.stream));
+    AQ_CUDA(cudaMemcpyAsync(dptr, pinned_host, bytes, cudaMemcpyHostToDevice, g_ingest_stream));
+    return 0;
+}
+int aqgpu_ingest_fence(void) {
+    AQ_REQUIRE_INIT();
+    AQ_TRY(copy_streams());
+    return order_after(g_ctx.stream, g_ingest_stream);
+}
+int aqgpu_writeback_async(void* pinned_host, const void* dptr, size_t bytes) {
+    AQ_REQUIRE_INIT();
+    if (!bytes) return 0;
+    if (!dptr || !pinned_host) return fail("writeback_async: null argument");
+    AQ_TRY(copy_streams());
+    AQ_TRY(order_after(g_writeback_stream, g_ctx.stream));
+    AQ_CUDA(cudaMemcpyAsync(pinned_host, dptr, bytes, cudaMemcpyDeviceToHost, g_writeback_stream));
+    return 0;
+}
+int aqgpu_writeback_fence(void) {
+    AQ_REQUIRE_INIT();
+    AQ_TRY(copy_streams());
+    return order_after(g_ctx.stream, g_writeback_stream);
+}
+int aqgpu_writeback_wait(void) {
+    AQ_REQUIRE_INIT();
+    if (g_writeback_stream) AQ_CUDA(cudaStreamSynchronize(g_writeback_stream));
+    return 0;
+}
+
 int aqgpu_trim_pool(void) {
     AQ_REQUIRE_INIT();
     if (g_arena.depth == 0 && g_arena.base && !g_vmm.ok) { cudaFreeAsync(g_arena.base, g_ctx.stream); g_arena.base = nullptr; g_arena.cap = 0; g_arena.off = 0; }

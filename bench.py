@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--k", type=int, default=100, help="h2o K (id1,id2,id4,id5 cardinality)")
     ap.add_argument("--nsym", type=float, default=1e6, help="trade: number of symbols (groups)")
     ap.add_argument("--queries", default="")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-verify", action="store_true")

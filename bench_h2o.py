@@ -77,8 +77,13 @@ def run_e2e(aq, args, table, runner, queries, n_total) -> dict:
     the reference, server/monetdb_conn.cpp:203-224); a step ingests it into the HBM column store
     (the 'C' cache message, server/server.cpp:552-583: one H2D copy per column), runs the queries on the
     store and writes every result column back to pinned host memory.  H2D and D2H are inside the timed
-    region."""
+    region.  Default: the copy-stream pipeline (aqgpu_ingest_async / aqgpu_writeback_async): a query starts as soon
+    as ITS columns have arrived, its results leave while later columns arrive and later queries run; the query with
+    the largest result (q10, G ~ N) goes last, so that its write-back overlaps the next step's ingest.  AQ_E2E_SERIAL=1: one synchronous copy after the other."""
+    import os
+    from aquery2_b200.h2o import columns_of
     L = aq.lib()
+    serial = os.environ.get("AQ_E2E_SERIAL") == "1"
     pinned, host = [], {}
     for c, d in table.items():
         pa = aq.PinnedArray(d.n, d.code)
@@ -87,42 +92,98 @@ def run_e2e(aq, args, table, runner, queries, n_total) -> dict:
         pinned.append(pa)
         host[c] = pa
     res_host = {}
+    # Copies of one direction execute in submission order across streams (measured, profiles/r02/e2e_pipeline_trace.txt): with
+    # q10 (36 GB of results) first, q1's 100-byte flag read-back waited 645 ms behind q10's write-back.  So the query with the
+    # largest result goes LAST: its write-back overlaps the NEXT step's ingest (the two directions do overlap, 45 + 45 GB/s).
+    order = list(queries) if serial else sorted(queries, key=lambda q: 1 if q == "q10" else 0)
+    need = {q: [c for c in columns_of([q]) if c in table] for q in queries}
+
+    def result_buffer(q, i, col, ng):
+        nb = ng * col.itemsize
+        key = (q, i)
+        if key not in res_host or res_host[key].n * res_host[key].itemsize < nb:
+            if key in res_host:
+                aq.writeback_wait()
+                res_host[key].free()
+            res_host[key] = aq.PinnedArray(max(ng, 1), col.code)
+            res_host[key].itemsize = col.itemsize
+            pinned.append(res_host[key])
+        return res_host[key], nb
+
+    trace = os.environ.get("AQ_E2E_TRACE") == "1"
+    t_step = [0.0]
+
+    def mark(what):
+        if trace:
+            import sys
+            print(f"[e2e trace] +{(time.perf_counter() - t_step[0]) * 1e3:8.1f} ms host: {what}", file=sys.stderr, flush=True)
 
     def one_step():
         bo = 0
-        for c, d in table.items():                 # ingest
-            aq.check(L.aqgpu_col_upload(ctypes.c_void_p(d.ptr), ctypes.c_void_p(host[c].ptr), ctypes.c_size_t(d.nbytes)))
         ngs = {}
-        for q in queries:
+        t_step[0] = time.perf_counter()
+        if serial:
+            for c, d in table.items():                 # ingest
+                aq.check(L.aqgpu_col_upload(ctypes.c_void_p(d.ptr), ctypes.c_void_p(host[c].ptr), ctypes.c_size_t(d.nbytes)))
+        arrived = set()
+        for qi, q in enumerate(order):
+            if not serial:
+                for c in need[q]:
+                    if c not in arrived:               # H2D on the ingest stream, after the queries already enqueued
+                        aq.ingest_async(table[c], host[c].ptr)
+                        arrived.add(c)
+                if qi == 0:
+                    aq.writeback_fence()               # the previous step's results have left before they are overwritten
+                aq.ingest_fence()                      # this query waits for the columns ingested so far
+            mark(f"{q}: columns and fences enqueued")
             ng = ngs[q] = runner.run(q)
+            mark(f"{q}: done ({ng} groups)")
             for i, col in enumerate(runner.result_columns(q)):     # write-back
-                nb = ng * col.itemsize
-                key = (q, i)
-                if key not in res_host or res_host[key].n * res_host[key].itemsize < nb:
-                    if key in res_host:
-                        res_host[key].free()
-                    res_host[key] = aq.PinnedArray(max(ng, 1), col.code)
-                    res_host[key].itemsize = col.itemsize
-                    pinned.append(res_host[key])
-                if nb:
-                    aq.check(L.aqgpu_col_download(ctypes.c_void_p(res_host[key].ptr), ctypes.c_void_p(col.ptr), ctypes.c_size_t(nb)))
+                buf, nb = result_buffer(q, i, col, ng)
+                if nb and serial:
+                    aq.check(L.aqgpu_col_download(ctypes.c_void_p(buf.ptr), ctypes.c_void_p(col.ptr), ctypes.c_size_t(nb)))
+                elif nb:
+                    aq.writeback_async(buf.ptr, col.ptr, nb)       # D2H on the write-back stream, after the query
                 bo += nb
+            mark(f"{q}: write-back enqueued")
+        if not serial:
+            for c in table:                            # columns no query of this run reads still count as ingested
+                if c not in arrived:
+                    aq.ingest_async(table[c], host[c].ptr)
         return ngs, bo
 
     one_step()                                     # warm-up (also sizes the pinned result buffers)
+    aq.writeback_wait()
+    aq.ingest_fence()
     aq.sync()
     t0 = time.perf_counter()
     aq.timer_begin()
     for _ in range(args.e2e_steps):
         ngs, bo = one_step()
+    aq.writeback_fence()                           # the timer's end event waits for the last result to land ...
+    aq.ingest_fence()
     ms = aq.timer_end()
+    aq.writeback_wait()
     wall = time.perf_counter() - t0
+    # the results that arrived in host memory are the ones the HBM-resident run produced (spot check: first query's first column)
+    q0 = order[-1]
+    col0 = runner.result_columns(q0)[0]
+    import numpy as np
+    got = np.ctypeslib.as_array((ctypes.c_uint8 * (ngs[q0] * col0.itemsize)).from_address(res_host[(q0, 0)].ptr)).copy()
+    want = np.zeros(ngs[q0] * col0.itemsize, np.uint8)
+    if want.size:
+        aq.check(L.aqgpu_col_download(want.ctypes.data_as(ctypes.c_void_p), ctypes.c_void_p(col0.ptr), ctypes.c_size_t(want.size)))
+    landed = bool(np.array_equal(got, want))
     bi = sum(d.nbytes for d in table.values())
     out = {"value": len(queries) * n_total / (ms * 1e-3 / args.e2e_steps), "unit": "rows/s",
            "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo, "steps": args.e2e_steps,
            "ms_per_step": ms / args.e2e_steps, "wall_s_per_step": wall / args.e2e_steps,
-           "host_memory": "pinned (aqgpu_host_alloc)",
-           "path": "ingest every column once per step (H2D) -> queries on the HBM store -> every result column D2H"}
+           "host_memory": "pinned (aqgpu_host_alloc)", "results_landed": landed,
+           "path": ("ingest every column once per step (H2D) -> queries on the HBM store -> every result column D2H, one synchronous copy after the other"
+                    if serial else
+                    "per step: every column H2D on the ingest stream, each query starts when its columns have arrived (q10 last), every result "
+                    "column D2H on the write-back stream while later columns arrive and later queries run; consecutive steps overlap on the "
+                    "two copy streams (a step's ingest waits for the previous step's queries, its first query for the previous step's write-back)")}
     for pa in pinned:
         pa.free()
     return out

@@ -502,6 +502,16 @@ template <class T> struct GroupVec {       // col[vecs[i]]: the values of one gr
         g->fetch_offsets();
         return vector_type<T>(const_cast<T*>(g->gather_all(col)) + g->offsets[gid], size);
     }
+    // Host-visible cells for user code that walks a group itself (elemental-return UDFs, engine/ast.py:768-777,
+    // tests/udf3.a `x[i]`, `x(0, i)`): the gather col[vecs[g]] runs ONCE on the device for all groups (aqgpu_group_gather), the
+    // UDF body then reads its group's slice of the host copy.
+    mutable const T* host = nullptr;       // this group's slice of the gathered host copy, resolved on first use
+    const T* data() const { if (!host) { g->fetch_offsets(); host = g->gather_all(col) + g->offsets[gid]; } return host; }
+    const T& operator[](uint32_t i) const { return data()[i]; }
+    const T* begin() const { return data(); }
+    const T* end() const { return data() + size; }
+    vector_type<T> subvec(uint32_t start, uint32_t stop) const { return vector_type<T>(const_cast<T*>(data()) + start, stop - start); }   // vector_type.hpp:353-355
+    vector_type<T> operator()(uint32_t start, uint32_t stop) const { return subvec(start, stop); }
 };
 template <class T> struct GroupedCol {     // col[g]: a column seen through ALL groups (whole-column code)
     const T* col; uint32_t n; std::shared_ptr<GroupsHandle> handle;
@@ -561,6 +571,19 @@ template <class... Ts> Groups<Ts...> group_by(const ColRef<Ts>&... cols) {
 
 template <class _Ty> aq::GroupVec<_Ty> ColRef<_Ty>::operator[](const aq::GroupRows& r) const { return aq::GroupVec<_Ty>{this->container, r.g, r.gid, r.size}; }
 template <class _Ty> template <class G, class> aq::GroupedCol<_Ty> ColRef<_Ty>::operator[](const G& g) const { return aq::GroupedCol<_Ty>{this->container, this->size, g.handle}; }
+
+// ---- host-visible views for user modules ---------------------------------------------------------------
+// SDK modules take ColRef<T> / vector_type<T> BY VALUE and dereference `container` on the CPU (sdk/example.cpp:4,
+// sdk/aquery.h:105-128 ColRef_storage); a column of the HBM store is materialised to host memory at that call site only.
+namespace aq {
+template <class T> ColRef<T> host_view(const ColRef<T>& c) {
+    ColRef<T> h;
+    if (!c.on_device()) { h.init_from(c.size, c.container); h.name = c.name; return h; }       // already dereferenceable: a view
+    h = ColRef<T>(c.size, c.name);
+    if (c.size) check(aqgpu_col_download(h.container, c.container, sizeof(T) * c.size));
+    return h;
+}
+}  // namespace aq
 
 // ---- TableInfo::order_by / distinct (server/table.h:446-461, 601-614) on the device --------------------------------------
 template <class... Types> template <int... cols>

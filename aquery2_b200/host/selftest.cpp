@@ -350,6 +350,47 @@ int main() {
         for (size_t i = 0; i < seen.size() && fails < 5; ++i) EXPECT(d.get_col<0>()[i] == seen[i].first && d.get_col<1>()[i] == seen[i].second);
         delete ord;
     }
+    {   // N4: an elemental-return UDF in the emitter's shape (engine/ast.py:768-777; tests/udf3.a) applied per group, and a
+        // module function taking ColRef by value (sdk/example.cpp:4) fed from the HBM store
+        auto running_cov = [](auto x, auto y, auto win, auto _builtin_len, auto& _builtin_ret) {     // generic lambda as emitted
+            double xs = 0, ys = 0, xy = 0;
+            for (uint32_t i = 0; i < _builtin_len; ++i) {
+                xs += x[i]; ys += y[i]; xy += (double)x[i] * y[i];
+                if (i >= (uint32_t)win) { xs -= x[i - win]; ys -= y[i - win]; xy -= (double)x[i - win] * y[i - win]; }
+                const double m = i < (uint32_t)win ? i + 1 : win;
+                _builtin_ret[i] = xy / m - (xs / m) * (ys / m);
+            }
+            return 0;
+        };
+        ColRef<int> c_k(n, id2.data()), c_a(n, v1.data());
+        ColRef<float> c_b(n, v3.data());
+        auto g = HashTableFactory<record<int>, transTypes<record<int>, hasher>>::get(c_k);
+        std::vector<std::vector<double>> outs(g.size);
+        for (uint32_t i = 0; i < g.size; ++i) {
+            auto& val = g.values[i];
+            const uint32_t len = val.size;                       // _builtin_len (define_len_var)
+            outs[i].resize(len);
+            running_cov(c_a[val], c_b[val], 4, len, outs[i]);
+        }
+        std::map<int, std::vector<uint32_t>> rows2; std::vector<int> ord2;
+        for (uint32_t i = 0; i < n; ++i) { if (!rows2.count(id2[i])) ord2.push_back(id2[i]); rows2[id2[i]].push_back(i); }
+        EXPECT(g.size == ord2.size());
+        for (uint32_t gi = 0; gi < g.size && fails < 5; ++gi) {
+            std::vector<uint32_t> desc(rows2[ord2[gi]].rbegin(), rows2[ord2[gi]].rend());     // descending row order inside a group
+            EXPECT(outs[gi].size() == desc.size());
+            std::vector<int> xa; std::vector<float> ya;
+            for (uint32_t r : desc) { xa.push_back(v1[r]); ya.push_back(v3[r]); }
+            std::vector<double> want(desc.size());
+            running_cov(xa, ya, 4, (uint32_t)desc.size(), want);
+            for (size_t j = 0; j < desc.size() && fails < 5; j += 97) EXPECT(outs[gi][j] == want[j]);
+        }
+        auto dev = c_b.to_device();
+        auto mulvec = [](int a, ColRef<float> b) { double s = 0; for (uint32_t i = 0; i < b.size; ++i) s += a * b.container[i]; return s; };   // CPU dereference
+        double want = 0; for (uint32_t i = 0; i < n; ++i) want += 2 * v3[i];
+        EXPECT(dev.on_device());
+        EXPECT(mulvec(2, aq::host_view(dev)) == want);
+        EXPECT(mulvec(2, aq::host_view(c_b)) == want);
+    }
     printf(fails ? "selftest: %d FAILED\n" : "selftest ok (%d failures)\n", fails);
     return fails ? 1 : 0;
 }

@@ -110,5 +110,72 @@ def main():
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 
 
+VEC_DTYPES = {"i32": np.int32, "i64": np.int64, "f32": np.float32, "f64": np.float64}
+VEC_OPS = {"add": 0, "sub": 1, "mul": 2, "div": 3, "gt": 7, "lt": 8, "gte": 9, "lte": 10, "eq": 11, "neq": 12}
+
+
+def vec_operand(rng, dt, n):
+    if np.dtype(dt).kind == "i":
+        v = rng.integers(-2000, 2000, n).astype(dt)
+        v[v == 0] = 7                                   # integer division by zero traps in the reference
+        if dt == np.int64:
+            v[::5] *= 3_000_007                         # beyond 32 bits and beyond the float mantissa, products stay below 2^63
+        return v
+    v = (rng.standard_normal(n) * 1000).astype(dt)
+    v[::7] = np.round(v[::7])
+    return v
+
+
+def special_keys(seed=21, n=1500):
+    """the key columns of special_small.npz, rebuilt by the tests from the stored bytes"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import keydata
+    rng = np.random.default_rng(seed)
+    return {"str": keydata.strings(rng, n, 120, long_tail=True), "date": keydata.dates(rng, n, 900),
+            "time": keydata.times(rng, n, 64), "timestamp": keydata.timestamps(rng, n, 64),
+            "k2": rng.integers(0, 4, n).astype(np.int32)}
+
+
+def gen_special():
+    """string / date / time / timestamp keys through the reference's AQHashTable (server/hasher.h:97-132) and the reference's
+    element-wise operators (server/vector_type.hpp:372-396, server/table.h:826-973): inputs AND outputs stored"""
+    ref = aqo.load_ref()
+    if ref is None:
+        raise SystemExit("oracle/_ref/libaqref.so missing: make -C oracle ref (needs /root/reference)")
+    cols = special_keys()
+    data, off = cols["str"].packed()
+    out = {"strcol_bytes": data, "strcol_offsets": off, "k2": cols["k2"]}
+    for name in ("date", "time", "timestamp"):
+        out[f"{name}_cells"] = cols[name].view(np.uint8).reshape(len(cols[name]), -1)
+    for name, keys in (("str", [cols["str"]]), ("date", [cols["date"]]), ("time", [cols["time"]]), ("timestamp", [cols["timestamp"]]),
+                       ("str_k2", [cols["str"], cols["k2"]])):
+        ng, gid, offs, perm = ref.groupby(keys)
+        out[f"{name}_ngroups"] = ng; out[f"{name}_gid"] = gid; out[f"{name}_offsets"] = offs; out[f"{name}_perm"] = perm
+    rng = np.random.default_rng(22)
+    n = 257
+    ops = {}
+    for na, ta in VEC_DTYPES.items():
+        out[f"vec_a_{na}"] = vec_operand(rng, ta, n)
+        out[f"vec_b_{na}"] = vec_operand(rng, ta, n)
+    for (na, ta), (nb, tb) in [(x, y) for x in VEC_DTYPES.items() for y in VEC_DTYPES.items()]:
+        a, b = out[f"vec_a_{na}"], out[f"vec_b_{nb}"]
+        for opn, op in VEC_OPS.items():
+            forms = {"vv": (a, b)}
+            if op <= 3 or op == 7:
+                forms["vs"] = (a, b[1])
+            if op <= 3:
+                forms["sv"] = (a[1], b)
+            for fn, (x, y) in forms.items():
+                cells, code = ref.vec_binary(op, x, y)
+                out[f"vec_{opn}_{na}_{nb}_{fn}"] = np.ascontiguousarray(cells).view(np.uint8).reshape(-1)
+                out[f"vect_{opn}_{na}_{nb}_{fn}"] = code
+    np.savez_compressed(os.path.join(GOLD, "special_small.npz"), **out)
+    print("special_small.npz", os.path.getsize(os.path.join(GOLD, "special_small.npz")))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "special":
+        gen_special()
+    else:
+        main()
+        gen_special()

@@ -46,3 +46,13 @@ def timestamps(rng, n, nd):
     ts["date"]["month"] = 7
     ts["time"] = times(rng, n, nd)
     return ts
+
+
+def from_golden(g):
+    """the key columns stored in tests/golden/special_small.npz (oracle/gen_golden.py gen_special)"""
+    data, off = g["strcol_bytes"], g["strcol_offsets"].astype(np.int64)
+    raw = data.tobytes()
+    cols = {"str": aqo.StrColumn([raw[off[i]:off[i + 1]] for i in range(len(off) - 1)]), "k2": g["k2"]}
+    for name, dt in (("date", aqo.DATE_DT), ("time", aqo.TIME_DT), ("timestamp", aqo.TIMESTAMP_DT)):
+        cols[name] = np.ascontiguousarray(g[f"{name}_cells"]).view(dt).reshape(-1)
+    return cols

@@ -118,3 +118,21 @@ def test_string_dict_errors(gpu):
     assert call([0, 2, 4, 6], 4) == 0 and nd.value == 3
     assert call([0, 0, 0, 0], 4) == 0 and nd.value == 1 and list(codes[:3]) == [0, 0, 0]    # three empty strings
     assert call([0], 4) == 0 and nd.value == 0                                              # no rows
+
+
+def test_special_keys_golden(gpu, golden):
+    """the GPU against the fixture the reference's own AQHashTable produced (tests/golden/special_small.npz)"""
+    g = golden("special_small.npz")
+    cols = keydata.from_golden(g)
+    codes, first = gpu.string_dict(*cols["str"].packed())
+    assert len(first) == int(g["str_ngroups"])
+    assert_same(codes, g["str_gid"], "string codes")
+    for name in ("date", "time", "timestamp"):
+        h = gpu.Groups(gpu.key_split(cols[name]))
+        o, p = h.csr()
+        assert h.ngroups == int(g[f"{name}_ngroups"]), name
+        assert_same(h.gid(), g[f"{name}_gid"], name); assert_same(o, g[f"{name}_offsets"], name); assert_same(p, g[f"{name}_perm"], name)
+    h = gpu.Groups([codes, cols["k2"]])
+    o, p = h.csr()
+    assert h.ngroups == int(g["str_k2_ngroups"])
+    assert_same(h.gid(), g["str_k2_gid"], "(str, int32)"); assert_same(o, g["str_k2_offsets"]); assert_same(p, g["str_k2_perm"])

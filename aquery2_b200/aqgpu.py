@@ -52,7 +52,7 @@ EXPORTS = [
     "aqgpu_comm_unique_id", "aqgpu_comm_init", "aqgpu_comm_destroy", "aqgpu_comm_size", "aqgpu_groupby_run_dist",
     "aqgpu_result_replicated", "aqgpu_group_median", "aqgpu_repartition_rows", "aqgpu_group_window_ordered",
     "aqgpu_partition_counts_noalloc", "aqgpu_key_cell_size", "aqgpu_key_split", "aqgpu_key_join", "aqgpu_string_dict",
-    "aqgpu_vec_out_type", "aqgpu_vec_binary", "aqgpu_take",
+    "aqgpu_vec_out_type", "aqgpu_vec_binary", "aqgpu_take", "aqgpu_vec_unary",
     "aqgpu_ingest_async", "aqgpu_ingest_fence", "aqgpu_writeback_async", "aqgpu_writeback_fence", "aqgpu_writeback_wait",
 ]
 
@@ -811,3 +811,15 @@ def writeback_fence() -> None:
 
 def writeback_wait() -> None:
     check(lib().aqgpu_writeback_wait())
+
+
+U_SQRT, U_TRUNCATE = 0, 1
+
+
+def vec_unary(op: int, x: np.ndarray, param: int = 0) -> np.ndarray:
+    """sqrt(x) (float64 cells) or truncate(x, param) (cells of x's type), aqgpu_vec_unary"""
+    x = np.ascontiguousarray(x)
+    out = np.zeros(len(x), np.float64 if op == U_SQRT else x.dtype)
+    check(lib().aqgpu_vec_unary(op, NP2CODE[x.dtype], x.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(param),
+                                out.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint32(len(x))))
+    return out

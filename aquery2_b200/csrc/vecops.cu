@@ -25,6 +25,9 @@
 // One kernel, templated on the compute type only; operand / result cell types are uniform run-time switches (the kernel
 // moves 8..32 bytes per row and is bound by HBM).
 #include "common.cuh"
+#include <cfloat>
+#include <cmath>
+#include <type_traits>
 
 namespace aq {
 
@@ -126,6 +129,30 @@ k_take(const T* __restrict__ col, const uint32_t rows, const uint32_t* __restric
     }
 }
 struct Cell12 { uint32_t w[3]; };
+
+// sqrt(v) -> double cells; truncate(v, precision) -> cells of v's type (server/aggregations.h:34-69).
+//   sqrt: the reference's `ret[i] = sqrt(v[i])` resolves to the float overload for float cells (the root is taken in float, then
+//         widened) and to sqrt(double) for integer cells -- probed with the reference build, pinned by tests/test_gpu_vecops.py;
+//   truncate: v[i] < max(T) / 10^p ? round(v[i] * 10^p) / 10^p : v[i], evaluated in double (the multiplier is a double), rounded
+//         half away from zero; a copy when aq_fp_precision<T> (float 7, double 16, integers 0; server/types.h:473-475) <= p.
+template <class T>
+__global__ void __launch_bounds__(256)
+k_vec_unary(const int op, const T* __restrict__ x, const double mult, const double max_trunc, void* __restrict__ out, const uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const T v = x[i];
+        if (op == AQ_U_SQRT) {
+            double r;
+            if constexpr (std::is_same<T, float>::value) r = (double)__fsqrt_rn(v);
+            else r = __dsqrt_rn((double)v);
+            static_cast<double*>(out)[i] = r;
+        } else {
+            T r = v;
+            if constexpr (std::is_floating_point<T>::value)
+                if (mult > 0.0 && (double)v < max_trunc) r = (T)__ddiv_rn(round(__dmul_rn((double)v, mult)), mult);
+            static_cast<T*>(out)[i] = r;
+        }
+    }
+}
 
 // 0 int32, 1 int64, 2 float, 3 double
 inline int vec_rank(int t) { return t == AQ_INT32 || t == AQ_BOOL ? 0 : t == AQ_INT64 ? 1 : t == AQ_FLOAT ? 2 : t == AQ_DOUBLE ? 3 : -1; }
@@ -235,5 +262,35 @@ extern "C" int aqgpu_take(int elem_bytes, const void* col, uint32_t col_rows, co
     AQ_TRY(oc.finish(size_t(elem_bytes) * nidx));
     AQ_CUDA(cudaStreamSynchronize(ctx().stream));
     if (flag) return fail("take: an index is beyond the column's %u rows", col_rows);
+    return 0;
+}
+
+extern "C" int aqgpu_vec_unary(int op, int type, const void* x, uint32_t param, void* out, uint32_t n) {
+    AQ_REQUIRE_INIT();
+    ArenaScope scope;
+    if (op != AQ_U_SQRT && op != AQ_U_TRUNCATE) return fail("vec_unary: unknown op %d", op);
+    if (!is_val_type(type)) return fail("vec_unary: dtype %d (int32, int64, float, double)", type);
+    if (n == 0) return 0;
+    if (!x || !out) return fail("vec_unary: null argument");
+    const size_t isz = dtype_size(type), osz = op == AQ_U_SQRT ? 8 : isz;
+    InCol ic; OutCol oc;
+    AQ_TRY(ic.bind(x, isz * n));
+    AQ_TRY(oc.bind(out, osz * n));
+    // truncate: a copy when the type's precision (float 7, double 16, integers 0) does not exceed the requested one
+    const uint32_t prec = type == AQ_FLOAT ? 7u : (type == AQ_DOUBLE ? 16u : 0u);
+    double mult = 0.0, max_trunc = 0.0;
+    if (op == AQ_U_TRUNCATE && prec > param) {
+        mult = std::pow(10.0, (double)param);
+        max_trunc = (type == AQ_FLOAT ? (double)FLT_MAX : DBL_MAX) / mult;
+    }
+    const int grid = grid_for(n, 256, 1, 16);
+    switch (type) {
+    case AQ_INT32: AQ_LAUNCH(k_vec_unary<int>, grid, 256, 0, op, static_cast<const int*>(ic.d), mult, max_trunc, oc.d, n); break;
+    case AQ_INT64: AQ_LAUNCH(k_vec_unary<long long>, grid, 256, 0, op, static_cast<const long long*>(ic.d), mult, max_trunc, oc.d, n); break;
+    case AQ_FLOAT: AQ_LAUNCH(k_vec_unary<float>, grid, 256, 0, op, static_cast<const float*>(ic.d), mult, max_trunc, oc.d, n); break;
+    default: AQ_LAUNCH(k_vec_unary<double>, grid, 256, 0, op, static_cast<const double*>(ic.d), mult, max_trunc, oc.d, n); break;
+    }
+    AQ_TRY(oc.finish(osz * n));
+    if (oc.host) AQ_CUDA(cudaStreamSynchronize(ctx().stream));
     return 0;
 }

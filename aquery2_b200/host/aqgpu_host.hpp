@@ -923,6 +923,18 @@ inline ColRef<long long> sums(const ColRef<bool>& c) {
     if (c.size) aq::check(aqgpu_group_scan(g.handle->h, AQ_SUMS, 0, AQ_INT32, wide.container, AQ_INT64, out.container));
     return out;
 }
+template <class T, class = std::enable_if_t<(aq::dtype_of<T>() >= 0 && aq::dtype_of<T>() != AQ_INT128 && aq::dtype_of<T>() != AQ_BOOL && aq::dtype_of<T>() != AQ_UINT32)>>
+ColRef<double> sqrt(const ColRef<T>& x) {                                                           // aggregations.h:34-47
+    ColRef<double> out = aq::alloc_like_input<double>(x.container, x.size);
+    if (x.size) aq::check(aqgpu_vec_unary(AQ_U_SQRT, aq::dtype_of<T>(), x.container, 0, out.container, x.size));
+    return out;
+}
+template <class T, class = std::enable_if_t<(aq::dtype_of<T>() >= 0 && aq::dtype_of<T>() != AQ_INT128 && aq::dtype_of<T>() != AQ_BOOL && aq::dtype_of<T>() != AQ_UINT32)>>
+ColRef<T> truncate(const ColRef<T>& x, const uint32_t precision) {                                  // aggregations.h:58-69
+    ColRef<T> out = aq::alloc_like_input<T>(x.container, x.size);
+    if (x.size) aq::check(aqgpu_vec_unary(AQ_U_TRUNCATE, aq::dtype_of<T>(), x.container, precision, out.container, x.size));
+    return out;
+}
 inline ColRef<double> pow(const ColRef<double>& x, double p) {                                      // q9: pow(corr(v1, v2), 2)
     ColRef<double> out = aq::alloc_like_input<double>(x.container, x.size);
     if (x.size) aq::check(aqgpu_vec_pow(x.container, p, out.container, x.size));

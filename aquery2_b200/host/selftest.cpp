@@ -311,6 +311,12 @@ int main() {
         auto s4 = 10 - c_v;    static_assert(std::is_same<decltype(s4), ColRef<int>>::value, "scalar - int column -> int");
         auto s5 = c_v * c_v;   static_assert(std::is_same<decltype(s5), ColRef<int>>::value, "column * column -> Coercion (vector_type.hpp:386-396)");
         auto s6 = c_f >= 50.f; static_assert(std::is_same<decltype(s6), ColRef<bool>>::value, "comparison -> bool");
+        auto sq = sqrt(c_f); auto tr = truncate(c_f, 1);
+        static_assert(std::is_same<decltype(sq), ColRef<double>>::value && std::is_same<decltype(tr), ColRef<float>>::value, "sqrt -> double, truncate -> T");
+        for (uint32_t i = 0; i < n && fails < 5; i += 13) {
+            EXPECT(sq[i] == (double)std::sqrt(v3[i]));
+            EXPECT(tr[i] == (float)(std::round((double)v3[i] * 10.0) / 10.0));
+        }
         ColRef<signed char> r8(n); aqop_lt(c_v, c_t, r8);   // root of an emitted expression: aqop_lt(lhs, rhs, ret) with the emitter's byte type
         for (uint32_t i = 0; i < n && fails < 5; ++i) {
             EXPECT(s1[i] == (float)v1[i] + v3[i]);

@@ -314,6 +314,12 @@ int aqgpu_group_window_ordered(aqgpu_groups_t* g, const void* order_col, int ord
 /* out[offsets[g] + j] = v[row j of group g]  -- the gather col[vecs[g]] of server/table.h:184-189 for
  * ALL groups at once, in the CSR order of the row lists.  out has nrows cells of vtype. */
 int aqgpu_group_gather(aqgpu_groups_t* g, int vtype, const void* v, void* out);
+/* sqrt(v) -> AQ_DOUBLE cells (float cells: the root is taken in float, then widened, as the reference's overload resolution
+ * does); truncate(v, precision) -> cells of v's type: round(v * 10^p) / 10^p in double, half away from zero, a copy for
+ * integer cells and when precision >= 7 (float) / 16 (double) (server/aggregations.h:34-69, server/types.h:473-475).
+ * param = precision for AQ_U_TRUNCATE. */
+enum aqgpu_vec_unary_op { AQ_U_SQRT = 0, AQ_U_TRUNCATE = 1 };
+int aqgpu_vec_unary(int op, int type, const void* x, uint32_t param, void* out, uint32_t n);
 /* out[j] = col[idx[j]], j < nidx: the gather ColRef<T>::operator[](vector_type<uint32_t>&) (server/table.h:184-189) and
  * TableInfo::materialize (server/table.h:429-440) for an explicit index vector.  Cells of 1, 2, 4, 8, 12 or 16 bytes;
  * an index >= col_rows fails the call (the reference reads out of bounds). */

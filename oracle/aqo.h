@@ -61,6 +61,12 @@ enum aqo_vec_op {
 int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n,
                    void* out, int* out_type);
 
+/* sqrt(v) -> double cells, truncate(v, precision) -> cells of v's type (server/aggregations.h:34-69); returns the Type_t
+ * code of the result cells.  aqo_fp_precision: aq_fp_precision<T> (server/types.h:473-475).  REFERENCE BUILD ONLY. */
+enum aqo_vec_unary_op { AQO_U_SQRT = 0, AQO_U_TRUNCATE = 1 };
+int aqo_vec_unary(int op, int t, const void* x, uint32_t param, uint32_t n, void* out);
+int aqo_fp_precision(int t);
+
 /* Which oracle is this?  "reference" (built from /root/reference) or "port" (C restatement). */
 const char* aqo_kind(void);
 

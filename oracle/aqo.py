@@ -140,6 +140,18 @@ class Oracle:
             return raw.view(np.int64).reshape(n, 2).copy(), code
         return raw.view({16: np.uint8, **_CODE2NP}[code]).copy(), code
 
+    def vec_unary(self, op: int, x, param: int = 0):
+        """sqrt (op 0) / truncate (op 1) through the reference's templates (server/aggregations.h:34-69); reference build only"""
+        if not hasattr(self.lib, "aqo_vec_unary"):
+            raise RuntimeError("aqo_vec_unary is exported by the reference build only")
+        x = np.ascontiguousarray(x)
+        out = np.zeros(len(x), np.float64 if op == 0 else x.dtype)
+        code = self.lib.aqo_vec_unary(op, _NP2CODE[x.dtype], _ptr(x), ctypes.c_uint32(param), ctypes.c_uint32(len(x)), _ptr(out))
+        if code < 0:
+            raise RuntimeError(f"aqo_vec_unary rc={code}")
+        assert _CODE2NP[code] == out.dtype.type, (code, out.dtype)
+        return out
+
     # -- A5 / A9 -----------------------------------------------------------------------------
     def reduce(self, op, v, offsets, perm, v2=None, raw128=False):
         if isinstance(op, str):

@@ -111,6 +111,7 @@ def main():
 
 
 VEC_DTYPES = {"i32": np.int32, "i64": np.int64, "f32": np.float32, "f64": np.float64}
+UNARY_PRECISIONS = (0, 2, 5, 7, 16)
 VEC_OPS = {"add": 0, "sub": 1, "mul": 2, "div": 3, "gt": 7, "lt": 8, "gte": 9, "lte": 10, "eq": 11, "neq": 12}
 
 
@@ -169,6 +170,13 @@ def gen_special():
                 cells, code = ref.vec_binary(op, x, y)
                 out[f"vec_{opn}_{na}_{nb}_{fn}"] = np.ascontiguousarray(cells).view(np.uint8).reshape(-1)
                 out[f"vect_{opn}_{na}_{nb}_{fn}"] = code
+    # sqrt / truncate (server/aggregations.h:34-69)
+    for na, ta in VEC_DTYPES.items():
+        x = np.abs(out[f"vec_a_{na}"]) if np.dtype(ta).kind == "f" else out[f"vec_a_{na}"]
+        out[f"una_x_{na}"] = x
+        out[f"una_sqrt_{na}"] = ref.vec_unary(0, np.abs(x))
+        for prec in UNARY_PRECISIONS:
+            out[f"una_trunc{prec}_{na}"] = ref.vec_unary(1, (x / 7).astype(ta) if np.dtype(ta).kind == "f" else x, prec)
     np.savez_compressed(os.path.join(GOLD, "special_small.npz"), **out)
     print("special_small.npz", os.path.getsize(os.path.join(GOLD, "special_small.npz")))
 

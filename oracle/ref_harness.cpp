@@ -304,6 +304,16 @@ int vec_binary_a(int op, const void* a, int a_scalar, int tb, const void* b, int
     }
 }
 
+/* sqrt / truncate over a vector (server/aggregations.h:34-69) */
+template <class T> int vec_unary_t(int op, const void* x, uint32_t param, uint32_t n, void* out) {
+    ensure_gc();
+    GC::scratch_space = nullptr;
+    vector_type<T> v(n, const_cast<void*>(x));
+    if (op == AQO_U_SQRT) { auto r = sqrt(v); memcpy(out, r.container, sizeof(double) * n); return AQO_DOUBLE; }
+    if (op == AQO_U_TRUNCATE) { auto r = truncate(v, param); memcpy(out, r.container, sizeof(T) * n); return (int)types::Types<T>::getType(); }
+    return -2;
+}
+
 #define DISPATCH_VTYPE(vtype, CALL)                 \
     switch (vtype) {                                \
     case AQO_INT32:  return CALL(int);              \
@@ -342,6 +352,17 @@ int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const vo
                    void* out, int* out_type) {
 #define CALL(T) vec_binary_a<T>(op, a, a_scalar, tb, b, b_scalar, n, out, out_type)
     DISPATCH_VTYPE(ta, CALL)
+#undef CALL
+}
+
+int aqo_vec_unary(int op, int t, const void* x, uint32_t param, uint32_t n, void* out) {
+#define CALL(T) vec_unary_t<T>(op, x, param, n, out)
+    DISPATCH_VTYPE(t, CALL)
+#undef CALL
+}
+int aqo_fp_precision(int t) {
+#define CALL(T) (int)aq_fp_precision<T>
+    DISPATCH_VTYPE(t, CALL)
 #undef CALL
 }
 

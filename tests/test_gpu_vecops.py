@@ -167,3 +167,30 @@ def test_cells_equal_the_golden_fixture(gpu, golden):
                     assert np.ascontiguousarray(got).view(np.uint8).reshape(-1).tobytes() == g[key].tobytes(), key
                     checked += 1
     assert checked == 16 * (10 + 5 + 4)
+
+
+@pytest.mark.gpu
+def test_sqrt_and_truncate_equal_the_reference(gpu, golden):
+    """server/aggregations.h:34-69 through aqgpu_vec_unary against the reference's cells (tests/golden/special_small.npz) and,
+    where oracle/_ref is built, against the reference's templates on larger seeded inputs; bit-exact (IEEE sqrt / mul / div)"""
+    from oracle import aqo
+    from oracle.gen_golden import VEC_DTYPES, UNARY_PRECISIONS
+    g = golden("special_small.npz")
+    for na, ta in VEC_DTYPES.items():
+        x = g[f"una_x_{na}"]
+        assert gpu.vec_unary(gpu.U_SQRT, np.abs(x)).tobytes() == g[f"una_sqrt_{na}"].tobytes(), f"sqrt {na}"
+        for prec in UNARY_PRECISIONS:
+            xin = (x / 7).astype(ta) if np.dtype(ta).kind == "f" else x
+            assert gpu.vec_unary(gpu.U_TRUNCATE, xin, prec).tobytes() == g[f"una_trunc{prec}_{na}"].tobytes(), f"truncate {na} {prec}"
+    ref = aqo.load_ref()
+    if ref is not None:
+        rng = np.random.default_rng(12)
+        for ta in VEC_DTYPES.values():
+            x = (rng.standard_normal(50_000) * 1e4).astype(ta)
+            x[:4] = [0, 1, 2, 3]
+            assert gpu.vec_unary(gpu.U_SQRT, np.abs(x)).tobytes() == ref.vec_unary(0, np.abs(x)).tobytes()
+            for prec in (0, 1, 3, 6, 7, 15, 16, 20):
+                assert gpu.vec_unary(gpu.U_TRUNCATE, x, prec).tobytes() == ref.vec_unary(1, x, prec).tobytes(), (ta, prec)
+    big = np.array([3.0e38, -3.0e38, 1.5, -2.5, 2.5], np.float32)          # beyond max / 10^p: left as they are
+    assert_same(gpu.vec_unary(gpu.U_TRUNCATE, big, 3), np.array([3.0e38, -3.0e38, 1.5, -2.5, 2.5], np.float32), "truncate near max")
+    assert_same(gpu.vec_unary(gpu.U_TRUNCATE, big, 0), np.array([3.0e38, -3.0e38, 2.0, -3.0, 3.0], np.float32), "half away from zero")

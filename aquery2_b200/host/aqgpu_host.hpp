@@ -572,6 +572,16 @@ template <class... Ts> Groups<Ts...> group_by(const ColRef<Ts>&... cols) {
 template <class _Ty> aq::GroupVec<_Ty> ColRef<_Ty>::operator[](const aq::GroupRows& r) const { return aq::GroupVec<_Ty>{this->container, r.g, r.gid, r.size}; }
 template <class _Ty> template <class G, class> aq::GroupedCol<_Ty> ColRef<_Ty>::operator[](const G& g) const { return aq::GroupedCol<_Ty>{this->container, this->size, g.handle}; }
 
+// ---- aggregates of a single value (server/aggregations.h:498-527): `SELECT max(x)` where x is a scalar expression ------------
+#define AQ_SCALAR(NAME, RET) template <class T, class = std::enable_if_t<std::is_arithmetic<T>::value>> constexpr T NAME(const T& v) { (void)v; return RET; }
+#define AQ_SCALARW(NAME, RET) template <class T, class = std::enable_if_t<std::is_arithmetic<T>::value>> constexpr T NAME(uint32_t, const T& v) { (void)v; return RET; }
+AQ_SCALAR(count, 1) AQ_SCALAR(var, 0) AQ_SCALAR(vars, 0) AQ_SCALAR(stddev, 0) AQ_SCALAR(stddevs, 0)
+AQ_SCALAR(max, v) AQ_SCALAR(min, v) AQ_SCALAR(avg, v) AQ_SCALAR(sum, v) AQ_SCALAR(maxs, v) AQ_SCALAR(mins, v) AQ_SCALAR(avgs, v) AQ_SCALAR(sums, v)
+AQ_SCALAR(last, v) AQ_SCALAR(first, v) AQ_SCALAR(prev, v) AQ_SCALAR(aggnext, v) AQ_SCALAR(deltas, 0) AQ_SCALAR(ratios, 1)
+AQ_SCALARW(varw, 0) AQ_SCALARW(stddevw, 0) AQ_SCALARW(maxw, v) AQ_SCALARW(minw, v) AQ_SCALARW(avgw, v) AQ_SCALARW(sumw, v) AQ_SCALARW(ratiow, 1)
+#undef AQ_SCALAR
+#undef AQ_SCALARW
+
 // ---- host-visible views for user modules ---------------------------------------------------------------
 // SDK modules take ColRef<T> / vector_type<T> BY VALUE and dereference `container` on the CPU (sdk/example.cpp:4,
 // sdk/aquery.h:105-128 ColRef_storage); a column of the HBM store is materialised to host memory at that call site only.

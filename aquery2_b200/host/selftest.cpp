@@ -135,6 +135,10 @@ __AQEXPORT__(int) dll_cached(Context* cxt) {
     return 0;
 }
 
+// aggregates of a single value (server/aggregations.h:498-527)
+static_assert(max(3) == 3 && min(2.5) == 2.5 && sum(7ll) == 7 && count(9) == 1 && var(4.f) == 0 && sumw(3u, 5) == 5 && ratiow(2u, 8.0) == 1 && deltas(6) == 0,
+              "scalar overloads");
+
 int main() {
     if (aqgpu_init(0) != 0) { printf("no CUDA device: %s\n", aqgpu_last_error()); return 2; }
     const uint32_t n = 100003;

@@ -118,8 +118,13 @@ static void vmm_release_all() {
     v.mapped = 0;
 }
 
-ArenaScope::ArenaScope() { ++g_arena.depth; }
+// Entry points that use scratch are serialised per process (= per device: one process per GPU): the reference runs one query at a
+// time on its engine thread, but triggers may call c(cxt) from pool threads (server/monetdb_conn.cpp:379-443).  The lock is
+// recursive because entry points nest (aqgpu_string_dict -> aqgpu_groupby_build, ...) and is held for the scope's lifetime.
+static std::recursive_mutex g_api_mu;
+ArenaScope::ArenaScope() { g_api_mu.lock(); ++g_arena.depth; }
 ArenaScope::~ArenaScope() {
+    struct Unlock { ~Unlock() { g_api_mu.unlock(); } } unlock_at_exit;      // runs on every path out of this destructor
     Arena& a = g_arena;
     if (--a.depth > 0) return;
     for (void* q : a.spilled) cudaFreeAsync(q, ctx().stream);

@@ -304,7 +304,16 @@ def run_b200(args, wl, queries):
     # ---- e2e: host-resident (pinned) columns -> HBM column store -> queries -> results back in pinned host memory
     e2e = None
     if not args.no_e2e and comm is None:
-        e2e = wl.run_e2e(aq, args, table, runner, queries, n_total)
+        try:
+            e2e = wl.run_e2e(aq, args, table, runner, queries, n_total)
+        except Exception as ex:                    # the copy-stream pipeline failed: measure the serial path and say so
+            first = f"{type(ex).__name__}: {ex}"[:300]
+            os.environ["AQ_E2E_SERIAL"] = "1"
+            try:
+                e2e = wl.run_e2e(aq, args, table, runner, queries, n_total)
+                e2e["pipeline_error"] = first
+            except Exception as ex2:
+                e2e = {"error": first, "serial_error": f"{type(ex2).__name__}: {ex2}"[:300]}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:

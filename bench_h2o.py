@@ -152,6 +152,18 @@ def run_e2e(aq, args, table, runner, queries, n_total) -> dict:
             mark(f"{q}: write-back enqueued")
         return ngs, bo
 
+    try:
+        return _run_e2e_timed(aq, L, args, table, runner, queries, n_total, serial, order, one_step, res_host)
+    finally:                                       # also on an exception: drain the copy streams, give the pinned memory back
+        try:
+            aq.writeback_wait(); aq.ingest_fence(); aq.sync()
+        except Exception:
+            pass
+        for pa in pinned:
+            pa.free()
+
+
+def _run_e2e_timed(aq, L, args, table, runner, queries, n_total, serial, order, one_step, res_host) -> dict:
     one_step()                                     # warm-up (also sizes the pinned result buffers)
     aq.writeback_wait()
     aq.ingest_fence()
@@ -184,6 +196,4 @@ def run_e2e(aq, args, table, runner, queries, n_total) -> dict:
                     "per step: every column H2D on the ingest stream, then the queries (q10 last), every result column D2H on the write-back "
                     "stream while later queries run; consecutive steps overlap on the "
                     "two copy streams (a step's ingest waits for the previous step's queries and small write-backs, its last query for the previous step's big write-back)")}
-    for pa in pinned:
-        pa.free()
     return out

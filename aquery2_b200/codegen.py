@@ -23,8 +23,11 @@ Expression nodes: {"col": name} | {"lit": number} | {"fn": name, "args": [...]} 
 """
 from __future__ import annotations
 
-CTYPE = {"int": "int", "float": "float", "double": "double", "long": "long long"}
-AQTYPE = {"int": "types::AINT32", "float": "types::AFLOAT", "double": "types::ADOUBLE", "long": "types::AINT64"}
+CTYPE = {"int": "int", "float": "float", "double": "double", "long": "long long", "str": "astring_view",
+         "date": "types::date_t", "time": "types::time_t", "timestamp": "types::timestamp_t"}
+AQTYPE = {"int": "types::AINT32", "float": "types::AFLOAT", "double": "types::ADOUBLE", "long": "types::AINT64", "str": "types::ASTR",
+          "date": "types::ADATE", "time": "types::ATIME", "timestamp": "types::ATIMESTAMP"}
+HOST_ONLY = {"str"}        # cells that are host pointers: lowered (packed + dictionary-encoded) by the group-by itself, never uploaded as is
 
 H2O_SCHEMA = [("id1", "int"), ("id2", "int"), ("id3", "int"), ("id4", "int"), ("id5", "int"), ("id6", "int"),
               ("v1", "int"), ("v2", "int"), ("v3", "float")]                   # benchmark/h2o/groupby_prep.sql:1
@@ -76,6 +79,23 @@ QUERIES = {
                         ("drawup", fn("max", {"op": "-", "l": col("price"), "r": fn("mins", col("price"))}))], assuming=("time", "asc")),
 }
 
+# Queries beyond integer keys, emitted and compiled against the drop-in headers by tests/test_codegen.py; their
+# hand-written twins run on the device in aquery2_b200/host/selftest.cpp.  tests/network.a:8-11:
+#   SELECT src, dst, count(*), avg(len) FROM network ASSUMING ASC src, ASC dst, ASC _time GROUP BY src, dst, sums(deltas(_time) > 120)
+NETWORK_SCHEMA = [("src", "str"), ("dst", "str"), ("len", "int"), ("_time", "int")]
+EXTRA_QUERIES = {
+    "network": {"name": "network", "table": "network", "schema": NETWORK_SCHEMA,
+                "group_by": ["src", "dst", {"name": "session", "expr": {"fn": "sums", "args": [{"op": ">", "l": {"fn": "deltas", "args": [{"col": "_time"}]}, "r": {"lit": 120}}]}}],
+                "select": [("src", {"col": "src"}), ("dst", {"col": "dst"}), ("cnt", {"fn": "count", "args": [{"col": "*"}]}),
+                           ("avg_len", {"fn": "avg", "args": [{"col": "len"}]})]},
+    # benchmark/quries/Aquery/load_data.a:1 `stocksymbol STRING`: max(price) - min(price) by symbol and trade date
+    "symrange": {"name": "symrange", "table": "ticks",
+                 "schema": [("stocksymbol", "str"), ("tradedate", "date"), ("price", "int")],
+                 "group_by": ["stocksymbol", "tradedate"],
+                 "select": [("stocksymbol", {"col": "stocksymbol"}), ("tradedate", {"col": "tradedate"}),
+                            ("range", {"op": "-", "l": {"fn": "max", "args": [{"col": "price"}]}, "r": {"fn": "min", "args": [{"col": "price"}]}})]},
+}
+
 SCALAR_AGGS = {"sum", "avg", "min", "max", "first", "last", "second", "stddev", "var"}
 # SQL spelling -> (scan op without window, scan op with window, result type as a C++ type expression of the value type T)
 VECTOR_AGGS = {"sums": ("AQ_SUMS", "AQ_SUMW", "types::GetLongType<{T}>"), "avgs": ("AQ_AVGS", "AQ_AVGW", "double"),
@@ -109,13 +129,32 @@ class Emitter:
     def emit(self, line: str = ""):
         self.lines.append("    " + line if line else "")
 
+    def key_names(self):
+        return [k if isinstance(k, str) else k["name"] for k in self.q["group_by"]]
+
+    # ---- expressions over WHOLE columns outside any group (a computed group key such as sums(deltas(_time) > 120)): the
+    # element-wise operators and the non-grouped vector functions of the drop-in headers (table.h:826-973, aggregations.h)
+    def plain(self, e: dict) -> str:
+        if "lit" in e:
+            return repr(e["lit"])
+        if "col" in e:
+            return self.cname(e["col"])
+        if "op" in e:
+            if e["op"] not in ("+", "-", "*", "/", ">", "<", ">=", "<=", "==", "!="):
+                raise NotImplementedError(e["op"])
+            return f"({self.plain(e['l'])} {e['op']} {self.plain(e['r'])})"
+        f, args = e["fn"], e["args"]
+        if f in VECTOR_AGGS or f in ("sqrt", "truncate"):
+            return f"{f}({', '.join(self.plain(a) for a in args)})"
+        raise NotImplementedError(f"{f} outside a group")
+
     # ---- expressions: returns a C++ expression whose value is a result column (ColRef / VecCol)
     def expr(self, e: dict) -> str:
         if "lit" in e:
             return repr(e["lit"])
         if "col" in e:
-            if e["col"] in self.q["group_by"]:
-                return f"g.key<{self.q['group_by'].index(e['col'])}>()"
+            if e["col"] in self.key_names():
+                return f"g.key<{self.key_names().index(e['col'])}>()"
             raise ValueError(f"column {e['col']} is neither aggregated nor a group key (engine/ast.py:742-746 rejects it too)")
         if "op" in e:
             if e["op"] != "-":
@@ -164,8 +203,14 @@ class Emitter:
         body = []
         for i, (name, e) in enumerate(q["select"]):
             body.append((name, self.expr(e)))
+        computed = []                        # (C++ name, expression) of group keys that are expressions over whole columns
+        key_vars = []
         for k in q["group_by"]:
-            self.cname(k)
+            if isinstance(k, str):
+                key_vars.append(self.cname(k))
+            else:
+                computed.append((f"key_{k['name']}", self.plain(k["expr"])))
+                key_vars.append(f"key_{k['name']}")
         if q.get("assuming"):
             self.cname(q["assuming"][0])
         out = ['#include "./server/libaquery.h"', '#include "./server/monetdb_conn.h"', '#include "./server/aggregations.h"',
@@ -178,9 +223,11 @@ class Emitter:
         self.emit("auto len = server->cnt;")
         for c in self.used:
             ty = self.schema[c]
-            dev = ".to_device()" if self.device else ""
+            dev = ".to_device()" if self.device and ty not in HOST_ONLY else ""
             self.emit(f"auto {self.cname(c)} = ColRef<{CTYPE[ty]}>(len, server->getCol({self.colpos[c]}, {AQTYPE[ty]})){dev};")
-        keys = ", ".join(self.cname(k) for k in q["group_by"])
+        for name, ex in computed:
+            self.emit(f"auto {name} = {ex};")
+        keys = ", ".join(key_vars)
         if q.get("row_order") == "asc":
             note = "ties of the ASSUMING order keep table order" if q.get("assuming") else "table sorted by time: row lists in time order"
             self.emit(f"auto g = aq::group_by_rows_ascending({keys});     // {note}")
@@ -217,7 +264,7 @@ class Emitter:
 
 
 def generate(name_or_query, device: bool = True, dump: bool = False) -> str:
-    q = QUERIES[name_or_query] if isinstance(name_or_query, str) else name_or_query
+    q = (QUERIES.get(name_or_query) or EXTRA_QUERIES[name_or_query]) if isinstance(name_or_query, str) else name_or_query
     return Emitter(q, device=device, dump=dump).generate()
 
 

@@ -86,6 +86,10 @@ struct timestamp_t {
     bool operator!=(const timestamp_t& o) const { return !(*this == o); }
 };
 static_assert(sizeof(date_t) == 4 && sizeof(time_t) == 8 && sizeof(timestamp_t) == 12, "cells of server/types.h");
+// printed like toString (server/libaquery.cpp:86-95, 138-149, 183-188): year-month-day, hours:minutes:seconds:ms
+inline std::ostream& operator<<(std::ostream& os, const date_t& v) { return os << (int)v.year << '-' << (int)v.month << '-' << (int)v.day; }
+inline std::ostream& operator<<(std::ostream& os, const time_t& v) { return os << (int)v.hours << ':' << (int)v.minutes << ':' << (int)v.seconds << ':' << v.ms; }
+inline std::ostream& operator<<(std::ostream& os, const timestamp_t& v) { return os << v.date << ' ' << v.time; }
 template <> struct Types<date_t> { static constexpr Type_t getType() { return ADATE; } };
 template <> struct Types<time_t> { static constexpr Type_t getType() { return ATIME; } };
 template <> struct Types<timestamp_t> { static constexpr Type_t getType() { return ATIMESTAMP; } };

@@ -24,7 +24,7 @@ def _workdir(tmp_path):
 
 def test_all_generated_units_compile(tmp_path):
     w = _workdir(tmp_path)
-    for name in codegen.QUERIES:
+    for name in list(codegen.QUERIES) + list(codegen.EXTRA_QUERIES):          # EXTRA: string / date keys, a computed key (tests/network.a)
         (w / "out.cpp").write_text(codegen.generate(name))
         r = subprocess.run(["g++", "-std=c++17", "-O0", "-w", "-fsyntax-only", f"-I{os.path.join(ROOT, 'include')}", "out.cpp"],
                            cwd=w, capture_output=True, text=True)
@@ -32,6 +32,9 @@ def test_all_generated_units_compile(tmp_path):
     text = codegen.generate("w5")
     assert "wb.add_reduced<int>(AQ_MINS, 0, price_a, true, AQ_MAX)" in text and text.count("wb.run()") == 1
     assert 'extern "C" int dll_q9(Context* cxt)' in codegen.generate("q9")
+    net = codegen.generate("network")
+    assert "auto key_session = sums((deltas(_time_d) > 120));" in net and "aq::group_by(src_b, dst_c, key_session)" in net
+    assert "ColRef<astring_view>(len, server->getCol(0, types::ASTR));" in net          # string cells are host pointers: not uploaded
 
 
 def _oracle_columns(port, q, t):

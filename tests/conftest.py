@@ -17,6 +17,17 @@ if ROOT not in sys.path:
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
+def pytest_sessionstart(session):
+    """A fresh checkout has no built artefacts (they are git-ignored): build them once, the way __graft_entry__.build() does, if the
+    CUDA library is missing and nvcc is here.  On the GPU box the built files travel with the snapshot and nothing happens."""
+    import shutil
+    lib = os.path.join(ROOT, "aquery2_b200", "libaqgpu.so")
+    if not os.path.exists(lib) and shutil.which("nvcc") and os.environ.get("AQ_TESTS_NO_BUILD") != "1":
+        sys.path.insert(0, ROOT)
+        import __graft_entry__
+        __graft_entry__.build()
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
 

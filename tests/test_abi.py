@@ -83,3 +83,19 @@ def test_host_headers_compile():
     assert os.path.exists(os.path.join(host, "selftest"))
     for h in ("vector_type.hpp", "table.h", "hasher.h", "aggregations.h", "types.h", "gc.h", "libaquery.h"):
         assert os.path.exists(os.path.join(host, "server", h)), h
+
+
+def test_header_is_plain_c(tmp_path):
+    """the boundary is a C ABI: include/aqgpu.h compiles as C99 / C11 with -pedantic, and a C program links against the library"""
+    import subprocess
+    src = os.path.join(ROOT, "tests", "native", "c_abi.c")
+    for std in ("c99", "c11"):
+        r = subprocess.run(["gcc", f"-std={std}", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", f"-I{os.path.join(ROOT, 'include')}", src],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-1500:]
+    lib = os.path.join(ROOT, "aquery2_b200")
+    exe = tmp_path / "c_abi"
+    r = subprocess.run(["gcc", "-std=c11", f"-I{os.path.join(ROOT, 'include')}", src, "-o", str(exe), f"-L{lib}", "-laqgpu", f"-Wl,-rpath,{lib}"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert subprocess.run([str(exe)]).returncode == 0           # aqgpu_abi_version() == AQGPU_ABI_VERSION

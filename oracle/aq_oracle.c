@@ -384,3 +384,105 @@ int64_t aqo_time_groupby_reduce(const void* const* keys, const int* key_types, i
     if (rc) return rc;
     return (int64_t)(t1.tv_sec - t0.tv_sec) * 1000000000LL + (t1.tv_nsec - t0.tv_nsec);
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Element-wise vector arithmetic / compare and sqrt / truncate.
+ * server/vector_type.hpp:372-396 (member operators: vector op vector -> Coercion<T1,T2>; vector > scalar),
+ * server/table.h:826-925 (vector op scalar, scalar op vector: + - -> Coercion, * -> GetLongType, / -> GetFPType),
+ * server/table.h:949-973 (aqop_x(lhs, rhs, ret): bool cells here), server/aggregations.h:34-69 (sqrt, truncate).
+ * Every cell is the C expression `lhs[i] op rhs[i]` in the usual arithmetic conversion type of the two cell types, then
+ * converted to the result cell type.  Pinned against the reference build by tests/test_oracle_vs_ref.py.
+ * ---------------------------------------------------------------------------------------------- */
+static int vrank(int t) { return t == AQO_INT32 ? 0 : t == AQO_INT64 ? 1 : t == AQO_FLOAT ? 2 : t == AQO_DOUBLE ? 3 : -1; }
+static int vcoercion(int ra, int rb) {                   /* types::Coercion (server/types.h:264-275) as a Type_t code */
+    const int fp = ra >= 2 || rb >= 2, wide = ra == 1 || ra == 3 || rb == 1 || rb == 3;
+    return fp ? (wide ? AQO_DOUBLE : AQO_FLOAT) : (wide ? AQO_INT64 : AQO_INT32);
+}
+static int vec_out_type(int op, int ta, int a_scalar, int tb, int b_scalar) {
+    const int ra = vrank(ta), rb = vrank(tb);
+    if (ra < 0 || rb < 0) return -1;
+    if (op >= AQO_V_GT) return AQO_BOOL;
+    const int k = vcoercion(ra, rb);
+    if (!a_scalar && !b_scalar) return k;
+    if (op == AQO_V_MUL) return (k == AQO_INT32 || k == AQO_INT64) ? AQO_INT128 : AQO_DOUBLE;
+    if (op == AQO_V_DIV) return k == AQO_INT32 ? AQO_FLOAT : (k == AQO_INT64 ? AQO_DOUBLE : k);
+    return k;
+}
+#define VLOAD(C, p, t, i) ((t) == AQO_INT32 ? (C)((const int32_t*)(p))[i] : (t) == AQO_INT64 ? (C)((const int64_t*)(p))[i] : \
+                           (t) == AQO_FLOAT ? (C)((const float*)(p))[i] : (C)((const double*)(p))[i])
+#define VSTORE(out, t, i, r)                                                                              \
+    do {                                                                                                  \
+        switch (t) {                                                                                      \
+        case AQO_INT32: ((int32_t*)(out))[i] = (int32_t)(r); break;                                       \
+        case AQO_INT64: ((int64_t*)(out))[i] = (int64_t)(r); break;                                       \
+        case AQO_FLOAT: ((float*)(out))[i] = (float)(r); break;                                           \
+        case AQO_DOUBLE: ((double*)(out))[i] = (double)(r); break;                                        \
+        case AQO_INT128: ((i128*)(out))[i] = (i128)(r); break;                                            \
+        default: ((unsigned char*)(out))[i] = (r) != 0; break;                                            \
+        }                                                                                                 \
+    } while (0)
+#define VLOOP(C, WRAP)                                                                                    \
+    for (uint32_t i = 0; i < n; ++i) {                                                                    \
+        const C x = VLOAD(C, a, ta, a_scalar ? 0 : i), y = VLOAD(C, b, tb, b_scalar ? 0 : i);             \
+        switch (op) {                                                                                     \
+        case AQO_V_ADD: { const C r = WRAP(x, +, y); VSTORE(out, ot, i, r); break; }                      \
+        case AQO_V_SUB: { const C r = WRAP(x, -, y); VSTORE(out, ot, i, r); break; }                      \
+        case AQO_V_MUL: { const C r = WRAP(x, *, y); VSTORE(out, ot, i, r); break; }                      \
+        case AQO_V_DIV: { const C r = x / y; VSTORE(out, ot, i, r); break; }                              \
+        case AQO_V_GT: ((unsigned char*)out)[i] = x > y; break;                                           \
+        case AQO_V_LT: ((unsigned char*)out)[i] = x < y; break;                                           \
+        case AQO_V_GTE: ((unsigned char*)out)[i] = x >= y; break;                                         \
+        case AQO_V_LTE: ((unsigned char*)out)[i] = x <= y; break;                                         \
+        case AQO_V_EQ: ((unsigned char*)out)[i] = x == y; break;                                          \
+        case AQO_V_NEQ: ((unsigned char*)out)[i] = x != y; break;                                         \
+        default: return -2;                                                                               \
+        }                                                                                                 \
+    }
+#define WRAP32(x, o, y) ((int32_t)((uint32_t)(x) o (uint32_t)(y)))       /* two's complement wrap, as the compiled reference does */
+#define WRAP64(x, o, y) ((int64_t)((uint64_t)(x) o (uint64_t)(y)))
+#define PLAIN(x, o, y) ((x) o (y))
+
+int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n,
+                   void* out, int* out_type) {
+    const int ra = vrank(ta), rb = vrank(tb);
+    if (ra < 0 || rb < 0 || (a_scalar && b_scalar)) return -2;
+    if (op > AQO_V_DIV && op < AQO_V_GT) return -2;                      /* and / or / xor: not driven through the oracle */
+    if (op == AQO_V_GT ? a_scalar : (op > AQO_V_GT && (a_scalar || b_scalar))) return -2;   /* forms the reference cannot evaluate */
+    const int ot = vec_out_type(op, ta, a_scalar, tb, b_scalar);
+    if (out_type) *out_type = ot;
+    const int osz = ot == AQO_BOOL ? 1 : ot == AQO_INT128 ? 16 : (ot == AQO_INT32 || ot == AQO_FLOAT) ? 4 : 8;
+    if (!out) return osz;
+    const int rc = (ra == 3 || rb == 3) ? 3 : (ra == 2 || rb == 2) ? 2 : (ra == 1 || rb == 1) ? 1 : 0;
+    switch (rc) {
+    case 0: VLOOP(int32_t, WRAP32) break;
+    case 1: VLOOP(int64_t, WRAP64) break;
+    case 2: VLOOP(float, PLAIN) break;
+    default: VLOOP(double, PLAIN) break;
+    }
+    return osz;
+}
+
+/* sqrt: float cells take the root in float (the overload the reference's call resolves to), integers in double; cells of double.
+ * truncate: v < max(T) / 10^p ? round(v * 10^p) / 10^p : v in double; a copy when aq_fp_precision<T> <= p (float 7, double 16,
+ * integers 0: server/types.h:473-475). */
+int aqo_fp_precision(int t) { return t == AQO_FLOAT ? 7 : t == AQO_DOUBLE ? 16 : vrank(t) >= 0 ? 0 : -2; }
+int aqo_vec_unary(int op, int t, const void* x, uint32_t param, uint32_t n, void* out) {
+    if (vrank(t) < 0) return -2;
+    if (op == AQO_U_SQRT) {
+        for (uint32_t i = 0; i < n; ++i)
+            ((double*)out)[i] = t == AQO_FLOAT ? (double)sqrtf(((const float*)x)[i]) : sqrt(VLOAD(double, x, t, i));
+        return AQO_DOUBLE;
+    }
+    if (op != AQO_U_TRUNCATE) return -2;
+    const int esz = (t == AQO_INT32 || t == AQO_FLOAT) ? 4 : 8;
+    if ((uint32_t)aqo_fp_precision(t) <= param) { memcpy(out, x, (size_t)esz * n); return t; }
+    const double mult = pow(10, param);
+    if (t == AQO_FLOAT) {
+        const double mx = FLT_MAX / mult;
+        for (uint32_t i = 0; i < n; ++i) { const float v = ((const float*)x)[i]; ((float*)out)[i] = v < mx ? (float)(round(v * mult) / mult) : v; }
+    } else {
+        const double mx = DBL_MAX / mult;
+        for (uint32_t i = 0; i < n; ++i) { const double v = ((const double*)x)[i]; ((double*)out)[i] = v < mx ? round(v * mult) / mult : v; }
+    }
+    return t;
+}

@@ -56,13 +56,13 @@ enum aqo_vec_op {
 /* out[i] = a[i] op b[i] with the reference's operators: infix + - * / > for vector-vector, vector-scalar and
  * scalar-vector operands (a scalar operand is a pointer to one cell), aqop_lt/gte/lte/eq/neq for two vectors with a
  * bool result.  *out_type = Type_t code of the result cells as the reference's templates deduce it; returns the
- * cell size in bytes, or < 0.  out may be NULL (type query).  REFERENCE BUILD ONLY (oracle/_ref): the plain-C port does
- * not export it -- the expected cells are otherwise restated with numpy in tests/test_gpu_vecops.py. */
+ * cell size in bytes, or < 0.  out may be NULL (type query).  Both oracles export it; forms the reference cannot evaluate
+ * (scalar > vector, other comparisons with a scalar: its member operators all compute `>`) return < 0. */
 int aqo_vec_binary(int op, int ta, const void* a, int a_scalar, int tb, const void* b, int b_scalar, uint32_t n,
                    void* out, int* out_type);
 
 /* sqrt(v) -> double cells, truncate(v, precision) -> cells of v's type (server/aggregations.h:34-69); returns the Type_t
- * code of the result cells.  aqo_fp_precision: aq_fp_precision<T> (server/types.h:473-475).  REFERENCE BUILD ONLY. */
+ * code of the result cells.  aqo_fp_precision: aq_fp_precision<T> (server/types.h:473-475). */
 enum aqo_vec_unary_op { AQO_U_SQRT = 0, AQO_U_TRUNCATE = 1 };
 int aqo_vec_unary(int op, int t, const void* x, uint32_t param, uint32_t n, void* out);
 int aqo_fp_precision(int t);

@@ -118,12 +118,10 @@ class Oracle:
             raise RuntimeError(f"aqo_groupby rc={rc}")
         return ng.value, gid, offsets[: ng.value + 1].copy(), perm
 
-    # -- A10 (reference build only) -------------------------------------------------------------
+    # -- A10 -------------------------------------------------------------------------------------
     def vec_binary(self, op: int, a, b):
         """a op b through the reference's own operators (server/vector_type.hpp:372-396, server/table.h:826-973);
         returns (cells, Type_t code of the result cells).  0-d operands are scalars."""
-        if not hasattr(self.lib, "aqo_vec_binary"):
-            raise RuntimeError("aqo_vec_binary is exported by the reference build only")
         a, b = np.asarray(a), np.asarray(b)
         sa, sb = int(a.ndim == 0), int(b.ndim == 0)
         a, b = np.ascontiguousarray(a.reshape(1) if sa else a), np.ascontiguousarray(b.reshape(1) if sb else b)
@@ -141,9 +139,7 @@ class Oracle:
         return raw.view({16: np.uint8, **_CODE2NP}[code]).copy(), code
 
     def vec_unary(self, op: int, x, param: int = 0):
-        """sqrt (op 0) / truncate (op 1) through the reference's templates (server/aggregations.h:34-69); reference build only"""
-        if not hasattr(self.lib, "aqo_vec_unary"):
-            raise RuntimeError("aqo_vec_unary is exported by the reference build only")
+        """sqrt (op 0) / truncate (op 1): server/aggregations.h:34-69"""
         x = np.ascontiguousarray(x)
         out = np.zeros(len(x), np.float64 if op == 0 else x.dtype)
         code = self.lib.aqo_vec_unary(op, _NP2CODE[x.dtype], _ptr(x), ctypes.c_uint32(param), ctypes.c_uint32(len(x)), _ptr(out))

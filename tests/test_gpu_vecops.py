@@ -25,8 +25,10 @@ def operands(rng, dt, n):
 
 
 @pytest.fixture(scope="module")
-def refop(ref):
-    return ref
+def refop(port):
+    """the reference's operators where oracle/_ref is built, else the C restatement that tests/test_oracle_vs_ref.py pins to them"""
+    from oracle import aqo
+    return aqo.load_ref() or port
 
 
 def test_result_types_follow_the_reference_templates(refop):

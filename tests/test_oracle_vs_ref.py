@@ -119,3 +119,29 @@ def test_groupby_special_keys_port_vs_reference(port, ref, seed):
     # a single row, and all rows equal
     one = keydata.strings(rng, 1, 5)
     assert port.groupby([one])[0] == ref.groupby([one])[0] == 1
+
+
+def test_vector_ops_port_vs_reference(port, ref):
+    """element-wise operators, sqrt, truncate: the C restatement against the reference's own templates, result
+    types included, for 16 type pairs x every operand form the reference can evaluate"""
+    import itertools
+    from oracle.gen_golden import VEC_DTYPES, VEC_OPS, vec_operand
+    rng = np.random.default_rng(31)
+    n, forms_checked = 3001, 0
+    for (na, ta), (nb, tb) in itertools.product(VEC_DTYPES.items(), VEC_DTYPES.items()):
+        a, b = vec_operand(rng, ta, n), vec_operand(rng, tb, n)
+        b[::3] = a[::3].astype(tb)
+        for opn, op in VEC_OPS.items():
+            forms = [(a, b)] + ([(a, b[1])] if op <= 3 or op == 7 else []) + ([(a[1], b)] if op <= 3 else [])
+            for x, y in forms:
+                (r, rc), (p, pc) = ref.vec_binary(op, x, y), port.vec_binary(op, x, y)
+                assert rc == pc and r.tobytes() == p.tobytes(), (opn, na, nb, np.ndim(x), np.ndim(y))
+                forms_checked += 1
+    assert forms_checked == 16 * 19
+    for ta in VEC_DTYPES.values():
+        x = vec_operand(rng, ta, n)
+        assert ref.vec_unary(0, np.abs(x)).tobytes() == port.vec_unary(0, np.abs(x)).tobytes()
+        for prec in (0, 1, 3, 6, 7, 15, 16, 20):
+            assert ref.vec_unary(1, x, prec).tobytes() == port.vec_unary(1, x, prec).tobytes(), (ta, prec)
+    with pytest.raises(RuntimeError):
+        port.vec_binary(8, np.zeros(3, np.int32), np.int32(1))          # `vector < scalar`: not a form the reference evaluates as written

@@ -100,6 +100,8 @@ struct DevBuf {
 struct ArenaScope {                      // opened by the entry points of the C ABI that allocate scratch
     ArenaScope();
     ~ArenaScope();
+    ArenaScope(const ArenaScope&) = delete;              // holds the API lock: one lock, one unlock
+    ArenaScope& operator=(const ArenaScope&) = delete;
 };
 
 bool is_device_ptr(const void* p);
